@@ -1,0 +1,208 @@
+/*
+ * srt.h — C ABI of the B200-native render core for leonlang/simple_raytracer scenes.
+ *
+ * This is the drop-in boundary for ONE path of the reference: the per-pixel render loop
+ *
+ *     ImageData sendRaysAndIntersectPointsColors(const glm::vec2& imageSize,
+ *                                                const glm::vec4& lightPos,
+ *                                                ObjectManager* objManager);
+ *                                      (reference simple_raytracer.cpp:505-525, caller :784)
+ *
+ * and everything it calls (rayIntersection :405-457, boundingBoxIntersection :296-317,
+ * intersectRayAabbNoOrigin :252-293, intersectRayAabb :204-248, rayTriangleIntersection :42-75,
+ * softShadow :348-401, shadowIntersection :321-342, phongIllumination :144-200,
+ * calculateBarycentricCoords :79-117, getTextureCoordinate :121-128) plus the image contract of
+ * drawImage :461-498 (8-bit conversion and sky fill).
+ *
+ * The host keeps the reference's scene objects (ObjectManager / Triangle / Node, Object.h:15-89).
+ * `srt_flatten.hpp` turns them into the plain arrays below; the functions here upload those
+ * arrays to one B200 and run the persistent sm_100a render kernel.  Plain C, POD only, no C++
+ * or torch types cross this boundary.  Every function returns 0 on success or a negative
+ * srt_status; srt_last_error() gives the message (thread-local).
+ *
+ * There is NO CPU fallback: without a CUDA device every compute entry point fails with
+ * SRT_ERR_NO_DEVICE.
+ */
+#ifndef SRT_H_
+#define SRT_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define SRT_ABI_VERSION 1
+#define SRT_MAX_LIGHTS 64          /* softShadow(lightAmount, …) :348; the reference ships 1, used 8/16/32 */
+#define SRT_LEAF_BIT 0x80000000u
+#define SRT_NO_INDEX 0xFFFFFFFFu
+
+typedef enum srt_status {
+    SRT_OK = 0,
+    SRT_ERR_INVALID_ARG = -1,
+    SRT_ERR_NO_DEVICE = -2,
+    SRT_ERR_CUDA = -3,
+    SRT_ERR_OOM = -4,
+    SRT_ERR_SCENE = -5,            /* scene violates a precondition the reference would crash on */
+    SRT_ERR_UNSUPPORTED = -6
+} srt_status;
+
+/* ---------------------------------------------------------------------------------------------
+ * Flattened scene (what replaces the pointer-linked Node tree, Object.h:46-57).
+ *
+ * Nodes of one object are stored in depth-first pre-order: the LEFT child of interior node i is
+ * node i+1, `a` holds the index of the RIGHT child.  A leaf has SRT_LEAF_BIT set in `b`; then
+ * `a` = first triangle (index into geom/attr), `b & ~SRT_LEAF_BIT` = triangle count (may be 0).
+ * Boxes are Node::minBox / Node::maxBox verbatim (computed from the un-divided xyz of the vec4
+ * points, Object.cpp:205-221).
+ * ------------------------------------------------------------------------------------------- */
+typedef struct srt_node {
+    float    bmin[3];
+    uint32_t a;
+    float    bmax[3];
+    uint32_t b;
+} srt_node;                                   /* 32 B: two 16-byte loads */
+
+/* Triangle geometry in candidate (leaf DFS) order — the order boundingBoxIntersection :296-317
+ * concatenates leaves in, so `index in this array` == the reference's visit index within the
+ * object.  p0 = vec3(pointOne)/pointOne.w, e1 = P2/w2 - P1/w1, e2 = P3/w3 - P1/w1: the first six
+ * operations of rayTriangleIntersection :45-51 and calculateBarycentricCoords :81-90, done once
+ * on the host with the same fp32 operations. */
+typedef struct srt_tri_geom {
+    float    p0[3];
+    int32_t  obj;                             /* owning object (index into objects[]) */
+    float    e1[3];
+    int32_t  tex;                             /* texture index or -1 (Triangle::textureName empty) */
+    float    e2[3];
+    uint32_t reserved;
+} srt_tri_geom;                               /* 48 B: three 16-byte loads */
+
+/* Shading attributes, same order as geom.  n = calculateTriangleNormal :32-37 (flat normal from
+ * the UN-divided xyz), uv = colorOne/Two/ThreeCoordinate (pixel-space, Object.cpp:113-119). */
+typedef struct srt_tri_attr {
+    float n[3];
+    float pad0;
+    float uv[3][2];
+    float pad1[2];
+} srt_tri_attr;                               /* 48 B */
+
+/* One entry per key of ObjectManager::objTriangles, in that unordered_map's ITERATION order
+ * (simple_raytracer.cpp:409, :322) — the order decides exact-tie resolution. */
+typedef struct srt_object {
+    float    color[3];                        /* objColors[name]                    Object.h:68 */
+    float    ambient, specular, shininess;    /* objProperties[name]                Object.h:64 */
+    uint32_t root;                            /* root node index                                 */
+    uint32_t tri_first, tri_count;            /* range in geom/attr (leaf order)                 */
+    uint32_t flat_first;                      /* range start in flat_geom (load order) or SRT_NO_INDEX */
+    float    box_min[3];                      /* minBox[name] / maxBox[name]        Object.h:61-62 */
+    float    box_max[3];
+} srt_object;                                 /* 64 B */
+
+/* RGB8 texture exactly as stbi_load(..., 3) returned it (Object.cpp:57-61). */
+typedef struct srt_texture_desc {
+    const uint8_t* rgb;
+    int32_t width, height;
+} srt_texture_desc;
+
+typedef struct srt_scene_desc {
+    const srt_node*     nodes;     uint64_t n_nodes;
+    const srt_tri_geom* geom;      /* leaf order */
+    const srt_tri_attr* attr;      uint64_t n_tris;
+    /* Optional (may be NULL / 0): triangles in objTriangles[name] LOAD order, for the legacy
+     * one-box-per-object path (simple_raytracer.cpp:415-420). */
+    const srt_tri_geom* flat_geom;
+    const srt_tri_attr* flat_attr; uint64_t n_flat;
+    const srt_object*   objects;   uint32_t n_objects;
+    const srt_texture_desc* textures; uint32_t n_textures;
+} srt_scene_desc;
+
+/* Every literal of the reference's hot path, as a parameter (defaults = the literals). */
+typedef struct srt_render_params {
+    int32_t width, height;        /* imageSize (600,400)                         :773 */
+    float   focal;                /* ray.direction.z = 400.0f                    :506 */
+    float   light_pos[3];         /* view-space light, lightPos.xyz              :778 */
+    int32_t light_count;          /* softShadow(1, …)                            :445 */
+    float   light_step;           /* += 3.0f staircase                           :372-382 */
+    float   light_color[3];       /* (1,1,1)                                     :433 */
+    float   shadow_div;           /* colorPhong /= 5                             :369 */
+    float   tone_k;               /* color / (color + 0.5f)                      :391 */
+    float   gamma;                /* pow(color, 1.1f)                            :396 */
+    uint8_t sky[3];               /* (173,216,230)                               :476 */
+    uint8_t pad0;
+    int32_t use_bvh;              /* 1: BVH path :422; 0: legacy one-box path :417 (needs flat_geom) */
+    int32_t row_begin, row_end;   /* render rows [row_begin,row_end); 0,0 = all rows (tile-row shard) */
+    int32_t variant;              /* SRT_VARIANT_* kernel selection, 0 = default */
+    int32_t no_sky_fill;          /* 1: leave miss / black-hit pixels (0,0,0) (rebuilding ImageData :518) */
+    int32_t reserved[3];
+} srt_render_params;
+
+enum { SRT_VARIANT_DEFAULT = 0, SRT_VARIANT_SIMPLE = 1, SRT_VARIANT_PACKET = 2 };
+
+/* Output planes; each pointer may be NULL (plane not wanted), a DEVICE pointer (written in place
+ * on the context stream, no copy) or a HOST pointer (rendered to an internal device buffer and
+ * copied back on the context stream).  Full-frame addressing: row r starts at r*width.
+ * rgb is interleaved RGB8, row-major, top row first, sky already filled (drawImage :476-487). */
+typedef struct srt_frame {
+    uint8_t* rgb;                 /* [height][width][3] */
+    int32_t* obj_id;              /* [height][width], -1 = miss                   */
+    int32_t* tri_id;              /* [height][width], global leaf-order (or flat) index, -1 = miss */
+    float*   t;                   /* [height][width], hit parameter, +inf = miss  */
+} srt_frame;
+
+typedef struct srt_stats {
+    uint64_t primary_rays;        /* rows*width */
+    uint64_t hit_pixels;
+    uint64_t shadow_rays;         /* light_count*hit_pixels if the scene has >= 2 objects else 0 */
+    uint64_t node_visits;         /* only counted by the instrumented variant, else 0 */
+    uint64_t tri_tests;
+    float    kernel_ms;           /* CUDA-event time of the render kernel */
+    float    pad;
+} srt_stats;
+
+typedef struct srt_context srt_context;
+typedef struct srt_scene   srt_scene;
+
+/* ---- lifetime ---- */
+int  srt_abi_version(void);
+int  srt_device_count(int* count);
+int  srt_context_create(int device, srt_context** out);
+void srt_context_destroy(srt_context* ctx);
+/* Use an existing cudaStream_t (e.g. torch's current stream) instead of the context's own. */
+int  srt_context_set_stream(srt_context* ctx, void* cuda_stream);
+int  srt_context_get_info(srt_context* ctx, int* sm_count, int* cc_major, int* cc_minor,
+                          size_t* l2_bytes);
+
+/* ---- scene ---- */
+/* Validates (returns SRT_ERR_SCENE where the reference would crash: textured triangle without
+ * texture, node/triangle index out of range, object without BVH …), allocates device memory and
+ * copies.  Synchronous with respect to the host arrays (they may be freed on return). */
+int  srt_scene_upload(srt_context* ctx, const srt_scene_desc* desc, srt_scene** out);
+/* Re-upload new contents into an existing scene object (per-frame scenes of an image series);
+ * device buffers are reused when large enough.  The copy is asynchronous on the context stream
+ * when the host arrays are pinned (srt_host_alloc). */
+int  srt_scene_update(srt_context* ctx, srt_scene* scene, const srt_scene_desc* desc);
+void srt_scene_destroy(srt_scene* scene);
+
+/* ---- render: the replacement for sendRaysAndIntersectPointsColors :505 ---- */
+/* Asynchronous on the context stream; call srt_sync before reading host outputs. */
+int  srt_render(srt_context* ctx, const srt_scene* scene, const srt_render_params* params,
+                const srt_frame* out);
+int  srt_sync(srt_context* ctx);
+/* Statistics of the most recent srt_render on this context (synchronises the context). */
+int  srt_last_stats(srt_context* ctx, srt_stats* out);
+
+/* ---- helpers ---- */
+void srt_default_params(srt_render_params* p);             /* fills the reference's literals */
+/* Light staircase of softShadow :363-383: out[3*i..] for i < count, sequential fp32 adds. */
+int  srt_light_positions(const srt_render_params* p, float* out_xyz);
+void* srt_host_alloc(size_t bytes);                        /* pinned host memory */
+void  srt_host_free(void* p);
+void* srt_device_alloc(srt_context* ctx, size_t bytes);
+void  srt_device_free(srt_context* ctx, void* p);
+const char* srt_last_error(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* SRT_H_ */
