@@ -1,0 +1,201 @@
+"""ctypes binding of the C ABI (include/srt.h) — the same entry points a C++ host would link.
+
+Plumbing only.  The render path is the CUDA library `lib/libsrt_b200.so`; if it is missing or there
+is no CUDA device, everything here raises — there is no CPU fallback of any kind.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from pathlib import Path
+from typing import Optional
+
+import numpy as np
+
+from . import _abi
+
+LIB_PATH = Path(__file__).resolve().parent / "lib" / "libsrt_b200.so"
+
+EXPORTS = [
+    "srt_abi_version", "srt_device_count", "srt_context_create", "srt_context_destroy",
+    "srt_context_set_stream", "srt_context_get_info", "srt_scene_upload", "srt_scene_update",
+    "srt_scene_destroy", "srt_render", "srt_sync", "srt_last_stats", "srt_default_params",
+    "srt_light_positions", "srt_host_alloc", "srt_host_free", "srt_device_alloc", "srt_device_free",
+    "srt_last_error",
+]
+
+
+class SrtError(RuntimeError):
+    def __init__(self, code: int, message: str):
+        super().__init__(f"srt error {code}: {message}")
+        self.code = code
+
+
+_lib = None
+
+
+def lib():
+    """Load libsrt_b200.so (built by `make` / __graft_entry__.build()).  Raises if absent."""
+    global _lib
+    if _lib is None:
+        if not LIB_PATH.exists():
+            raise FileNotFoundError(
+                f"{LIB_PATH} not built — run `make` (or __graft_entry__.build()); there is no fallback path")
+        L = C.CDLL(str(LIB_PATH))
+        vp = C.c_void_p
+        L.srt_abi_version.restype = C.c_int
+        L.srt_device_count.argtypes = [C.POINTER(C.c_int)]
+        L.srt_context_create.argtypes = [C.c_int, C.POINTER(vp)]
+        L.srt_context_destroy.argtypes = [vp]
+        L.srt_context_destroy.restype = None
+        L.srt_context_set_stream.argtypes = [vp, vp]
+        L.srt_context_get_info.argtypes = [vp, C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_int),
+                                           C.POINTER(C.c_size_t)]
+        L.srt_scene_upload.argtypes = [vp, C.POINTER(_abi.SceneDesc), C.POINTER(vp)]
+        L.srt_scene_update.argtypes = [vp, vp, C.POINTER(_abi.SceneDesc)]
+        L.srt_scene_destroy.argtypes = [vp]
+        L.srt_scene_destroy.restype = None
+        L.srt_render.argtypes = [vp, vp, C.POINTER(_abi.RenderParams), C.POINTER(_abi.Frame)]
+        L.srt_sync.argtypes = [vp]
+        L.srt_last_stats.argtypes = [vp, C.POINTER(_abi.Stats)]
+        L.srt_default_params.argtypes = [C.POINTER(_abi.RenderParams)]
+        L.srt_default_params.restype = None
+        L.srt_light_positions.argtypes = [C.POINTER(_abi.RenderParams), C.POINTER(C.c_float)]
+        L.srt_host_alloc.argtypes = [C.c_size_t]
+        L.srt_host_alloc.restype = vp
+        L.srt_host_free.argtypes = [vp]
+        L.srt_host_free.restype = None
+        L.srt_device_alloc.argtypes = [vp, C.c_size_t]
+        L.srt_device_alloc.restype = vp
+        L.srt_device_free.argtypes = [vp, vp]
+        L.srt_device_free.restype = None
+        L.srt_last_error.restype = C.c_char_p
+        _lib = L
+    return _lib
+
+
+def _check(rc: int):
+    if rc != 0:
+        raise SrtError(rc, lib().srt_last_error().decode(errors="replace"))
+
+
+def device_count() -> int:
+    n = C.c_int(0)
+    rc = lib().srt_device_count(C.byref(n))
+    return n.value if rc == 0 else 0
+
+
+class PinnedArray:
+    """numpy view over pinned host memory from srt_host_alloc (for asynchronous H2D/D2H copies)."""
+
+    def __init__(self, shape, dtype):
+        self.dtype = np.dtype(dtype)
+        self.shape = tuple(int(s) for s in (shape if isinstance(shape, (tuple, list)) else (shape,)))
+        n = int(np.prod(self.shape)) * self.dtype.itemsize
+        self.ptr = lib().srt_host_alloc(max(n, 1))
+        if not self.ptr:
+            raise SrtError(_abi.SRT_ERR_OOM, "srt_host_alloc failed")
+        buf = (C.c_char * max(n, 1)).from_address(self.ptr)
+        self.array = np.frombuffer(buf, dtype=self.dtype, count=int(np.prod(self.shape))).reshape(self.shape)
+
+    def free(self):
+        if self.ptr:
+            self.array = None
+            lib().srt_host_free(self.ptr)
+            self.ptr = None
+
+    def __del__(self):
+        try:
+            self.free()
+        except Exception:
+            pass
+
+
+class Scene:
+    def __init__(self, ctx: "Context", handle):
+        self.ctx = ctx
+        self.h = handle
+
+    def update(self, arrays_or_desc):
+        """Re-upload new contents (next frame of a series) into the same device buffers, async."""
+        d = arrays_or_desc.desc() if hasattr(arrays_or_desc, "desc") else arrays_or_desc
+        self._keep = (arrays_or_desc, d)
+        _check(lib().srt_scene_update(self.ctx.h, self.h, C.byref(d)))
+
+    def destroy(self):
+        if self.h:
+            lib().srt_scene_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.destroy()
+        except Exception:
+            pass
+
+
+class Context:
+    """One per GPU (srt_context).  Renders are asynchronous on the context stream."""
+
+    def __init__(self, device: int = 0, stream: Optional[int] = None):
+        h = C.c_void_p()
+        _check(lib().srt_context_create(int(device), C.byref(h)))
+        self.h = h
+        self.device = int(device)
+        if stream is not None:
+            _check(lib().srt_context_set_stream(self.h, C.c_void_p(stream)))
+
+    def info(self):
+        sm, ma, mi, l2 = C.c_int(), C.c_int(), C.c_int(), C.c_size_t()
+        _check(lib().srt_context_get_info(self.h, C.byref(sm), C.byref(ma), C.byref(mi), C.byref(l2)))
+        return dict(sm_count=sm.value, cc=(ma.value, mi.value), l2_bytes=l2.value)
+
+    def upload(self, arrays: _abi.FlatSceneArrays) -> Scene:
+        d = arrays.desc()
+        h = C.c_void_p()
+        _check(lib().srt_scene_upload(self.h, C.byref(d), C.byref(h)))
+        return Scene(self, h)
+
+    def render_raw(self, scene: Scene, params: _abi.RenderParams, rgb=None, obj_id=None, tri_id=None, t=None):
+        """Pointers (ints) may be host or device addresses; asynchronous."""
+        fr = _abi.Frame()
+        fr.rgb, fr.obj_id, fr.tri_id, fr.t = rgb, obj_id, tri_id, t
+        _check(lib().srt_render(self.h, scene.h, C.byref(params), C.byref(fr)))
+
+    def render(self, scene: Scene, params: _abi.RenderParams, ids: bool = True, want_t: bool = True):
+        """Render into fresh host arrays (synchronous convenience wrapper)."""
+        H, W = params.height, params.width
+        rgb = np.zeros((H, W, 3), np.uint8)
+        obj = np.full((H, W), -1, np.int32) if ids else None
+        tri = np.full((H, W), -1, np.int32) if ids else None
+        tt = np.full((H, W), np.inf, np.float32) if want_t else None
+        self.render_raw(scene, params, rgb.ctypes.data, obj.ctypes.data if ids else None,
+                        tri.ctypes.data if ids else None, tt.ctypes.data if want_t else None)
+        self.sync()
+        return dict(rgb=rgb, obj_id=obj, tri_id=tri, t=tt, stats=self.last_stats())
+
+    def sync(self):
+        _check(lib().srt_sync(self.h))
+
+    def last_stats(self) -> dict:
+        s = _abi.Stats()
+        _check(lib().srt_last_stats(self.h, C.byref(s)))
+        return dict(primary_rays=int(s.primary_rays), hit_pixels=int(s.hit_pixels), shadow_rays=int(s.shadow_rays),
+                    node_visits=int(s.node_visits), tri_tests=int(s.tri_tests), kernel_ms=float(s.kernel_ms))
+
+    def destroy(self):
+        if self.h:
+            lib().srt_context_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.destroy()
+        except Exception:
+            pass
+
+
+def light_positions(params: _abi.RenderParams) -> np.ndarray:
+    out = np.zeros((max(params.light_count, 0), 3), np.float32)
+    if params.light_count > 0:
+        _check(lib().srt_light_positions(C.byref(params), out.ctypes.data_as(C.POINTER(C.c_float))))
+    return out

@@ -1,0 +1,476 @@
+// srt_capi.cu — implementation of the C ABI in include/srt.h (contexts, scene upload, render).
+// Host-side plumbing only: device memory, streams, events, argument validation.  There is no CPU
+// render path in this library — every compute entry point needs a CUDA device and fails loudly
+// (SRT_ERR_NO_DEVICE / SRT_ERR_CUDA) without one.
+#include <cuda_runtime.h>
+
+#include <cmath>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "srt.h"
+#include "srt_kernels.cuh"
+
+namespace {
+
+thread_local std::string g_err;
+
+int fail(int code, const char* fmt, ...) {
+    char buf[1024];
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(buf, sizeof buf, fmt, ap);
+    va_end(ap);
+    g_err = buf;
+    return code;
+}
+
+#define CU(call)                                                                                   \
+    do {                                                                                           \
+        cudaError_t e__ = (call);                                                                  \
+        if (e__ != cudaSuccess)                                                                    \
+            return fail(e__ == cudaErrorMemoryAllocation ? SRT_ERR_OOM : SRT_ERR_CUDA, "%s: %s",   \
+                        #call, cudaGetErrorString(e__));                                           \
+    } while (0)
+
+struct DevBuf {
+    void* p = nullptr;
+    size_t cap = 0;
+    int reserve(size_t bytes) {
+        if (bytes <= cap) return SRT_OK;
+        if (p) cudaFree(p);
+        p = nullptr; cap = 0;
+        size_t want = bytes + bytes / 8 + 256;
+        cudaError_t e = cudaMalloc(&p, want);
+        if (e != cudaSuccess) return fail(SRT_ERR_OOM, "cudaMalloc(%zu): %s", want, cudaGetErrorString(e));
+        cap = want;
+        return SRT_OK;
+    }
+    void release() { if (p) cudaFree(p); p = nullptr; cap = 0; }
+};
+
+bool is_device_pointer(const void* p) {
+    cudaPointerAttributes at;
+    if (cudaPointerGetAttributes(&at, p) != cudaSuccess) { cudaGetLastError(); return false; }
+    return at.type == cudaMemoryTypeDevice || at.type == cudaMemoryTypeManaged;
+}
+
+}  // namespace
+
+struct srt_context {
+    int device = 0;
+    cudaStream_t stream = nullptr;
+    bool own_stream = true;
+    int sm_count = 0, cc_major = 0, cc_minor = 0;
+    size_t l2_bytes = 0;
+    unsigned long long* counters = nullptr;      // device, srtk::CNT_WORDS
+    unsigned long long* counters_host = nullptr; // pinned
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr, ev_copy = nullptr;
+    DevBuf out_rgb, out_obj, out_tri, out_t;     // staging for HOST output pointers
+    // last render
+    bool have_last = false;
+    uint64_t last_primary = 0;
+    int last_lights = 0;
+    uint32_t last_objects = 0;
+};
+
+struct srt_scene {
+    srt_context* ctx = nullptr;
+    DevBuf nodes, geom, attr, flat_geom, flat_attr, objects, texdesc;
+    std::vector<DevBuf> tex;
+    std::vector<srtk::TexDev> tex_host;
+    uint64_t n_nodes = 0, n_tris = 0, n_flat = 0;
+    uint32_t n_objects = 0, n_textures = 0;
+    uint32_t max_depth = 0;
+};
+
+extern "C" {
+
+int srt_abi_version(void) { return SRT_ABI_VERSION; }
+
+const char* srt_last_error(void) { return g_err.c_str(); }
+
+int srt_device_count(int* count) {
+    if (!count) return fail(SRT_ERR_INVALID_ARG, "count is NULL");
+    int n = 0;
+    cudaError_t e = cudaGetDeviceCount(&n);
+    if (e != cudaSuccess) { *count = 0; cudaGetLastError(); return fail(SRT_ERR_NO_DEVICE, "cudaGetDeviceCount: %s", cudaGetErrorString(e)); }
+    *count = n;
+    return SRT_OK;
+}
+
+int srt_context_create(int device, srt_context** out) {
+    if (!out) return fail(SRT_ERR_INVALID_ARG, "out is NULL");
+    *out = nullptr;
+    int n = 0;
+    cudaError_t e = cudaGetDeviceCount(&n);
+    if (e != cudaSuccess || n == 0) {
+        cudaGetLastError();
+        return fail(SRT_ERR_NO_DEVICE, "no CUDA device (%s); this library has no CPU fallback",
+                    e != cudaSuccess ? cudaGetErrorString(e) : "device count is 0");
+    }
+    if (device < 0 || device >= n) return fail(SRT_ERR_INVALID_ARG, "device %d out of range [0,%d)", device, n);
+    CU(cudaSetDevice(device));
+    cudaDeviceProp prop;
+    CU(cudaGetDeviceProperties(&prop, device));
+    if (prop.major < 10)
+        return fail(SRT_ERR_UNSUPPORTED, "device %d is sm_%d%d; this library carries sm_100a code only", device,
+                    prop.major, prop.minor);
+    srt_context* c = new srt_context();
+    c->device = device;
+    c->sm_count = prop.multiProcessorCount;
+    c->cc_major = prop.major; c->cc_minor = prop.minor;
+    c->l2_bytes = (size_t)prop.l2CacheSize;
+    CU(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
+    CU(cudaMalloc(&c->counters, sizeof(unsigned long long) * srtk::CNT_WORDS));
+    CU(cudaMallocHost(&c->counters_host, sizeof(unsigned long long) * srtk::CNT_WORDS));
+    CU(cudaEventCreate(&c->ev0));
+    CU(cudaEventCreate(&c->ev1));
+    CU(cudaEventCreateWithFlags(&c->ev_copy, cudaEventDisableTiming));
+    *out = c;
+    return SRT_OK;
+}
+
+void srt_context_destroy(srt_context* c) {
+    if (!c) return;
+    cudaSetDevice(c->device);
+    cudaStreamSynchronize(c->stream);
+    c->out_rgb.release(); c->out_obj.release(); c->out_tri.release(); c->out_t.release();
+    if (c->counters) cudaFree(c->counters);
+    if (c->counters_host) cudaFreeHost(c->counters_host);
+    if (c->ev0) cudaEventDestroy(c->ev0);
+    if (c->ev1) cudaEventDestroy(c->ev1);
+    if (c->ev_copy) cudaEventDestroy(c->ev_copy);
+    if (c->own_stream && c->stream) cudaStreamDestroy(c->stream);
+    delete c;
+}
+
+int srt_context_set_stream(srt_context* c, void* cuda_stream) {
+    if (!c) return fail(SRT_ERR_INVALID_ARG, "ctx is NULL");
+    CU(cudaSetDevice(c->device));
+    CU(cudaStreamSynchronize(c->stream));
+    if (c->own_stream && c->stream) cudaStreamDestroy(c->stream);
+    c->stream = (cudaStream_t)cuda_stream;
+    c->own_stream = false;
+    return SRT_OK;
+}
+
+int srt_context_get_info(srt_context* c, int* sm_count, int* cc_major, int* cc_minor, size_t* l2_bytes) {
+    if (!c) return fail(SRT_ERR_INVALID_ARG, "ctx is NULL");
+    if (sm_count) *sm_count = c->sm_count;
+    if (cc_major) *cc_major = c->cc_major;
+    if (cc_minor) *cc_minor = c->cc_minor;
+    if (l2_bytes) *l2_bytes = c->l2_bytes;
+    return SRT_OK;
+}
+
+void srt_default_params(srt_render_params* p) {
+    if (!p) return;
+    std::memset(p, 0, sizeof *p);
+    p->width = 600; p->height = 400;                 // simple_raytracer.cpp:773
+    p->focal = 400.0f;                               // :506
+    p->light_pos[0] = 500.0f; p->light_pos[1] = -300.0f; p->light_pos[2] = -200.0f;   // :776 (world space)
+    p->light_count = 1;                              // :445
+    p->light_step = 3.0f;                            // :372-382
+    p->light_color[0] = p->light_color[1] = p->light_color[2] = 1.0f;   // :433
+    p->shadow_div = 5.0f;                            // :369
+    p->tone_k = 0.5f;                                // :391
+    p->gamma = 1.1f;                                 // :396
+    p->sky[0] = 173; p->sky[1] = 216; p->sky[2] = 230;   // :476
+    p->use_bvh = 1;
+}
+
+// softShadow :363-383: L0 = lightPos; after sample i: i%3==0 -> x += step, 1 -> y, 2 -> z
+// (sequential fp32 adds on the host, compiled without contraction — nothing to contract here).
+int srt_light_positions(const srt_render_params* p, float* out) {
+    if (!p || !out) return fail(SRT_ERR_INVALID_ARG, "NULL argument");
+    if (p->light_count < 0 || p->light_count > SRT_MAX_LIGHTS)
+        return fail(SRT_ERR_INVALID_ARG, "light_count %d outside [0,%d]", p->light_count, SRT_MAX_LIGHTS);
+    volatile float L[3] = {p->light_pos[0], p->light_pos[1], p->light_pos[2]};
+    for (int i = 0; i < p->light_count; ++i) {
+        out[3 * i] = L[0]; out[3 * i + 1] = L[1]; out[3 * i + 2] = L[2];
+        L[i % 3] = L[i % 3] + p->light_step;
+    }
+    return SRT_OK;
+}
+
+void* srt_host_alloc(size_t bytes) {
+    void* p = nullptr;
+    if (cudaMallocHost(&p, bytes ? bytes : 1) != cudaSuccess) { cudaGetLastError(); g_err = "cudaMallocHost failed"; return nullptr; }
+    return p;
+}
+void srt_host_free(void* p) { if (p) cudaFreeHost(p); }
+
+void* srt_device_alloc(srt_context* c, size_t bytes) {
+    if (!c) return nullptr;
+    cudaSetDevice(c->device);
+    void* p = nullptr;
+    if (cudaMalloc(&p, bytes ? bytes : 1) != cudaSuccess) { cudaGetLastError(); g_err = "cudaMalloc failed"; return nullptr; }
+    return p;
+}
+void srt_device_free(srt_context* c, void* p) {
+    if (!c || !p) return;
+    cudaSetDevice(c->device);
+    cudaFree(p);
+}
+
+int srt_sync(srt_context* c) {
+    if (!c) return fail(SRT_ERR_INVALID_ARG, "ctx is NULL");
+    CU(cudaSetDevice(c->device));
+    CU(cudaStreamSynchronize(c->stream));
+    return SRT_OK;
+}
+
+}  // extern "C"
+
+// ---------------------------------------------------------------------------------------------
+// Scene validation + upload
+namespace {
+
+// Rejects what would make the kernel (or the reference) read out of bounds.
+int validate_scene(const srt_scene_desc* d, uint32_t* max_depth_out) {
+    if (!d) return fail(SRT_ERR_INVALID_ARG, "scene desc is NULL");
+    if (d->n_objects == 0) { *max_depth_out = 0; return SRT_OK; }
+    if (!d->objects) return fail(SRT_ERR_INVALID_ARG, "objects is NULL");
+    if (d->n_nodes && !d->nodes) return fail(SRT_ERR_INVALID_ARG, "nodes is NULL");
+    if (d->n_tris && (!d->geom || !d->attr)) return fail(SRT_ERR_INVALID_ARG, "geom/attr is NULL");
+    if (d->n_flat && (!d->flat_geom || !d->flat_attr)) return fail(SRT_ERR_INVALID_ARG, "flat_geom/flat_attr is NULL");
+    if (d->n_textures && !d->textures) return fail(SRT_ERR_INVALID_ARG, "textures is NULL");
+    if (d->n_nodes >= 0x7fffffffull || d->n_tris >= 0x7fffffffull || d->n_flat >= 0x7fffffffull)
+        return fail(SRT_ERR_UNSUPPORTED, "scene too large for 31-bit indices");
+    for (uint32_t t = 0; t < d->n_textures; ++t)
+        if (!d->textures[t].rgb || d->textures[t].width <= 0 || d->textures[t].height <= 0)
+            return fail(SRT_ERR_SCENE, "texture %u has no data (the reference dereferences textureData[...] at simple_raytracer.cpp:354-358)", t);
+    uint32_t max_depth = 0;
+    std::vector<std::pair<uint32_t, uint32_t>> stack;
+    for (uint32_t o = 0; o < d->n_objects; ++o) {
+        const srt_object& ob = d->objects[o];
+        if (ob.root >= d->n_nodes) return fail(SRT_ERR_SCENE, "object %u: root node %u out of range (object without bounding hierarchy?)", o, ob.root);
+        if ((uint64_t)ob.tri_first + ob.tri_count > d->n_tris) return fail(SRT_ERR_SCENE, "object %u: triangle range out of bounds", o);
+        if (ob.flat_first != SRT_NO_INDEX && (uint64_t)ob.flat_first + ob.tri_count > d->n_flat)
+            return fail(SRT_ERR_SCENE, "object %u: flat triangle range out of bounds", o);
+        stack.clear();
+        stack.push_back({ob.root, 0u});
+        uint64_t visited = 0;
+        while (!stack.empty()) {
+            auto [ni, depth] = stack.back();
+            stack.pop_back();
+            if (++visited > d->n_nodes) return fail(SRT_ERR_SCENE, "object %u: node graph is not a tree", o);
+            if (depth > max_depth) max_depth = depth;
+            const srt_node& n = d->nodes[ni];
+            if (n.b & SRT_LEAF_BIT) {
+                const uint32_t cnt = n.b & ~SRT_LEAF_BIT;
+                if ((uint64_t)n.a + cnt > d->n_tris) return fail(SRT_ERR_SCENE, "node %u: leaf triangle range out of bounds", ni);
+            } else {
+                if (ni + 1 >= d->n_nodes || n.a <= ni + 1 || n.a >= d->n_nodes)
+                    return fail(SRT_ERR_SCENE, "node %u: child index out of range", ni);
+                stack.push_back({n.a, depth + 1});
+                stack.push_back({ni + 1, depth + 1});
+            }
+        }
+    }
+    if (max_depth + 2 > (uint32_t)srtk::kMaxStack)
+        return fail(SRT_ERR_UNSUPPORTED, "BVH depth %u exceeds the kernel's traversal stack (%d)", max_depth, srtk::kMaxStack);
+    auto check_tris = [&](const srt_tri_geom* g, uint64_t n, const char* what) -> int {
+        for (uint64_t i = 0; i < n; ++i) {
+            if (g[i].tex < -1 || g[i].tex >= (int32_t)d->n_textures)
+                return fail(SRT_ERR_SCENE, "%s triangle %llu: texture index %d not loaded (textured triangle without texture, simple_raytracer.cpp:354)", what,
+                            (unsigned long long)i, g[i].tex);
+            if (g[i].obj < 0 || g[i].obj >= (int32_t)d->n_objects)
+                return fail(SRT_ERR_SCENE, "%s triangle %llu: object index %d out of range", what, (unsigned long long)i, g[i].obj);
+        }
+        return SRT_OK;
+    };
+    int rc = check_tris(d->geom, d->n_tris, "leaf-order");
+    if (rc) return rc;
+    rc = check_tris(d->flat_geom, d->n_flat, "load-order");
+    if (rc) return rc;
+    *max_depth_out = max_depth;
+    return SRT_OK;
+}
+
+int copy_in(srt_context* c, DevBuf& dst, const void* src, size_t bytes) {
+    if (bytes == 0) return SRT_OK;
+    int rc = dst.reserve(bytes);
+    if (rc) return rc;
+    CU(cudaMemcpyAsync(dst.p, src, bytes, cudaMemcpyHostToDevice, c->stream));
+    return SRT_OK;
+}
+
+int fill_scene(srt_context* c, srt_scene* s, const srt_scene_desc* d, bool textures_too) {
+    uint32_t depth = 0;
+    int rc = validate_scene(d, &depth);
+    if (rc) return rc;
+    CU(cudaSetDevice(c->device));
+    if ((rc = copy_in(c, s->nodes, d->nodes, d->n_nodes * sizeof(srt_node)))) return rc;
+    if ((rc = copy_in(c, s->geom, d->geom, d->n_tris * sizeof(srt_tri_geom)))) return rc;
+    if ((rc = copy_in(c, s->attr, d->attr, d->n_tris * sizeof(srt_tri_attr)))) return rc;
+    if ((rc = copy_in(c, s->flat_geom, d->flat_geom, d->n_flat * sizeof(srt_tri_geom)))) return rc;
+    if ((rc = copy_in(c, s->flat_attr, d->flat_attr, d->n_flat * sizeof(srt_tri_attr)))) return rc;
+    if ((rc = copy_in(c, s->objects, d->objects, d->n_objects * sizeof(srt_object)))) return rc;
+    s->n_nodes = d->n_nodes; s->n_tris = d->n_tris; s->n_flat = d->n_flat; s->n_objects = d->n_objects;
+    s->max_depth = depth;
+    if (textures_too) {
+        for (auto& t : s->tex) t.release();
+        s->tex.assign(d->n_textures, DevBuf());
+        s->tex_host.assign(d->n_textures, srtk::TexDev());
+        for (uint32_t t = 0; t < d->n_textures; ++t) {
+            const size_t bytes = (size_t)d->textures[t].width * d->textures[t].height * 3;
+            if ((rc = copy_in(c, s->tex[t], d->textures[t].rgb, bytes))) return rc;
+            s->tex_host[t].rgb = (const uint8_t*)s->tex[t].p;
+            s->tex_host[t].width = d->textures[t].width;
+            s->tex_host[t].height = d->textures[t].height;
+        }
+        s->n_textures = d->n_textures;
+        if ((rc = copy_in(c, s->texdesc, s->tex_host.data(), s->tex_host.size() * sizeof(srtk::TexDev)))) return rc;
+    } else if (d->n_textures != s->n_textures) {
+        return fail(SRT_ERR_INVALID_ARG, "srt_scene_update: texture count changed (%u -> %u); upload a new scene", s->n_textures, d->n_textures);
+    }
+    return SRT_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int srt_scene_upload(srt_context* c, const srt_scene_desc* d, srt_scene** out) {
+    if (!c || !out) return fail(SRT_ERR_INVALID_ARG, "NULL argument");
+    *out = nullptr;
+    srt_scene* s = new srt_scene();
+    s->ctx = c;
+    int rc = fill_scene(c, s, d, true);
+    if (rc == SRT_OK) {
+        cudaError_t e = cudaStreamSynchronize(c->stream);   // host arrays may be freed on return
+        if (e != cudaSuccess) rc = fail(SRT_ERR_CUDA, "cudaStreamSynchronize: %s", cudaGetErrorString(e));
+    }
+    if (rc != SRT_OK) { srt_scene_destroy(s); return rc; }
+    *out = s;
+    return SRT_OK;
+}
+
+int srt_scene_update(srt_context* c, srt_scene* s, const srt_scene_desc* d) {
+    if (!c || !s || s->ctx != c) return fail(SRT_ERR_INVALID_ARG, "scene does not belong to this context");
+    // Textures are immutable across updates unless the caller passes new ones explicitly.
+    const bool tex = d && d->textures != nullptr && d->n_textures > 0 && d->n_textures != s->n_textures;
+    return fill_scene(c, s, d, tex);
+}
+
+void srt_scene_destroy(srt_scene* s) {
+    if (!s) return;
+    if (s->ctx) { cudaSetDevice(s->ctx->device); cudaStreamSynchronize(s->ctx->stream); }
+    s->nodes.release(); s->geom.release(); s->attr.release(); s->flat_geom.release(); s->flat_attr.release();
+    s->objects.release(); s->texdesc.release();
+    for (auto& t : s->tex) t.release();
+    delete s;
+}
+
+}  // extern "C"
+
+// ---------------------------------------------------------------------------------------------
+// Render: the replacement for sendRaysAndIntersectPointsColors (simple_raytracer.cpp:505-525).
+extern "C" {
+
+int srt_render(srt_context* c, const srt_scene* s, const srt_render_params* p, const srt_frame* out) {
+    if (!c || !s || !p || !out) return fail(SRT_ERR_INVALID_ARG, "NULL argument");
+    if (s->ctx != c) return fail(SRT_ERR_INVALID_ARG, "scene does not belong to this context");
+    if (p->width <= 0 || p->height <= 0 || (long long)p->width * p->height > 0x7fffffffLL)
+        return fail(SRT_ERR_INVALID_ARG, "bad image size %dx%d", p->width, p->height);
+    if (p->light_count < 0 || p->light_count > SRT_MAX_LIGHTS)
+        return fail(SRT_ERR_INVALID_ARG, "light_count %d outside [0,%d]", p->light_count, SRT_MAX_LIGHTS);
+    int rb = p->row_begin, re = p->row_end;
+    if (rb == 0 && re == 0) re = p->height;
+    if (rb < 0 || re > p->height || rb > re) return fail(SRT_ERR_INVALID_ARG, "bad row range [%d,%d)", rb, re);
+    if (!p->use_bvh && s->n_objects > 0 && s->n_flat == 0)
+        return fail(SRT_ERR_INVALID_ARG, "use_bvh=0 (legacy one-box path) needs a scene flattened with load-order lists");
+    CU(cudaSetDevice(c->device));
+
+    srtk::KArgs a;
+    std::memset(&a, 0, sizeof a);
+    a.nodes = (const float4*)s->nodes.p;
+    a.geom = (const float4*)s->geom.p;
+    a.attr = (const float4*)s->attr.p;
+    a.flat_geom = (const float4*)s->flat_geom.p;
+    a.flat_attr = (const float4*)s->flat_attr.p;
+    a.objects = (const srt_object*)s->objects.p;
+    a.textures = (const srtk::TexDev*)s->texdesc.p;
+    a.n_objects = s->n_objects;
+    a.width = p->width; a.height = p->height; a.row_begin = rb; a.row_end = re;
+    // loop bounds of :511/:513 — `int i = -imageSize.x / 2` truncates the float toward zero
+    a.i0 = (int)(-(float)p->width / 2);
+    a.j0 = (int)(-(float)p->height / 2);
+    a.focal = p->focal;
+    a.light_count = p->light_count;
+    for (int k = 0; k < 3; ++k) a.light_color[k] = p->light_color[k];
+    a.shadow_div = p->shadow_div; a.tone_k = p->tone_k; a.gamma = p->gamma;
+    a.sky[0] = p->sky[0]; a.sky[1] = p->sky[1]; a.sky[2] = p->sky[2];
+    a.no_sky_fill = p->no_sky_fill ? 1 : 0;
+    a.use_bvh = p->use_bvh;
+    a.tiles_x = (p->width + srtk::kTileW - 1) / srtk::kTileW;
+    a.tiles_y = (re - rb + srtk::kTileH - 1) / srtk::kTileH;
+    a.counters = c->counters;
+    int rc = srt_light_positions(p, a.lights);
+    if (rc) return rc;
+
+    // Output planes: device pointers are written in place, host pointers through staging buffers.
+    const size_t npix = (size_t)p->width * p->height;
+    struct Plane { void* user; DevBuf* stage; size_t elem; void** karg; bool host; };
+    Plane planes[4] = {
+        {out->rgb, &c->out_rgb, 3, (void**)&a.rgb, false},
+        {out->obj_id, &c->out_obj, 4, (void**)&a.obj_id, false},
+        {out->tri_id, &c->out_tri, 4, (void**)&a.tri_id, false},
+        {out->t, &c->out_t, 4, (void**)&a.t, false},
+    };
+    for (auto& pl : planes) {
+        if (!pl.user) { *pl.karg = nullptr; continue; }
+        if (is_device_pointer(pl.user)) { *pl.karg = pl.user; continue; }
+        pl.host = true;
+        if ((rc = pl.stage->reserve(npix * pl.elem))) return rc;
+        *pl.karg = pl.stage->p;
+    }
+
+    CU(cudaMemsetAsync(c->counters, 0, sizeof(unsigned long long) * srtk::CNT_WORDS, c->stream));
+    CU(cudaEventRecord(c->ev0, c->stream));
+    if (s->n_objects == 0 || a.tiles_x * a.tiles_y == 0) {
+        // nothing to intersect: still an image (all sky) — run the kernel with zero objects
+    }
+    cudaError_t e = srtk::launch_render(a, p->variant, c->sm_count, c->stream);
+    if (e != cudaSuccess) return fail(SRT_ERR_CUDA, "render kernel launch: %s", cudaGetErrorString(e));
+    CU(cudaEventRecord(c->ev1, c->stream));
+    CU(cudaMemcpyAsync(c->counters_host, c->counters, sizeof(unsigned long long) * srtk::CNT_WORDS,
+                       cudaMemcpyDeviceToHost, c->stream));
+    // copy back only the rendered rows
+    const size_t row0 = (size_t)rb * p->width, nrow = (size_t)(re - rb) * p->width;
+    for (auto& pl : planes) {
+        if (!pl.host || nrow == 0) continue;
+        CU(cudaMemcpyAsync((char*)pl.user + row0 * pl.elem, (char*)pl.stage->p + row0 * pl.elem, nrow * pl.elem,
+                           cudaMemcpyDeviceToHost, c->stream));
+    }
+    c->have_last = true;
+    c->last_primary = (uint64_t)(re - rb) * (uint64_t)p->width;
+    c->last_lights = p->light_count;
+    c->last_objects = s->n_objects;
+    return SRT_OK;
+}
+
+int srt_last_stats(srt_context* c, srt_stats* out) {
+    if (!c || !out) return fail(SRT_ERR_INVALID_ARG, "NULL argument");
+    if (!c->have_last) return fail(SRT_ERR_INVALID_ARG, "no render has been issued on this context");
+    CU(cudaSetDevice(c->device));
+    CU(cudaStreamSynchronize(c->stream));
+    std::memset(out, 0, sizeof *out);
+    out->primary_rays = c->last_primary;
+    out->hit_pixels = c->counters_host[srtk::CNT_HIT];
+    // ray-count rule of SURVEY.md §8d: the shadow rays the final image depends on
+    out->shadow_rays = c->last_objects >= 2 ? (uint64_t)c->last_lights * out->hit_pixels : 0;
+    out->node_visits = c->counters_host[srtk::CNT_NODE];
+    out->tri_tests = c->counters_host[srtk::CNT_TRI];
+    float ms = 0.f;
+    CU(cudaEventElapsedTime(&ms, c->ev0, c->ev1));
+    out->kernel_ms = ms;
+    return SRT_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,231 @@
+// srt_kernels.cu — the render kernels (sm_100a).  See DESIGN.md §Kernels.
+//
+// K1 "simple": persistent grid, one warp = one 8x4 pixel tile pulled from an atomic tile counter,
+// one thread = one pixel: primary ray -> stack traversal of every object's flattened BVH with the
+// reference's slab test -> Moeller-Trumbore on every leaf the line pierces -> closest hit with
+// the reference's first-visited-wins rule -> N staircase lights, each with an any-hit shadow ray
+// through the OTHER objects -> Phong -> tone map / gamma -> 8-bit quantise -> sky fill.
+// Replaces simple_raytracer.cpp:505-525 (pixel loop), :405-457, :296-317, :321-401, and the
+// 8-bit / sky rules of drawImage :461-498.
+#include "srt_kernels.cuh"
+#include "srt_device.cuh"
+
+namespace srtk {
+using namespace srtd;
+
+namespace {
+
+struct Hit { float t; int32_t tri; int32_t obj; };
+
+__device__ __forceinline__ float4 ldg4(const float4* p) { return __ldg(p); }
+
+// boundingBoxIntersection :296-317 merged with the candidate loop of rayIntersection :424-431:
+// depth-first, left child first, every leaf whose box passes the slab test; strict '<' keeps the
+// first-visited triangle on equal t (S5, S6).
+template <bool COUNT>
+__device__ __forceinline__ void closest_in_tree(const KArgs& a, uint32_t root, int32_t obj, V3 o, V3 d, Hit& h,
+                                                unsigned& nodes_seen, unsigned& tris_seen) {
+    uint32_t stack[kMaxStack];
+    int sp = 0;
+    uint32_t ni = root;
+    for (;;) {
+        const float4 n0 = ldg4(a.nodes + 2 * (size_t)ni);
+        const float4 n1 = ldg4(a.nodes + 2 * (size_t)ni + 1);
+        if (COUNT) ++nodes_seen;
+        bool descend = false;
+        if (slab_exact(o, d, n0, n1)) {
+            const uint32_t na = __float_as_uint(n0.w), nb = __float_as_uint(n1.w);
+            if (nb & SRT_LEAF_BIT) {
+                const uint32_t cnt = nb & ~SRT_LEAF_BIT;
+                for (uint32_t k = 0; k < cnt; ++k) {
+                    const float4* g = a.geom + 3 * (size_t)(na + k);
+                    const float t = moller_trumbore(o, d, ldg4(g), ldg4(g + 1), ldg4(g + 2));
+                    if (COUNT) ++tris_seen;
+                    if (t != -INFINITY && t < h.t) { h.t = t; h.tri = (int32_t)(na + k); h.obj = obj; }
+                }
+            } else {
+                stack[sp++] = na;          // right child later
+                ni = ni + 1;               // left child first
+                descend = true;
+            }
+        }
+        if (!descend) {
+            if (sp == 0) break;
+            ni = stack[--sp];
+        }
+    }
+}
+
+// Legacy one-box path :415-420.
+template <bool COUNT>
+__device__ __forceinline__ void closest_in_flat(const KArgs& a, const srt_object& ob, int32_t obj, V3 d, Hit& h,
+                                                unsigned& nodes_seen, unsigned& tris_seen) {
+    const V3 o = v3(0.f, 0.f, 0.f);
+    if (COUNT) ++nodes_seen;
+    const float4 lo = make_float4(ob.box_min[0], ob.box_min[1], ob.box_min[2], 0.f);
+    const float4 hi = make_float4(ob.box_max[0], ob.box_max[1], ob.box_max[2], 0.f);
+    if (!slab_exact(o, d, lo, hi)) return;                                   // intersectRayAabb :417
+    for (uint32_t k = 0; k < ob.tri_count; ++k) {
+        const float4* g = a.flat_geom + 3 * (size_t)(ob.flat_first + k);
+        const float t = moller_trumbore(o, d, ldg4(g), ldg4(g + 1), ldg4(g + 2));
+        if (COUNT) ++tris_seen;
+        if (t != -INFINITY && t < h.t) { h.t = t; h.tri = (int32_t)(ob.flat_first + k); h.obj = obj; }
+    }
+}
+
+// shadowIntersection :321-342 restricted to one object's tree: true as soon as ANY candidate
+// triangle returns a hit (any t >= 0, no upper bound at the light, no epsilon — S11).
+template <bool COUNT>
+__device__ __forceinline__ bool any_hit_in_tree(const KArgs& a, uint32_t root, V3 o, V3 d, unsigned& nodes_seen,
+                                                unsigned& tris_seen) {
+    uint32_t stack[kMaxStack];
+    int sp = 0;
+    uint32_t ni = root;
+    for (;;) {
+        const float4 n0 = ldg4(a.nodes + 2 * (size_t)ni);
+        const float4 n1 = ldg4(a.nodes + 2 * (size_t)ni + 1);
+        if (COUNT) ++nodes_seen;
+        bool descend = false;
+        if (slab_exact(o, d, n0, n1)) {
+            const uint32_t na = __float_as_uint(n0.w), nb = __float_as_uint(n1.w);
+            if (nb & SRT_LEAF_BIT) {
+                const uint32_t cnt = nb & ~SRT_LEAF_BIT;
+                for (uint32_t k = 0; k < cnt; ++k) {
+                    const float4* g = a.geom + 3 * (size_t)(na + k);
+                    if (COUNT) ++tris_seen;
+                    if (moller_trumbore(o, d, ldg4(g), ldg4(g + 1), ldg4(g + 2)) != -INFINITY) return true;
+                }
+            } else {
+                stack[sp++] = na;
+                ni = ni + 1;
+                descend = true;
+            }
+        }
+        if (!descend) {
+            if (sp == 0) break;
+            ni = stack[--sp];
+        }
+    }
+    return false;
+}
+
+// Base colour (:437-443, :350-361) and the light-independent part of phongIllumination.
+__device__ __forceinline__ PhongPixel prepare_pixel(const KArgs& a, const Hit& h, V3 d, bool use_flat) {
+    const float4* gp = (use_flat ? a.flat_geom : a.geom) + 3 * (size_t)h.tri;
+    const float4* ap = (use_flat ? a.flat_attr : a.attr) + 3 * (size_t)h.tri;
+    const float4 g0 = ldg4(gp), g1 = ldg4(gp + 1), g2 = ldg4(gp + 2);
+    const float4 a0 = ldg4(ap);
+    const srt_object& ob = a.objects[h.obj];
+    PhongPixel px;
+    px.n = v3(a0.x, a0.y, a0.z);
+    // ray->origin + distance * ray->direction, origin = (0,0,0)          :156 / :351
+    px.P = v3(add(0.0f, mul(h.t, d.x)), add(0.0f, mul(h.t, d.y)), add(0.0f, mul(h.t, d.z)));
+    px.v = normalize3(v3(-d.x, -d.y, -d.z));                              // :190
+    px.oc = v3(ob.color[0], ob.color[1], ob.color[2]);                    // :439
+    px.ambientStrength = ob.ambient; px.specularStrength = ob.specular; px.shininess = ob.shininess;
+    const int32_t tex = __float_as_int(g1.w);
+    if (tex >= 0) {                                                       // :350
+        const float4 a1 = ldg4(ap + 1), a2 = ldg4(ap + 2);
+        // uv[0] = (a0.w? no) — layout: n.xyz pad | uv0.x uv0.y uv1.x uv1.y | uv2.x uv2.y pad pad
+        const V3 bc = barycentric(v3(g0.x, g0.y, g0.z), v3(g1.x, g1.y, g1.z), v3(g2.x, g2.y, g2.z), px.P);
+        // getTextureCoordinate :123-125: (b.x*A + b.y*B) + b.z*C per component
+        const float ux = add(add(mul(bc.x, a1.x), mul(bc.y, a1.z)), mul(bc.z, a2.x));
+        const float uy = add(add(mul(bc.x, a1.y), mul(bc.y, a1.w)), mul(bc.z, a2.y));
+        const TexDev tx = a.textures[tex];
+        long long idx = ((long long)(__float2int_rz(uy) * tx.width + __float2int_rz(ux))) * 3;   // :357
+        const long long last = ((long long)tx.width * tx.height - 1) * 3;
+        idx = idx < 0 ? 0 : (idx > last ? last : idx);   // the reference reads out of bounds here (UB): clamp
+        px.oc = v3(dvd((float)tx.rgb[idx + 0], 255.0f), dvd((float)tx.rgb[idx + 1], 255.0f),
+                   dvd((float)tx.rgb[idx + 2], 255.0f));                  // :358-360
+    }
+    return px;
+}
+
+__device__ __forceinline__ void store_pixel(const KArgs& a, int px, int py, bool hit, V3 color, const Hit& h) {
+    const size_t at = (size_t)py * a.width + px;
+    if (a.rgb) {
+        int r = 0, g = 0, b = 0;
+        if (hit) {
+            r = tone_quantise(color.x, a.tone_k, a.gamma) & 0xff;         // :391-398, :447-449, :470-472
+            g = tone_quantise(color.y, a.tone_k, a.gamma) & 0xff;
+            b = tone_quantise(color.z, a.tone_k, a.gamma) & 0xff;
+        }
+        if ((r | g | b) == 0 && !a.no_sky_fill) { r = a.sky[0]; g = a.sky[1]; b = a.sky[2]; }   // :518, :476-487
+        uint8_t* p = a.rgb + at * 3;
+        p[0] = (uint8_t)r; p[1] = (uint8_t)g; p[2] = (uint8_t)b;
+    }
+    if (a.obj_id) a.obj_id[at] = h.obj;
+    if (a.tri_id) a.tri_id[at] = h.tri;
+    if (a.t) a.t[at] = h.t;
+}
+
+template <bool COUNT>
+__global__ void __launch_bounds__(128) render_simple(const __grid_constant__ KArgs a) {
+    const unsigned lane = threadIdx.x & 31;
+    const int n_tiles = a.tiles_x * a.tiles_y;
+    unsigned hits = 0, nodes_seen = 0, tris_seen = 0;
+    const bool use_flat = !a.use_bvh;
+    for (;;) {
+        unsigned tile = 0;
+        if (lane == 0) tile = (unsigned)atomicAdd(&a.counters[CNT_TILE], 1ull);
+        tile = __shfl_sync(0xffffffffu, tile, 0);
+        if ((int)tile >= n_tiles) break;
+        const int tx = (int)(tile % (unsigned)a.tiles_x), ty = (int)(tile / (unsigned)a.tiles_x);
+        const int px = tx * kTileW + (int)(lane & 7), py = a.row_begin + ty * kTileH + (int)(lane >> 3);
+        if (px >= a.width || py >= a.row_end) continue;
+        // ray.direction = (i, j, focal), i = px + i0, j = py + j0            :511-515 (S1)
+        const V3 o = v3(0.f, 0.f, 0.f);
+        const V3 d = v3((float)(px + a.i0), (float)(py + a.j0), a.focal);
+        Hit h; h.t = INFINITY; h.tri = -1; h.obj = -1;
+        for (uint32_t ob = 0; ob < a.n_objects; ++ob) {                       // :409 (S2 order)
+            if (use_flat) closest_in_flat<COUNT>(a, a.objects[ob], (int32_t)ob, d, h, nodes_seen, tris_seen);
+            else closest_in_tree<COUNT>(a, a.objects[ob].root, (int32_t)ob, o, d, h, nodes_seen, tris_seen);
+        }
+        V3 color = v3(0.f, 0.f, 0.f);
+        const bool hit = h.tri >= 0;
+        if (hit) {
+            ++hits;
+            const PhongPixel pp = prepare_pixel(a, h, d, use_flat);
+            const V3 so = v3(mul(d.x, h.t), mul(d.y, h.t), mul(d.z, h.t));    // shadowRay.origin :326
+            const V3 lc = v3(a.light_color[0], a.light_color[1], a.light_color[2]);
+            for (int i = 0; i < a.light_count; ++i) {                         // :366
+                const V3 L = v3(a.lights[3 * i], a.lights[3 * i + 1], a.lights[3 * i + 2]);
+                bool shadowed = false;
+                const V3 sd = v3(sub(L.x, so.x), sub(L.y, so.y), sub(L.z, so.z));   // :325
+                for (uint32_t ob = 0; ob < a.n_objects && !shadowed; ++ob) {  // :322
+                    if ((int32_t)ob == h.obj) continue;                       // :331
+                    shadowed = any_hit_in_tree<COUNT>(a, a.objects[ob].root, so, sd, nodes_seen, tris_seen);
+                }
+                V3 c = phong(pp, L, lc);                                      // :368
+                if (shadowed) { c.x = dvd(c.x, a.shadow_div); c.y = dvd(c.y, a.shadow_div); c.z = dvd(c.z, a.shadow_div); }  // :369
+                color.x = add(color.x, c.x); color.y = add(color.y, c.y); color.z = add(color.z, c.z);   // :370
+            }
+        }
+        store_pixel(a, px, py, hit, color, h);
+    }
+    // one atomic per warp for the statistics
+    for (int s = 16; s > 0; s >>= 1) {
+        hits += __shfl_xor_sync(0xffffffffu, hits, s);
+        if (COUNT) { nodes_seen += __shfl_xor_sync(0xffffffffu, nodes_seen, s); tris_seen += __shfl_xor_sync(0xffffffffu, tris_seen, s); }
+    }
+    if (lane == 0) {
+        atomicAdd(&a.counters[CNT_HIT], (unsigned long long)hits);
+        if (COUNT) { atomicAdd(&a.counters[CNT_NODE], (unsigned long long)nodes_seen); atomicAdd(&a.counters[CNT_TRI], (unsigned long long)tris_seen); }
+    }
+}
+
+}  // namespace
+
+cudaError_t launch_render(const KArgs& a, int variant, int sm_count, cudaStream_t stream) {
+    const int n_tiles = a.tiles_x * a.tiles_y;
+    if (n_tiles <= 0) return cudaSuccess;
+    const int warps_per_block = 4;
+    int blocks = sm_count * 8;                       // persistent: 8 resident CTAs of 4 warps per SM
+    const int need = (n_tiles + warps_per_block - 1) / warps_per_block;
+    if (blocks > need) blocks = need;
+    if (variant == 100) render_simple<true><<<blocks, 128, 0, stream>>>(a);      // instrumented (node / triangle counts)
+    else render_simple<false><<<blocks, 128, 0, stream>>>(a);
+    return cudaGetLastError();
+}
+
+}  // namespace srtk

@@ -1,0 +1,52 @@
+// srt_kernels.cuh — launch-side view of the render kernels (shared by srt_kernels.cu / srt_capi.cu).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "srt.h"
+
+namespace srtk {
+
+struct TexDev {
+    const uint8_t* rgb;
+    int32_t width, height;
+};
+
+// Slots of the per-context device counter block.
+enum { CNT_TILE = 0, CNT_HIT = 1, CNT_NODE = 2, CNT_TRI = 3, CNT_WORDS = 8 };
+
+// Everything one frame needs, passed by value as a __grid_constant__ kernel parameter.
+struct KArgs {
+    const float4* nodes;        // srt_node as 2 x float4
+    const float4* geom;         // srt_tri_geom as 3 x float4 (leaf order)
+    const float4* attr;         // srt_tri_attr as 3 x float4
+    const float4* flat_geom;    // load order (legacy one-box path) or null
+    const float4* flat_attr;
+    const srt_object* objects;
+    const TexDev* textures;
+    uint32_t n_objects;
+    int32_t width, height, row_begin, row_end;
+    int32_t i0, j0;             // first values of the loops :511 / :513 (float -> int truncation of -W/2, -H/2)
+    float focal;
+    int32_t light_count;
+    float light_color[3];
+    float shadow_div, tone_k, gamma;
+    uint8_t sky[3];
+    uint8_t no_sky_fill;
+    int32_t use_bvh;
+    int32_t tiles_x, tiles_y;   // 8x4-pixel warp tiles over [row_begin,row_end)
+    uint8_t* rgb;
+    int32_t* obj_id;
+    int32_t* tri_id;
+    float* t;
+    unsigned long long* counters;   // CNT_* slots, zeroed before launch
+    float lights[3 * SRT_MAX_LIGHTS];   // staircase positions, softShadow :363-383
+};
+
+constexpr int kTileW = 8, kTileH = 4;          // one warp = 8x4 pixels
+constexpr int kMaxStack = 64;                  // >= deepest BVH the upload accepts
+
+// variant: SRT_VARIANT_*; returns cudaError_t from the launch.
+cudaError_t launch_render(const KArgs& a, int variant, int sm_count, cudaStream_t stream);
+
+}  // namespace srtk
