@@ -1,0 +1,108 @@
+"""GPU parity: the CUDA path (through the C ABI) against the oracle on the same flattened scene.
+
+Gates (BASELINE.json north_star): primary-hit object/triangle ids identical on >= 99.9 % of pixels,
+8-bit image max abs error <= 1 LSB, PSNR >= 50 dB.  The kernel is written to be bit-exact in
+everything but powf (see srt_device.cuh), so these tests additionally report — and bound — the
+number of pixels that differ at all.
+"""
+import numpy as np
+import pytest
+
+from conftest import compare_images
+from oracle import pyoracle
+from simple_raytracer_b200 import _abi, scenes
+
+pytestmark = [pytest.mark.gpu, pytest.mark.ref]
+
+# (config, width, height, focal, lights)
+CASES = [
+    ("C1", 512, 512, 400.0, 1),         # BASELINE configs[0] at full size, legacy one-box path
+    ("C1b", 512, 512, 400.0, 1),
+    ("shipped", 600, 400, 400.0, 1),    # the shipped main() constants
+    ("C2", 480, 270, 270.0, 1),
+    ("C3", 480, 270, 270.0, 16),
+    ("spheres", 300, 200, 200.0, 8),
+    ("cubes4", 300, 200, 200.0, 4),
+]
+
+
+@pytest.mark.parametrize("key,W,H,focal,N", CASES, ids=[c[0] for c in CASES])
+def test_frame_parity(gpu_ctx, ref_scene, key, W, H, focal, N):
+    cfg = scenes.CONFIGS[key]
+    _b, arrays, light = ref_scene(key)
+    p = _abi.default_params(W, H, focal, light, N, cfg.use_bvh)
+    want = pyoracle.oracle_render(arrays, p)
+    sc = gpu_ctx.upload(arrays)
+    got = gpu_ctx.render(sc, p)
+    sc.destroy()
+    npx = W * H
+    same_obj = np.count_nonzero(got["obj_id"] == want["obj_id"])
+    same_tri = np.count_nonzero(got["tri_id"] == want["tri_id"])
+    mx, psnr = compare_images(got["rgb"], want["rgb"])
+    ndiff = int(np.count_nonzero((got["rgb"] != want["rgb"]).any(axis=2)))
+    print(f"{key}: ids obj {same_obj}/{npx} tri {same_tri}/{npx}; rgb max|d|={mx} psnr={psnr:.1f} dB "
+          f"pixels differing={ndiff}; kernel {got['stats']['kernel_ms']:.3f} ms")
+    assert same_obj == npx and same_tri == npx, "primary-hit ids must be identical (exact arithmetic)"
+    assert np.array_equal(got["t"], want["t"]), "hit parameter t must be bit-identical"
+    assert mx <= 1 and psnr >= 50.0
+    assert ndiff <= max(2, npx // 20000), "more 1-LSB pixels than double-precision pow should allow"
+    assert got["stats"]["hit_pixels"] == want["counters"]["hit_pixels"]
+    assert got["stats"]["shadow_rays"] == want["counters"]["shadow_rays"]
+
+
+def test_instrumented_counts_match_oracle(gpu_ctx, ref_scene):
+    """Node-visit / triangle-test counters of the instrumented kernel == the oracle's (same traversal rules)."""
+    _b, arrays, light = ref_scene("C3")
+    p = _abi.default_params(240, 136, 136.0, light, 4, True)
+    want = pyoracle.oracle_render(arrays, p)
+    p.variant = 100
+    sc = gpu_ctx.upload(arrays)
+    got = gpu_ctx.render(sc, p)
+    sc.destroy()
+    c = want["counters"]
+    assert np.array_equal(got["tri_id"], want["tri_id"])
+    # any-hit shadow traversal may stop at a different triangle than the oracle's fixed order only
+    # if visit order differed; it does not, so counts are equal.
+    assert got["stats"]["node_visits"] == c["node_visits_primary"] + c["node_visits_shadow"]
+    assert got["stats"]["tri_tests"] == c["tri_tests_primary"] + c["tri_tests_shadow"]
+
+
+def test_row_shard_equals_full_frame(gpu_ctx, ref_scene):
+    """Tile-row sharding (multi-GPU single-frame mode) must be byte-identical to one full render."""
+    _b, arrays, light = ref_scene("C3")
+    W, H = 320, 180
+    p = _abi.default_params(W, H, 180.0, light, 4, True)
+    sc = gpu_ctx.upload(arrays)
+    full = gpu_ctx.render(sc, p)
+    rgb = np.zeros((H, W, 3), np.uint8)
+    tri = np.full((H, W), -1, np.int32)
+    for r0, r1 in ((0, 44), (44, 45), (45, 128), (128, 180)):
+        p.row_begin, p.row_end = r0, r1
+        gpu_ctx.render_raw(sc, p, rgb.ctypes.data, None, tri.ctypes.data, None)
+        gpu_ctx.sync()
+    sc.destroy()
+    assert np.array_equal(rgb, full["rgb"]) and np.array_equal(tri, full["tri_id"])
+
+
+def test_odd_sizes_and_centre_lines(gpu_ctx, ref_scene):
+    """Odd image sizes (float->int truncation of -W/2, :511) and the d.x = 0 / d.y = 0 centre lines (0/0 NaN in the slab test)."""
+    _b, arrays, light = ref_scene("shipped")
+    for W, H in ((101, 67), (64, 33), (7, 5)):
+        p = _abi.default_params(W, H, 50.0, light, 2, True)
+        want = pyoracle.oracle_render(arrays, p)
+        sc = gpu_ctx.upload(arrays)
+        got = gpu_ctx.render(sc, p)
+        sc.destroy()
+        assert np.array_equal(got["tri_id"], want["tri_id"])
+        assert np.array_equal(got["t"], want["t"])
+        assert compare_images(got["rgb"], want["rgb"])[0] <= 1
+
+
+def test_oracle_matches_reference_on_gpu_box(ref_scene):
+    """The C restatement vs the reference's own functions, re-checked where the GPU tests run."""
+    b, arrays, light = ref_scene("C3")
+    p = _abi.default_params(96, 54, 54.0, light, 3, True)
+    want = b.render(96, 54, 54.0, light, 3, True, faithful=True)
+    got = pyoracle.oracle_render(arrays, p)
+    for k in ("rgb", "obj_id", "tri_id", "t"):
+        assert np.array_equal(want[k], got[k]), k
