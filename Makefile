@@ -7,11 +7,11 @@ ARCH     := -gencode arch=compute_100a,code=sm_100a
 # -fmad=false / --prec-div / --prec-sqrt: belt and braces; the device code already spells every
 # operation with __fmul_rn/__fadd_rn/__fdiv_rn/__fsqrt_rn.
 NVFLAGS  := $(ARCH) -O3 -std=c++17 -lineinfo -fmad=false --prec-div=true --prec-sqrt=true --ftz=false \
-            -Xcompiler -fPIC,-O2,-ffp-contract=off -Iinclude -Isimple_raytracer_b200/csrc
+            -Xcompiler -fPIC,-O2,-ffp-contract=off -Iinclude -Isimple_raytracer_b200/csrc -Isimple_raytracer_b200/csrc/host
 CSRC     := simple_raytracer_b200/csrc
 LIB      := simple_raytracer_b200/lib/libsrt_b200.so
 SRCS     := $(CSRC)/srt_capi.cu $(CSRC)/srt_kernels.cu $(wildcard $(CSRC)/host/*.cpp)
-HDRS     := include/srt.h $(wildcard $(CSRC)/*.cuh) $(wildcard $(CSRC)/host/*.hpp)
+HDRS     := include/srt.h include/srt_host.h $(wildcard $(CSRC)/*.cuh) $(wildcard $(CSRC)/host/*.hpp)
 
 .PHONY: all lib oracle ref clean
 all: lib
