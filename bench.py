@@ -1,0 +1,420 @@
+#!/usr/bin/env python
+"""bench.py — the headline measurement: Mrays/s (and frames/s) of the per-pixel render loop on the
+bunny + ground, 16-light soft-shadow scene at 1920x1080 (BASELINE.json configs[2] = SURVEY.md C3,
+frames of the configs[4] image series C5 when several GPUs shard the series by frame).
+
+    python bench.py --gpus 1 --steps K --warmup W                 # one B200
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 \
+           --master-port P bench.py --gpus N --steps K --warmup W # N B200s, one rank per GPU
+    python bench.py --impl reference ...                          # the reference's CPU code, same metric
+
+A "step" is one 1080p frame: rank r renders series frame (step*N + r) (camera angle 1.5 deg per
+frame, frame 0 == C3).  `value` = rays of all ranks / max-over-ranks device time, scenes resident in
+HBM; `e2e` = the same through the C ABI from pinned HOST buffers (scene upload + render + NCCL gather
+to rank 0 + download of the frames).  Ray-count rule:
+rays = W*H + light_count * hit_pixels * [scene has >= 2 objects].
+
+torch is plumbing here (device buffers, streams, events, torch.distributed); the render path is
+simple_raytracer_b200/lib/libsrt_b200.so through include/srt.h and raises if it is missing.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+from pathlib import Path
+
+import numpy as np
+
+REPO = Path(__file__).resolve().parent
+if str(REPO) not in sys.path:
+    sys.path.insert(0, str(REPO))
+
+METRIC = "Mrays/s (bunny + ground, 16-light soft shadows, 1920x1080)"
+UNIT = "Mrays/s"
+WORKLOAD = ("C3/C5: stanford-bunny.obj (x150) + ground cube, 16 staircase lights, 1920x1080, focal 1080, BVH; "
+            "rank r renders image-series frame step*N+r at 1.5 deg/frame (frame 0 = C3)")
+L2_FLUSH_BYTES = 512 << 20
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--config", default="C3", help="scene config key (bench lines use C3; others are for profiling)")
+    ap.add_argument("--height", type=int, default=0, help="override the image height (same field of view)")
+    ap.add_argument("--lights", type=int, default=-1)
+    ap.add_argument("--variant", type=int, default=0)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--cpu-seconds", type=float, default=20.0, help="CPU work (core-seconds) of the cpu_baseline sample")
+    ap.add_argument("--still", action="store_true", help="render frame 0 on every step (profiling)")
+    return ap.parse_args()
+
+
+# ------------------------------------------------------------------------------------------------
+def frame_setup(args):
+    from simple_raytracer_b200 import scenes
+    cfg = scenes.CONFIGS[args.config]
+    if args.height > 0:
+        W, H, focal = scenes.scaled(cfg, args.height)
+    else:
+        W, H, focal = cfg.width, cfg.height, cfg.focal
+    N = cfg.light_count if args.lights < 0 else args.lights
+    return cfg, W, H, focal, N
+
+
+def build_frame(backend_factory, cfg, frame_index, still=False):
+    """Host prep of one series frame through the scene surface: load, transform, BVH, flatten."""
+    from simple_raytracer_b200 import scenes
+    b = backend_factory()
+    angle = 0.0 if still else scenes.SERIES_DEG_PER_FRAME * (frame_index % scenes.SERIES_FRAMES)
+    view = cfg.build(b, angle)
+    light = scenes.light_view_space(b, view) if view is not None else np.array(scenes.LIGHT_WORLD, np.float32)
+    arrays = b.flatten(with_flat_lists=not cfg.use_bvh)
+    return b, arrays, np.asarray(light, np.float32)
+
+
+def ray_count(W, H, N, hit_pixels, n_objects):
+    return W * H + (N * hit_pixels if n_objects >= 2 else 0)
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled every 100 ms while the timed region runs."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.rows, self.proc, self.thread = [], None, None
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(index), f"--query-gpu={self.Q}",
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._read, daemon=True)
+            self.thread.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append((time.time(), line.strip()))
+
+    def stop(self, t0, t1):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm, mx, pw, reasons = [], [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        rows = [r for (t, r) in self.rows if t0 - 0.05 <= t <= t1 + 0.15] or [r for (_t, r) in self.rows]
+        for r in rows:
+            f = [x.strip() for x in r.split(",")]
+            if len(f) < 7:
+                continue
+            try:
+                sm.append(float(f[0])); mx.append(float(f[1])); pw.append(float(f[2]))
+            except ValueError:
+                continue
+            for k, n in enumerate(names):
+                if f[3 + k].lower().startswith("active"):
+                    reasons.add(n)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "power_w_max": max(pw) if pw else None, "samples": len(sm), "reasons": sorted(reasons)}
+
+
+# ------------------------------------------------------------------------------------------------
+def cpu_reference_sample(cfg, W, H, focal, N, core_seconds, threads=0, per_step_wall=None):
+    """Times the reference's CPU implementation of the path (oracle/_ref when present, else the C
+    oracle port) on a bounded column sample of the frame.  Returns (fn(step)->(rays, seconds), info)."""
+    from oracle import pyoracle
+    from simple_raytracer_b200 import _abi, host
+    ncores = threads or len(os.sched_getaffinity(0)) or (os.cpu_count() or 1)
+    if pyoracle.ref_available():
+        kind = "reference"
+        b, arrays, light = build_frame(pyoracle.RefBackend, cfg, 0, still=True)
+
+        def run(col_begin, col_step, th):
+            r = b.render(W, H, focal, light, N, cfg.use_bvh, faithful=True, threads=th, col_begin=col_begin,
+                         col_step=col_step, ids=False)
+            cols = np.arange(col_begin, W, col_step)
+            hits = int(np.count_nonzero(r["obj_id"][:, cols] >= 0))
+            return r["traced"], hits, r["seconds"]
+    else:
+        kind = "port"
+        b, arrays, light = build_frame(host.HostScene, cfg, 0, still=True)
+        p = _abi.default_params(W, H, focal, light, N, cfg.use_bvh)
+
+        def run(col_begin, col_step, th):
+            r = pyoracle.oracle_render(arrays, p, threads=th, col_begin=col_begin, col_step=col_step)
+            return r["traced"], r["counters"]["hit_pixels"], r["seconds"]
+    n_obj = len(arrays.objects)
+    # calibrate on ~24 columns spread over the frame, all threads
+    cal_step = max(1, W // 24)
+    run(cal_step // 2, cal_step, ncores)              # untimed: first touch of the scene, thread start-up
+    traced, hits, sec = run(cal_step // 2, cal_step, ncores)
+    core_s_per_col = sec * min(ncores, len(range(cal_step // 2, W, cal_step))) / max(1, len(range(cal_step // 2, W, cal_step)))
+    if per_step_wall is not None:
+        want_cols = int(per_step_wall * ncores / max(core_s_per_col, 1e-9))
+    else:
+        want_cols = int(core_seconds / max(core_s_per_col, 1e-9))
+    want_cols = max(min(want_cols, W), min(W, ncores))
+    col_step = max(1, W // want_cols)
+    ncols = len(range(0, W, col_step))
+    sample = (f"{'unmodified reference (oracle/_ref, re-shading on every closer hit like :429-449)' if kind == 'reference' else 'C oracle port'}"
+              f", {ncols} of {W} pixel columns (every {col_step}th) x {H} rows of the frame, {ncores} threads")
+
+    def step(_i):
+        traced, hits, sec = run(0, col_step, ncores)
+        return ray_count(1, traced, N, hits, n_obj), sec, traced   # W*H replaced by the traced pixel count
+
+    return step, dict(kind=kind, cores=ncores, sample=sample)
+
+
+def run_reference_arm(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return 0
+    cfg, W, H, focal, N = frame_setup(args)
+    step, info = cpu_reference_sample(cfg, W, H, focal, N, 0.0, per_step_wall=1.0)
+    for i in range(args.warmup):
+        step(i)
+    rays = 0
+    sec = 0.0
+    pixels = 0
+    for i in range(args.steps):
+        r, s, px = step(i)
+        rays += r; sec += s; pixels += px
+    v = rays / sec / 1e6
+    line = {
+        "impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": 1e3 * sec / max(args.steps, 1), "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": WORKLOAD, "width": W, "height": H, "focal": focal, "lights": N,
+                   "note": "each step is a bounded column sample of the frame; Mrays/s is per-ray so it extrapolates linearly"},
+        "frames_per_s_extrapolated": (pixels / (W * H)) / sec if sec > 0 else None,
+        "cpu_baseline": {"value": v, "unit": UNIT, **info},
+        "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line))
+    return 0
+
+
+# ------------------------------------------------------------------------------------------------
+def run_b200_arm(args):
+    import torch
+    import torch.distributed as dist
+    from simple_raytracer_b200 import _abi, capi, host
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available() or capi.device_count() == 0:
+        raise RuntimeError("bench.py: no CUDA device — the render path has no CPU fallback")
+    torch.cuda.set_device(local)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    dev = torch.device("cuda", local)
+    stream = torch.cuda.current_stream()
+    ctx = capi.Context(local, stream=stream.cuda_stream)
+    info = ctx.info()
+
+    cfg, W, H, focal, N = frame_setup(args)
+    K, Wm = args.steps, args.warmup
+    n_unique = min(K + Wm, 24)                     # distinct series frames kept resident per rank
+
+    # ---- host prep (outside every timed region; reported) ----
+    t_prep0 = time.time()
+    frames = []
+    for s in range(n_unique):
+        f = s * world + rank
+        _b, arrays, light = build_frame(host.HostScene, cfg, f, still=args.still)
+        frames.append((arrays, light))
+        del _b
+    prep_ms = 1e3 * (time.time() - t_prep0) / max(n_unique, 1)
+    scenes_dev = [ctx.upload(a) for (a, _l) in frames]
+    params = []
+    for (_a, light) in frames:
+        p = _abi.default_params(W, H, focal, light, N, cfg.use_bvh)
+        p.variant = args.variant
+        params.append(p)
+    n_obj = len(frames[0][0].objects)
+    scene_bytes = frames[0][0].nbytes()
+
+    rgb = torch.empty((H, W, 3), dtype=torch.uint8, device=dev)
+    flush = torch.empty(L2_FLUSH_BYTES, dtype=torch.uint8, device=dev)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def render_step(s):
+        k = s % n_unique
+        ctx.render_raw(scenes_dev[k], params[k], rgb=rgb.data_ptr())
+
+    hit_cache = {}
+
+    def hits_of(s):
+        k = s % n_unique
+        if k not in hit_cache:
+            render_step(s)
+            hit_cache[k] = ctx.last_stats()["hit_pixels"]
+        return hit_cache[k]
+
+    # ---- device-timed region: scenes resident in HBM ----
+    for s in range(Wm):
+        flush.zero_()
+        render_step(s)
+    rays_local = sum(ray_count(W, H, N, hits_of(Wm + s), n_obj) for s in range(K))
+    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(K)]
+    kernel_ms = []
+    barrier()
+    sampler = ClockSampler(local) if rank == 0 else None
+    t0 = time.time()
+    for s in range(K):
+        flush.zero_()                               # L2 flush between timed iterations (512 MiB > 126 MB L2)
+        ev[s][0].record()
+        render_step(Wm + s)
+        ev[s][1].record()
+    barrier()
+    t1 = time.time()
+    clocks = sampler.stop(t0, t1) if sampler else None
+    step_ms = [a.elapsed_time(b) for a, b in ev]
+    total_ms = float(sum(step_ms))
+    # the render kernel alone (events inside srt_render, same stream) for the roofline
+    for s in range(min(K, 8)):
+        flush.zero_()
+        render_step(Wm + s)
+        kernel_ms.append(ctx.last_stats()["kernel_ms"])
+    kern_ms = float(np.mean(kernel_ms)) if kernel_ms else float("nan")
+
+    # ---- end to end through the C ABI from pinned host buffers ----
+    e2e = None
+    if not args.no_e2e:
+        pinned = []
+        for (a, _l) in frames:
+            keep = {}
+            for name in ("nodes", "geom", "attr", "objects"):
+                src = getattr(a, name)
+                pa = capi.PinnedArray(src.shape, src.dtype)
+                pa.array[...] = src
+                keep[name] = pa
+            pinned.append((_abi.FlatSceneArrays(keep["nodes"].array, keep["geom"].array, keep["attr"].array,
+                                                keep["objects"].array, a.textures), keep))
+        sc = ctx.upload(pinned[0][0])
+        host_rgb = torch.empty((world if rank == 0 else 1, H, W, 3), dtype=torch.uint8).pin_memory()
+        gathered = [torch.empty_like(rgb) for _ in range(world)] if (rank == 0 and world > 1) else None
+        h2d = sum(getattr(pinned[0][0], n).nbytes for n in ("nodes", "geom", "attr", "objects"))
+        d2h = host_rgb.numel() if rank == 0 else 0
+
+        def e2e_step(s):
+            k = s % n_unique
+            sc.update(pinned[k][0])                                  # H2D of this frame's scene (async, pinned)
+            ctx.render_raw(sc, params[k], rgb=rgb.data_ptr())        # the render kernel
+            if world > 1:
+                dist.gather(rgb, gathered, dst=0)                    # framebuffers -> rank 0 over NVLink (NCCL)
+                if rank == 0:
+                    for r in range(world):
+                        host_rgb[r].copy_(gathered[r], non_blocking=True)
+            else:
+                host_rgb[0].copy_(rgb, non_blocking=True)            # D2H of the finished frame
+
+        for s in range(Wm):
+            flush.zero_()
+            e2e_step(s)
+        ev2 = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(K)]
+        barrier()
+        for s in range(K):
+            flush.zero_()
+            ev2[s][0].record()
+            e2e_step(Wm + s)
+            ev2[s][1].record()
+        barrier()
+        e2e_ms = float(sum(a.elapsed_time(b) for a, b in ev2))
+        e2e = (e2e_ms, h2d, d2h)
+        sc.destroy()
+
+    # ---- max over ranks, totals ----
+    agg = torch.tensor([total_ms, e2e[0] if e2e else 0.0, kern_ms, prep_ms], dtype=torch.float64, device=dev)
+    tot = torch.tensor([float(rays_local)], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(agg, op=dist.ReduceOp.MAX)
+        dist.all_reduce(tot, op=dist.ReduceOp.SUM)
+    total_ms, e2e_ms, kern_ms_max, prep_ms_max = [float(x) for x in agg.tolist()]
+    rays_total = float(tot.item())
+
+    line = None
+    if rank == 0:
+        value = rays_total / (total_ms * 1e-3) / 1e6
+        peaks = {}
+        try:
+            peaks = json.loads((REPO / "MEASURED_PEAKS.json").read_text())
+        except Exception:
+            pass
+        hbm_peak = float(peaks.get("hbm_gbs", 6650.0))
+        # algorithmic HBM bytes of one launch: one read of the scene + one write of the RGB8 frame
+        alg_bytes = scene_bytes + W * H * 3
+        ach = alg_bytes / (kern_ms * 1e-3) / 1e9
+        line = {
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": K, "warmup": Wm,
+            "ms_per_step": total_ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "f32", "data": "synthetic",
+            "config": {"workload": WORKLOAD if args.config == "C3" and not args.still else f"{cfg.key}: {cfg.description}",
+                       "width": W, "height": H, "focal": focal, "lights": N, "triangles": int(len(frames[0][0].geom)),
+                       "bvh_nodes": int(len(frames[0][0].nodes)), "parallelism": f"frame-sharded x{world}",
+                       "l2": "flushed between timed iterations (512 MiB device memset)", "variant": args.variant,
+                       "sm_count": info["sm_count"]},
+            "frames_per_s": world * K / (total_ms * 1e-3),
+            "rays_per_frame": rays_total / (K * world),
+            "kernel_ms": kern_ms,
+            "host_prep_ms_per_frame": prep_ms_max,
+            "gpu_launches": K * world,
+            "clocks": clocks,
+            "roofline": {"bound": "hbm", "achieved": ach, "peak": hbm_peak, "unit": "GB/s", "frac": ach / hbm_peak,
+                         "traffic": None, "peak_source": "measured (MEASURED_PEAKS.json)" if peaks else "fallback",
+                         "note": "scene is L2-resident by design: compulsory HBM bytes = one scene read + one RGB8 frame write; "
+                                 "the kernel is latency/issue-bound, see DESIGN.md and profiles/"},
+        }
+        if e2e:
+            line["e2e"] = {"value": rays_total / (e2e_ms * 1e-3) / 1e6, "unit": UNIT, "h2d_bytes_per_step": int(e2e[1]),
+                           "d2h_bytes_per_step": int(e2e[2]), "ms_per_step": e2e_ms / K,
+                           "frames_per_s": world * K / (e2e_ms * 1e-3),
+                           "what": "srt_scene_update from pinned host arrays + srt_render + NCCL gather to rank 0 + D2H of the RGB8 frames"}
+        if world == 1 and not args.no_cpu_baseline:
+            try:
+                step, cinfo = cpu_reference_sample(cfg, W, H, focal, N, args.cpu_seconds)
+                r, s, _px = step(0)
+                line["cpu_baseline"] = {"value": r / s / 1e6, "unit": UNIT, **cinfo, "seconds": s}
+            except Exception as e:      # the CPU baseline is reporting, never the product path
+                line["cpu_baseline"] = {"value": None, "unit": UNIT, "cores": 0, "kind": "port", "sample": f"failed: {e}"}
+        print(json.dumps(line))
+    for s_ in scenes_dev:
+        s_.destroy()
+    ctx.destroy()
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+    return 0
+
+
+def main():
+    args = parse_args()
+    if args.impl == "reference":
+        return run_reference_arm(args)
+    return run_b200_arm(args)
+
+
+if __name__ == "__main__":
+    sys.exit(main())
