@@ -159,7 +159,7 @@ __device__ __forceinline__ void store_pixel(const KArgs& a, int px, int py, bool
     if (a.t) a.t[at] = h.t;
 }
 
-template <bool COUNT>
+template <bool COUNT, bool TIMELINE = false>
 __global__ void __launch_bounds__(128) render_simple(const __grid_constant__ KArgs a) {
     const unsigned lane = threadIdx.x & 31;
     const int n_tiles = a.tiles_x * a.tiles_y;
@@ -172,6 +172,8 @@ __global__ void __launch_bounds__(128) render_simple(const __grid_constant__ KAr
         if ((int)tile >= n_tiles) break;
         const int tx = (int)(tile % (unsigned)a.tiles_x), ty = (int)(tile / (unsigned)a.tiles_x);
         const int px = tx * kTileW + (int)(lane & 7), py = a.row_begin + ty * kTileH + (int)(lane >> 3);
+        long long tl_c0 = 0; unsigned long long tl_ns = 0;
+        if (TIMELINE) { tl_c0 = clock64(); asm volatile("mov.u64 %0, %globaltimer;" : "=l"(tl_ns)); }
         if (px >= a.width || py >= a.row_end) continue;
         // ray.direction = (i, j, focal), i = px + i0, j = py + j0            :511-515 (S1)
         const V3 o = v3(0.f, 0.f, 0.f);
@@ -202,6 +204,15 @@ __global__ void __launch_bounds__(128) render_simple(const __grid_constant__ KAr
             }
         }
         store_pixel(a, px, py, hit, color, h);
+        if (TIMELINE) {   // debugging aid: per-tile cost map instead of the id / t planes
+            __syncwarp();
+            const long long dc = clock64() - tl_c0;
+            unsigned smid; asm volatile("mov.u32 %0, %smid;" : "=r"(smid));
+            const size_t at = (size_t)py * a.width + px;
+            if (a.t) a.t[at] = (float)dc;
+            if (a.obj_id) a.obj_id[at] = (int32_t)smid;
+            if (a.tri_id) a.tri_id[at] = (int32_t)(tl_ns & 0x7fffffffull);
+        }
     }
     // one atomic per warp for the statistics
     for (int s = 16; s > 0; s >>= 1) {
@@ -224,6 +235,7 @@ cudaError_t launch_render(const KArgs& a, int variant, int sm_count, cudaStream_
     const int need = (n_tiles + warps_per_block - 1) / warps_per_block;
     if (blocks > need) blocks = need;
     if (variant == 100) render_simple<true><<<blocks, 128, 0, stream>>>(a);      // instrumented (node / triangle counts)
+    else if (variant == 101) render_simple<false, true><<<blocks, 128, 0, stream>>>(a);   // per-tile timeline in the id / t planes
     else render_simple<false><<<blocks, 128, 0, stream>>>(a);
     return cudaGetLastError();
 }

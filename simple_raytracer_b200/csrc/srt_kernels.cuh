@@ -13,7 +13,8 @@ struct TexDev {
 };
 
 // Slots of the per-context device counter block.
-enum { CNT_TILE = 0, CNT_HIT = 1, CNT_NODE = 2, CNT_TRI = 3, CNT_WORDS = 8 };
+enum { CNT_TILE = 0, CNT_HIT = 1, CNT_NODE = 2, CNT_TRI = 3, CNT_LIST = 4, CNT_SHADOW = 5, CNT_SHADE = 6,
+       CNT_EXACT = 7, CNT_WORDS = 8 };
 
 // Everything one frame needs, passed by value as a __grid_constant__ kernel parameter.
 struct KArgs {
@@ -41,6 +42,16 @@ struct KArgs {
     float* t;
     unsigned long long* counters;   // CNT_* slots, zeroed before launch
     float lights[3 * SRT_MAX_LIGHTS];   // staircase positions, softShadow :363-383
+    // ---- phased kernel only (device-internal data built at upload, scratch owned by the context) ----
+    const float4* wide;         // per interior node i: the two child boxes + child refs, 4 x float4 at wide[4*i]
+    const uint32_t* root_ref;   // per object: traversal ref of its root
+    float* hit_t;               // [height][width] scratch: closest-hit parameter
+    int32_t* hit_tri;           // [height][width] scratch: closest-hit triangle (leaf order) or -1
+    uint32_t* tile_interest;    // [tiles] lanes whose shadow rays can reach another object's root box
+    uint32_t* tile_list;        // compacted list of tiles with tile_interest != 0
+    uint32_t* shadow_mask;      // [tiles][light_count] ballot of occluded lanes
+    float coord_bound;          // max |coordinate| over all root boxes (margin of the filtered slab test)
+    int32_t stack_cap;          // per-thread traversal stack entries (shared memory)
 };
 
 constexpr int kTileW = 8, kTileH = 4;          // one warp = 8x4 pixels
@@ -48,5 +59,16 @@ constexpr int kMaxStack = 64;                  // >= deepest BVH the upload acce
 
 // variant: SRT_VARIANT_*; returns cudaError_t from the launch.
 cudaError_t launch_render(const KArgs& a, int variant, int sm_count, cudaStream_t stream);
+
+// ---- phased kernel (srt_phased.cu) ----
+constexpr uint32_t kRefNone = 0x7FFFFFFFu;      // traversal refs: < kRefNone interior node index; bit 31 = leaf
+constexpr uint32_t kLeafMaxCount = 15, kLeafFirstBits = 27;
+// Builds wide[] / root_ref[] from nodes[] / objects[] on the device (after every scene upload).
+cudaError_t launch_build_wide(const float4* nodes, const srt_object* objects, uint32_t n_nodes, uint32_t n_objects,
+                              float4* wide, uint32_t* root_ref, cudaStream_t stream);
+// Shared memory the phased kernel needs per CTA for `stack_cap`, and whether it fits.
+size_t phased_smem_bytes(int stack_cap);
+// Single cooperative launch (variant SRT_VARIANT_DEFAULT) or three launches (SRT_VARIANT_SPLIT).
+cudaError_t launch_render_phased(const KArgs& a, int variant, int sm_count, cudaStream_t stream, int* launches);
 
 }  // namespace srtk
