@@ -137,7 +137,11 @@ typedef struct srt_render_params {
     int32_t reserved[3];
 } srt_render_params;
 
-enum { SRT_VARIANT_DEFAULT = 0, SRT_VARIANT_SIMPLE = 1, SRT_VARIANT_PACKET = 2 };
+enum { SRT_VARIANT_DEFAULT = 0,   /* phased persistent kernel (falls back to SIMPLE for the legacy one-box path) */
+       SRT_VARIANT_SIMPLE = 1,    /* one thread = one pixel, whole pixel per work item */
+       SRT_VARIANT_SPLIT = 3,     /* the phased kernel as three launches (profiling) */
+       SRT_VARIANT_COUNT = 100,   /* SIMPLE + node / triangle counters */
+       SRT_VARIANT_TIMELINE = 101 /* SIMPLE + per-tile cost map in the id / t planes (debug) */ };
 
 /* Output planes; each pointer may be NULL (plane not wanted), a DEVICE pointer (written in place
  * on the context stream, no copy) or a HOST pointer (rendered to an internal device buffer and
@@ -156,8 +160,9 @@ typedef struct srt_stats {
     uint64_t shadow_rays;         /* light_count*hit_pixels if the scene has >= 2 objects else 0 */
     uint64_t node_visits;         /* only counted by the instrumented variant, else 0 */
     uint64_t tri_tests;
-    float    kernel_ms;           /* CUDA-event time of the render kernel */
-    float    pad;
+    uint64_t exact_slab_tests;    /* phased kernel: slab tests the filter could not decide (ran the exact divisions) */
+    float    kernel_ms;           /* CUDA-event time of the render kernel(s) */
+    int32_t  kernel_launches;     /* kernels launched by the last srt_render (1, or 3 for SRT_VARIANT_SPLIT) */
 } srt_stats;
 
 typedef struct srt_context srt_context;

@@ -23,7 +23,9 @@ SRT_ERR_UNSUPPORTED = -6
 
 VARIANT_DEFAULT = 0
 VARIANT_SIMPLE = 1
-VARIANT_PACKET = 2
+VARIANT_SPLIT = 3
+VARIANT_COUNT = 100
+VARIANT_TIMELINE = 101
 
 # numpy record layouts of the flattened scene (include/srt.h)
 NODE_DTYPE = np.dtype([("bmin", "<f4", 3), ("a", "<u4"), ("bmax", "<f4", 3), ("b", "<u4")])
@@ -69,7 +71,8 @@ class Frame(C.Structure):
 class Stats(C.Structure):
     _fields_ = [
         ("primary_rays", C.c_uint64), ("hit_pixels", C.c_uint64), ("shadow_rays", C.c_uint64),
-        ("node_visits", C.c_uint64), ("tri_tests", C.c_uint64), ("kernel_ms", C.c_float), ("pad", C.c_float),
+        ("node_visits", C.c_uint64), ("tri_tests", C.c_uint64), ("exact_slab_tests", C.c_uint64),
+        ("kernel_ms", C.c_float), ("kernel_launches", C.c_int32),
     ]
 
 

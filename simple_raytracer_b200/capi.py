@@ -180,7 +180,8 @@ class Context:
         s = _abi.Stats()
         _check(lib().srt_last_stats(self.h, C.byref(s)))
         return dict(primary_rays=int(s.primary_rays), hit_pixels=int(s.hit_pixels), shadow_rays=int(s.shadow_rays),
-                    node_visits=int(s.node_visits), tri_tests=int(s.tri_tests), kernel_ms=float(s.kernel_ms))
+                    node_visits=int(s.node_visits), tri_tests=int(s.tri_tests), exact_slab_tests=int(s.exact_slab_tests),
+                    kernel_ms=float(s.kernel_ms), kernel_launches=int(s.kernel_launches))
 
     def destroy(self):
         if self.h:

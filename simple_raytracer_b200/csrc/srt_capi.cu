@@ -70,6 +70,8 @@ struct srt_context {
     unsigned long long* counters_host = nullptr; // pinned
     cudaEvent_t ev0 = nullptr, ev1 = nullptr, ev_copy = nullptr;
     DevBuf out_rgb, out_obj, out_tri, out_t;     // staging for HOST output pointers
+    DevBuf hit_t, hit_tri, tile_interest, tile_list, shadow_mask;   // scratch of the phased kernel
+    int last_launches = 0;
     // last render
     bool have_last = false;
     uint64_t last_primary = 0;
@@ -80,6 +82,9 @@ struct srt_context {
 struct srt_scene {
     srt_context* ctx = nullptr;
     DevBuf nodes, geom, attr, flat_geom, flat_attr, objects, texdesc;
+    DevBuf wide, root_ref;                        // device-internal traversal layout (srt_phased.cu)
+    bool phased_ok = false;                       // leaf sizes / index ranges fit the packed traversal refs
+    float coord_bound = 0.f;                      // max |coordinate| over the root boxes
     std::vector<DevBuf> tex;
     std::vector<srtk::TexDev> tex_host;
     uint64_t n_nodes = 0, n_tris = 0, n_flat = 0;
@@ -139,6 +144,7 @@ void srt_context_destroy(srt_context* c) {
     cudaSetDevice(c->device);
     cudaStreamSynchronize(c->stream);
     c->out_rgb.release(); c->out_obj.release(); c->out_tri.release(); c->out_t.release();
+    c->hit_t.release(); c->hit_tri.release(); c->tile_interest.release(); c->tile_list.release(); c->shadow_mask.release();
     if (c->counters) cudaFree(c->counters);
     if (c->counters_host) cudaFreeHost(c->counters_host);
     if (c->ev0) cudaEventDestroy(c->ev0);
@@ -231,7 +237,8 @@ int srt_sync(srt_context* c) {
 namespace {
 
 // Rejects what would make the kernel (or the reference) read out of bounds.
-int validate_scene(const srt_scene_desc* d, uint32_t* max_depth_out) {
+int validate_scene(const srt_scene_desc* d, uint32_t* max_depth_out, uint32_t* max_leaf_out = nullptr) {
+    if (max_leaf_out) *max_leaf_out = 0;
     if (!d) return fail(SRT_ERR_INVALID_ARG, "scene desc is NULL");
     if (d->n_objects == 0) { *max_depth_out = 0; return SRT_OK; }
     if (!d->objects) return fail(SRT_ERR_INVALID_ARG, "objects is NULL");
@@ -264,6 +271,7 @@ int validate_scene(const srt_scene_desc* d, uint32_t* max_depth_out) {
             if (n.b & SRT_LEAF_BIT) {
                 const uint32_t cnt = n.b & ~SRT_LEAF_BIT;
                 if ((uint64_t)n.a + cnt > d->n_tris) return fail(SRT_ERR_SCENE, "node %u: leaf triangle range out of bounds", ni);
+                if (max_leaf_out && cnt > *max_leaf_out) *max_leaf_out = cnt;
             } else {
                 if (ni + 1 >= d->n_nodes || n.a <= ni + 1 || n.a >= d->n_nodes)
                     return fail(SRT_ERR_SCENE, "node %u: child index out of range", ni);
@@ -301,8 +309,8 @@ int copy_in(srt_context* c, DevBuf& dst, const void* src, size_t bytes) {
 }
 
 int fill_scene(srt_context* c, srt_scene* s, const srt_scene_desc* d, bool textures_too) {
-    uint32_t depth = 0;
-    int rc = validate_scene(d, &depth);
+    uint32_t depth = 0, max_leaf = 0;
+    int rc = validate_scene(d, &depth, &max_leaf);
     if (rc) return rc;
     CU(cudaSetDevice(c->device));
     if ((rc = copy_in(c, s->nodes, d->nodes, d->n_nodes * sizeof(srt_node)))) return rc;
@@ -313,6 +321,24 @@ int fill_scene(srt_context* c, srt_scene* s, const srt_scene_desc* d, bool textu
     if ((rc = copy_in(c, s->objects, d->objects, d->n_objects * sizeof(srt_object)))) return rc;
     s->n_nodes = d->n_nodes; s->n_tris = d->n_tris; s->n_flat = d->n_flat; s->n_objects = d->n_objects;
     s->max_depth = depth;
+    // device-internal traversal layout of the phased kernel: child boxes side by side, packed refs
+    s->phased_ok = d->n_objects > 0 && max_leaf <= srtk::kLeafMaxCount && d->n_tris < (1ull << srtk::kLeafFirstBits) &&
+                   d->n_nodes < 0x40000000ull;
+    s->coord_bound = 0.f;
+    for (uint32_t o = 0; o < d->n_objects; ++o) {
+        const srt_node& rn = d->nodes[d->objects[o].root];
+        for (int k = 0; k < 3; ++k) {
+            s->coord_bound = std::fmax(s->coord_bound, std::fabs(rn.bmin[k]));
+            s->coord_bound = std::fmax(s->coord_bound, std::fabs(rn.bmax[k]));
+        }
+    }
+    if (s->phased_ok) {
+        if ((rc = s->wide.reserve(d->n_nodes * 64))) return rc;
+        if ((rc = s->root_ref.reserve(d->n_objects * sizeof(uint32_t)))) return rc;
+        cudaError_t e = srtk::launch_build_wide((const float4*)s->nodes.p, (const srt_object*)s->objects.p, (uint32_t)d->n_nodes,
+                                                d->n_objects, (float4*)s->wide.p, (uint32_t*)s->root_ref.p, c->stream);
+        if (e != cudaSuccess) return fail(SRT_ERR_CUDA, "build_wide launch: %s", cudaGetErrorString(e));
+    }
     if (textures_too) {
         for (auto& t : s->tex) t.release();
         s->tex.assign(d->n_textures, DevBuf());
@@ -362,7 +388,7 @@ void srt_scene_destroy(srt_scene* s) {
     if (!s) return;
     if (s->ctx) { cudaSetDevice(s->ctx->device); cudaStreamSynchronize(s->ctx->stream); }
     s->nodes.release(); s->geom.release(); s->attr.release(); s->flat_geom.release(); s->flat_attr.release();
-    s->objects.release(); s->texdesc.release();
+    s->objects.release(); s->texdesc.release(); s->wide.release(); s->root_ref.release();
     for (auto& t : s->tex) t.release();
     delete s;
 }
@@ -436,7 +462,29 @@ int srt_render(srt_context* c, const srt_scene* s, const srt_render_params* p, c
     if (s->n_objects == 0 || a.tiles_x * a.tiles_y == 0) {
         // nothing to intersect: still an image (all sky) — run the kernel with zero objects
     }
-    cudaError_t e = srtk::launch_render(a, p->variant, c->sm_count, c->stream);
+    // kernel selection: the phased kernel unless the scene / request needs the simple one
+    a.stack_cap = (int)(s->max_depth + s->n_objects + 2);
+    const bool want_phased = (p->variant == SRT_VARIANT_DEFAULT || p->variant == SRT_VARIANT_SPLIT) && p->use_bvh &&
+                             s->phased_ok && srtk::phased_smem_bytes(a.stack_cap) <= 96 * 1024;
+    cudaError_t e;
+    if (want_phased) {
+        const size_t n_tiles = (size_t)a.tiles_x * a.tiles_y;
+        if ((rc = c->hit_t.reserve(npix * 4))) return rc;
+        if ((rc = c->hit_tri.reserve(npix * 4))) return rc;
+        if ((rc = c->tile_interest.reserve(n_tiles * 4))) return rc;
+        if ((rc = c->tile_list.reserve(n_tiles * 4))) return rc;
+        if ((rc = c->shadow_mask.reserve(n_tiles * 4 * (size_t)(p->light_count > 0 ? p->light_count : 1)))) return rc;
+        a.wide = (const float4*)s->wide.p;
+        a.root_ref = (const uint32_t*)s->root_ref.p;
+        a.hit_t = (float*)c->hit_t.p; a.hit_tri = (int32_t*)c->hit_tri.p;
+        a.tile_interest = (uint32_t*)c->tile_interest.p; a.tile_list = (uint32_t*)c->tile_list.p;
+        a.shadow_mask = (uint32_t*)c->shadow_mask.p;
+        a.coord_bound = s->coord_bound;
+        e = srtk::launch_render_phased(a, p->variant, c->sm_count, c->stream, &c->last_launches);
+    } else {
+        e = srtk::launch_render(a, p->variant, c->sm_count, c->stream);
+        c->last_launches = 1;
+    }
     if (e != cudaSuccess) return fail(SRT_ERR_CUDA, "render kernel launch: %s", cudaGetErrorString(e));
     CU(cudaEventRecord(c->ev1, c->stream));
     CU(cudaMemcpyAsync(c->counters_host, c->counters, sizeof(unsigned long long) * srtk::CNT_WORDS,
@@ -467,6 +515,8 @@ int srt_last_stats(srt_context* c, srt_stats* out) {
     out->shadow_rays = c->last_objects >= 2 ? (uint64_t)c->last_lights * out->hit_pixels : 0;
     out->node_visits = c->counters_host[srtk::CNT_NODE];
     out->tri_tests = c->counters_host[srtk::CNT_TRI];
+    out->exact_slab_tests = c->counters_host[srtk::CNT_EXACT];
+    out->kernel_launches = c->last_launches;
     float ms = 0.f;
     CU(cudaEventElapsedTime(&ms, c->ev0, c->ev1));
     out->kernel_ms = ms;

@@ -1,0 +1,439 @@
+// srt_phased.cu — the production render kernel (sm_100a): one persistent cooperative grid, three
+// phases separated by grid barriers.  See DESIGN.md §Kernels.
+//
+//   P  primary   work item = 8x4 pixel tile (one warp, lane = pixel): primary ray (:505-517), closest hit
+//                over every object's BVH (:405-431, :296-317, :42-75) -> hit record (t, triangle) in
+//                scratch; then, with the hit still in registers, the root-box test of each of the N
+//                shadow rays against every OTHER object (:321-328): lanes none of whose shadow rays
+//                can enter another object's hierarchy are finished (never occluded); tiles that have
+//                interested lanes are appended to a compact list.
+//   S  shadow    work item = (listed tile, light), light-major: any-hit traversal (:321-342) of the
+//                other objects; result = one ballot word per (tile, light).  Items are 1/N of a
+//                tile's shadow work, so the heaviest tile no longer dictates the kernel's tail
+//                (profiles/r01_simple_ncu_summary.txt: 40 % of SM cycles idle with whole-pixel items).
+//   C  shade     work item = tile: base colour / texture (:350-361, :437-443), N x Phong (:144-200)
+//                with the /5 of occluded lights (:369), tone map, gamma, quantise, sky (:391-398,
+//                :447-449, :476-487).
+//
+// Arithmetic: everything that reaches an output (Moeller-Trumbore, hit point, Phong, tone map) is the
+// exact operation sequence of srt_device.cuh.  The slab test is evaluated with a FILTER: an
+// approximate test (one FFMA per plane with a per-ray reciprocal) whose rounding error is bounded;
+// when the approximate near/far values are further apart than the bound, the exact test
+// (true divisions, reference compare order, :252-293) provably gives the same answer; otherwise —
+// and for every ray with a zero / denormal / non-finite direction component — the exact test is run.
+// The set of leaves visited is therefore exactly the reference's (S3/S5), only cheaper.
+// Closest hit uses the order-independent rule min over (t, visit index) (S6), so traversal order is free.
+#include <cooperative_groups.h>
+
+#include "srt_kernels.cuh"
+#include "srt_device.cuh"
+#include "srt_shade.cuh"
+
+namespace cg = cooperative_groups;
+
+namespace srtk {
+using namespace srtd;
+
+namespace {
+
+constexpr int kThreads = 128;
+constexpr unsigned kFull = 0xffffffffu;
+
+// ---------------------------------------------------------------------------------------------
+// Filtered slab test.
+//
+// Reference value per plane: t* = RN(RN(b - o) / d).  Filter value: t~ = RN(b*i + n) with
+// i = rcp.approx(d) (|rel err| <= 2^-22) and n = RN(-o*i).  With q = (b-o)/d:
+//   |t* - q| <= 2*2^-24 |q|,   |t~ - q| <= 1.5*2^-22 |q| + 2^-24 |n|   (plus 2^-149 absolute)
+// so |t~ - t*| <= 2^-24 (8.1 |q| + |n|).  Every |q| of a ray is <= A = max_axis(B*|i| + |n|) (1 + 2^-20),
+// B = largest |coordinate| of any box.  The reference's decision is  max(near*) <= min(far*)
+// (its swap / merge / compare sequence reduces to that when no NaN is involved; NaN needs 0/0 or
+// inf-inf, which only rays with a zero or non-finite component produce — those are `degenerate`).
+// Hence with  m = 2^-24 (20 A + 3 max|n|) + 1e-37 :  far~ - near~ >= m  => reference says HIT,
+// far~ - near~ < -m => reference says MISS; in between the exact test decides.
+struct FRay {
+    V3 o, d;          // the exact ray (reference values)
+    float ix, iy, iz; // approximate reciprocals
+    float nx, ny, nz; // -o * i
+    float m;          // decision margin
+    bool degenerate;  // exact test always
+};
+
+__device__ __forceinline__ float rcp_approx(float x) {
+    float r;
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+    return r;
+}
+
+__device__ __forceinline__ FRay make_fray(V3 o, V3 d, float coord_bound) {
+    FRay r;
+    r.o = o; r.d = d;
+    r.ix = rcp_approx(d.x); r.iy = rcp_approx(d.y); r.iz = rcp_approx(d.z);
+    r.nx = -(o.x * r.ix); r.ny = -(o.y * r.iy); r.nz = -(o.z * r.iz);
+    const float ax = fabsf(r.ix), ay = fabsf(r.iy), az = fabsf(r.iz);
+    const float bx = fabsf(r.nx), by = fabsf(r.ny), bz = fabsf(r.nz);
+    const float A = fmaxf(fmaxf(fmaf(coord_bound, ax, bx), fmaf(coord_bound, ay, by)), fmaf(coord_bound, az, bz));
+    const float nmax = fmaxf(fmaxf(bx, by), bz);
+    r.m = fmaf(A, 20.0f * 5.9604645e-8f, fmaf(nmax, 3.0f * 5.9604645e-8f, 1e-37f));
+    // zero / denormal / huge direction components, or anything that made the margin non-finite
+    const float lo = 1e-30f, hi = 1e30f;
+    r.degenerate = !(ax > lo && ax < hi && ay > lo && ay < hi && az > lo && az < hi && r.m < 1e30f);
+    return r;
+}
+
+// Returns the reference's decision for this box.  `tn_out` = approximate entry parameter (ordering only).
+__device__ __forceinline__ bool slab_filtered(const FRay& r, float lox, float loy, float loz, float hix, float hiy,
+                                              float hiz, float& tn_out, float& tf_out, unsigned& exact_count) {
+    const float x0 = fmaf(lox, r.ix, r.nx), x1 = fmaf(hix, r.ix, r.nx);
+    const float y0 = fmaf(loy, r.iy, r.ny), y1 = fmaf(hiy, r.iy, r.ny);
+    const float z0 = fmaf(loz, r.iz, r.nz), z1 = fmaf(hiz, r.iz, r.nz);
+    const float tn = fmaxf(fmaxf(fminf(x0, x1), fminf(y0, y1)), fminf(z0, z1));
+    const float tf = fminf(fminf(fmaxf(x0, x1), fmaxf(y0, y1)), fmaxf(z0, z1));
+    tn_out = tn; tf_out = tf;
+    const float diff = tf - tn;
+    if (!r.degenerate) {
+        if (diff >= r.m) return true;
+        if (diff < -r.m) return false;
+    }
+    ++exact_count;
+    return slab_exact(r.o, r.d, make_float4(lox, loy, loz, 0.f), make_float4(hix, hiy, hiz, 0.f));
+}
+
+// ---------------------------------------------------------------------------------------------
+// Traversal stack: per thread, in shared memory, one column per thread (bank = tid % 32).
+struct Stack {
+    uint32_t* base;   // &smem[threadIdx.x]
+    int sp;
+    __device__ __forceinline__ void push(uint32_t v) { base[sp * kThreads] = v; ++sp; }
+    __device__ __forceinline__ uint32_t pop() { if (sp == 0) return kRefNone; --sp; return base[sp * kThreads]; }
+};
+
+__device__ __forceinline__ bool is_interior(uint32_t ref) { return ref < kRefNone; }
+__device__ __forceinline__ bool is_leaf(uint32_t ref) { return (ref >> 31) != 0u; }
+__device__ __forceinline__ uint32_t leaf_first(uint32_t ref) { return ref & ((1u << kLeafFirstBits) - 1u); }
+__device__ __forceinline__ uint32_t leaf_count(uint32_t ref) { return (ref >> kLeafFirstBits) & 15u; }
+
+// Closest hit over everything on the stack (refs of nodes whose own box already passed).
+// While-while: every lane descends until it holds a leaf (or nothing), then the warp intersects.
+__device__ __forceinline__ void trace_closest(const KArgs& a, const FRay& r, Stack& st, Hit& h, unsigned& exact_count) {
+    uint32_t ref = st.pop();
+    while (ref != kRefNone) {
+        while (is_interior(ref)) {
+            const float4* w = a.wide + 4 * (size_t)ref;
+            const float4 w0 = ldg4(w), w1 = ldg4(w + 1), w2 = ldg4(w + 2), w3 = ldg4(w + 3);
+            float tnl, tfl, tnr, tfr;
+            const bool hl = slab_filtered(r, w0.x, w0.y, w0.z, w0.w, w1.x, w1.y, tnl, tfl, exact_count);
+            const bool hr = slab_filtered(r, w1.z, w1.w, w2.x, w2.y, w2.z, w2.w, tnr, tfr, exact_count);
+            const uint32_t rl = __float_as_uint(w3.x), rr = __float_as_uint(w3.y);
+            if (hl) { if (hr) st.push(rr); ref = rl; }
+            else if (hr) ref = rr;
+            else ref = st.pop();
+        }
+        if (is_leaf(ref)) {
+            const uint32_t first = leaf_first(ref), cnt = leaf_count(ref);
+            for (uint32_t k = 0; k < cnt; ++k) {
+                const float4* g = a.geom + 3 * (size_t)(first + k);
+                const float t = moller_trumbore(r.o, r.d, ldg4(g), ldg4(g + 1), ldg4(g + 2));
+                const int32_t idx = (int32_t)(first + k);
+                // S6: first visited wins ties == smallest visit index wins ties
+                if (t != -INFINITY && (t < h.t || (t == h.t && idx < h.tri))) { h.t = t; h.tri = idx; }
+            }
+            ref = st.pop();
+        }
+    }
+}
+
+// Any hit (shadowIntersection :321-342): true as soon as one candidate triangle reports t >= 0.
+// Order is free for a boolean; children are visited nearest-entry-first, boxes wholly behind the
+// origin last, so occluded rays usually stop after a few leaves.
+__device__ __forceinline__ bool trace_any(const KArgs& a, const FRay& r, Stack& st, unsigned& exact_count) {
+    uint32_t ref = st.pop();
+    while (ref != kRefNone) {
+        while (is_interior(ref)) {
+            const float4* w = a.wide + 4 * (size_t)ref;
+            const float4 w0 = ldg4(w), w1 = ldg4(w + 1), w2 = ldg4(w + 2), w3 = ldg4(w + 3);
+            float tnl, tfl, tnr, tfr;
+            const bool hl = slab_filtered(r, w0.x, w0.y, w0.z, w0.w, w1.x, w1.y, tnl, tfl, exact_count);
+            const bool hr = slab_filtered(r, w1.z, w1.w, w2.x, w2.y, w2.z, w2.w, tnr, tfr, exact_count);
+            const uint32_t rl = __float_as_uint(w3.x), rr = __float_as_uint(w3.y);
+            if (hl && hr) {
+                const float kl = tfl < 0.f ? 3.0e38f : fmaxf(tnl, 0.f);
+                const float kr = tfr < 0.f ? 3.0e38f : fmaxf(tnr, 0.f);
+                if (kr < kl) { st.push(rl); ref = rr; } else { st.push(rr); ref = rl; }
+            } else if (hl) ref = rl;
+            else if (hr) ref = rr;
+            else ref = st.pop();
+        }
+        if (is_leaf(ref)) {
+            const uint32_t first = leaf_first(ref), cnt = leaf_count(ref);
+            bool found = false;
+            for (uint32_t k = 0; k < cnt; ++k) {
+                const float4* g = a.geom + 3 * (size_t)(first + k);
+                if (moller_trumbore(r.o, r.d, ldg4(g), ldg4(g + 1), ldg4(g + 2)) != -INFINITY) found = true;
+            }
+            if (found) return true;
+            ref = st.pop();
+        }
+    }
+    return false;
+}
+
+// ---------------------------------------------------------------------------------------------
+// Work distribution: one warp = one item, pulled from a global counter.
+__device__ __forceinline__ unsigned next_item(unsigned long long* counter, unsigned lane) {
+    unsigned v = 0;
+    if (lane == 0) v = (unsigned)atomicAdd(counter, 1ull);
+    return __shfl_sync(kFull, v, 0);
+}
+
+struct Pixel { int px, py; bool valid; };
+
+__device__ __forceinline__ Pixel pixel_of(const KArgs& a, unsigned tile, unsigned lane) {
+    const int tx = (int)(tile % (unsigned)a.tiles_x), ty = (int)(tile / (unsigned)a.tiles_x);
+    Pixel p;
+    p.px = tx * kTileW + (int)(lane & 7);
+    p.py = a.row_begin + ty * kTileH + (int)(lane >> 3);
+    p.valid = p.px < a.width && p.py < a.row_end;
+    return p;
+}
+
+// ray.direction = (i, j, focal), i = px + i0, j = py + j0            :511-515 (S1)
+__device__ __forceinline__ V3 primary_dir(const KArgs& a, const Pixel& p) {
+    return v3((float)(p.px + a.i0), (float)(p.py + a.j0), a.focal);
+}
+
+// Root-box tests of one ray against the objects (all, or all but `skip`); passing roots are pushed
+// in reverse so object 0 is traversed first.  Returns true if anything was pushed.
+__device__ __forceinline__ bool push_roots(const KArgs& a, const FRay& r, Stack& st, int32_t skip, unsigned& exact_count) {
+    bool any = false;
+    for (int ob = (int)a.n_objects - 1; ob >= 0; --ob) {
+        if (ob == skip) continue;                                             // :331
+        const float4* n = a.nodes + 2 * (size_t)a.objects[ob].root;
+        const float4 n0 = ldg4(n), n1 = ldg4(n + 1);
+        float tn, tf;
+        if (slab_filtered(r, n0.x, n0.y, n0.z, n1.x, n1.y, n1.z, tn, tf, exact_count)) {
+            st.push(__ldg(a.root_ref + ob));
+            any = true;
+        }
+    }
+    return any;
+}
+
+// shadowRay of light i for the hit point of `d`, `t`                  :325-326
+__device__ __forceinline__ void shadow_ray(const KArgs& a, V3 d, float t, int i, V3& so, V3& sd) {
+    so = v3(mul(d.x, t), mul(d.y, t), mul(d.z, t));
+    sd = v3(sub(a.lights[3 * i], so.x), sub(a.lights[3 * i + 1], so.y), sub(a.lights[3 * i + 2], so.z));
+}
+
+// ---- phase P ------------------------------------------------------------------------------------
+__device__ __forceinline__ void phase_primary(const KArgs& a, uint32_t* smem, unsigned& exact_count) {
+    const unsigned lane = threadIdx.x & 31;
+    const unsigned n_tiles = (unsigned)(a.tiles_x * a.tiles_y);
+    Stack st; st.base = smem + threadIdx.x; st.sp = 0;
+    unsigned hits = 0;
+    const bool shadows = a.n_objects >= 2 && a.light_count > 0;
+    for (;;) {
+        const unsigned tile = next_item(&a.counters[CNT_TILE], lane);
+        if (tile >= n_tiles) break;
+        const Pixel p = pixel_of(a, tile, lane);
+        const V3 d = primary_dir(a, p);
+        const FRay r = make_fray(v3(0.f, 0.f, 0.f), d, a.coord_bound);
+        Hit h; h.t = INFINITY; h.tri = -1; h.obj = -1;
+        st.sp = 0;
+        if (p.valid) push_roots(a, r, st, -1, exact_count);                   // :409 (S2 order via S6 rule)
+        trace_closest(a, r, st, h, exact_count);
+        bool interested = false;
+        if (p.valid) {
+            const size_t at = (size_t)p.py * a.width + p.px;
+            if (h.tri >= 0) h.obj = __float_as_int(ldg4(a.geom + 3 * (size_t)h.tri).w);
+            a.hit_t[at] = h.t;
+            a.hit_tri[at] = h.tri;
+            if (a.obj_id) a.obj_id[at] = h.obj;
+            if (a.tri_id) a.tri_id[at] = h.tri;
+            if (a.t) a.t[at] = h.t;
+            if (h.tri >= 0 && shadows) {
+                // Can any of the N shadow rays enter another object's hierarchy at all?  (root test of :328)
+                for (int i = 0; i < a.light_count && !interested; ++i) {
+                    V3 so, sd;
+                    shadow_ray(a, d, h.t, i, so, sd);
+                    const FRay s = make_fray(so, sd, a.coord_bound);
+                    st.sp = 0;
+                    interested = push_roots(a, s, st, h.obj, exact_count);
+                }
+                st.sp = 0;
+            }
+        }
+        const unsigned hit_ballot = __ballot_sync(kFull, p.valid && h.tri >= 0);
+        const unsigned int_ballot = __ballot_sync(kFull, interested);
+        if (lane == 0) {
+            hits += __popc(hit_ballot);
+            a.tile_interest[tile] = int_ballot;
+            if (int_ballot) {
+                const unsigned slot = (unsigned)atomicAdd(&a.counters[CNT_LIST], 1ull);
+                a.tile_list[slot] = tile;
+            }
+        }
+    }
+    if (lane == 0 && hits) atomicAdd(&a.counters[CNT_HIT], (unsigned long long)hits);
+}
+
+// ---- phase S ------------------------------------------------------------------------------------
+__device__ __forceinline__ void phase_shadow(const KArgs& a, uint32_t* smem, unsigned& exact_count) {
+    const unsigned lane = threadIdx.x & 31;
+    const unsigned n_list = (unsigned)a.counters[CNT_LIST];
+    const unsigned n_items = n_list * (unsigned)a.light_count;
+    Stack st; st.base = smem + threadIdx.x; st.sp = 0;
+    for (;;) {
+        const unsigned item = next_item(&a.counters[CNT_SHADOW], lane);
+        if (item >= n_items) break;
+        const int light = (int)(item / n_list);                               // light-major: a tile's N items are spread over the phase
+        const unsigned tile = a.tile_list[item % n_list];
+        const unsigned interest = a.tile_interest[tile];
+        const Pixel p = pixel_of(a, tile, lane);
+        st.sp = 0;
+        V3 so = v3(0.f, 0.f, 0.f), sd = v3(1.f, 1.f, 1.f);
+        int32_t obj = -1;
+        const bool mine = (interest >> lane) & 1u;
+        if (mine) {
+            const size_t at = (size_t)p.py * a.width + p.px;
+            const float t = a.hit_t[at];
+            const int32_t tri = a.hit_tri[at];
+            obj = __float_as_int(ldg4(a.geom + 3 * (size_t)tri).w);
+            shadow_ray(a, primary_dir(a, p), t, light, so, sd);
+        }
+        const FRay s = make_fray(so, sd, a.coord_bound);
+        if (mine) push_roots(a, s, st, obj, exact_count);
+        const bool occluded = trace_any(a, s, st, exact_count);
+        const unsigned ballot = __ballot_sync(kFull, mine && occluded);
+        if (lane == 0) a.shadow_mask[(size_t)tile * a.light_count + light] = ballot;
+    }
+}
+
+// ---- phase C ------------------------------------------------------------------------------------
+__device__ __forceinline__ void phase_shade(const KArgs& a) {
+    const unsigned lane = threadIdx.x & 31;
+    const unsigned n_tiles = (unsigned)(a.tiles_x * a.tiles_y);
+    const V3 lc = v3(a.light_color[0], a.light_color[1], a.light_color[2]);
+    for (;;) {
+        const unsigned tile = next_item(&a.counters[CNT_SHADE], lane);
+        if (tile >= n_tiles) break;
+        const Pixel p = pixel_of(a, tile, lane);
+        if (!p.valid) continue;
+        const size_t at = (size_t)p.py * a.width + p.px;
+        Hit h; h.t = a.hit_t[at]; h.tri = a.hit_tri[at]; h.obj = -1;
+        V3 color = v3(0.f, 0.f, 0.f);
+        const bool hit = h.tri >= 0;
+        if (hit) {
+            h.obj = __float_as_int(ldg4(a.geom + 3 * (size_t)h.tri).w);
+            const V3 d = primary_dir(a, p);
+            const PhongPixel pp = prepare_pixel(a, h, d, false);
+            const bool mine = (a.tile_interest[tile] >> lane) & 1u;
+            const uint32_t* masks = a.shadow_mask + (size_t)tile * a.light_count;
+            for (int i = 0; i < a.light_count; ++i) {                         // :366
+                const V3 L = v3(a.lights[3 * i], a.lights[3 * i + 1], a.lights[3 * i + 2]);
+                const bool shadowed = mine && ((masks[i] >> lane) & 1u);      // :367
+                V3 c = phong(pp, L, lc);                                      // :368
+                if (shadowed) { c.x = dvd(c.x, a.shadow_div); c.y = dvd(c.y, a.shadow_div); c.z = dvd(c.z, a.shadow_div); }  // :369
+                color.x = add(color.x, c.x); color.y = add(color.y, c.y); color.z = add(color.z, c.z);   // :370
+            }
+        }
+        // ids / t planes were written in phase P; store_pixel only writes the colour here
+        store_pixel(a, p.px, p.py, hit, color, h, false);
+    }
+}
+
+// ---- kernels --------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(kThreads) render_phased(const __grid_constant__ KArgs a) {
+    extern __shared__ uint32_t smem[];
+    cg::grid_group grid = cg::this_grid();
+    unsigned exact_count = 0;
+    phase_primary(a, smem, exact_count);
+    grid.sync();
+    if (a.n_objects >= 2 && a.light_count > 0) phase_shadow(a, smem, exact_count);
+    grid.sync();
+    phase_shade(a);
+    for (int s = 16; s > 0; s >>= 1) exact_count += __shfl_xor_sync(kFull, exact_count, s);
+    if ((threadIdx.x & 31) == 0 && exact_count) atomicAdd(&a.counters[CNT_EXACT], (unsigned long long)exact_count);
+}
+
+// The same three phases as three launches (profiling each phase on its own; no cooperative launch).
+template <int PHASE>
+__global__ void __launch_bounds__(kThreads) render_phase(const __grid_constant__ KArgs a) {
+    extern __shared__ uint32_t smem[];
+    unsigned exact_count = 0;
+    if (PHASE == 0) phase_primary(a, smem, exact_count);
+    if (PHASE == 1) phase_shadow(a, smem, exact_count);
+    if (PHASE == 2) phase_shade(a);
+    for (int s = 16; s > 0; s >>= 1) exact_count += __shfl_xor_sync(kFull, exact_count, s);
+    if ((threadIdx.x & 31) == 0 && exact_count) atomicAdd(&a.counters[CNT_EXACT], (unsigned long long)exact_count);
+}
+
+// wide[4*i .. 4*i+3] for interior node i: {Lmin.xyz, Lmax.x} {Lmax.yz, Rmin.xy} {Rmin.z, Rmax.xyz} {Lref, Rref, 0, 0}
+__device__ __forceinline__ uint32_t ref_of(const float4* nodes, uint32_t i) {
+    const uint32_t na = __float_as_uint(nodes[2 * (size_t)i].w), nb = __float_as_uint(nodes[2 * (size_t)i + 1].w);
+    if (nb & SRT_LEAF_BIT) return SRT_LEAF_BIT | ((nb & 15u) << kLeafFirstBits) | (na & ((1u << kLeafFirstBits) - 1u));
+    return i;
+}
+
+__global__ void build_wide_kernel(const float4* nodes, const srt_object* objects, uint32_t n_nodes, uint32_t n_objects,
+                                  float4* wide, uint32_t* root_ref) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n_objects) root_ref[i] = ref_of(nodes, objects[i].root);
+    if (i >= n_nodes) return;
+    const float4 n0 = nodes[2 * (size_t)i], n1 = nodes[2 * (size_t)i + 1];
+    if (__float_as_uint(n1.w) & SRT_LEAF_BIT) return;
+    const uint32_t l = i + 1, r = __float_as_uint(n0.w);
+    const float4 l0 = nodes[2 * (size_t)l], l1 = nodes[2 * (size_t)l + 1];
+    const float4 r0 = nodes[2 * (size_t)r], r1 = nodes[2 * (size_t)r + 1];
+    float4* w = wide + 4 * (size_t)i;
+    w[0] = make_float4(l0.x, l0.y, l0.z, l1.x);
+    w[1] = make_float4(l1.y, l1.z, r0.x, r0.y);
+    w[2] = make_float4(r0.z, r1.x, r1.y, r1.z);
+    w[3] = make_float4(__uint_as_float(ref_of(nodes, l)), __uint_as_float(ref_of(nodes, r)), 0.f, 0.f);
+}
+
+}  // namespace
+
+cudaError_t launch_build_wide(const float4* nodes, const srt_object* objects, uint32_t n_nodes, uint32_t n_objects,
+                              float4* wide, uint32_t* root_ref, cudaStream_t stream) {
+    const uint32_t n = n_nodes > n_objects ? n_nodes : n_objects;
+    if (n == 0) return cudaSuccess;
+    build_wide_kernel<<<(n + 255) / 256, 256, 0, stream>>>(nodes, objects, n_nodes, n_objects, wide, root_ref);
+    return cudaGetLastError();
+}
+
+size_t phased_smem_bytes(int stack_cap) { return (size_t)stack_cap * kThreads * sizeof(uint32_t); }
+
+cudaError_t launch_render_phased(const KArgs& a, int variant, int sm_count, cudaStream_t stream, int* launches) {
+    const int n_tiles = a.tiles_x * a.tiles_y;
+    if (launches) *launches = 0;
+    if (n_tiles <= 0) return cudaSuccess;
+    const size_t smem = phased_smem_bytes(a.stack_cap);
+    static bool attr_set = false;
+    if (!attr_set) {
+        cudaFuncSetAttribute(render_phased, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024);
+        cudaFuncSetAttribute(render_phase<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024);
+        cudaFuncSetAttribute(render_phase<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024);
+        cudaFuncSetAttribute(render_phase<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024);
+        attr_set = true;
+    }
+    int per_sm = 0;
+    cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, render_phased, kThreads, smem);
+    if (e != cudaSuccess) return e;
+    if (per_sm < 1) return cudaErrorLaunchOutOfResources;
+    int blocks = sm_count * per_sm;
+    const int need = (n_tiles + kThreads / 32 - 1) / (kThreads / 32);
+    if (blocks > need) blocks = need;
+    if (variant == SRT_VARIANT_SPLIT) {
+        render_phase<0><<<blocks, kThreads, smem, stream>>>(a);
+        if (a.n_objects >= 2 && a.light_count > 0) render_phase<1><<<blocks, kThreads, smem, stream>>>(a);
+        render_phase<2><<<blocks, kThreads, smem, stream>>>(a);
+        if (launches) *launches = 3;
+        return cudaGetLastError();
+    }
+    void* params[] = {(void*)&a};
+    if (launches) *launches = 1;
+    return cudaLaunchCooperativeKernel((const void*)render_phased, dim3(blocks), dim3(kThreads), params, smem, stream);
+}
+
+}  // namespace srtk

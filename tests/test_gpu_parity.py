@@ -26,11 +26,14 @@ CASES = [
 ]
 
 
+# kernel variants: 0 = phased persistent kernel (default), 3 = the same as three launches, 1 = simple
+@pytest.mark.parametrize("variant", [0, 3, 1], ids=["phased", "split", "simple"])
 @pytest.mark.parametrize("key,W,H,focal,N", CASES, ids=[c[0] for c in CASES])
-def test_frame_parity(gpu_ctx, ref_scene, key, W, H, focal, N):
+def test_frame_parity(gpu_ctx, ref_scene, key, W, H, focal, N, variant):
     cfg = scenes.CONFIGS[key]
     _b, arrays, light = ref_scene(key)
     p = _abi.default_params(W, H, focal, light, N, cfg.use_bvh)
+    p.variant = variant
     want = pyoracle.oracle_render(arrays, p)
     sc = gpu_ctx.upload(arrays)
     got = gpu_ctx.render(sc, p)
@@ -41,7 +44,8 @@ def test_frame_parity(gpu_ctx, ref_scene, key, W, H, focal, N):
     mx, psnr = compare_images(got["rgb"], want["rgb"])
     ndiff = int(np.count_nonzero((got["rgb"] != want["rgb"]).any(axis=2)))
     print(f"{key}: ids obj {same_obj}/{npx} tri {same_tri}/{npx}; rgb max|d|={mx} psnr={psnr:.1f} dB "
-          f"pixels differing={ndiff}; kernel {got['stats']['kernel_ms']:.3f} ms")
+          f"pixels differing={ndiff}; kernel {got['stats']['kernel_ms']:.3f} ms, exact slab fallbacks "
+          f"{got['stats']['exact_slab_tests']}, launches {got['stats']['kernel_launches']}")
     assert same_obj == npx and same_tri == npx, "primary-hit ids must be identical (exact arithmetic)"
     assert np.array_equal(got["t"], want["t"]), "hit parameter t must be bit-identical"
     assert mx <= 1 and psnr >= 50.0
