@@ -139,7 +139,7 @@ typedef struct srt_render_params {
 
 enum { SRT_VARIANT_DEFAULT = 0,   /* phased persistent kernel (falls back to SIMPLE for the legacy one-box path) */
        SRT_VARIANT_SIMPLE = 1,    /* one thread = one pixel, whole pixel per work item */
-       SRT_VARIANT_SPLIT = 3,     /* the phased kernel as three launches (profiling) */
+       SRT_VARIANT_SPLIT = 3,     /* the phased kernel as separate launches, one per phase (profiling) */
        SRT_VARIANT_COUNT = 100,   /* SIMPLE + node / triangle counters */
        SRT_VARIANT_TIMELINE = 101 /* SIMPLE + per-tile cost map in the id / t planes (debug) */ };
 
@@ -162,7 +162,7 @@ typedef struct srt_stats {
     uint64_t tri_tests;
     uint64_t exact_slab_tests;    /* phased kernel: slab tests the filter could not decide (ran the exact divisions) */
     float    kernel_ms;           /* CUDA-event time of the render kernel(s) */
-    int32_t  kernel_launches;     /* kernels launched by the last srt_render (1, or 3 for SRT_VARIANT_SPLIT) */
+    int32_t  kernel_launches;     /* kernels launched by the last srt_render (1, or one per phase for SRT_VARIANT_SPLIT) */
 } srt_stats;
 
 typedef struct srt_context srt_context;

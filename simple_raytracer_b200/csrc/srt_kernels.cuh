@@ -14,7 +14,7 @@ struct TexDev {
 
 // Slots of the per-context device counter block.
 enum { CNT_TILE = 0, CNT_HIT = 1, CNT_NODE = 2, CNT_TRI = 3, CNT_LIST = 4, CNT_SHADOW = 5, CNT_SHADE = 6,
-       CNT_EXACT = 7, CNT_WORDS = 8 };
+       CNT_EXACT = 7, CNT_HEAVY = 8, CNT_LIGHT = 9, CNT_WORDS = 16 };
 
 // Everything one frame needs, passed by value as a __grid_constant__ kernel parameter.
 struct KArgs {
@@ -49,9 +49,11 @@ struct KArgs {
     int32_t* hit_tri;           // [height][width] scratch: closest-hit triangle (leaf order) or -1
     uint32_t* tile_interest;    // [tiles] lanes whose shadow rays can reach another object's root box
     uint32_t* tile_list;        // compacted list of tiles with tile_interest != 0
+    uint32_t* tile_order;       // [tiles] phase-P queue order: expected-heavy tiles first
     uint32_t* shadow_mask;      // [tiles][light_count] ballot of occluded lanes
     float coord_bound;          // max |coordinate| over all root boxes (margin of the filtered slab test)
     int32_t stack_cap;          // per-thread traversal stack entries (shared memory)
+    int32_t debug_timeline;     // 1: phase P overwrites the t / obj_id / tri_id planes with per-tile cycles / SM / start ns
 };
 
 constexpr int kTileW = 8, kTileH = 4;          // one warp = 8x4 pixels

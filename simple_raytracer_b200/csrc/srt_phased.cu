@@ -65,19 +65,36 @@ __device__ __forceinline__ float rcp_approx(float x) {
     return r;
 }
 
+// NaN-propagating min / max (FMNMX.NAN): a NaN plane value (0 * inf) must reach the decision, where
+// it makes both comparisons false and so selects the exact test.
+__device__ __forceinline__ float minn(float a, float b) { float r; asm("min.NaN.f32 %0, %1, %2;" : "=f"(r) : "f"(a), "f"(b)); return r; }
+__device__ __forceinline__ float maxn(float a, float b) { float r; asm("max.NaN.f32 %0, %1, %2;" : "=f"(r) : "f"(a), "f"(b)); return r; }
+
+// A zero direction component with a zero origin component (the centre row / column of the primary
+// rays, S3) stays on the filter: i = rcp(+-0) = +-inf and n = 0 give b*i = +-inf, which IS the
+// reference's b/0 (same sign rules), and 0*inf = NaN where the reference has 0/0.  The margin only
+// has to cover the axes with finite values.
 __device__ __forceinline__ FRay make_fray(V3 o, V3 d, float coord_bound) {
     FRay r;
     r.o = o; r.d = d;
     r.ix = rcp_approx(d.x); r.iy = rcp_approx(d.y); r.iz = rcp_approx(d.z);
-    r.nx = -(o.x * r.ix); r.ny = -(o.y * r.iy); r.nz = -(o.z * r.iz);
-    const float ax = fabsf(r.ix), ay = fabsf(r.iy), az = fabsf(r.iz);
+    r.nx = o.x == 0.f ? 0.f : -(o.x * r.ix);
+    r.ny = o.y == 0.f ? 0.f : -(o.y * r.iy);
+    r.nz = o.z == 0.f ? 0.f : -(o.z * r.iz);
+    const float inf = __int_as_float(0x7f800000);
+    const bool zx = d.x == 0.f && o.x == 0.f, zy = d.y == 0.f && o.y == 0.f, zz = d.z == 0.f && o.z == 0.f;
+    const float ax = zx ? 0.f : fabsf(r.ix), ay = zy ? 0.f : fabsf(r.iy), az = zz ? 0.f : fabsf(r.iz);
     const float bx = fabsf(r.nx), by = fabsf(r.ny), bz = fabsf(r.nz);
     const float A = fmaxf(fmaxf(fmaf(coord_bound, ax, bx), fmaf(coord_bound, ay, by)), fmaf(coord_bound, az, bz));
     const float nmax = fmaxf(fmaxf(bx, by), bz);
     r.m = fmaf(A, 20.0f * 5.9604645e-8f, fmaf(nmax, 3.0f * 5.9604645e-8f, 1e-37f));
-    // zero / denormal / huge direction components, or anything that made the margin non-finite
+    // denormal / huge direction components, a zero component with a non-zero origin, or anything
+    // that made the margin non-finite: always the exact test
     const float lo = 1e-30f, hi = 1e30f;
-    r.degenerate = !(ax > lo && ax < hi && ay > lo && ay < hi && az > lo && az < hi && r.m < 1e30f);
+    const bool okx = zx ? (fabsf(r.ix) == inf) : (ax > lo && ax < hi);
+    const bool oky = zy ? (fabsf(r.iy) == inf) : (ay > lo && ay < hi);
+    const bool okz = zz ? (fabsf(r.iz) == inf) : (az > lo && az < hi);
+    r.degenerate = !(okx && oky && okz && r.m < 1e30f) || (zx && zy && zz);
     return r;
 }
 
@@ -87,8 +104,8 @@ __device__ __forceinline__ bool slab_filtered(const FRay& r, float lox, float lo
     const float x0 = fmaf(lox, r.ix, r.nx), x1 = fmaf(hix, r.ix, r.nx);
     const float y0 = fmaf(loy, r.iy, r.ny), y1 = fmaf(hiy, r.iy, r.ny);
     const float z0 = fmaf(loz, r.iz, r.nz), z1 = fmaf(hiz, r.iz, r.nz);
-    const float tn = fmaxf(fmaxf(fminf(x0, x1), fminf(y0, y1)), fminf(z0, z1));
-    const float tf = fminf(fminf(fmaxf(x0, x1), fmaxf(y0, y1)), fmaxf(z0, z1));
+    const float tn = maxn(maxn(minn(x0, x1), minn(y0, y1)), minn(z0, z1));
+    const float tf = minn(minn(maxn(x0, x1), maxn(y0, y1)), maxn(z0, z1));
     tn_out = tn; tf_out = tf;
     const float diff = tf - tn;
     if (!r.degenerate) {
@@ -225,6 +242,53 @@ __device__ __forceinline__ void shadow_ray(const KArgs& a, V3 d, float t, int i,
     sd = v3(sub(a.lights[3 * i], so.x), sub(a.lights[3 * i + 1], so.y), sub(a.lights[3 * i + 2], so.z));
 }
 
+// ---- phase 0: queue order -------------------------------------------------------------------------
+// Tiles whose rays enter the root box of a large object cost 10-50x more than ground / sky tiles
+// (profiles/r01_*: 100-400 k cycles against 6-20 k).  To keep them out of the tail they are queued
+// first.  Heuristic only (lane = tile, its four corner rays, approximate test): a wrong class moves
+// a tile in the queue, never changes a result.
+constexpr uint32_t kBigObjectTris = 64;
+
+__device__ __forceinline__ void phase_classify(const KArgs& a) {
+    const unsigned lane = threadIdx.x & 31;
+    const unsigned n_tiles = (unsigned)(a.tiles_x * a.tiles_y);
+    const unsigned warps = gridDim.x * (kThreads / 32), gw = blockIdx.x * (kThreads / 32) + (threadIdx.x >> 5);
+    for (unsigned base = gw * 32; base < n_tiles; base += warps * 32) {
+        const unsigned tile = base + lane;
+        bool heavy = false;
+        if (tile < n_tiles) {
+            const int tx = (int)(tile % (unsigned)a.tiles_x), ty = (int)(tile / (unsigned)a.tiles_x);
+            for (int c = 0; c < 4 && !heavy; ++c) {
+                const int px = tx * kTileW + ((c & 1) ? kTileW - 1 : 0);
+                const int py = a.row_begin + ty * kTileH + ((c & 2) ? kTileH - 1 : 0);
+                const V3 d = v3((float)(px + a.i0), (float)(py + a.j0), a.focal);
+                const float ix = rcp_approx(d.x), iy = rcp_approx(d.y), iz = rcp_approx(d.z);
+                for (uint32_t ob = 0; ob < a.n_objects && !heavy; ++ob) {
+                    if (a.objects[ob].tri_count < kBigObjectTris) continue;
+                    const float4* n = a.nodes + 2 * (size_t)a.objects[ob].root;
+                    const float4 n0 = ldg4(n), n1 = ldg4(n + 1);
+                    const float x0 = n0.x * ix, x1 = n1.x * ix, y0 = n0.y * iy, y1 = n1.y * iy, z0 = n0.z * iz, z1 = n1.z * iz;
+                    const float tn = fmaxf(fmaxf(fminf(x0, x1), fminf(y0, y1)), fminf(z0, z1));
+                    const float tf = fminf(fminf(fmaxf(x0, x1), fmaxf(y0, y1)), fmaxf(z0, z1));
+                    heavy = tn <= tf;
+                }
+            }
+        }
+        const unsigned hb = __ballot_sync(kFull, heavy);
+        const unsigned lb = __ballot_sync(kFull, tile < n_tiles && !heavy);
+        unsigned hbase = 0, lbase = 0;
+        if (lane == 0) {
+            if (hb) hbase = (unsigned)atomicAdd(&a.counters[CNT_HEAVY], (unsigned long long)__popc(hb));
+            if (lb) lbase = (unsigned)atomicAdd(&a.counters[CNT_LIGHT], (unsigned long long)__popc(lb));
+        }
+        hbase = __shfl_sync(kFull, hbase, 0);
+        lbase = __shfl_sync(kFull, lbase, 0);
+        const unsigned below = (1u << lane) - 1u;
+        if (heavy) a.tile_order[hbase + __popc(hb & below)] = tile;                       // front of the queue
+        else if (tile < n_tiles) a.tile_order[n_tiles - 1 - (lbase + __popc(lb & below))] = tile;   // back of the queue
+    }
+}
+
 // ---- phase P ------------------------------------------------------------------------------------
 __device__ __forceinline__ void phase_primary(const KArgs& a, uint32_t* smem, unsigned& exact_count) {
     const unsigned lane = threadIdx.x & 31;
@@ -233,8 +297,11 @@ __device__ __forceinline__ void phase_primary(const KArgs& a, uint32_t* smem, un
     unsigned hits = 0;
     const bool shadows = a.n_objects >= 2 && a.light_count > 0;
     for (;;) {
-        const unsigned tile = next_item(&a.counters[CNT_TILE], lane);
-        if (tile >= n_tiles) break;
+        const unsigned q = next_item(&a.counters[CNT_TILE], lane);
+        if (q >= n_tiles) break;
+        const unsigned tile = a.tile_order[q];
+        long long tl_c0 = 0; unsigned long long tl_ns = 0;
+        if (a.debug_timeline) { tl_c0 = clock64(); asm volatile("mov.u64 %0, %globaltimer;" : "=l"(tl_ns)); }
         const Pixel p = pixel_of(a, tile, lane);
         const V3 d = primary_dir(a, p);
         const FRay r = make_fray(v3(0.f, 0.f, 0.f), d, a.coord_bound);
@@ -265,6 +332,14 @@ __device__ __forceinline__ void phase_primary(const KArgs& a, uint32_t* smem, un
         }
         const unsigned hit_ballot = __ballot_sync(kFull, p.valid && h.tri >= 0);
         const unsigned int_ballot = __ballot_sync(kFull, interested);
+        if (a.debug_timeline && p.valid) {
+            __syncwarp();
+            const size_t at = (size_t)p.py * a.width + p.px;
+            unsigned smid; asm volatile("mov.u32 %0, %smid;" : "=r"(smid));
+            if (a.t) a.t[at] = (float)(clock64() - tl_c0);
+            if (a.obj_id) a.obj_id[at] = (int32_t)smid;
+            if (a.tri_id) a.tri_id[at] = (int32_t)(tl_ns & 0x7fffffffull);
+        }
         if (lane == 0) {
             hits += __popc(hit_ballot);
             a.tile_interest[tile] = int_ballot;
@@ -343,10 +418,12 @@ __device__ __forceinline__ void phase_shade(const KArgs& a) {
 }
 
 // ---- kernels --------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(kThreads) render_phased(const __grid_constant__ KArgs a) {
+__global__ void __launch_bounds__(kThreads, 8) render_phased(const __grid_constant__ KArgs a) {
     extern __shared__ uint32_t smem[];
     cg::grid_group grid = cg::this_grid();
     unsigned exact_count = 0;
+    phase_classify(a);
+    grid.sync();
     phase_primary(a, smem, exact_count);
     grid.sync();
     if (a.n_objects >= 2 && a.light_count > 0) phase_shadow(a, smem, exact_count);
@@ -361,6 +438,7 @@ template <int PHASE>
 __global__ void __launch_bounds__(kThreads) render_phase(const __grid_constant__ KArgs a) {
     extern __shared__ uint32_t smem[];
     unsigned exact_count = 0;
+    if (PHASE == 3) phase_classify(a);
     if (PHASE == 0) phase_primary(a, smem, exact_count);
     if (PHASE == 1) phase_shadow(a, smem, exact_count);
     if (PHASE == 2) phase_shade(a);
@@ -415,6 +493,7 @@ cudaError_t launch_render_phased(const KArgs& a, int variant, int sm_count, cuda
         cudaFuncSetAttribute(render_phase<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024);
         cudaFuncSetAttribute(render_phase<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024);
         cudaFuncSetAttribute(render_phase<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024);
+        cudaFuncSetAttribute(render_phase<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024);
         attr_set = true;
     }
     int per_sm = 0;
@@ -425,10 +504,11 @@ cudaError_t launch_render_phased(const KArgs& a, int variant, int sm_count, cuda
     const int need = (n_tiles + kThreads / 32 - 1) / (kThreads / 32);
     if (blocks > need) blocks = need;
     if (variant == SRT_VARIANT_SPLIT) {
+        render_phase<3><<<blocks, kThreads, smem, stream>>>(a);
         render_phase<0><<<blocks, kThreads, smem, stream>>>(a);
         if (a.n_objects >= 2 && a.light_count > 0) render_phase<1><<<blocks, kThreads, smem, stream>>>(a);
         render_phase<2><<<blocks, kThreads, smem, stream>>>(a);
-        if (launches) *launches = 3;
+        if (launches) *launches = 4;
         return cudaGetLastError();
     }
     void* params[] = {(void*)&a};
