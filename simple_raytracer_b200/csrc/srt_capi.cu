@@ -70,7 +70,8 @@ struct srt_context {
     unsigned long long* counters_host = nullptr; // pinned
     cudaEvent_t ev0 = nullptr, ev1 = nullptr, ev_copy = nullptr;
     DevBuf out_rgb, out_obj, out_tri, out_t;     // staging for HOST output pointers
-    DevBuf hit_t, hit_tri, tile_interest, tile_list, tile_order, shadow_mask;   // scratch of the phased kernel
+    DevBuf hit_t, hit_tri, tile_interest, tile_list, tile_order, tile_done, shadow_mask;
+    uint32_t frame_seq = 0;   // scratch of the phased kernel
     int last_launches = 0;
     // last render
     bool have_last = false;
@@ -144,7 +145,7 @@ void srt_context_destroy(srt_context* c) {
     cudaSetDevice(c->device);
     cudaStreamSynchronize(c->stream);
     c->out_rgb.release(); c->out_obj.release(); c->out_tri.release(); c->out_t.release();
-    c->hit_t.release(); c->hit_tri.release(); c->tile_interest.release(); c->tile_list.release(); c->tile_order.release(); c->shadow_mask.release();
+    c->hit_t.release(); c->hit_tri.release(); c->tile_interest.release(); c->tile_list.release(); c->tile_order.release(); c->tile_done.release(); c->shadow_mask.release();
     if (c->counters) cudaFree(c->counters);
     if (c->counters_host) cudaFreeHost(c->counters_host);
     if (c->ev0) cudaEventDestroy(c->ev0);
@@ -464,8 +465,8 @@ int srt_render(srt_context* c, const srt_scene* s, const srt_render_params* p, c
     }
     // kernel selection: the phased kernel unless the scene / request needs the simple one
     a.stack_cap = (int)(s->max_depth + s->n_objects + 2);
-    const bool tl = p->variant == 102;            // debug: per-tile cost map of phase P
-    a.debug_timeline = tl ? 1 : 0;
+    const bool tl = p->variant == 102 || p->variant == 103;   // debug: per-tile cost map of the primary stage / per-warp timestamps
+    a.debug_timeline = p->variant == 102 ? 1 : (p->variant == 103 ? 2 : 0);
     const bool want_phased = (p->variant == SRT_VARIANT_DEFAULT || p->variant == SRT_VARIANT_SPLIT || tl) && p->use_bvh &&
                              s->phased_ok && srtk::phased_smem_bytes(a.stack_cap) <= 96 * 1024;
     cudaError_t e;
@@ -474,13 +475,20 @@ int srt_render(srt_context* c, const srt_scene* s, const srt_render_params* p, c
         if ((rc = c->hit_t.reserve(npix * 4))) return rc;
         if ((rc = c->hit_tri.reserve(npix * 4))) return rc;
         if ((rc = c->tile_interest.reserve(n_tiles * 4))) return rc;
-        if ((rc = c->tile_list.reserve(n_tiles * 4))) return rc;
+        {
+            const void* before = c->tile_list.p;
+            if ((rc = c->tile_list.reserve(n_tiles * 8))) return rc;
+            if (c->tile_list.p != before) CU(cudaMemsetAsync(c->tile_list.p, 0, c->tile_list.cap, c->stream));   // tag 0 = never published
+        }
+        if ((rc = c->tile_done.reserve(n_tiles * 4))) return rc;
         if ((rc = c->tile_order.reserve(n_tiles * 4))) return rc;
         if ((rc = c->shadow_mask.reserve(n_tiles * 4 * (size_t)(p->light_count > 0 ? p->light_count : 1)))) return rc;
         a.wide = (const float4*)s->wide.p;
         a.root_ref = (const uint32_t*)s->root_ref.p;
         a.hit_t = (float*)c->hit_t.p; a.hit_tri = (int32_t*)c->hit_tri.p;
-        a.tile_interest = (uint32_t*)c->tile_interest.p; a.tile_list = (uint32_t*)c->tile_list.p; a.tile_order = (uint32_t*)c->tile_order.p;
+        a.tile_interest = (uint32_t*)c->tile_interest.p; a.tile_list = (unsigned long long*)c->tile_list.p; a.tile_done = (uint32_t*)c->tile_done.p;
+        if (++c->frame_seq == 0) c->frame_seq = 1;
+        a.frame_seq = c->frame_seq; a.tile_order = (uint32_t*)c->tile_order.p;
         a.shadow_mask = (uint32_t*)c->shadow_mask.p;
         a.coord_bound = s->coord_bound;
         e = srtk::launch_render_phased(a, p->variant, c->sm_count, c->stream, &c->last_launches);
@@ -520,6 +528,9 @@ int srt_last_stats(srt_context* c, srt_stats* out) {
     out->tri_tests = c->counters_host[srtk::CNT_TRI];
     out->exact_slab_tests = c->counters_host[srtk::CNT_EXACT];
     out->kernel_launches = c->last_launches;
+    if (c->counters_host[srtk::CNT_TIMEOUT])
+        return fail(SRT_ERR_CUDA, "render kernel: %llu warps gave up waiting for a published tile (internal error; frame incomplete)",
+                    (unsigned long long)c->counters_host[srtk::CNT_TIMEOUT]);
     float ms = 0.f;
     CU(cudaEventElapsedTime(&ms, c->ev0, c->ev1));
     out->kernel_ms = ms;

@@ -14,7 +14,7 @@ struct TexDev {
 
 // Slots of the per-context device counter block.
 enum { CNT_TILE = 0, CNT_HIT = 1, CNT_NODE = 2, CNT_TRI = 3, CNT_LIST = 4, CNT_SHADOW = 5, CNT_SHADE = 6,
-       CNT_EXACT = 7, CNT_HEAVY = 8, CNT_LIGHT = 9, CNT_WORDS = 16 };
+       CNT_EXACT = 7, CNT_HEAVY = 8, CNT_LIGHT = 9, CNT_PDONE = 10, CNT_TIMEOUT = 11, CNT_WORDS = 16 };
 
 // Everything one frame needs, passed by value as a __grid_constant__ kernel parameter.
 struct KArgs {
@@ -48,7 +48,9 @@ struct KArgs {
     float* hit_t;               // [height][width] scratch: closest-hit parameter
     int32_t* hit_tri;           // [height][width] scratch: closest-hit triangle (leaf order) or -1
     uint32_t* tile_interest;    // [tiles] lanes whose shadow rays can reach another object's root box
-    uint32_t* tile_list;        // compacted list of tiles with tile_interest != 0
+    unsigned long long* tile_list;   // published tiles with tile_interest != 0: (frame_seq << 32) | tile
+    uint32_t* tile_done;        // [tiles] shadow items completed
+    uint32_t frame_seq;         // tag of this launch's tile_list entries (no clearing between frames)
     uint32_t* tile_order;       // [tiles] phase-P queue order: expected-heavy tiles first
     uint32_t* shadow_mask;      // [tiles][light_count] ballot of occluded lanes
     float coord_bound;          // max |coordinate| over all root boxes (margin of the filtered slab test)

@@ -1,5 +1,5 @@
-// srt_phased.cu — the production render kernel (sm_100a): one persistent cooperative grid, three
-// phases separated by grid barriers.  See DESIGN.md §Kernels.
+// srt_phased.cu — the production render kernel (sm_100a): one persistent grid, three stages connected
+// by dataflow (no grid barrier).  See DESIGN.md §Kernels.
 //
 //   P  primary   work item = 8x4 pixel tile (one warp, lane = pixel): primary ray (:505-517), closest hit
 //                over every object's BVH (:405-431, :296-317, :42-75) -> hit record (t, triangle) in
@@ -23,13 +23,9 @@
 // and for every ray with a zero / denormal / non-finite direction component — the exact test is run.
 // The set of leaves visited is therefore exactly the reference's (S3/S5), only cheaper.
 // Closest hit uses the order-independent rule min over (t, visit index) (S6), so traversal order is free.
-#include <cooperative_groups.h>
-
 #include "srt_kernels.cuh"
 #include "srt_device.cuh"
 #include "srt_shade.cuh"
-
-namespace cg = cooperative_groups;
 
 namespace srtk {
 using namespace srtd;
@@ -289,70 +285,138 @@ __device__ __forceinline__ void phase_classify(const KArgs& a) {
     }
 }
 
-// ---- phase P ------------------------------------------------------------------------------------
+// ---- per-item bodies (shared by the dataflow kernel and the per-phase profiling kernels) ------------
+// Reads of data another warp wrote during this launch (hit records, interest words, shadow masks)
+// go through L2 (__ldcg): L1 is not coherent between SMs.
+
+// Closest hit of one tile (lane = pixel) + the hit record + "can any shadow ray of this pixel reach
+// another object's root box" (the root test of :328).  Returns the ballot of interested lanes.
+__device__ __forceinline__ unsigned primary_tile(const KArgs& a, Stack& st, unsigned tile, unsigned lane, Pixel& p, V3& d,
+                                                 Hit& h, unsigned& hit_ballot, unsigned& exact_count) {
+    long long tl_c0 = 0; unsigned long long tl_ns = 0;
+    if (a.debug_timeline == 1) { tl_c0 = clock64(); asm volatile("mov.u64 %0, %globaltimer;" : "=l"(tl_ns)); }
+    p = pixel_of(a, tile, lane);
+    d = primary_dir(a, p);
+    const FRay r = make_fray(v3(0.f, 0.f, 0.f), d, a.coord_bound);
+    h.t = INFINITY; h.tri = -1; h.obj = -1;
+    st.sp = 0;
+    if (p.valid) push_roots(a, r, st, -1, exact_count);                       // :409 (S2 order via the S6 rule)
+    trace_closest(a, r, st, h, exact_count);
+    bool interested = false;
+    if (p.valid) {
+        const size_t at = (size_t)p.py * a.width + p.px;
+        if (h.tri >= 0) h.obj = __float_as_int(ldg4(a.geom + 3 * (size_t)h.tri).w);
+        a.hit_t[at] = h.t;
+        a.hit_tri[at] = h.tri;
+        if (a.obj_id) a.obj_id[at] = h.obj;
+        if (a.tri_id) a.tri_id[at] = h.tri;
+        if (a.t && a.debug_timeline != 2) a.t[at] = h.t;
+        if (h.tri >= 0 && a.n_objects >= 2) {
+            for (int i = 0; i < a.light_count && !interested; ++i) {
+                V3 so, sd;
+                shadow_ray(a, d, h.t, i, so, sd);
+                const FRay s = make_fray(so, sd, a.coord_bound);
+                st.sp = 0;
+                interested = push_roots(a, s, st, h.obj, exact_count);
+            }
+            st.sp = 0;
+        }
+    }
+    hit_ballot = __ballot_sync(kFull, p.valid && h.tri >= 0);
+    const unsigned int_ballot = __ballot_sync(kFull, interested);
+    if (a.debug_timeline == 1 && p.valid) {
+        __syncwarp();
+        const size_t at = (size_t)p.py * a.width + p.px;
+        unsigned smid; asm volatile("mov.u32 %0, %smid;" : "=r"(smid));
+        if (a.t) a.t[at] = (float)(clock64() - tl_c0);
+        if (a.obj_id) a.obj_id[at] = (int32_t)smid;
+        if (a.tri_id) a.tri_id[at] = (int32_t)(tl_ns & 0x7fffffffull);
+    }
+    return int_ballot;
+}
+
+// Occlusion of one light for the interested lanes of one tile -> one ballot word (:321-342).
+__device__ __forceinline__ void shadow_item(const KArgs& a, Stack& st, unsigned tile, int light, unsigned lane,
+                                            unsigned& exact_count) {
+    const unsigned interest = __ldcg(a.tile_interest + tile);
+    const Pixel p = pixel_of(a, tile, lane);
+    st.sp = 0;
+    V3 so = v3(0.f, 0.f, 0.f), sd = v3(1.f, 1.f, 1.f);
+    int32_t obj = -1;
+    const bool mine = (interest >> lane) & 1u;
+    if (mine) {
+        const size_t at = (size_t)p.py * a.width + p.px;
+        const float t = __ldcg(a.hit_t + at);
+        const int32_t tri = __ldcg(a.hit_tri + at);
+        obj = __float_as_int(ldg4(a.geom + 3 * (size_t)tri).w);
+        shadow_ray(a, primary_dir(a, p), t, light, so, sd);
+    }
+    const FRay s = make_fray(so, sd, a.coord_bound);
+    if (mine) push_roots(a, s, st, obj, exact_count);
+    const bool occluded = trace_any(a, s, st, exact_count);
+    const unsigned ballot = __ballot_sync(kFull, mine && occluded);
+    if (lane == 0) a.shadow_mask[(size_t)tile * a.light_count + light] = ballot;
+}
+
+// Shading of one pixel (:350-401, :437-449, :476-487).  `mine`: this lane has shadow masks to read.
+__device__ __forceinline__ void shade_pixel(const KArgs& a, const Pixel& p, const Hit& h, V3 d, bool mine, unsigned tile,
+                                            unsigned lane) {
+    if (!p.valid) return;
+    V3 color = v3(0.f, 0.f, 0.f);
+    const bool hit = h.tri >= 0;
+    if (hit) {
+        const V3 lc = v3(a.light_color[0], a.light_color[1], a.light_color[2]);
+        const PhongPixel pp = prepare_pixel(a, h, d, false);
+        const uint32_t* masks = a.shadow_mask + (size_t)tile * a.light_count;
+        for (int i = 0; i < a.light_count; ++i) {                             // :366
+            const V3 L = v3(a.lights[3 * i], a.lights[3 * i + 1], a.lights[3 * i + 2]);
+            const bool shadowed = mine && ((__ldcg(masks + i) >> lane) & 1u); // :367
+            V3 c = phong(pp, L, lc);                                          // :368
+            if (shadowed) { c.x = dvd(c.x, a.shadow_div); c.y = dvd(c.y, a.shadow_div); c.z = dvd(c.z, a.shadow_div); }  // :369
+            color.x = add(color.x, c.x); color.y = add(color.y, c.y); color.z = add(color.z, c.z);   // :370
+        }
+    }
+    store_pixel(a, p.px, p.py, hit, color, h, false);   // ids / t planes were written with the hit record
+}
+
+// Shading of a tile from its stored hit records (after its shadow items).
+__device__ __forceinline__ void shade_tile_from_memory(const KArgs& a, unsigned tile, unsigned lane) {
+    const Pixel p = pixel_of(a, tile, lane);
+    Hit h; h.t = INFINITY; h.tri = -1; h.obj = -1;
+    if (p.valid) {
+        const size_t at = (size_t)p.py * a.width + p.px;
+        h.t = __ldcg(a.hit_t + at);
+        h.tri = __ldcg(a.hit_tri + at);
+        if (h.tri >= 0) h.obj = __float_as_int(ldg4(a.geom + 3 * (size_t)h.tri).w);
+    }
+    const bool mine = (__ldcg(a.tile_interest + tile) >> lane) & 1u;
+    shade_pixel(a, p, h, primary_dir(a, p), mine, tile, lane);
+}
+
+// ---- the three phases as separate passes (SRT_VARIANT_SPLIT: one launch each, for profiling) -------
 __device__ __forceinline__ void phase_primary(const KArgs& a, uint32_t* smem, unsigned& exact_count) {
     const unsigned lane = threadIdx.x & 31;
     const unsigned n_tiles = (unsigned)(a.tiles_x * a.tiles_y);
     Stack st; st.base = smem + threadIdx.x; st.sp = 0;
     unsigned hits = 0;
-    const bool shadows = a.n_objects >= 2 && a.light_count > 0;
     for (;;) {
         const unsigned q = next_item(&a.counters[CNT_TILE], lane);
         if (q >= n_tiles) break;
         const unsigned tile = a.tile_order[q];
-        long long tl_c0 = 0; unsigned long long tl_ns = 0;
-        if (a.debug_timeline) { tl_c0 = clock64(); asm volatile("mov.u64 %0, %globaltimer;" : "=l"(tl_ns)); }
-        const Pixel p = pixel_of(a, tile, lane);
-        const V3 d = primary_dir(a, p);
-        const FRay r = make_fray(v3(0.f, 0.f, 0.f), d, a.coord_bound);
-        Hit h; h.t = INFINITY; h.tri = -1; h.obj = -1;
-        st.sp = 0;
-        if (p.valid) push_roots(a, r, st, -1, exact_count);                   // :409 (S2 order via S6 rule)
-        trace_closest(a, r, st, h, exact_count);
-        bool interested = false;
-        if (p.valid) {
-            const size_t at = (size_t)p.py * a.width + p.px;
-            if (h.tri >= 0) h.obj = __float_as_int(ldg4(a.geom + 3 * (size_t)h.tri).w);
-            a.hit_t[at] = h.t;
-            a.hit_tri[at] = h.tri;
-            if (a.obj_id) a.obj_id[at] = h.obj;
-            if (a.tri_id) a.tri_id[at] = h.tri;
-            if (a.t) a.t[at] = h.t;
-            if (h.tri >= 0 && shadows) {
-                // Can any of the N shadow rays enter another object's hierarchy at all?  (root test of :328)
-                for (int i = 0; i < a.light_count && !interested; ++i) {
-                    V3 so, sd;
-                    shadow_ray(a, d, h.t, i, so, sd);
-                    const FRay s = make_fray(so, sd, a.coord_bound);
-                    st.sp = 0;
-                    interested = push_roots(a, s, st, h.obj, exact_count);
-                }
-                st.sp = 0;
-            }
-        }
-        const unsigned hit_ballot = __ballot_sync(kFull, p.valid && h.tri >= 0);
-        const unsigned int_ballot = __ballot_sync(kFull, interested);
-        if (a.debug_timeline && p.valid) {
-            __syncwarp();
-            const size_t at = (size_t)p.py * a.width + p.px;
-            unsigned smid; asm volatile("mov.u32 %0, %smid;" : "=r"(smid));
-            if (a.t) a.t[at] = (float)(clock64() - tl_c0);
-            if (a.obj_id) a.obj_id[at] = (int32_t)smid;
-            if (a.tri_id) a.tri_id[at] = (int32_t)(tl_ns & 0x7fffffffull);
-        }
+        Pixel p; V3 d; Hit h; unsigned hit_ballot;
+        const unsigned int_ballot = primary_tile(a, st, tile, lane, p, d, h, hit_ballot, exact_count);
         if (lane == 0) {
             hits += __popc(hit_ballot);
             a.tile_interest[tile] = int_ballot;
             if (int_ballot) {
                 const unsigned slot = (unsigned)atomicAdd(&a.counters[CNT_LIST], 1ull);
-                a.tile_list[slot] = tile;
+                a.tile_list[slot] = ((unsigned long long)a.frame_seq << 32) | tile;
             }
         }
     }
     if (lane == 0 && hits) atomicAdd(&a.counters[CNT_HIT], (unsigned long long)hits);
 }
 
-// ---- phase S ------------------------------------------------------------------------------------
 __device__ __forceinline__ void phase_shadow(const KArgs& a, uint32_t* smem, unsigned& exact_count) {
     const unsigned lane = threadIdx.x & 31;
     const unsigned n_list = (unsigned)a.counters[CNT_LIST];
@@ -361,84 +425,137 @@ __device__ __forceinline__ void phase_shadow(const KArgs& a, uint32_t* smem, uns
     for (;;) {
         const unsigned item = next_item(&a.counters[CNT_SHADOW], lane);
         if (item >= n_items) break;
-        const int light = (int)(item / n_list);                               // light-major: a tile's N items are spread over the phase
-        const unsigned tile = a.tile_list[item % n_list];
-        const unsigned interest = a.tile_interest[tile];
-        const Pixel p = pixel_of(a, tile, lane);
-        st.sp = 0;
-        V3 so = v3(0.f, 0.f, 0.f), sd = v3(1.f, 1.f, 1.f);
-        int32_t obj = -1;
-        const bool mine = (interest >> lane) & 1u;
-        if (mine) {
-            const size_t at = (size_t)p.py * a.width + p.px;
-            const float t = a.hit_t[at];
-            const int32_t tri = a.hit_tri[at];
-            obj = __float_as_int(ldg4(a.geom + 3 * (size_t)tri).w);
-            shadow_ray(a, primary_dir(a, p), t, light, so, sd);
-        }
-        const FRay s = make_fray(so, sd, a.coord_bound);
-        if (mine) push_roots(a, s, st, obj, exact_count);
-        const bool occluded = trace_any(a, s, st, exact_count);
-        const unsigned ballot = __ballot_sync(kFull, mine && occluded);
-        if (lane == 0) a.shadow_mask[(size_t)tile * a.light_count + light] = ballot;
+        const unsigned slot = item / (unsigned)a.light_count;
+        shadow_item(a, st, (unsigned)(a.tile_list[slot] & 0xffffffffull), (int)(item - slot * (unsigned)a.light_count), lane,
+                    exact_count);
     }
 }
 
-// ---- phase C ------------------------------------------------------------------------------------
 __device__ __forceinline__ void phase_shade(const KArgs& a) {
     const unsigned lane = threadIdx.x & 31;
     const unsigned n_tiles = (unsigned)(a.tiles_x * a.tiles_y);
-    const V3 lc = v3(a.light_color[0], a.light_color[1], a.light_color[2]);
     for (;;) {
         const unsigned tile = next_item(&a.counters[CNT_SHADE], lane);
         if (tile >= n_tiles) break;
-        const Pixel p = pixel_of(a, tile, lane);
-        if (!p.valid) continue;
-        const size_t at = (size_t)p.py * a.width + p.px;
-        Hit h; h.t = a.hit_t[at]; h.tri = a.hit_tri[at]; h.obj = -1;
-        V3 color = v3(0.f, 0.f, 0.f);
-        const bool hit = h.tri >= 0;
-        if (hit) {
-            h.obj = __float_as_int(ldg4(a.geom + 3 * (size_t)h.tri).w);
-            const V3 d = primary_dir(a, p);
-            const PhongPixel pp = prepare_pixel(a, h, d, false);
-            const bool mine = (a.tile_interest[tile] >> lane) & 1u;
-            const uint32_t* masks = a.shadow_mask + (size_t)tile * a.light_count;
-            for (int i = 0; i < a.light_count; ++i) {                         // :366
-                const V3 L = v3(a.lights[3 * i], a.lights[3 * i + 1], a.lights[3 * i + 2]);
-                const bool shadowed = mine && ((masks[i] >> lane) & 1u);      // :367
-                V3 c = phong(pp, L, lc);                                      // :368
-                if (shadowed) { c.x = dvd(c.x, a.shadow_div); c.y = dvd(c.y, a.shadow_div); c.z = dvd(c.z, a.shadow_div); }  // :369
-                color.x = add(color.x, c.x); color.y = add(color.y, c.y); color.z = add(color.z, c.z);   // :370
-            }
-        }
-        // ids / t planes were written in phase P; store_pixel only writes the colour here
-        store_pixel(a, p.px, p.py, hit, color, h, false);
+        shade_tile_from_memory(a, tile, lane);
     }
 }
 
-// ---- kernels --------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(kThreads, 8) render_phased(const __grid_constant__ KArgs a) {
-    extern __shared__ uint32_t smem[];
-    cg::grid_group grid = cg::this_grid();
-    unsigned exact_count = 0;
-    phase_classify(a);
-    grid.sync();
-    phase_primary(a, smem, exact_count);
-    grid.sync();
-    if (a.n_objects >= 2 && a.light_count > 0) phase_shadow(a, smem, exact_count);
-    grid.sync();
-    phase_shade(a);
-    for (int s = 16; s > 0; s >>= 1) exact_count += __shfl_xor_sync(kFull, exact_count, s);
-    if ((threadIdx.x & 31) == 0 && exact_count) atomicAdd(&a.counters[CNT_EXACT], (unsigned long long)exact_count);
+// ---- the production kernel: one persistent grid, dataflow between the stages ------------------------
+// Every warp first pulls primary tiles (expected-heavy first).  A tile none of whose lanes can be
+// shadowed is shaded on the spot, from registers.  Otherwise the tile is PUBLISHED: its hit records
+// and interest word are made visible (fence), then its id tagged with this frame's sequence number
+// goes into the next slot of tile_list.  When the tile queue is exhausted a warp turns to shadow
+// items (slot, light); an item whose slot is not published yet is waited for — the publishers are
+// running warps that never wait themselves, so this cannot deadlock — and the warp that completes a
+// tile's last shadow item shades that tile.  No grid-wide barrier: the long primary tiles at the end
+// of the queue (bunny silhouette: 400 us against a 300 us phase) overlap with shadow and shading
+// work instead of idling the machine (profiles/r01_phased_fused: 35 % of warp samples sat in barriers).
+__device__ __forceinline__ unsigned long long ld_volatile_u64(const unsigned long long* p) {
+    return *reinterpret_cast<const volatile unsigned long long*>(p);
 }
 
-// The same three phases as three launches (profiling each phase on its own; no cooperative launch).
+__global__ void __launch_bounds__(kThreads, 8) render_dataflow(const __grid_constant__ KArgs a) {
+    extern __shared__ uint32_t smem[];
+    const unsigned lane = threadIdx.x & 31;
+    const unsigned n_tiles = (unsigned)(a.tiles_x * a.tiles_y);
+    const unsigned N = (unsigned)a.light_count;
+    const unsigned long long seq = a.frame_seq;
+    Stack st; st.base = smem + threadIdx.x; st.sp = 0;
+    unsigned hits = 0, exact_count = 0;
+    // debug_timeline == 2: per-warp timestamps (start, primary queue empty, end) + item counts in the t plane
+    unsigned long long ts0 = 0, ts1 = 0, ts2 = 0; unsigned n_p = 0, n_s = 0, n_c = 0;
+    if (a.debug_timeline == 2) asm volatile("mov.u64 %0, %globaltimer;" : "=l"(ts0));
+
+    for (;;) {
+        const unsigned q = next_item(&a.counters[CNT_TILE], lane);
+        if (q >= n_tiles) break;
+        ++n_p;
+        const unsigned tile = a.tile_order[q];
+        Pixel p; V3 d; Hit h; unsigned hit_ballot;
+        const unsigned int_ballot = primary_tile(a, st, tile, lane, p, d, h, hit_ballot, exact_count);
+        if (int_ballot == 0) {
+            shade_pixel(a, p, h, d, false, tile, lane);
+        } else {
+            __threadfence();                                   // this lane's hit record before the publication
+            __syncwarp();
+        }
+        if (lane == 0) {
+            hits += __popc(hit_ballot);
+            if (int_ballot) {
+                a.tile_interest[tile] = int_ballot;
+                a.tile_done[tile] = 0u;
+                const unsigned slot = (unsigned)atomicAdd(&a.counters[CNT_LIST], 1ull);
+                __threadfence();
+                *reinterpret_cast<volatile unsigned long long*>(a.tile_list + slot) = (seq << 32) | tile;
+                __threadfence();
+            }
+            atomicAdd(&a.counters[CNT_PDONE], 1ull);
+        }
+    }
+
+    if (a.debug_timeline == 2) asm volatile("mov.u64 %0, %globaltimer;" : "=l"(ts1));
+    if (a.n_objects >= 2 && N > 0) {
+        for (;;) {
+            const unsigned s = next_item(&a.counters[CNT_SHADOW], lane);
+            const unsigned slot = s / N;
+            const int light = (int)(s - slot * N);
+            unsigned long long e = 0;
+            if (lane == 0 && slot < n_tiles) {
+                for (unsigned spins = 0;; ++spins) {
+                    e = ld_volatile_u64(a.tile_list + slot);
+                    if ((e >> 32) == seq) break;
+                    if (spins > (1u << 23)) { atomicAdd(&a.counters[CNT_TIMEOUT], 1ull); break; }   // > 1 s: give up loudly
+                    if (ld_volatile_u64(a.counters + CNT_PDONE) >= n_tiles) {      // every tile decided: final answer
+                        __threadfence();
+                        e = ld_volatile_u64(a.tile_list + slot);
+                        break;
+                    }
+                    __nanosleep(200);
+                }
+            }
+            e = __shfl_sync(kFull, e, 0);
+            if ((e >> 32) != seq) break;                       // beyond the last published tile: no more work
+            __threadfence();
+            const unsigned tile = (unsigned)(e & 0xffffffffull);
+            shadow_item(a, st, tile, light, lane, exact_count);
+            ++n_s;
+            unsigned last = 0;
+            if (lane == 0) {
+                __threadfence();                               // the mask before the completion count
+                last = atomicAdd(a.tile_done + tile, 1u) == N - 1 ? 1u : 0u;
+            }
+            last = __shfl_sync(kFull, last, 0);
+            if (last) {
+                __threadfence();
+                shade_tile_from_memory(a, tile, lane);
+                ++n_c;
+            }
+        }
+    }
+
+    if (a.debug_timeline == 2 && a.t) {
+        asm volatile("mov.u64 %0, %globaltimer;" : "=l"(ts2));
+        __syncwarp();
+        if (lane == 0) {
+            unsigned long long* out = reinterpret_cast<unsigned long long*>(a.t) + 8 * (size_t)(blockIdx.x * (kThreads / 32) + (threadIdx.x >> 5));
+            out[0] = ts0; out[1] = ts1; out[2] = ts2; out[3] = n_p; out[4] = n_s; out[5] = n_c;
+        }
+    }
+    for (int s = 16; s > 0; s >>= 1) exact_count += __shfl_xor_sync(kFull, exact_count, s);
+    if (lane == 0) {
+        if (hits) atomicAdd(&a.counters[CNT_HIT], (unsigned long long)hits);
+        if (exact_count) atomicAdd(&a.counters[CNT_EXACT], (unsigned long long)exact_count);
+    }
+}
+
+__global__ void __launch_bounds__(kThreads) classify_kernel(const __grid_constant__ KArgs a) { phase_classify(a); }
+
+// The stages as separate launches (profiling each on its own).
 template <int PHASE>
 __global__ void __launch_bounds__(kThreads) render_phase(const __grid_constant__ KArgs a) {
     extern __shared__ uint32_t smem[];
     unsigned exact_count = 0;
-    if (PHASE == 3) phase_classify(a);
     if (PHASE == 0) phase_primary(a, smem, exact_count);
     if (PHASE == 1) phase_shadow(a, smem, exact_count);
     if (PHASE == 2) phase_shade(a);
@@ -489,31 +606,34 @@ cudaError_t launch_render_phased(const KArgs& a, int variant, int sm_count, cuda
     const size_t smem = phased_smem_bytes(a.stack_cap);
     static bool attr_set = false;
     if (!attr_set) {
-        cudaFuncSetAttribute(render_phased, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024);
+        cudaFuncSetAttribute(render_dataflow, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024);
         cudaFuncSetAttribute(render_phase<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024);
         cudaFuncSetAttribute(render_phase<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024);
         cudaFuncSetAttribute(render_phase<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024);
-        cudaFuncSetAttribute(render_phase<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024);
         attr_set = true;
     }
     int per_sm = 0;
-    cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, render_phased, kThreads, smem);
+    cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, render_dataflow, kThreads, smem);
     if (e != cudaSuccess) return e;
     if (per_sm < 1) return cudaErrorLaunchOutOfResources;
+    // Persistent grid: exactly the resident capacity.  (The dataflow kernel's waiting warps only wait for
+    // warps that already hold a tile, so it would also be correct with a larger grid.)
     int blocks = sm_count * per_sm;
     const int need = (n_tiles + kThreads / 32 - 1) / (kThreads / 32);
     if (blocks > need) blocks = need;
+    int cblocks = (n_tiles + kThreads - 1) / kThreads;
+    if (cblocks > sm_count * 8) cblocks = sm_count * 8;
+    classify_kernel<<<cblocks, kThreads, 0, stream>>>(a);
     if (variant == SRT_VARIANT_SPLIT) {
-        render_phase<3><<<blocks, kThreads, smem, stream>>>(a);
         render_phase<0><<<blocks, kThreads, smem, stream>>>(a);
         if (a.n_objects >= 2 && a.light_count > 0) render_phase<1><<<blocks, kThreads, smem, stream>>>(a);
         render_phase<2><<<blocks, kThreads, smem, stream>>>(a);
         if (launches) *launches = 4;
         return cudaGetLastError();
     }
-    void* params[] = {(void*)&a};
-    if (launches) *launches = 1;
-    return cudaLaunchCooperativeKernel((const void*)render_phased, dim3(blocks), dim3(kThreads), params, smem, stream);
+    render_dataflow<<<blocks, kThreads, smem, stream>>>(a);
+    if (launches) *launches = 2;
+    return cudaGetLastError();
 }
 
 }  // namespace srtk
