@@ -507,3 +507,17 @@ int ref_selfcheck(void* h, int W, int H, const float* light4) {
 int ref_chdir(const char* dir) { return chdir(dir); }
 
 }  // extern "C"
+
+// Decode an image file with the reference's own stb_image (compiled into Object.o): used by
+// oracle/stage_assets.py to write the `.rgb8` sidecars the product's host mirror reads.
+extern "C" unsigned char* stbi_load(char const* filename, int* x, int* y, int* channels_in_file, int desired_channels);
+extern "C" void stbi_image_free(void* p);
+extern "C" int ref_decode_texture(const char* path, unsigned char* out, int cap, int* w, int* h) {
+    int ch = 0;
+    unsigned char* d = stbi_load(path, w, h, &ch, 3);
+    if (!d) return -1;
+    const long n = (long)(*w) * (*h) * 3;
+    if (out && n <= cap) std::memcpy(out, d, (size_t)n);
+    stbi_image_free(d);
+    return (out && n > cap) ? -2 : 0;
+}

@@ -74,6 +74,47 @@ def ref_scene():
     return get
 
 
+def flat_from_fixture(fx):
+    """FlatSceneArrays from the arrays embedded in a golden frame fixture."""
+    from simple_raytracer_b200 import _abi
+    return _abi.FlatSceneArrays(fx["nodes"], fx["geom"], fx["attr"], fx["objects"], (),
+                                fx["flat_geom"] if "flat_geom" in fx.files else None,
+                                fx["flat_attr"] if "flat_attr" in fx.files else None,
+                                [str(x) for x in fx["object_names"]])
+
+
+_fixture_scene_cache = {}
+
+
+def scene_for_fixture(key, fx):
+    """(arrays, light) for golden frame `key`: the embedded scene when the fixture carries one, else built
+    with this repo's host mirror from the staged assets (textured C4: through oracle/_ref, because the
+    mirror triangulates 7 n-gon faces of house.obj differently — DESIGN.md)."""
+    from oracle import pyoracle
+    from simple_raytracer_b200 import host, scenes
+    if key in _fixture_scene_cache:
+        return _fixture_scene_cache[key]
+    if "nodes" in fx.files:
+        out = (flat_from_fixture(fx), np.asarray(fx["light"], np.float32))
+    else:
+        cfg = scenes.CONFIGS[key]
+        if cfg.needs_textures:
+            if not pyoracle.ref_available():
+                pytest.skip("textured golden needs oracle/_ref (reference-built scene)")
+            b = pyoracle.RefBackend()
+        else:
+            try:
+                host.assets_dir()
+            except FileNotFoundError:
+                pytest.skip("staged assets not present")
+            b = host.HostScene()
+        view = cfg.build(b, 0.0)
+        light = scenes.light_view_space(b, view) if view is not None else np.array(scenes.LIGHT_WORLD, np.float32)
+        out = (b.flatten(with_flat_lists=not cfg.use_bvh), np.asarray(light, np.float32))
+    _fixture_scene_cache[key] = out
+    return out
+
+
 def compare_images(a, b):
     """max abs error and PSNR between two uint8 images."""
     d = a.astype(np.int32) - b.astype(np.int32)

@@ -23,6 +23,7 @@ CASES = [
     ("C3", 480, 270, 270.0, 16),
     ("spheres", 300, 200, 200.0, 8),
     ("cubes4", 300, 200, 200.0, 4),
+    ("C4", 480, 270, 270.0, 2),         # textured multi-object scene (texture lookup path :350-361)
 ]
 
 
@@ -110,3 +111,55 @@ def test_oracle_matches_reference_on_gpu_box(ref_scene):
     got = pyoracle.oracle_render(arrays, p)
     for k in ("rgb", "obj_id", "tri_id", "t"):
         assert np.array_equal(want[k], got[k]), k
+
+
+def test_full_size_c3_variants_agree_and_sample_matches_oracle(gpu_ctx, ref_scene):
+    """BASELINE configs[2] at its full size (1920x1080, 16 lights): the three kernel variants give identical
+    bytes (the simple kernel evaluates every slab test with the exact divisions, the phased ones with the
+    filter), and every 48th pixel column equals the oracle."""
+    _b, arrays, light = ref_scene("C3")
+    W, H, focal, N = 1920, 1080, 1080.0, 16
+    sc = gpu_ctx.upload(arrays)
+    outs = []
+    for variant in (0, 3, 1):
+        p = _abi.default_params(W, H, focal, light, N, True)
+        p.variant = variant
+        outs.append(gpu_ctx.render(sc, p))
+    sc.destroy()
+    for o in outs[1:]:
+        for k in ("rgb", "obj_id", "tri_id", "t"):
+            assert np.array_equal(outs[0][k], o[k]), k
+    assert outs[0]["stats"]["kernel_launches"] == 2 and outs[1]["stats"]["kernel_launches"] == 4
+    p = _abi.default_params(W, H, focal, light, N, True)
+    want = pyoracle.oracle_render(arrays, p, col_begin=7, col_step=48)
+    cols = np.arange(7, W, 48)
+    assert np.array_equal(outs[0]["tri_id"][:, cols], want["tri_id"][:, cols])
+    assert np.array_equal(outs[0]["t"][:, cols], want["t"][:, cols])
+    assert compare_images(outs[0]["rgb"][:, cols], want["rgb"][:, cols])[0] <= 1
+    rays = W * H + N * outs[0]["stats"]["hit_pixels"]
+    print(f"C3 full size: {rays/1e6:.1f} M rays, phased {outs[0]['stats']['kernel_ms']:.3f} ms, split "
+          f"{outs[1]['stats']['kernel_ms']:.3f} ms, simple {outs[2]['stats']['kernel_ms']:.3f} ms; exact slab fallbacks "
+          f"{outs[0]['stats']['exact_slab_tests']}")
+
+
+def test_full_size_c4_textured_4k(gpu_ctx, ref_scene):
+    """BASELINE configs[3] at 3840x2160: variants agree byte for byte, a column sample equals the oracle,
+    and rendering twice gives the same bytes (idempotence)."""
+    _b, arrays, light = ref_scene("C4")
+    W, H, focal, N = 3840, 2160, 2160.0, 1
+    sc = gpu_ctx.upload(arrays)
+    p = _abi.default_params(W, H, focal, light, N, True)
+    a = gpu_ctx.render(sc, p)
+    b = gpu_ctx.render(sc, p)
+    p.variant = 1
+    c = gpu_ctx.render(sc, p)
+    sc.destroy()
+    for k in ("rgb", "obj_id", "tri_id", "t"):
+        assert np.array_equal(a[k], b[k]) and np.array_equal(a[k], c[k]), k
+    p.variant = 0
+    want = pyoracle.oracle_render(arrays, p, col_begin=11, col_step=96)
+    cols = np.arange(11, W, 96)
+    assert np.array_equal(a["tri_id"][:, cols], want["tri_id"][:, cols])
+    assert np.array_equal(a["t"][:, cols], want["t"][:, cols])
+    assert compare_images(a["rgb"][:, cols], want["rgb"][:, cols])[0] <= 1
+    print(f"C4 4K: phased {a['stats']['kernel_ms']:.3f} ms, simple {c['stats']['kernel_ms']:.3f} ms, hit pixels {a['stats']['hit_pixels']}")

@@ -1,0 +1,124 @@
+"""CPU tests of the host-side scene mirror (csrc/host): same names, argument meaning and error behaviour
+as the reference's ObjectManager / Transformation (Object.h:59-89, Transformation.h:10-20), and — where
+oracle/_ref exists — byte-identical flattened scenes."""
+import numpy as np
+import pytest
+
+from oracle import pyoracle
+from simple_raytracer_b200 import _abi, capi, host, scenes
+
+
+def need_assets():
+    try:
+        host.assets_dir()
+    except FileNotFoundError:
+        pytest.skip("staged assets not present")
+
+
+def test_obj_number_parser():
+    """tinyobjloader's tryParseDouble rules that decide vertex bits."""
+    assert host.parse_obj_number("1.5") == 1.5
+    assert host.parse_obj_number("-0.033") == -0.033
+    assert host.parse_obj_number("1e3") == 1000.0
+    assert host.parse_obj_number("+2.5E-2") == 0.025
+    assert host.parse_obj_number(".5") == 0.5
+    assert host.parse_obj_number("abc") is None
+
+
+def test_load_defaults_and_errors():
+    need_assets()
+    s = host.HostScene()
+    n = s.load_obj("cube.obj")
+    assert n == 12
+    assert s.get_properties("cube.obj") == (np.float32(0.2), np.float32(0.5), np.float32(15.0))   # Object.cpp:29-34
+    tris, flags = s.triangles("cube.obj")
+    assert tris.shape == (12, 30) and not flags.any()
+    assert np.all(tris[:, [3, 7, 11]] == 1.0)                                                     # w = 1
+    with pytest.raises(KeyError):
+        s.clone("nope.obj", "x.obj", False)                                                       # std::out_of_range, Object.cpp:174
+    with pytest.raises(KeyError):
+        s.triangles("nope.obj")
+    # an object without a bounding hierarchy is what the reference would dereference as a null Node* (:298)
+    with pytest.raises(capi.SrtError) as e:
+        s.flatten()
+    assert e.value.code == _abi.SRT_ERR_SCENE
+    s.create_bounding_hierarchy("cube.obj")
+    a = s.flatten(with_flat_lists=True)
+    assert len(a.geom) == 12 and len(a.flat_geom) == 12 and len(a.nodes) == 3 and a.max_depth == 1
+    # missing file: the reference prints and continues with an empty object (Object.cpp:35-39)
+    s2 = host.HostScene()
+    assert s2.load_obj("does_not_exist.obj") <= 0
+
+
+def test_flat_layout_invariants():
+    need_assets()
+    s = host.HostScene()
+    view = scenes.build_bunny_ground(s, 0.0)
+    a = s.flatten()
+    assert a.object_names == ["./obj/stanford-bunny.obj", "./obj/cube.obj"]          # unordered_map iteration order (S2)
+    assert len(a.geom) == 69451 + 12
+    leaf = (a.nodes["b"] & _abi.SRT_LEAF_BIT) != 0
+    cnt = a.nodes["b"][leaf] & 0x7fffffff
+    assert cnt.max() <= 8 and cnt.sum() == len(a.geom)                               # leaf size rule, Object.cpp:261
+    assert np.array_equal(np.sort(a.nodes["a"][leaf]), np.concatenate([[0], np.cumsum(cnt[np.argsort(a.nodes["a"][leaf])])[:-1]]))
+    # every triangle lies inside its leaf's box (boxes are min/max of the vertices, Object.cpp:205-221)
+    first = a.nodes["a"][leaf]; lo = a.nodes["bmin"][leaf]; hi = a.nodes["bmax"][leaf]
+    for f, c, l, h in list(zip(first, cnt, lo, hi))[::97]:
+        g = a.geom[f:f + c]
+        pts = np.concatenate([g["p0"], g["p0"] + g["e1"], g["p0"] + g["e2"]])
+        assert np.all(pts >= l - 1e-4) and np.all(pts <= h + 1e-4)
+    light = scenes.light_view_space(s, view)
+    assert np.allclose(light[:3], [-200.00002, 8.493649, -514.7114], atol=1e-3)
+
+
+@pytest.mark.ref
+@pytest.mark.parametrize("key", ["C1", "C3", "shipped", "spheres", "cubes4"])
+def test_mirror_flattens_byte_identical_to_reference(key):
+    cfg = scenes.CONFIGS[key]
+    rb = pyoracle.RefBackend(); rv = cfg.build(rb, 0.0); ra = rb.flatten(with_flat_lists=not cfg.use_bvh)
+    hb = host.HostScene(); hv = cfg.build(hb, 0.0); ha = hb.flatten(with_flat_lists=not cfg.use_bvh)
+    assert ra.object_names == ha.object_names
+    for k in ("nodes", "geom", "attr", "objects"):
+        assert np.array_equal(getattr(ra, k).view(np.uint8), getattr(ha, k).view(np.uint8)), k
+    if not cfg.use_bvh:
+        assert np.array_equal(ra.flat_geom.view(np.uint8), ha.flat_geom.view(np.uint8))
+    if rv is not None:
+        assert np.array_equal(np.asarray(rv).view(np.uint32), np.asarray(hv).view(np.uint32))
+
+
+@pytest.mark.ref
+def test_mirror_series_frame_and_textured_scene():
+    """A rotated series frame (C5) is byte-identical; the textured scene is identical except house.obj,
+    whose 7 n-gon faces the mirror fan-triangulates (the reference uses earcut) — DESIGN.md open item."""
+    cfg = scenes.CONFIGS["C3"]
+    rb = pyoracle.RefBackend(); cfg.build(rb, 37.5); ra = rb.flatten()
+    hb = host.HostScene(); cfg.build(hb, 37.5); ha = hb.flatten()
+    for k in ("nodes", "geom", "attr", "objects"):
+        assert np.array_equal(getattr(ra, k).view(np.uint8), getattr(ha, k).view(np.uint8)), k
+    cfg = scenes.CONFIGS["C4"]
+    rb = pyoracle.RefBackend(); cfg.build(rb, 0.0); ra = rb.flatten()
+    hb = host.HostScene(); cfg.build(hb, 0.0); ha = hb.flatten()
+    assert ra.object_names == ha.object_names and ra.texture_names == ha.texture_names
+    assert all(np.array_equal(a, b) for a, b in zip(ra.textures, ha.textures))       # sidecars == stb_image pixels
+    assert np.array_equal(ra.objects.view(np.uint8), ha.objects.view(np.uint8))
+    house = ra.object_names.index("./obj/house/house.obj")
+    other = ra.geom["obj"] != house
+    assert np.array_equal(ra.geom[other].view(np.uint8), ha.geom[other].view(np.uint8))
+    assert np.array_equal(ra.attr[other].view(np.uint8), ha.attr[other].view(np.uint8))
+
+
+def test_transformation_matrices():
+    """Transformation.cpp:6-90: column-major mat4, translation in column 3, view = T*Rz*Ry*Rx."""
+    s = host.HostScene()
+    T = s.xf_translate(1, 2, 3).reshape(4, 4)
+    assert T[3].tolist() == [1, 2, 3, 1]
+    S = s.xf_scale(2, 3, 4).reshape(4, 4)
+    assert np.diag(S).tolist() == [2, 3, 4, 1]
+    R = s.xf_rotate_y(s.radians(90.0)).reshape(4, 4)
+    v = s.mat_vec(R.reshape(16), (1, 0, 0, 1))
+    assert np.allclose(np.abs(v[:3]), [0, 0, 1], atol=1e-6)
+    M = s.xf_view((1, 2, 3), (0.1, 0.2, 0.3))
+    I = s.mat_mul(M, s.mat_inverse(M)).reshape(4, 4)
+    assert np.allclose(I, np.eye(4), atol=1e-5)
+    Mi = s.xf_mirror(1, 0, 0).reshape(4, 4)
+    assert np.diag(Mi).tolist() == [-1, 1, 1, 1]

@@ -1,0 +1,135 @@
+"""CPU tests: the oracle (oracle/srt_oracle.c, the plain-C restatement) against the committed golden
+vectors, which are outputs of the UNMODIFIED reference (tests/golden/make_golden.py), and — where
+oracle/_ref exists — against the reference itself, live.  Everything here is bit-exact."""
+import ctypes as C
+from pathlib import Path
+
+import numpy as np
+import pytest
+
+from conftest import GOLDEN, flat_from_fixture, scene_for_fixture
+from oracle import pyoracle
+from simple_raytracer_b200 import _abi
+
+f32 = np.float32
+_f32p = C.POINTER(C.c_float)
+FRAME_KEYS = ["C1", "C1b", "cubes4", "spheres", "shipped", "C2", "C3", "C4"]
+
+
+def fp(a):
+    return np.ascontiguousarray(a, dtype=f32).ctypes.data_as(_f32p)
+
+
+@pytest.fixture(scope="module")
+def kat():
+    return np.load(GOLDEN / "leaf_kat.npz")
+
+
+def tri_edges(tri):
+    """The flattener's p0 / e1 / e2 (rayTriangleIntersection :45-51) from 3 x vec4, in fp32."""
+    p = tri.reshape(-1, 3, 4)
+    c = (p[:, :, :3] / p[:, :, 3:4]).astype(f32)
+    return c[:, 0], (c[:, 1] - c[:, 0]).astype(f32), (c[:, 2] - c[:, 0]).astype(f32)
+
+
+def same_bits(a, b):
+    a = np.ascontiguousarray(a, f32).view(np.uint32)
+    b = np.ascontiguousarray(b, f32).view(np.uint32)
+    nan = np.isnan(a.view(f32)) & np.isnan(b.view(f32))
+    return bool(np.all((a == b) | nan | ((a.view(f32) == 0) & (b.view(f32) == 0))))
+
+
+def test_moller_trumbore_kat(kat):
+    lib = pyoracle.oracle_lib()
+    p0, e1, e2 = tri_edges(kat["tri"])
+    got = np.array([lib.srt_oracle_moller_trumbore(fp(kat["o"][i]), fp(kat["d"][i]), fp(p0[i]), fp(e1[i]), fp(e2[i]))
+                    for i in range(len(p0))], f32)
+    assert same_bits(got, kat["t"])
+    assert np.isfinite(kat["t"]).sum() > 500            # the vectors do exercise hits
+
+
+def test_slab_kat(kat):
+    lib = pyoracle.oracle_lib()
+    n = len(kat["o"])
+    got = np.array([lib.srt_oracle_slab(fp(kat["o"][i]), fp(kat["d"][i]), fp(kat["bmin"][i]), fp(kat["bmax"][i])) for i in range(n)])
+    assert np.array_equal(got != 0, kat["slab"] != 0)
+    zero = np.zeros(3, f32)                             # intersectRayAabb :204-248 == origin (0,0,0)
+    got0 = np.array([lib.srt_oracle_slab(fp(zero), fp(kat["d"][i]), fp(kat["bmin"][i]), fp(kat["bmax"][i])) for i in range(n)])
+    assert np.array_equal(got0 != 0, kat["slab0"] != 0)
+
+
+def test_barycentric_and_phong_kat(kat):
+    lib = pyoracle.oracle_lib()
+    p0, e1, e2 = tri_edges(kat["tri"])
+    n = len(p0)
+    white = np.ones(3, f32)
+    bary = np.zeros((n, 3), f32)
+    ph = np.zeros((n, 3), f32)
+    for i in range(n):
+        out = np.zeros(3, f32)
+        lib.srt_oracle_barycentric(fp(p0[i]), fp(e1[i]), fp(e2[i]), fp(kat["point"][i]), fp(out))
+        bary[i] = out
+        out2 = np.zeros(3, f32)
+        a, s, sh = [float(x) for x in kat["props"][i]]
+        lib.srt_oracle_phong(fp(kat["normal"][i]), fp(kat["d"][i]), fp(kat["light"][i]), fp(white), fp(kat["color"][i]),
+                             a, s, sh, float(kat["tdist"][i]), fp(out2))
+        ph[i] = out2
+    assert same_bits(bary, kat["bary"])
+    assert same_bits(ph, kat["phong"])
+
+
+def test_tonemap_quantise_kat(kat):
+    lib = pyoracle.oracle_lib()
+    m = len(kat["tone_in"])
+    for i in range(m):
+        out = np.zeros(3, f32)
+        q = np.zeros(3, np.int32)
+        lib.srt_oracle_tonemap_quantise(fp(kat["tone_in"][i]), 0.5, f32(1.1), fp(out), q.ctypes.data_as(C.POINTER(C.c_int32)))
+        assert same_bits(out, kat["tone"][i]), i
+        assert np.array_equal(q & 0xff, kat["q"][i] & 0xff), i
+
+
+def test_light_staircase_matches_reference_sequence():
+    """softShadow :363-383: +3 on x, y, z cyclically, sequential fp32 adds."""
+    lib = pyoracle.oracle_lib()
+    L0 = np.array([-200.00002, 8.493649, -514.7114], f32)
+    out = np.zeros((16, 3), f32)
+    lib.srt_oracle_light_positions(fp(L0), 16, 3.0, fp(out))
+    want = np.zeros((16, 3), f32)
+    L = L0.copy()
+    for i in range(16):
+        want[i] = L
+        L[i % 3] = f32(L[i % 3] + f32(3.0))
+    assert same_bits(out, want)
+
+
+@pytest.mark.parametrize("key", FRAME_KEYS)
+def test_oracle_reproduces_reference_frames(key):
+    """Whole frames rendered by the reference (committed) == the oracle on the same scene, every plane."""
+    fx = np.load(GOLDEN / f"frame_{key}.npz")
+    arrays, light = scene_for_fixture(key, fx)
+    W, H, focal, N, use_bvh = [float(x) for x in fx["params"]]
+    assert np.allclose(light[:3], fx["light"], rtol=0, atol=0)
+    p = _abi.default_params(int(W), int(H), focal, fx["light"], int(N), bool(use_bvh))
+    got = pyoracle.oracle_render(arrays, p)
+    assert np.array_equal(got["obj_id"], fx["obj_id"])
+    assert np.array_equal(got["tri_id"], fx["tri_id"])
+    assert same_bits(got["t"], fx["t"])
+    assert np.array_equal(got["rgb"], fx["rgb"])
+    assert (fx["obj_id"] >= 0).sum() > 100
+
+
+@pytest.mark.ref
+def test_oracle_vs_live_reference_and_selfcheck(ref_scene):
+    """Restated loops == the verbatim sendRaysAndIntersectPointsColors at the shipped constants, and the
+    oracle == the reference's functions on a frame that is not among the committed ones."""
+    b, arrays, light = ref_scene("shipped")
+    l4 = np.array([light[0], light[1], light[2], 1.0], f32)
+    assert b.selfcheck(60, 40, l4) == 0
+    for (W, H, focal, N) in ((75, 50, 50.0, 3), (33, 21, 400.0, 1)):
+        p = _abi.default_params(W, H, focal, light, N, True)
+        want = b.render(W, H, focal, light, N, True, faithful=True)
+        got = pyoracle.oracle_render(arrays, p)
+        for k in ("rgb", "obj_id", "tri_id"):
+            assert np.array_equal(want[k], got[k]), k
+        assert same_bits(want["t"], got["t"])
