@@ -134,7 +134,11 @@ typedef struct srt_render_params {
     int32_t row_begin, row_end;   /* render rows [row_begin,row_end); 0,0 = all rows (tile-row shard) */
     int32_t variant;              /* SRT_VARIANT_* kernel selection, 0 = default */
     int32_t no_sky_fill;          /* 1: leave miss / black-hit pixels (0,0,0) (rebuilding ImageData :518) */
-    int32_t reserved[3];
+    /* Interleaved row-block sharding of ONE frame over several GPUs: of the blocks of `row_block` rows
+     * (a multiple of 4; 0 = no sharding) that make up [row_begin,row_end), render blocks shard_index,
+     * shard_index + shard_count, ...  Pixels are independent (:511-523), so the union of the shards is
+     * byte-identical to one full render. */
+    int32_t row_block, shard_index, shard_count;
 } srt_render_params;
 
 enum { SRT_VARIANT_DEFAULT = 0,   /* phased persistent kernel (falls back to SIMPLE for the legacy one-box path) */

@@ -60,7 +60,8 @@ class RenderParams(C.Structure):
         ("light_color", C.c_float * 3), ("shadow_div", C.c_float), ("tone_k", C.c_float),
         ("gamma", C.c_float), ("sky", C.c_uint8 * 3), ("pad0", C.c_uint8),
         ("use_bvh", C.c_int32), ("row_begin", C.c_int32), ("row_end", C.c_int32),
-        ("variant", C.c_int32), ("no_sky_fill", C.c_int32), ("reserved", C.c_int32 * 3),
+        ("variant", C.c_int32), ("no_sky_fill", C.c_int32), ("row_block", C.c_int32),
+        ("shard_index", C.c_int32), ("shard_count", C.c_int32),
     ]
 
 

@@ -141,6 +141,7 @@ class Context:
         _check(lib().srt_context_create(int(device), C.byref(h)))
         self.h = h
         self.device = int(device)
+        self.stream = stream              # None: the context's own stream
         if stream is not None:
             _check(lib().srt_context_set_stream(self.h, C.c_void_p(stream)))
 

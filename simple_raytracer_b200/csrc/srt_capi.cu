@@ -437,6 +437,23 @@ int srt_render(srt_context* c, const srt_scene* s, const srt_render_params* p, c
     a.use_bvh = p->use_bvh;
     a.tiles_x = (p->width + srtk::kTileW - 1) / srtk::kTileW;
     a.tiles_y = (re - rb + srtk::kTileH - 1) / srtk::kTileH;
+    uint64_t my_rows = (uint64_t)(re - rb);
+    if (p->row_block != 0 || p->shard_count > 1) {
+        if (p->row_block <= 0 || p->row_block % srtk::kTileH != 0 || p->shard_count < 1 || p->shard_index < 0 ||
+            p->shard_index >= p->shard_count)
+            return fail(SRT_ERR_INVALID_ARG, "bad row sharding: row_block %d (multiple of %d), shard %d of %d", p->row_block,
+                        srtk::kTileH, p->shard_index, p->shard_count);
+        a.block_tile_rows = p->row_block / srtk::kTileH;
+        a.shard_index = p->shard_index; a.shard_count = p->shard_count;
+        const int n_blocks = (a.tiles_y + a.block_tile_rows - 1) / a.block_tile_rows;
+        const int mine = n_blocks > p->shard_index ? (n_blocks - p->shard_index + p->shard_count - 1) / p->shard_count : 0;
+        a.tiles_y = mine * a.block_tile_rows;
+        my_rows = 0;
+        for (int b = p->shard_index; b < n_blocks; b += p->shard_count) {
+            const int r0 = rb + b * p->row_block, r1 = r0 + p->row_block < re ? r0 + p->row_block : re;
+            my_rows += (uint64_t)(r1 - r0);
+        }
+    }
     a.counters = c->counters;
     int rc = srt_light_positions(p, a.lights);
     if (rc) return rc;
@@ -500,15 +517,22 @@ int srt_render(srt_context* c, const srt_scene* s, const srt_render_params* p, c
     CU(cudaEventRecord(c->ev1, c->stream));
     CU(cudaMemcpyAsync(c->counters_host, c->counters, sizeof(unsigned long long) * srtk::CNT_WORDS,
                        cudaMemcpyDeviceToHost, c->stream));
-    // copy back only the rendered rows
-    const size_t row0 = (size_t)rb * p->width, nrow = (size_t)(re - rb) * p->width;
+    // copy back only the rendered rows (per owned block when the frame is sharded)
     for (auto& pl : planes) {
-        if (!pl.host || nrow == 0) continue;
-        CU(cudaMemcpyAsync((char*)pl.user + row0 * pl.elem, (char*)pl.stage->p + row0 * pl.elem, nrow * pl.elem,
-                           cudaMemcpyDeviceToHost, c->stream));
+        if (!pl.host) continue;
+        const int step = a.block_tile_rows > 0 ? p->row_block * p->shard_count : (re - rb);
+        const int first = a.block_tile_rows > 0 ? rb + p->shard_index * p->row_block : rb;
+        const int rows = a.block_tile_rows > 0 ? p->row_block : (re - rb);
+        for (int r0 = first; r0 < re && step > 0; r0 += step) {
+            const int r1 = r0 + rows < re ? r0 + rows : re;
+            const size_t at = (size_t)r0 * p->width, n = (size_t)(r1 - r0) * p->width;
+            if (n == 0) continue;
+            CU(cudaMemcpyAsync((char*)pl.user + at * pl.elem, (char*)pl.stage->p + at * pl.elem, n * pl.elem,
+                               cudaMemcpyDeviceToHost, c->stream));
+        }
     }
     c->have_last = true;
-    c->last_primary = (uint64_t)(re - rb) * (uint64_t)p->width;
+    c->last_primary = my_rows * (uint64_t)p->width;
     c->last_lights = p->light_count;
     c->last_objects = s->n_objects;
     return SRT_OK;

@@ -119,7 +119,8 @@ __global__ void __launch_bounds__(128) render_simple(const __grid_constant__ KAr
         tile = __shfl_sync(0xffffffffu, tile, 0);
         if ((int)tile >= n_tiles) break;
         const int tx = (int)(tile % (unsigned)a.tiles_x), ty = (int)(tile / (unsigned)a.tiles_x);
-        const int px = tx * kTileW + (int)(lane & 7), py = a.row_begin + ty * kTileH + (int)(lane >> 3);
+        const int px = tx * kTileW + (int)(lane & 7);
+        const int py = tile_row_to_py(a.row_begin, a.block_tile_rows, a.shard_index, a.shard_count, ty) + (int)(lane >> 3);
         long long tl_c0 = 0; unsigned long long tl_ns = 0;
         if (TIMELINE) { tl_c0 = clock64(); asm volatile("mov.u64 %0, %globaltimer;" : "=l"(tl_ns)); }
         if (px >= a.width || py >= a.row_end) continue;

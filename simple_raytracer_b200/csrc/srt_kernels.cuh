@@ -35,7 +35,8 @@ struct KArgs {
     uint8_t sky[3];
     uint8_t no_sky_fill;
     int32_t use_bvh;
-    int32_t tiles_x, tiles_y;   // 8x4-pixel warp tiles over [row_begin,row_end)
+    int32_t tiles_x, tiles_y;   // 8x4-pixel warp tiles this launch renders (its shard of [row_begin,row_end))
+    int32_t block_tile_rows, shard_index, shard_count;   // row-block sharding: tile rows per block; 0 = off
     uint8_t* rgb;
     int32_t* obj_id;
     int32_t* tri_id;
@@ -59,6 +60,15 @@ struct KArgs {
 };
 
 constexpr int kTileW = 8, kTileH = 4;          // one warp = 8x4 pixels
+
+// First pixel row of local tile row `ty` (interleaved row-block sharding, see srt_render_params).
+__host__ __device__ inline int tile_row_to_py(int row_begin, int block_tile_rows, int shard_index, int shard_count, int ty) {
+    if (block_tile_rows > 0) {
+        const int blk = ty / block_tile_rows, off = ty - blk * block_tile_rows;
+        ty = (blk * shard_count + shard_index) * block_tile_rows + off;
+    }
+    return row_begin + ty * kTileH;
+}
 constexpr int kMaxStack = 64;                  // >= deepest BVH the upload accepts
 
 // variant: SRT_VARIANT_*; returns cudaError_t from the launch.

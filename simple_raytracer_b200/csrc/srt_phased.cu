@@ -205,7 +205,7 @@ __device__ __forceinline__ Pixel pixel_of(const KArgs& a, unsigned tile, unsigne
     const int tx = (int)(tile % (unsigned)a.tiles_x), ty = (int)(tile / (unsigned)a.tiles_x);
     Pixel p;
     p.px = tx * kTileW + (int)(lane & 7);
-    p.py = a.row_begin + ty * kTileH + (int)(lane >> 3);
+    p.py = tile_row_to_py(a.row_begin, a.block_tile_rows, a.shard_index, a.shard_count, ty) + (int)(lane >> 3);
     p.valid = p.px < a.width && p.py < a.row_end;
     return p;
 }
@@ -256,7 +256,7 @@ __device__ __forceinline__ void phase_classify(const KArgs& a) {
             const int tx = (int)(tile % (unsigned)a.tiles_x), ty = (int)(tile / (unsigned)a.tiles_x);
             for (int c = 0; c < 4 && !heavy; ++c) {
                 const int px = tx * kTileW + ((c & 1) ? kTileW - 1 : 0);
-                const int py = a.row_begin + ty * kTileH + ((c & 2) ? kTileH - 1 : 0);
+                const int py = tile_row_to_py(a.row_begin, a.block_tile_rows, a.shard_index, a.shard_count, ty) + ((c & 2) ? kTileH - 1 : 0);
                 const V3 d = v3((float)(px + a.i0), (float)(py + a.j0), a.focal);
                 const float ix = rcp_approx(d.x), iy = rcp_approx(d.y), iz = rcp_approx(d.z);
                 for (uint32_t ob = 0; ob < a.n_objects && !heavy; ++ob) {

@@ -163,3 +163,31 @@ def test_full_size_c4_textured_4k(gpu_ctx, ref_scene):
     assert np.array_equal(a["t"][:, cols], want["t"][:, cols])
     assert compare_images(a["rgb"][:, cols], want["rgb"][:, cols])[0] <= 1
     print(f"C4 4K: phased {a['stats']['kernel_ms']:.3f} ms, simple {c['stats']['kernel_ms']:.3f} ms, hit pixels {a['stats']['hit_pixels']}")
+
+
+@pytest.mark.parametrize("variant", [0, 1], ids=["phased", "simple"])
+def test_interleaved_row_block_shards_equal_full_frame(gpu_ctx, ref_scene, variant):
+    """Multi-GPU single-frame mode (row_block / shard_index / shard_count): the shards of 1, 3 and 8 'ranks',
+    rendered one after the other into the same buffers, reproduce the unsharded frame byte for byte."""
+    _b, arrays, light = ref_scene("C3")
+    W, H = 322, 181                      # not a multiple of the tile or the block size
+    p = _abi.default_params(W, H, 181.0, light, 4, True)
+    p.variant = variant
+    sc = gpu_ctx.upload(arrays)
+    full = gpu_ctx.render(sc, p)
+    for world, block in ((3, 16), (8, 4), (2, 32)):
+        rgb = np.zeros((H, W, 3), np.uint8)
+        tri = np.full((H, W), -7, np.int32)
+        t = np.zeros((H, W), np.float32)
+        hits = 0
+        for r in range(world):
+            p.row_block, p.shard_index, p.shard_count = block, r, world
+            gpu_ctx.render_raw(sc, p, rgb.ctypes.data, None, tri.ctypes.data, t.ctypes.data)
+            gpu_ctx.sync()
+            hits += gpu_ctx.last_stats()["hit_pixels"]
+        assert np.array_equal(rgb, full["rgb"]) and np.array_equal(tri, full["tri_id"]) and np.array_equal(t, full["t"])
+        assert hits == full["stats"]["hit_pixels"]
+    p.row_block, p.shard_index, p.shard_count = 6, 0, 2       # not a multiple of the tile height
+    with pytest.raises(Exception):
+        gpu_ctx.render_raw(sc, p, None, None, None, None)
+    sc.destroy()
