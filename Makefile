@@ -21,7 +21,7 @@ $(LIB): $(SRCS) $(HDRS)
 	$(NVCC) $(NVFLAGS) -shared -cudart static -o $@ $(SRCS)
 oracle:
 	$(MAKE) -C oracle oracle
-ref:
+ref: lib
 	$(MAKE) -C oracle ref
 clean:
 	rm -f $(LIB)

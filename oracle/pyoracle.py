@@ -149,6 +149,10 @@ def ref_lib():
         lib.ref_render_verbatim.restype = C.c_long
         lib.ref_render_verbatim.argtypes = [vp, i32, i32, _f32p, vp, C.POINTER(C.c_double)]
         lib.ref_selfcheck.argtypes = [vp, i32, i32, _f32p]
+        lib.ref_dropin_render.restype = C.c_long
+        lib.ref_dropin_render.argtypes = [vp, i32, i32, _f32p, _f32p, _f32p, C.c_long, C.c_char_p, i32]
+        lib.ref_verbatim_sparse.restype = C.c_long
+        lib.ref_verbatim_sparse.argtypes = [vp, i32, i32, _f32p, _f32p, _f32p, C.c_long]
         lib.ref_leaf_moller_trumbore.argtypes = [i32, _f32p, _f32p, _f32p, _f32p]
         lib.ref_leaf_slab.argtypes = [i32, _f32p, _f32p, _f32p, _f32p, C.POINTER(C.c_uint8)]
         lib.ref_leaf_slab_origin0.argtypes = [i32, _f32p, _f32p, _f32p, C.POINTER(C.c_uint8)]
@@ -344,6 +348,22 @@ class RefBackend:
         sec = C.c_double(0)
         n = self.lib.ref_render_verbatim(self.h, width, height, _fp(l4), rgb.ctypes.data, C.byref(sec))
         return dict(rgb=rgb, seconds=sec.value, points=int(n))
+
+    def sparse(self, width, height, light4, dropin):
+        """ImageData (points, colours) of the verbatim :505 function, or of include/srt_dropin.hpp's
+        srt::Renderer compiled against the reference's own types (needs a GPU)."""
+        l4 = np.asarray(light4, np.float32)
+        cap = width * height
+        pts = np.zeros((cap, 2), np.float32)
+        col = np.zeros((cap, 3), np.float32)
+        if dropin:
+            err = C.create_string_buffer(1024)
+            n = self.lib.ref_dropin_render(self.h, width, height, _fp(l4), _fp(pts), _fp(col), cap, err, 1024)
+            if n < 0:
+                raise RuntimeError("srt_dropin: " + err.value.decode(errors="replace"))
+        else:
+            n = self.lib.ref_verbatim_sparse(self.h, width, height, _fp(l4), _fp(pts), _fp(col), cap)
+        return pts[:n].copy(), col[:n].copy()
 
     def selfcheck(self, width, height, light4):
         l4 = np.asarray(light4, np.float32)

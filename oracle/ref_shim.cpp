@@ -521,3 +521,40 @@ extern "C" int ref_decode_texture(const char* path, unsigned char* out, int cap,
     stbi_image_free(d);
     return (out && n > cap) ? -2 : 0;
 }
+
+// ---- the drop-in adapter (include/srt_dropin.hpp) compiled against the REFERENCE's own types -------
+// Test only: proves that srt::Renderer::sendRaysAndIntersectPointsColors is a drop-in for :505 — same
+// ImageData type, same sparse column-major contents — by running it on the reference's ObjectManager.
+#include "srt_dropin.hpp"
+extern "C" long ref_dropin_render(void* h, int W, int Hh, const float* light4, float* points2, float* colors3, long cap,
+                                  char* err, int errlen) {
+    RefScene* s = (RefScene*)h;
+    try {
+        static srt::Renderer* gpu = nullptr;       // one context for the test process
+        if (!gpu) gpu = new srt::Renderer(0);
+        ImageData d = gpu->sendRaysAndIntersectPointsColors<ImageData>(glm::vec2((float)W, (float)Hh),
+                                                                      glm::vec4(light4[0], light4[1], light4[2], light4[3]), &s->om);
+        const long n = (long)d.imagePoints.size();
+        for (long i = 0; i < n && i < cap; ++i) {
+            points2[2 * i] = d.imagePoints[i].x; points2[2 * i + 1] = d.imagePoints[i].y;
+            colors3[3 * i] = d.imageColors[i].x; colors3[3 * i + 1] = d.imageColors[i].y; colors3[3 * i + 2] = d.imageColors[i].z;
+        }
+        return n;
+    } catch (const std::exception& e) {
+        if (err && errlen > 0) std::snprintf(err, (size_t)errlen, "%s", e.what());
+        return -1;
+    }
+}
+// The verbatim function's sparse output, for comparison.
+extern "C" long ref_verbatim_sparse(void* h, int W, int Hh, const float* light4, float* points2, float* colors3, long cap) {
+    RefScene* s = (RefScene*)h;
+    prepare_scene(s);
+    ImageData d = sendRaysAndIntersectPointsColors(glm::vec2((float)W, (float)Hh),
+                                                   glm::vec4(light4[0], light4[1], light4[2], light4[3]), &s->om);
+    const long n = (long)d.imagePoints.size();
+    for (long i = 0; i < n && i < cap; ++i) {
+        points2[2 * i] = d.imagePoints[i].x; points2[2 * i + 1] = d.imagePoints[i].y;
+        colors3[3 * i] = d.imageColors[i].x; colors3[3 * i + 1] = d.imageColors[i].y; colors3[3 * i + 2] = d.imageColors[i].z;
+    }
+    return n;
+}

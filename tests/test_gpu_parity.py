@@ -191,3 +191,19 @@ def test_interleaved_row_block_shards_equal_full_frame(gpu_ctx, ref_scene, varia
     with pytest.raises(Exception):
         gpu_ctx.render_raw(sc, p, None, None, None, None)
     sc.destroy()
+
+
+def test_dropin_adapter_equals_verbatim_reference_function(ref_scene):
+    """include/srt_dropin.hpp compiled against the REFERENCE's own ObjectManager / ImageData / glm types:
+    srt::Renderer::sendRaysAndIntersectPointsColors(imageSize, lightPos, &objManager) returns the same sparse,
+    column-major ImageData as the verbatim simple_raytracer.cpp:505 (same points in the same order; colours
+    within 1 LSB because powf is not bit-defined)."""
+    b, _arrays, light = ref_scene("shipped")
+    l4 = np.array([light[0], light[1], light[2], 1.0], np.float32)
+    W, H = 150, 100
+    want_p, want_c = b.sparse(W, H, l4, dropin=False)
+    got_p, got_c = b.sparse(W, H, l4, dropin=True)
+    assert len(want_p) > 1000
+    assert np.array_equal(want_p, got_p)
+    assert np.abs(want_c - got_c).max() <= 1.0
+    assert np.count_nonzero(want_c != got_c) <= 3
