@@ -299,6 +299,18 @@ def run_b200_arm(args):
         render_step(Wm + s)
         kernel_ms.append(ctx.last_stats()["kernel_ms"])
     kern_ms = float(np.mean(kernel_ms)) if kernel_ms else float("nan")
+    launches_per_step = ctx.last_stats()["kernel_launches"]
+    # algorithmic work of frame Wm (the first timed one) under the REFERENCE's traversal rules, counted by the
+    # instrumented CUDA kernel (SRT_VARIANT_COUNT; tests check its counters against the oracle's)
+    work = None
+    if rank == 0 and cfg.use_bvh:
+        k0 = Wm % n_unique
+        pc = _abi.default_params(W, H, focal, frames[k0][1], N, cfg.use_bvh)
+        pc.variant = _abi.VARIANT_COUNT
+        ctx.render_raw(scenes_dev[k0], pc, rgb=rgb.data_ptr())
+        st = ctx.last_stats()
+        work = dict(node_visits=st["node_visits"], tri_tests=st["tri_tests"], hit_pixels=st["hit_pixels"],
+                    light_evals=N * st["hit_pixels"])
 
     # ---- end to end through the C ABI from pinned host buffers ----
     e2e = None
@@ -380,13 +392,29 @@ def run_b200_arm(args):
             "rays_per_frame": rays_total / (K * world),
             "kernel_ms": kern_ms,
             "host_prep_ms_per_frame": prep_ms_max,
-            "gpu_launches": K * world,
+            "gpu_launches": K * world * launches_per_step,
             "clocks": clocks,
             "roofline": {"bound": "hbm", "achieved": ach, "peak": hbm_peak, "unit": "GB/s", "frac": ach / hbm_peak,
                          "traffic": None, "peak_source": "measured (MEASURED_PEAKS.json)" if peaks else "fallback",
                          "note": "scene is L2-resident by design: compulsory HBM bytes = one scene read + one RGB8 frame write; "
                                  "the kernel is latency/issue-bound, see DESIGN.md and profiles/"},
         }
+        if work:
+            # F_alg = 12 V + 45 T + 75 S + 30 hit flops, B_alg,L2 = 32 V + 48 T + 48 hit bytes per frame
+            V, T, S, hp = work["node_visits"], work["tri_tests"], work["light_evals"], work["hit_pixels"]
+            flops = 12.0 * V + 45.0 * T + 75.0 * S + 30.0 * hp
+            l2b = 32.0 * V + 48.0 * T + 48.0 * hp
+            sm_hz = (clocks or {}).get("sm_mhz") or float(peaks.get("sm_max_mhz", 1965.0))
+            fp32_peak = info["sm_count"] * 128 * sm_hz * 1e6 / 1e12          # non-FMA: the parity arithmetic may not contract
+            l2_peak = 6300.0 * sm_hz * 1e6 / 1e9                              # B300_MICROARCH.md LTS cap (B/cycle), not measured here
+            line["algorithmic_work_per_frame"] = dict(work, flops=flops, l2_bytes=l2b,
+                                                      rule="reference traversal rules (S3/S5/S11), own-object shadow traversal excluded")
+            line["roofline_fp32"] = {"bound": "fp32 issue (non-FMA)", "achieved": flops / (kern_ms * 1e-3) / 1e12, "peak": fp32_peak,
+                                     "unit": "TFLOP/s", "frac": flops / (kern_ms * 1e-3) / 1e12 / fp32_peak,
+                                     "peak_source": "148 SMs x 128 lanes x SM clock under load"}
+            line["roofline_l2"] = {"bound": "l2", "achieved": l2b / (kern_ms * 1e-3) / 1e9, "peak": l2_peak, "unit": "GB/s",
+                                   "frac": l2b / (kern_ms * 1e-3) / 1e9 / l2_peak,
+                                   "peak_source": "6300 B/cycle (microarchitecture guide, measured on B300) x SM clock"}
         if e2e:
             line["e2e"] = {"value": rays_total / (e2e_ms * 1e-3) / 1e6, "unit": UNIT, "h2d_bytes_per_step": int(e2e[1]),
                            "d2h_bytes_per_step": int(e2e[2]), "ms_per_step": e2e_ms / K,
