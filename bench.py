@@ -55,6 +55,8 @@ def parse_args():
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--cpu-seconds", type=float, default=20.0, help="CPU work (core-seconds) of the cpu_baseline sample")
     ap.add_argument("--still", action="store_true", help="render frame 0 on every step (profiling)")
+    ap.add_argument("--series-frames", type=int, default=-1,
+                    help="frames of the pipelined image-series leg incl. host prep (-1: 3 x host threads, max 96; 0: skip)")
     return ap.parse_args()
 
 
@@ -358,13 +360,35 @@ def run_b200_arm(args):
         e2e = (e2e_ms, h2d, d2h)
         sc.destroy()
 
+    # ---- image series including host prep (parse cache + prep thread pool + upload + render + download) ----
+    series = None
+    if args.series_frames != 0 and not args.still:
+        from simple_raytracer_b200 import scenes as _sc, series as _series
+        threads = max(1, len(os.sched_getaffinity(0)) // max(1, int(os.environ.get("LOCAL_WORLD_SIZE", world))))
+        n_fr = args.series_frames if args.series_frames > 0 else min(96, 3 * threads)
+        sr = _series.SeriesRenderer(ctx, cfg, W, H, focal, N, workers=threads, variant=args.variant)
+        my = [(_sc.SERIES_DEG_PER_FRAME * ((i * world + rank) % _sc.SERIES_FRAMES)) for i in range(n_fr)]
+        pin = capi.PinnedArray((H, W, 3), np.uint8)
+        buf = pin.array
+        list(sr.frames(my[:2], out=buf))                               # warm-up: fills the asset cache
+        barrier()
+        t_s0 = time.time()
+        tms = [tm for (_i, _rgb, tm) in sr.frames(my, out=buf)]
+        waits = [tm["wait_prep_ms"] for tm in tms]
+        gpu_leg = float(np.mean([tm["gpu_ms"] for tm in tms]))
+        torch.cuda.synchronize()
+        t_s1 = time.time()
+        sr.close()
+        series = (t_s1 - t_s0, n_fr, threads, float(np.mean(waits)), gpu_leg)
+
     # ---- max over ranks, totals ----
-    agg = torch.tensor([total_ms, e2e[0] if e2e else 0.0, kern_ms, prep_ms], dtype=torch.float64, device=dev)
+    agg = torch.tensor([total_ms, e2e[0] if e2e else 0.0, kern_ms, prep_ms, series[0] if series else 0.0],
+                       dtype=torch.float64, device=dev)
     tot = torch.tensor([float(rays_local)], dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(agg, op=dist.ReduceOp.MAX)
         dist.all_reduce(tot, op=dist.ReduceOp.SUM)
-    total_ms, e2e_ms, kern_ms_max, prep_ms_max = [float(x) for x in agg.tolist()]
+    total_ms, e2e_ms, kern_ms_max, prep_ms_max, series_s = [float(x) for x in agg.tolist()]
     rays_total = float(tot.item())
 
     line = None
@@ -420,6 +444,12 @@ def run_b200_arm(args):
                            "d2h_bytes_per_step": int(e2e[2]), "ms_per_step": e2e_ms / K,
                            "frames_per_s": world * K / (e2e_ms * 1e-3),
                            "what": "srt_scene_update from pinned host arrays + srt_render + NCCL gather to rank 0 + D2H of the RGB8 frames"}
+        if series:
+            line["series_with_host_prep"] = {
+                "frames_per_s": world * series[1] / series_s, "frames": world * series[1], "host_threads_per_rank": series[2],
+                "mean_wait_for_prep_ms": series[3], "mean_upload_render_download_ms": series[4],
+                "what": "whole image-series pipeline per rank: cached assets, per-frame transform + BVH build + flatten on a host "
+                        "thread pool (bit-identical to rebuilding from files), upload, render, download to host"}
         if world == 1 and not args.no_cpu_baseline:
             try:
                 step, cinfo = cpu_reference_sample(cfg, W, H, focal, N, args.cpu_seconds)

@@ -61,6 +61,11 @@ const srt_scene_desc* srt_host_flat_desc(srt_host_scene* s);
 int  srt_host_flat_max_depth(srt_host_scene* s);
 int  srt_host_flat_texture_name(srt_host_scene* s, int i, char* buf, int buflen);
 
+/* Process-wide cache of parsed OBJ/MTL files and decoded textures: the reference re-reads them on every frame
+ * of its loop (simple_raytracer.cpp:537, :554); loading is deterministic, so cached loads are bit-identical.
+ * Thread-safe; off by default; disabling clears the cache. */
+void srt_host_set_asset_cache(int enabled);
+
 /* OBJ number parser (for tests): returns 1 and the value, or 0. */
 int  srt_host_parse_double(const char* text, double* out);
 

@@ -13,7 +13,9 @@ import numpy as np
 
 from . import _abi
 
-LIB_PATH = Path(__file__).resolve().parent / "lib" / "libsrt_b200.so"
+import os as _os
+
+LIB_PATH = Path(_os.environ.get("SRT_LIB") or (Path(__file__).resolve().parent / "lib" / "libsrt_b200.so"))   # SRT_LIB: A/B builds
 
 EXPORTS = [
     "srt_abi_version", "srt_device_count", "srt_context_create", "srt_context_destroy",

@@ -150,6 +150,8 @@ int srt_host_flat_texture_name(srt_host_scene* s, int i, char* buf, int buflen) 
     return (int)s->flat.texture_names[(size_t)i].size();
 }
 
+void srt_host_set_asset_cache(int enabled) { srt::set_asset_cache(enabled != 0); }
+
 int srt_host_parse_double(const char* text, double* out) {
     const char* end = text + std::strcspn(text, " \t\r");
     return srt::parse_obj_double(text, end, out) ? 1 : 0;

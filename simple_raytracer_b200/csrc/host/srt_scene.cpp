@@ -1,4 +1,9 @@
 // srt_scene.cpp — ObjectManager / Transformation of this repository (see srt_scene.hpp).
+#include <memory>
+#include <mutex>
+#include <cstring>
+#include <cstdlib>
+
 #include "srt_scene.hpp"
 
 #include <algorithm>
@@ -175,20 +180,76 @@ void ObjectManager::createBoundingHierarchy(const std::string& objFilename) {
     slot = root;
 }
 
+// ---- asset cache (not in the reference, which re-parses every OBJ and re-decodes every texture on every
+// frame of its loop, simple_raytracer.cpp:537, :554).  Parsing and decoding are deterministic functions of the
+// files, so serving the parsed mesh / decoded pixels from memory gives bit-identical scenes.  Off by default.
+namespace {
+std::mutex g_cache_mutex;
+bool g_cache_enabled = false;
+struct CachedMesh { ObjMesh mesh; bool ok; };
+std::unordered_map<std::string, std::shared_ptr<const CachedMesh>> g_mesh_cache;
+struct CachedImage { std::vector<unsigned char> rgb; int w, h; };
+std::unordered_map<std::string, std::shared_ptr<const CachedImage>> g_image_cache;
+
+std::shared_ptr<const CachedMesh> cached_read_obj(const std::string& path) {
+    {
+        std::lock_guard<std::mutex> lock(g_cache_mutex);
+        auto it = g_mesh_cache.find(path);
+        if (g_cache_enabled && it != g_mesh_cache.end()) return it->second;
+    }
+    auto m = std::make_shared<CachedMesh>();
+    m->ok = read_obj(path, m->mesh);
+    std::lock_guard<std::mutex> lock(g_cache_mutex);
+    if (g_cache_enabled) g_mesh_cache[path] = m;
+    return m;
+}
+
+unsigned char* cached_decode(TextureDecoder decode, const std::string& path, int* w, int* h) {
+    {
+        std::lock_guard<std::mutex> lock(g_cache_mutex);
+        auto it = g_image_cache.find(path);
+        if (g_cache_enabled && it != g_image_cache.end()) {
+            const CachedImage& im = *it->second;
+            unsigned char* copy = (unsigned char*)std::malloc(im.rgb.size() ? im.rgb.size() : 1);
+            if (!copy) return nullptr;
+            std::memcpy(copy, im.rgb.data(), im.rgb.size());
+            *w = im.w; *h = im.h;
+            return copy;
+        }
+    }
+    unsigned char* data = decode(path.c_str(), w, h);
+    if (data && g_cache_enabled) {
+        auto im = std::make_shared<CachedImage>();
+        im->rgb.assign(data, data + (size_t)(*w) * (size_t)(*h) * 3);
+        im->w = *w; im->h = *h;
+        std::lock_guard<std::mutex> lock(g_cache_mutex);
+        g_image_cache[path] = im;
+    }
+    return data;
+}
+}  // namespace
+
+void set_asset_cache(bool enabled) {
+    std::lock_guard<std::mutex> lock(g_cache_mutex);
+    g_cache_enabled = enabled;
+    if (!enabled) { g_mesh_cache.clear(); g_image_cache.clear(); }
+}
+
 // loadObjFile, Object.cpp:25-170.
 void ObjectManager::loadObjFile(const std::string& objFilename) {
     objColors[objFilename] = vec3(1.f, 0.f, 0.f);                 // :29
     objProperties[objFilename] = vec3(0.2f, 0.5f, 15.0f);         // :31-34
-    ObjMesh mesh;
     lastWarning.clear();
-    if (!read_obj(objFilename, mesh)) lastWarning = "ObjReader: " + mesh.error;   // the reference prints and continues (:35-39)
+    const std::shared_ptr<const CachedMesh> parsed = cached_read_obj(objFilename);
+    const ObjMesh& mesh = parsed->mesh;
+    if (!parsed->ok) lastWarning = "ObjReader: " + mesh.error;    // the reference prints and continues (:35-39)
     TextureDecoder decode = textureDecoder ? textureDecoder : &decode_image_rgb8;
     for (const ObjMaterial& material : mesh.materials) {          // :52-68
         if (material.diffuse_texname.empty()) continue;
         const std::string& texturePath = material.diffuse_texname;   // as written in the MTL, relative to the CWD
         if (textureData.find(texturePath) != textureData.end()) continue;
         int width = 0, height = 0;
-        unsigned char* data = decode(texturePath.c_str(), &width, &height);
+        unsigned char* data = cached_decode(decode, texturePath, &width, &height);
         if (data) {
             textureData[texturePath] = data;
             textureDimensions[texturePath] = ivec2(width, height);

@@ -102,6 +102,9 @@ bool read_obj(const std::string& path, ObjMesh& out);
 // The float parser used for every number in OBJ/MTL files (restates tinyobjloader's tryParseDouble).
 bool parse_obj_double(const char* s, const char* s_end, double* result);
 
+// Process-wide cache of parsed OBJ/MTL files and decoded textures (thread-safe; off by default; disabling clears it).
+void set_asset_cache(bool enabled);
+
 // --- image decoding (srt_image.cpp) -------------------------------------------------------------
 unsigned char* decode_image_rgb8(const char* path, int* width, int* height);
 

@@ -33,6 +33,9 @@ using namespace srtd;
 namespace {
 
 constexpr int kThreads = 128;
+#ifndef SRT_MINBLOCKS
+#define SRT_MINBLOCKS 8
+#endif
 constexpr unsigned kFull = 0xffffffffu;
 
 // ---------------------------------------------------------------------------------------------
@@ -94,6 +97,12 @@ __device__ __forceinline__ FRay make_fray(V3 o, V3 d, float coord_bound) {
     return r;
 }
 
+#ifdef SRT_EXACT_NOINLINE
+__device__ __noinline__ bool slab_exact_call(V3 o, V3 d, float4 lo, float4 hi) { return slab_exact(o, d, lo, hi); }
+#else
+__device__ __forceinline__ bool slab_exact_call(V3 o, V3 d, float4 lo, float4 hi) { return slab_exact(o, d, lo, hi); }
+#endif
+
 // Returns the reference's decision for this box.  `tn_out` = approximate entry parameter (ordering only).
 __device__ __forceinline__ bool slab_filtered(const FRay& r, float lox, float loy, float loz, float hix, float hiy,
                                               float hiz, float& tn_out, float& tf_out, unsigned& exact_count) {
@@ -109,7 +118,7 @@ __device__ __forceinline__ bool slab_filtered(const FRay& r, float lox, float lo
         if (diff < -r.m) return false;
     }
     ++exact_count;
-    return slab_exact(r.o, r.d, make_float4(lox, loy, loz, 0.f), make_float4(hix, hiy, hiz, 0.f));
+    return slab_exact_call(r.o, r.d, make_float4(lox, loy, loz, 0.f), make_float4(hix, hiy, hiz, 0.f));
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -455,7 +464,7 @@ __device__ __forceinline__ unsigned long long ld_volatile_u64(const unsigned lon
     return *reinterpret_cast<const volatile unsigned long long*>(p);
 }
 
-__global__ void __launch_bounds__(kThreads, 8) render_dataflow(const __grid_constant__ KArgs a) {
+__global__ void __launch_bounds__(kThreads, SRT_MINBLOCKS) render_dataflow(const __grid_constant__ KArgs a) {
     extern __shared__ uint32_t smem[];
     const unsigned lane = threadIdx.x & 31;
     const unsigned n_tiles = (unsigned)(a.tiles_x * a.tiles_y);

@@ -81,6 +81,8 @@ def _lib():
         L.srt_host_flat_max_depth.argtypes = [vp]
         L.srt_host_flat_texture_name.argtypes = [vp, i32, cp, i32]
         L.srt_host_parse_double.argtypes = [cp, C.POINTER(C.c_double)]
+        L.srt_host_set_asset_cache.argtypes = [i32]
+        L.srt_host_set_asset_cache.restype = None
         _bound = True
     return L
 
@@ -250,6 +252,11 @@ class HostScene:
             names.append(buf.value.decode())
         return _abi.FlatSceneArrays.from_desc_pointer(d, self.object_names(), names,
                                                       self.lib.srt_host_flat_max_depth(self.h))
+
+
+def set_asset_cache(enabled: bool):
+    """Parse each OBJ/MTL and decode each texture once per process instead of once per frame (bit-identical)."""
+    _lib().srt_host_set_asset_cache(1 if enabled else 0)
 
 
 def parse_obj_number(text: str):

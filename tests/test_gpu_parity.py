@@ -207,3 +207,22 @@ def test_dropin_adapter_equals_verbatim_reference_function(ref_scene):
     assert np.array_equal(want_p, got_p)
     assert np.abs(want_c - got_c).max() <= 1.0
     assert np.count_nonzero(want_c != got_c) <= 3
+
+
+def test_series_driver_equals_frame_by_frame(gpu_ctx):
+    """series.SeriesRenderer (asset cache + prep thread pool + scene update in place) renders the same bytes
+    as building and uploading every frame from scratch."""
+    from simple_raytracer_b200 import host, series
+    cfg = scenes.CONFIGS["C3"]
+    W, H, focal = scenes.scaled(cfg, 180)
+    angles = [0.0, 1.5, 3.0, 40.5, 181.5]
+    sr = series.SeriesRenderer(gpu_ctx, cfg, W, H, focal, 4, workers=3)
+    got = {i: rgb.copy() for i, rgb, _tm in sr.frames(angles)}
+    sr.close()
+    host.set_asset_cache(False)
+    for i, ang in enumerate(angles):
+        hs = host.HostScene(); view = cfg.build(hs, ang); light = scenes.light_view_space(hs, view)
+        sc = gpu_ctx.upload(hs.flatten())
+        want = gpu_ctx.render(sc, _abi.default_params(W, H, focal, light, 4, True), ids=False, want_t=False)["rgb"]
+        sc.destroy()
+        assert np.array_equal(got[i], want), f"frame {i}"
