@@ -320,17 +320,22 @@ def run_b200_arm(args):
         pinned = []
         for (a, _l) in frames:
             keep = {}
-            for name in ("nodes", "geom", "attr", "objects"):
+            for name in ("nodes", "geom", "attr", "objects", "flat_geom", "flat_attr"):
                 src = getattr(a, name)
+                if src is None:
+                    continue
                 pa = capi.PinnedArray(src.shape, src.dtype)
                 pa.array[...] = src
                 keep[name] = pa
             pinned.append((_abi.FlatSceneArrays(keep["nodes"].array, keep["geom"].array, keep["attr"].array,
-                                                keep["objects"].array, a.textures), keep))
+                                                keep["objects"].array, a.textures,
+                                                keep["flat_geom"].array if "flat_geom" in keep else None,
+                                                keep["flat_attr"].array if "flat_attr" in keep else None), keep))
         sc = ctx.upload(pinned[0][0])
         host_rgb = torch.empty((world if rank == 0 else 1, H, W, 3), dtype=torch.uint8).pin_memory()
         gathered = [torch.empty_like(rgb) for _ in range(world)] if (rank == 0 and world > 1) else None
-        h2d = sum(getattr(pinned[0][0], n).nbytes for n in ("nodes", "geom", "attr", "objects"))
+        h2d = sum(getattr(pinned[0][0], n).nbytes for n in ("nodes", "geom", "attr", "objects", "flat_geom", "flat_attr")
+                  if getattr(pinned[0][0], n) is not None)
         d2h = host_rgb.numel() if rank == 0 else 0
 
         def e2e_step(s):

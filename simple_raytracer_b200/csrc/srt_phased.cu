@@ -36,6 +36,13 @@ constexpr int kThreads = 128;
 #ifndef SRT_MINBLOCKS
 #define SRT_MINBLOCKS 8
 #endif
+// queue entries a warp takes per atomic: consecutive tiles / consecutive lights of one tile (locality in the SM's L1)
+#ifndef SRT_PCHUNK
+#define SRT_PCHUNK 1
+#endif
+#ifndef SRT_SCHUNK
+#define SRT_SCHUNK 1
+#endif
 constexpr unsigned kFull = 0xffffffffu;
 
 // ---------------------------------------------------------------------------------------------
@@ -202,9 +209,9 @@ __device__ __forceinline__ bool trace_any(const KArgs& a, const FRay& r, Stack& 
 
 // ---------------------------------------------------------------------------------------------
 // Work distribution: one warp = one item, pulled from a global counter.
-__device__ __forceinline__ unsigned next_item(unsigned long long* counter, unsigned lane) {
+__device__ __forceinline__ unsigned next_item(unsigned long long* counter, unsigned lane, unsigned chunk = 1) {
     unsigned v = 0;
-    if (lane == 0) v = (unsigned)atomicAdd(counter, 1ull);
+    if (lane == 0) v = (unsigned)atomicAdd(counter, (unsigned long long)chunk);
     return __shfl_sync(kFull, v, 0);
 }
 
@@ -477,8 +484,9 @@ __global__ void __launch_bounds__(kThreads, SRT_MINBLOCKS) render_dataflow(const
     if (a.debug_timeline == 2) asm volatile("mov.u64 %0, %globaltimer;" : "=l"(ts0));
 
     for (;;) {
-        const unsigned q = next_item(&a.counters[CNT_TILE], lane);
-        if (q >= n_tiles) break;
+      const unsigned qbase = next_item(&a.counters[CNT_TILE], lane, SRT_PCHUNK);
+      if (qbase >= n_tiles) break;
+      for (unsigned q = qbase; q < qbase + SRT_PCHUNK && q < n_tiles; ++q) {
         ++n_p;
         const unsigned tile = a.tile_order[q];
         Pixel p; V3 d; Hit h; unsigned hit_ballot;
@@ -501,12 +509,15 @@ __global__ void __launch_bounds__(kThreads, SRT_MINBLOCKS) render_dataflow(const
             }
             atomicAdd(&a.counters[CNT_PDONE], 1ull);
         }
+      }
     }
 
     if (a.debug_timeline == 2) asm volatile("mov.u64 %0, %globaltimer;" : "=l"(ts1));
     if (a.n_objects >= 2 && N > 0) {
-        for (;;) {
-            const unsigned s = next_item(&a.counters[CNT_SHADOW], lane);
+        bool finished = false;
+        while (!finished) {
+          const unsigned sbase = next_item(&a.counters[CNT_SHADOW], lane, SRT_SCHUNK);
+          for (unsigned s = sbase; s < sbase + SRT_SCHUNK; ++s) {
             const unsigned slot = s / N;
             const int light = (int)(s - slot * N);
             unsigned long long e = 0;
@@ -524,7 +535,7 @@ __global__ void __launch_bounds__(kThreads, SRT_MINBLOCKS) render_dataflow(const
                 }
             }
             e = __shfl_sync(kFull, e, 0);
-            if ((e >> 32) != seq) break;                       // beyond the last published tile: no more work
+            if ((e >> 32) != seq) { finished = true; break; }  // beyond the last published tile: no more work
             __threadfence();
             const unsigned tile = (unsigned)(e & 0xffffffffull);
             shadow_item(a, st, tile, light, lane, exact_count);
@@ -540,6 +551,7 @@ __global__ void __launch_bounds__(kThreads, SRT_MINBLOCKS) render_dataflow(const
                 shade_tile_from_memory(a, tile, lane);
                 ++n_c;
             }
+          }
         }
     }
 
