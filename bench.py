@@ -8,10 +8,11 @@ frames of the configs[4] image series C5 when several GPUs shard the series by f
            --master-port P bench.py --gpus N --steps K --warmup W # N B200s, one rank per GPU
     python bench.py --impl reference ...                          # the reference's CPU code, same metric
 
-A "step" is one 1080p frame: rank r renders series frame (step*N + r) (camera angle 1.5 deg per
-frame, frame 0 == C3).  `value` = rays of all ranks / max-over-ranks device time, scenes resident in
-HBM; `e2e` = the same through the C ABI from pinned HOST buffers (scene upload + render + NCCL gather
-to rank 0 + download of the frames).  Ray-count rule:
+A "step" is one 1080p frame per rank: the N*(K+W) frames of a run are an image series over one full camera
+orbit (frame g at angle 360*g/(N*(K+W)) degrees, frame 0 == C3), frame g = step*N + rank — so the mix of
+cheap and expensive views is the same whatever N is.  `value` = rays of all ranks / max-over-ranks device
+time, scenes resident in HBM; `e2e` = the same through the C ABI from pinned HOST buffers (scene upload +
+render + download of the rank's frame; --gather adds the NCCL gather of all frames to rank 0).  Ray-count rule:
 rays = W*H + light_count * hit_pixels * [scene has >= 2 objects].
 
 torch is plumbing here (device buffers, streams, events, torch.distributed); the render path is
@@ -37,7 +38,7 @@ if str(REPO) not in sys.path:
 METRIC = "Mrays/s (bunny + ground, 16-light soft shadows, 1920x1080)"
 UNIT = "Mrays/s"
 WORKLOAD = ("C3/C5: stanford-bunny.obj (x150) + ground cube, 16 staircase lights, 1920x1080, focal 1080, BVH; "
-            "rank r renders image-series frame step*N+r at 1.5 deg/frame (frame 0 = C3)")
+            "image series over one camera orbit, frame step*N+rank of N*(steps+warmup), frame 0 = C3")
 L2_FLUSH_BYTES = 512 << 20
 
 
@@ -55,6 +56,7 @@ def parse_args():
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--cpu-seconds", type=float, default=20.0, help="CPU work (core-seconds) of the cpu_baseline sample")
     ap.add_argument("--still", action="store_true", help="render frame 0 on every step (profiling)")
+    ap.add_argument("--gather", action="store_true", help="e2e: gather every rank's frame to rank 0 over NCCL before the download")
     ap.add_argument("--series-frames", type=int, default=-1,
                     help="frames of the pipelined image-series leg incl. host prep (-1: 3 x host threads, max 96; 0: skip)")
     return ap.parse_args()
@@ -72,11 +74,16 @@ def frame_setup(args):
     return cfg, W, H, focal, N
 
 
-def build_frame(backend_factory, cfg, frame_index, still=False):
+def build_frame(backend_factory, cfg, frame_index, still=False, total_frames=0):
     """Host prep of one series frame through the scene surface: load, transform, BVH, flatten."""
     from simple_raytracer_b200 import scenes
     b = backend_factory()
-    angle = 0.0 if still else scenes.SERIES_DEG_PER_FRAME * (frame_index % scenes.SERIES_FRAMES)
+    if still:
+        angle = 0.0
+    elif total_frames > 0:
+        angle = 360.0 * (frame_index % total_frames) / total_frames
+    else:
+        angle = scenes.SERIES_DEG_PER_FRAME * (frame_index % scenes.SERIES_FRAMES)
     view = cfg.build(b, angle)
     light = scenes.light_view_space(b, view) if view is not None else np.array(scenes.LIGHT_WORLD, np.float32)
     arrays = b.flatten(with_flat_lists=not cfg.use_bvh)
@@ -135,17 +142,21 @@ class ClockSampler:
 
 
 # ------------------------------------------------------------------------------------------------
-def cpu_reference_sample(cfg, W, H, focal, N, core_seconds, threads=0, per_step_wall=None):
+def cpu_reference_sample(cfg, W, H, focal, N, core_seconds, threads=0, per_step_wall=None, orbit_views=1):
     """Times the reference's CPU implementation of the path (oracle/_ref when present, else the C
-    oracle port) on a bounded column sample of the frame.  Returns (fn(step)->(rays, seconds), info)."""
+    oracle port) on a bounded column sample of the frame.  `orbit_views` > 1: step i samples view i % orbit_views
+    of that many views spread over the camera orbit (the GPU arm's frame mix).  Returns (fn(step), info)."""
     from oracle import pyoracle
     from simple_raytracer_b200 import _abi, host
     ncores = threads or len(os.sched_getaffinity(0)) or (os.cpu_count() or 1)
+    views = []
     if pyoracle.ref_available():
         kind = "reference"
-        b, arrays, light = build_frame(pyoracle.RefBackend, cfg, 0, still=True)
+        for v in range(orbit_views):
+            views.append(build_frame(pyoracle.RefBackend, cfg, v, still=(orbit_views == 1), total_frames=orbit_views))
 
-        def run(col_begin, col_step, th):
+        def run(col_begin, col_step, th, view=0):
+            b, _arrays, light = views[view]
             r = b.render(W, H, focal, light, N, cfg.use_bvh, faithful=True, threads=th, col_begin=col_begin,
                          col_step=col_step, ids=False)
             cols = np.arange(col_begin, W, col_step)
@@ -153,13 +164,15 @@ def cpu_reference_sample(cfg, W, H, focal, N, core_seconds, threads=0, per_step_
             return r["traced"], hits, r["seconds"]
     else:
         kind = "port"
-        b, arrays, light = build_frame(host.HostScene, cfg, 0, still=True)
-        p = _abi.default_params(W, H, focal, light, N, cfg.use_bvh)
+        for v in range(orbit_views):
+            views.append(build_frame(host.HostScene, cfg, v, still=(orbit_views == 1), total_frames=orbit_views))
 
-        def run(col_begin, col_step, th):
+        def run(col_begin, col_step, th, view=0):
+            _b, arrays, light = views[view]
+            p = _abi.default_params(W, H, focal, light, N, cfg.use_bvh)
             r = pyoracle.oracle_render(arrays, p, threads=th, col_begin=col_begin, col_step=col_step)
             return r["traced"], r["counters"]["hit_pixels"], r["seconds"]
-    n_obj = len(arrays.objects)
+    n_obj = len(views[0][1].objects)
     # calibrate on ~24 columns spread over the frame, all threads
     cal_step = max(1, W // 24)
     run(cal_step // 2, cal_step, ncores)              # untimed: first touch of the scene, thread start-up
@@ -175,8 +188,11 @@ def cpu_reference_sample(cfg, W, H, focal, N, core_seconds, threads=0, per_step_
     sample = (f"{'unmodified reference (oracle/_ref, re-shading on every closer hit like :429-449)' if kind == 'reference' else 'C oracle port'}"
               f", {ncols} of {W} pixel columns (every {col_step}th) x {H} rows of the frame, {ncores} threads")
 
-    def step(_i):
-        traced, hits, sec = run(0, col_step, ncores)
+    if orbit_views > 1:
+        sample += f", step i on view i % {orbit_views} of {orbit_views} views spread over the camera orbit"
+
+    def step(i):
+        traced, hits, sec = run(0, col_step, ncores, i % orbit_views)
         return ray_count(1, traced, N, hits, n_obj), sec, traced   # W*H replaced by the traced pixel count
 
     return step, dict(kind=kind, cores=ncores, sample=sample)
@@ -187,7 +203,7 @@ def run_reference_arm(args):
     if rank != 0:
         return 0
     cfg, W, H, focal, N = frame_setup(args)
-    step, info = cpu_reference_sample(cfg, W, H, focal, N, 0.0, per_step_wall=1.0)
+    step, info = cpu_reference_sample(cfg, W, H, focal, N, 0.0, per_step_wall=1.0, orbit_views=1 if args.still else 8)
     for i in range(args.warmup):
         step(i)
     rays = 0
@@ -234,14 +250,15 @@ def run_b200_arm(args):
 
     cfg, W, H, focal, N = frame_setup(args)
     K, Wm = args.steps, args.warmup
-    n_unique = min(K + Wm, 24)                     # distinct series frames kept resident per rank
+    n_unique = min(K + Wm, 32)                     # distinct series frames kept resident per rank
+    total_frames = world * n_unique
 
     # ---- host prep (outside every timed region; reported) ----
     t_prep0 = time.time()
     frames = []
     for s in range(n_unique):
         f = s * world + rank
-        _b, arrays, light = build_frame(host.HostScene, cfg, f, still=args.still)
+        _b, arrays, light = build_frame(host.HostScene, cfg, f, still=args.still, total_frames=total_frames)
         frames.append((arrays, light))
         del _b
     prep_ms = 1e3 * (time.time() - t_prep0) / max(n_unique, 1)
@@ -332,23 +349,24 @@ def run_b200_arm(args):
                                                 keep["flat_geom"].array if "flat_geom" in keep else None,
                                                 keep["flat_attr"].array if "flat_attr" in keep else None), keep))
         sc = ctx.upload(pinned[0][0])
-        host_rgb = torch.empty((world if rank == 0 else 1, H, W, 3), dtype=torch.uint8).pin_memory()
-        gathered = [torch.empty_like(rgb) for _ in range(world)] if (rank == 0 and world > 1) else None
+        do_gather = args.gather and world > 1
+        host_rgb = torch.empty((world if (rank == 0 and do_gather) else 1, H, W, 3), dtype=torch.uint8).pin_memory()
+        gathered = [torch.empty_like(rgb) for _ in range(world)] if (rank == 0 and do_gather) else None
         h2d = sum(getattr(pinned[0][0], n).nbytes for n in ("nodes", "geom", "attr", "objects", "flat_geom", "flat_attr")
                   if getattr(pinned[0][0], n) is not None)
-        d2h = host_rgb.numel() if rank == 0 else 0
+        d2h = host_rgb.numel() if (rank == 0 or not do_gather) else 0
 
         def e2e_step(s):
             k = s % n_unique
             sc.update(pinned[k][0])                                  # H2D of this frame's scene (async, pinned)
             ctx.render_raw(sc, params[k], rgb=rgb.data_ptr())        # the render kernel
-            if world > 1:
+            if do_gather:
                 dist.gather(rgb, gathered, dst=0)                    # framebuffers -> rank 0 over NVLink (NCCL)
                 if rank == 0:
                     for r in range(world):
                         host_rgb[r].copy_(gathered[r], non_blocking=True)
             else:
-                host_rgb[0].copy_(rgb, non_blocking=True)            # D2H of the finished frame
+                host_rgb[0].copy_(rgb, non_blocking=True)            # D2H of this rank's finished frame
 
         for s in range(Wm):
             flush.zero_()
@@ -372,7 +390,7 @@ def run_b200_arm(args):
         threads = max(1, len(os.sched_getaffinity(0)) // max(1, int(os.environ.get("LOCAL_WORLD_SIZE", world))))
         n_fr = args.series_frames if args.series_frames > 0 else min(96, 3 * threads)
         sr = _series.SeriesRenderer(ctx, cfg, W, H, focal, N, workers=threads, variant=args.variant)
-        my = [(_sc.SERIES_DEG_PER_FRAME * ((i * world + rank) % _sc.SERIES_FRAMES)) for i in range(n_fr)]
+        my = [360.0 * (i * world + rank) / (n_fr * world) for i in range(n_fr)]
         pin = capi.PinnedArray((H, W, 3), np.uint8)
         buf = pin.array
         list(sr.frames(my[:2], out=buf))                               # warm-up: fills the asset cache
@@ -445,10 +463,11 @@ def run_b200_arm(args):
                                    "frac": l2b / (kern_ms * 1e-3) / 1e9 / l2_peak,
                                    "peak_source": "6300 B/cycle (microarchitecture guide, measured on B300) x SM clock"}
         if e2e:
-            line["e2e"] = {"value": rays_total / (e2e_ms * 1e-3) / 1e6, "unit": UNIT, "h2d_bytes_per_step": int(e2e[1]),
-                           "d2h_bytes_per_step": int(e2e[2]), "ms_per_step": e2e_ms / K,
+            line["e2e"] = {"value": rays_total / (e2e_ms * 1e-3) / 1e6, "unit": UNIT, "h2d_bytes_per_step": int(e2e[1]) * world,
+                           "d2h_bytes_per_step": int(e2e[2]) * (1 if args.gather else world), "ms_per_step": e2e_ms / K,
                            "frames_per_s": world * K / (e2e_ms * 1e-3),
-                           "what": "srt_scene_update from pinned host arrays + srt_render + NCCL gather to rank 0 + D2H of the RGB8 frames"}
+                           "what": "per rank: srt_scene_update from pinned host arrays + srt_render + D2H of the RGB8 frame to pinned host memory"
+                                   + (" (all frames gathered to rank 0 over NCCL first)" if args.gather else "")}
         if series:
             line["series_with_host_prep"] = {
                 "frames_per_s": world * series[1] / series_s, "frames": world * series[1], "host_threads_per_rank": series[2],
@@ -457,8 +476,10 @@ def run_b200_arm(args):
                         "thread pool (bit-identical to rebuilding from files), upload, render, download to host"}
         if world == 1 and not args.no_cpu_baseline:
             try:
-                step, cinfo = cpu_reference_sample(cfg, W, H, focal, N, args.cpu_seconds)
-                r, s, _px = step(0)
+                nv = 1 if args.still else 4
+                step, cinfo = cpu_reference_sample(cfg, W, H, focal, N, args.cpu_seconds / nv, orbit_views=nv)
+                rs = [step(i) for i in range(nv)]
+                r, s = sum(x[0] for x in rs), sum(x[1] for x in rs)
                 line["cpu_baseline"] = {"value": r / s / 1e6, "unit": UNIT, **cinfo, "seconds": s}
             except Exception as e:      # the CPU baseline is reporting, never the product path
                 line["cpu_baseline"] = {"value": None, "unit": UNIT, "cores": 0, "kind": "port", "sample": f"failed: {e}"}
