@@ -319,17 +319,36 @@ def run_b200_arm(args):
         kernel_ms.append(ctx.last_stats()["kernel_ms"])
     kern_ms = float(np.mean(kernel_ms)) if kernel_ms else float("nan")
     launches_per_step = ctx.last_stats()["kernel_launches"]
+    # the metric's own configuration (C3 = frame 0 of the orbit) on its own, device-timed the same way
+    c3_still = None
+    if rank == 0 and not args.still:
+        k0 = 0                                            # frames[0] is global frame `rank` = 0 on rank 0: angle 0
+        evs = []
+        for it in range(3 + 8):
+            flush.zero_()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record(); ctx.render_raw(scenes_dev[k0], params[k0], rgb=rgb.data_ptr()); e1.record()
+            evs.append((e0, e1))
+        torch.cuda.synchronize()
+        ms0 = float(np.mean([a.elapsed_time(b) for a, b in evs[3:]]))
+        rays0 = ray_count(W, H, N, hits_of(k0), n_obj)
+        c3_still = {"ms_per_frame": ms0, "value": rays0 / (ms0 * 1e-3) / 1e6, "unit": UNIT, "rays_per_frame": rays0,
+                    "what": "frame 0 of the orbit = BASELINE configs[2] (C3) itself, same timing method"}
     # algorithmic work of frame Wm (the first timed one) under the REFERENCE's traversal rules, counted by the
     # instrumented CUDA kernel (SRT_VARIANT_COUNT; tests check its counters against the oracle's)
     work = None
     if rank == 0 and cfg.use_bvh:
-        k0 = Wm % n_unique
-        pc = _abi.default_params(W, H, focal, frames[k0][1], N, cfg.use_bvh)
-        pc.variant = _abi.VARIANT_COUNT
-        ctx.render_raw(scenes_dev[k0], pc, rgb=rgb.data_ptr())
-        st = ctx.last_stats()
-        work = dict(node_visits=st["node_visits"], tri_tests=st["tri_tests"], hit_pixels=st["hit_pixels"],
-                    light_evals=N * st["hit_pixels"])
+        tot = dict(node_visits=0, tri_tests=0, hit_pixels=0, light_evals=0)
+        nk = min(K, 8)                                   # the same frames kern_ms was averaged over
+        for s in range(nk):
+            k0 = (Wm + s) % n_unique
+            pc = _abi.default_params(W, H, focal, frames[k0][1], N, cfg.use_bvh)
+            pc.variant = _abi.VARIANT_COUNT
+            ctx.render_raw(scenes_dev[k0], pc, rgb=rgb.data_ptr())
+            st = ctx.last_stats()
+            tot["node_visits"] += st["node_visits"]; tot["tri_tests"] += st["tri_tests"]
+            tot["hit_pixels"] += st["hit_pixels"]; tot["light_evals"] += N * st["hit_pixels"]
+        work = {k: v / nk for k, v in tot.items()}
 
     # ---- end to end through the C ABI from pinned host buffers ----
     e2e = None
@@ -468,6 +487,8 @@ def run_b200_arm(args):
                            "frames_per_s": world * K / (e2e_ms * 1e-3),
                            "what": "per rank: srt_scene_update from pinned host arrays + srt_render + D2H of the RGB8 frame to pinned host memory"
                                    + (" (all frames gathered to rank 0 over NCCL first)" if args.gather else "")}
+        if c3_still:
+            line["c3_frame0"] = c3_still
         if series:
             line["series_with_host_prep"] = {
                 "frames_per_s": world * series[1] / series_s, "frames": world * series[1], "host_threads_per_rank": series[2],

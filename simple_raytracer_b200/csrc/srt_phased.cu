@@ -175,7 +175,8 @@ __device__ __forceinline__ void trace_closest(const KArgs& a, const FRay& r, Sta
 // Any hit (shadowIntersection :321-342): true as soon as one candidate triangle reports t >= 0.
 // Order is free for a boolean; children are visited nearest-entry-first, boxes wholly behind the
 // origin last, so occluded rays usually stop after a few leaves.
-__device__ __forceinline__ bool trace_any(const KArgs& a, const FRay& r, Stack& st, unsigned& exact_count) {
+template <bool COUNT = false>
+__device__ __forceinline__ bool trace_any(const KArgs& a, const FRay& r, Stack& st, unsigned& exact_count, unsigned* boxes = nullptr) {
     uint32_t ref = st.pop();
     while (ref != kRefNone) {
         while (is_interior(ref)) {
@@ -184,6 +185,7 @@ __device__ __forceinline__ bool trace_any(const KArgs& a, const FRay& r, Stack& 
             float tnl, tfl, tnr, tfr;
             const bool hl = slab_filtered(r, w0.x, w0.y, w0.z, w0.w, w1.x, w1.y, tnl, tfl, exact_count);
             const bool hr = slab_filtered(r, w1.z, w1.w, w2.x, w2.y, w2.z, w2.w, tnr, tfr, exact_count);
+            if (COUNT) *boxes += 2;
             const uint32_t rl = __float_as_uint(w3.x), rr = __float_as_uint(w3.y);
             if (hl && hr) {
                 const float kl = tfl < 0.f ? 3.0e38f : fmaxf(tnl, 0.f);
@@ -352,8 +354,9 @@ __device__ __forceinline__ unsigned primary_tile(const KArgs& a, Stack& st, unsi
 }
 
 // Occlusion of one light for the interested lanes of one tile -> one ballot word (:321-342).
+template <bool COUNT = false>
 __device__ __forceinline__ void shadow_item(const KArgs& a, Stack& st, unsigned tile, int light, unsigned lane,
-                                            unsigned& exact_count) {
+                                            unsigned& exact_count, unsigned* box_occluded = nullptr, unsigned* box_free = nullptr) {
     const unsigned interest = __ldcg(a.tile_interest + tile);
     const Pixel p = pixel_of(a, tile, lane);
     st.sp = 0;
@@ -369,7 +372,9 @@ __device__ __forceinline__ void shadow_item(const KArgs& a, Stack& st, unsigned 
     }
     const FRay s = make_fray(so, sd, a.coord_bound);
     if (mine) push_roots(a, s, st, obj, exact_count);
-    const bool occluded = trace_any(a, s, st, exact_count);
+    unsigned boxes = 0;
+    const bool occluded = trace_any<COUNT>(a, s, st, exact_count, &boxes);
+    if (COUNT) { if (occluded) *box_occluded += boxes; else *box_free += boxes; }
     const unsigned ballot = __ballot_sync(kFull, mine && occluded);
     if (lane == 0) a.shadow_mask[(size_t)tile * a.light_count + light] = ballot;
 }
@@ -471,6 +476,7 @@ __device__ __forceinline__ unsigned long long ld_volatile_u64(const unsigned lon
     return *reinterpret_cast<const volatile unsigned long long*>(p);
 }
 
+template <bool COUNT>
 __global__ void __launch_bounds__(kThreads, SRT_MINBLOCKS) render_dataflow(const __grid_constant__ KArgs a) {
     extern __shared__ uint32_t smem[];
     const unsigned lane = threadIdx.x & 31;
@@ -481,6 +487,7 @@ __global__ void __launch_bounds__(kThreads, SRT_MINBLOCKS) render_dataflow(const
     unsigned hits = 0, exact_count = 0;
     // debug_timeline == 2: per-warp timestamps (start, primary queue empty, end) + item counts in the t plane
     unsigned long long ts0 = 0, ts1 = 0, ts2 = 0; unsigned n_p = 0, n_s = 0, n_c = 0;
+    unsigned box_occluded = 0, box_free = 0;   // COUNT: shadow-stage box tests by rays that ended occluded / unoccluded
     if (a.debug_timeline == 2) asm volatile("mov.u64 %0, %globaltimer;" : "=l"(ts0));
 
     for (;;) {
@@ -538,7 +545,7 @@ __global__ void __launch_bounds__(kThreads, SRT_MINBLOCKS) render_dataflow(const
             if ((e >> 32) != seq) { finished = true; break; }  // beyond the last published tile: no more work
             __threadfence();
             const unsigned tile = (unsigned)(e & 0xffffffffull);
-            shadow_item(a, st, tile, light, lane, exact_count);
+            shadow_item<COUNT>(a, st, tile, light, lane, exact_count, &box_occluded, &box_free);
             ++n_s;
             unsigned last = 0;
             if (lane == 0) {
@@ -562,6 +569,10 @@ __global__ void __launch_bounds__(kThreads, SRT_MINBLOCKS) render_dataflow(const
             unsigned long long* out = reinterpret_cast<unsigned long long*>(a.t) + 8 * (size_t)(blockIdx.x * (kThreads / 32) + (threadIdx.x >> 5));
             out[0] = ts0; out[1] = ts1; out[2] = ts2; out[3] = n_p; out[4] = n_s; out[5] = n_c;
         }
+    }
+    if (COUNT) {
+        for (int s = 16; s > 0; s >>= 1) { box_occluded += __shfl_xor_sync(kFull, box_occluded, s); box_free += __shfl_xor_sync(kFull, box_free, s); }
+        if (lane == 0) { atomicAdd(&a.counters[CNT_NODE], (unsigned long long)box_occluded); atomicAdd(&a.counters[CNT_TRI], (unsigned long long)box_free); }
     }
     for (int s = 16; s > 0; s >>= 1) exact_count += __shfl_xor_sync(kFull, exact_count, s);
     if (lane == 0) {
@@ -627,14 +638,15 @@ cudaError_t launch_render_phased(const KArgs& a, int variant, int sm_count, cuda
     const size_t smem = phased_smem_bytes(a.stack_cap);
     static bool attr_set = false;
     if (!attr_set) {
-        cudaFuncSetAttribute(render_dataflow, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024);
+        cudaFuncSetAttribute(render_dataflow<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024);
+        cudaFuncSetAttribute(render_dataflow<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024);
         cudaFuncSetAttribute(render_phase<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024);
         cudaFuncSetAttribute(render_phase<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024);
         cudaFuncSetAttribute(render_phase<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024);
         attr_set = true;
     }
     int per_sm = 0;
-    cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, render_dataflow, kThreads, smem);
+    cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, render_dataflow<false>, kThreads, smem);
     if (e != cudaSuccess) return e;
     if (per_sm < 1) return cudaErrorLaunchOutOfResources;
     // Persistent grid: exactly the resident capacity.  (The dataflow kernel's waiting warps only wait for
@@ -652,7 +664,8 @@ cudaError_t launch_render_phased(const KArgs& a, int variant, int sm_count, cuda
         if (launches) *launches = 4;
         return cudaGetLastError();
     }
-    render_dataflow<<<blocks, kThreads, smem, stream>>>(a);
+    if (a.debug_timeline == 3) render_dataflow<true><<<blocks, kThreads, smem, stream>>>(a);   // node_visits / tri_tests = shadow box tests of occluded / free rays
+    else render_dataflow<false><<<blocks, kThreads, smem, stream>>>(a);
     if (launches) *launches = 2;
     return cudaGetLastError();
 }
