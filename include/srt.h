@@ -211,6 +211,22 @@ void* srt_device_alloc(srt_context* ctx, size_t bytes);
 void  srt_device_free(srt_context* ctx, void* p);
 const char* srt_last_error(void);
 
+/* ---- leaf evaluation (test hook; not on the render path) ----
+ * Runs ONE device leaf function of the render kernels on n independent cases so that tests can hold it against
+ * the reference's own functions (tests/golden/leaf_kat.npz).  `in` / `out` are HOST arrays, row-major
+ * [n][in_width] / [n][out_width]:
+ *   SRT_LEAF_POWF      in  x, y                                                            out powf(x, y)          (:196, :398)
+ *   SRT_LEAF_SLAB      in  o[3], d[3], bmin[3], bmax[3]                                    out exact, filtered, used_exact
+ *                      (intersectRayAabbNoOrigin :252-293; `filtered` is the decision of the kernels' filtered
+ *                      slab test, which must equal `exact`; used_exact = 1 when the filter deferred to the exact test)
+ *   SRT_LEAF_TRIANGLE  in  o[3], d[3], p0[3], e1[3], e2[3]                                 out t or -inf           (:42-75)
+ *   SRT_LEAF_PHONG     in  n[3], d[3], light[3], light_color[3], obj_color[3],
+ *                          ambient, specular, shininess, t                                 out rgb[3]              (:144-200)
+ *   SRT_LEAF_TONE      in  c, tone_k, gamma                                                out q (0..255)          (:391-398, :447-449)
+ */
+enum { SRT_LEAF_POWF = 0, SRT_LEAF_SLAB = 1, SRT_LEAF_TRIANGLE = 2, SRT_LEAF_PHONG = 3, SRT_LEAF_TONE = 4 };
+int  srt_eval_leaf(srt_context* ctx, int op, const float* in, float* out, size_t n);
+
 #ifdef __cplusplus
 }
 #endif

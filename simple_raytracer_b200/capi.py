@@ -22,7 +22,7 @@ EXPORTS = [
     "srt_context_set_stream", "srt_context_get_info", "srt_scene_upload", "srt_scene_update",
     "srt_scene_destroy", "srt_render", "srt_sync", "srt_last_stats", "srt_default_params",
     "srt_light_positions", "srt_host_alloc", "srt_host_free", "srt_device_alloc", "srt_device_free",
-    "srt_last_error",
+    "srt_last_error", "srt_eval_leaf",
 ]
 
 
@@ -62,6 +62,7 @@ def lib():
         L.srt_default_params.argtypes = [C.POINTER(_abi.RenderParams)]
         L.srt_default_params.restype = None
         L.srt_light_positions.argtypes = [C.POINTER(_abi.RenderParams), C.POINTER(C.c_float)]
+        L.srt_eval_leaf.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_float), C.POINTER(C.c_float), C.c_size_t]
         L.srt_host_alloc.argtypes = [C.c_size_t]
         L.srt_host_alloc.restype = vp
         L.srt_host_free.argtypes = [vp]
@@ -196,6 +197,20 @@ class Context:
             self.destroy()
         except Exception:
             pass
+
+
+LEAF_POWF, LEAF_SLAB, LEAF_TRIANGLE, LEAF_PHONG, LEAF_TONE = range(5)
+_LEAF_WIDTHS = {LEAF_POWF: (2, 1), LEAF_SLAB: (12, 3), LEAF_TRIANGLE: (15, 1), LEAF_PHONG: (19, 3), LEAF_TONE: (3, 1)}
+
+
+def eval_leaf(ctx: "Context", op: int, cases) -> np.ndarray:
+    """srt_eval_leaf: one device leaf function of the render kernels on n cases ([n][in_width] float32)."""
+    wi, wo = _LEAF_WIDTHS[op]
+    x = np.ascontiguousarray(cases, np.float32).reshape(-1, wi)
+    out = np.zeros((len(x), wo), np.float32)
+    fp = C.POINTER(C.c_float)
+    _check(lib().srt_eval_leaf(ctx.h, op, x.ctypes.data_as(fp), out.ctypes.data_as(fp), len(x)))
+    return out
 
 
 def light_positions(params: _abi.RenderParams) -> np.ndarray:

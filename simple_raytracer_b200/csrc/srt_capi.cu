@@ -211,6 +211,24 @@ void* srt_host_alloc(size_t bytes) {
 }
 void srt_host_free(void* p) { if (p) cudaFreeHost(p); }
 
+int srt_eval_leaf(srt_context* c, int op, const float* in, float* out, size_t n) {
+    if (!c || (!in && n) || (!out && n)) return fail(SRT_ERR_INVALID_ARG, "srt_eval_leaf: null argument");
+    const int wi = srtk::leaf_in_width(op), wo = srtk::leaf_out_width(op);
+    if (wi == 0) return fail(SRT_ERR_INVALID_ARG, "srt_eval_leaf: unknown leaf function %d", op);
+    if (n == 0) return SRT_OK;
+    cudaSetDevice(c->device);
+    float *din = nullptr, *dout = nullptr;
+    cudaError_t e = cudaMalloc(&din, n * wi * sizeof(float));
+    if (e == cudaSuccess) e = cudaMalloc(&dout, n * wo * sizeof(float));
+    if (e == cudaSuccess) e = cudaMemcpyAsync(din, in, n * wi * sizeof(float), cudaMemcpyHostToDevice, c->stream);
+    if (e == cudaSuccess) e = srtk::launch_eval_leaf(op, din, dout, n, c->stream);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(out, dout, n * wo * sizeof(float), cudaMemcpyDeviceToHost, c->stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(c->stream);
+    cudaFree(din); cudaFree(dout);
+    if (e != cudaSuccess) { cudaGetLastError(); return fail(SRT_ERR_CUDA, "srt_eval_leaf: %s", cudaGetErrorString(e)); }
+    return SRT_OK;
+}
+
 void* srt_device_alloc(srt_context* c, size_t bytes) {
     if (!c) return nullptr;
     cudaSetDevice(c->device);

@@ -10,6 +10,8 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 
+#include "srt_powf_tables.cuh"
+
 namespace srtd {
 
 #define SRT_DEV __device__ __forceinline__
@@ -40,10 +42,42 @@ SRT_DEV V3 normalize3(V3 v) {
 SRT_DEV float glm_max(float x, float y) { return (x < y) ? y : x; }
 
 // std::pow(float,float) (glibc powf: evaluated in double, result within 0.52 ulp before the final
-// rounding).  libdevice powf is only good to a few ulp, which would move ~1e-4 of all 8-bit
-// channel values by one LSB; pow() in double rounded once to float agrees with glibc except when
-// the exact value lies within ~1e-9 relative of a float rounding boundary.
-SRT_DEV float srt_powf(float x, float y) { return (float)pow((double)x, (double)y); }
+// rounding — about 1e-3 of its results are not the correctly rounded value).  libdevice powf is only
+// good to a few ulp, which would move ~1e-4 of all 8-bit channel values by one LSB.  Here x^y =
+// exp2(y * log2 x) is evaluated in double to a relative error below 2^-44 and rounded once to float
+// (tables and error budget: tools/gen_powf_tables.py): the correctly rounded powf except when the
+// exact value lies within ~1e-13 relative of a float rounding boundary.  Everything outside the
+// plain case (x not positive-normal, y not finite, results near the double range) goes to pow() in
+// double, which has the same property and all the special cases of C99 Annex F.
+SRT_DEV float srt_powf(float x, float y) {
+    namespace T = srtk::powf_tab;
+    const uint32_t ix = __float_as_uint(x);
+    if (ix == 0x3f800000u) return 1.0f;                                   // pow(1, y) = 1 for every y
+    if (ix == 0u && y > 0.0f) return 0.0f;                                // pow(+0, y > 0) = +0 (the clamped specular term)
+    if (ix - 0x00800000u < 0x7f000000u && fabsf(y) < 3.0e38f) {           // x positive, normal, finite; y finite
+        const uint32_t tmp = ix - T::kOff;
+        const double2 c = __ldg(&T::kLog[(tmp >> (23 - T::kLogBits)) & ((1u << T::kLogBits) - 1u)]);
+        const double z = (double)__uint_as_float(ix - (tmp & 0xff800000u));
+        const double k = (double)((int32_t)tmp >> 23);
+        const double r = fma(z, c.x, -1.0);
+        double p = fma(T::kL7, r, T::kL6);
+        p = fma(p, r, T::kL5); p = fma(p, r, T::kL4); p = fma(p, r, T::kL3); p = fma(p, r, T::kL2); p = fma(p, r, T::kL1);
+        const double t = (double)y * fma(p, r, c.y + k);                  // y * log2 x
+        if (fabs(t) < 1000.0) {
+            const double shift = 6755399441055744.0;                      // 1.5 * 2^52: round to nearest integer
+            double kd = fma(t, (double)(1 << T::kExpBits), shift);
+            const int32_t ki = __double2loint(kd);
+            kd -= shift;
+            const double q = fma(kd, -1.0 / (double)(1 << T::kExpBits), t);   // |q| <= 1/64
+            double e = fma(T::kE5, q, T::kE4);
+            e = fma(e, q, T::kE3); e = fma(e, q, T::kE2); e = fma(e, q, T::kE1); e = fma(e, q, 1.0);
+            const double s = __ldg(&T::kExp[ki & ((1 << T::kExpBits) - 1)]);
+            const int hi = __double2hiint(s) + ((ki >> T::kExpBits) << 20);   // times 2^(ki div 32)
+            return (float)(__hiloint2double(hi, __double2loint(s)) * e);
+        }
+    }
+    return (float)pow((double)x, (double)y);
+}
 
 // ---------------------------------------------------------------------------------------------
 // intersectRayAabbNoOrigin :252-293 (and intersectRayAabb :204-248, which is the same function

@@ -83,6 +83,11 @@ cudaError_t launch_build_wide(const float4* nodes, const srt_object* objects, ui
 // Shared memory the phased kernel needs per CTA for `stack_cap`, and whether it fits.
 size_t phased_smem_bytes(int stack_cap);
 // Single cooperative launch (variant SRT_VARIANT_DEFAULT) or three launches (SRT_VARIANT_SPLIT).
+// Leaf evaluation hook (srt_eval_leaf): `in` / `out` are device arrays.
+int leaf_in_width(int op);
+int leaf_out_width(int op);
+cudaError_t launch_eval_leaf(int op, const float* in, float* out, size_t n, cudaStream_t stream);
+
 cudaError_t launch_render_phased(const KArgs& a, int variant, int sm_count, cudaStream_t stream, int* launches);
 
 }  // namespace srtk

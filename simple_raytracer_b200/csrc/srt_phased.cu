@@ -61,8 +61,7 @@ struct FRay {
     V3 o, d;          // the exact ray (reference values)
     float ix, iy, iz; // approximate reciprocals
     float nx, ny, nz; // -o * i
-    float m;          // decision margin
-    bool degenerate;  // exact test always
+    float m;          // decision margin; NaN = exact test always (both comparisons below are then false)
 };
 
 __device__ __forceinline__ float rcp_approx(float x) {
@@ -100,7 +99,7 @@ __device__ __forceinline__ FRay make_fray(V3 o, V3 d, float coord_bound) {
     const bool okx = zx ? (fabsf(r.ix) == inf) : (ax > lo && ax < hi);
     const bool oky = zy ? (fabsf(r.iy) == inf) : (ay > lo && ay < hi);
     const bool okz = zz ? (fabsf(r.iz) == inf) : (az > lo && az < hi);
-    r.degenerate = !(okx && oky && okz && r.m < 1e30f) || (zx && zy && zz);
+    if (!(okx && oky && okz && r.m < 1e30f) || (zx && zy && zz)) r.m = __int_as_float(0x7fc00000);
     return r;
 }
 
@@ -120,12 +119,38 @@ __device__ __forceinline__ bool slab_filtered(const FRay& r, float lox, float lo
     const float tf = minn(minn(maxn(x0, x1), maxn(y0, y1)), maxn(z0, z1));
     tn_out = tn; tf_out = tf;
     const float diff = tf - tn;
-    if (!r.degenerate) {
-        if (diff >= r.m) return true;
-        if (diff < -r.m) return false;
-    }
+    if (diff >= r.m) return true;
+    if (diff < -r.m) return false;
     ++exact_count;
     return slab_exact_call(r.o, r.d, make_float4(lox, loy, loz, 0.f), make_float4(hix, hiy, hiz, 0.f));
+}
+
+// Both child boxes of a wide node (w0..w2 = lo/hi of the left box, lo/hi of the right box): the twelve
+// plane values are independent, and ONE rarely taken branch covers the uncertain cases of both boxes.
+__device__ __forceinline__ void slab_filtered_pair(const FRay& r, const float4& w0, const float4& w1, const float4& w2,
+                                                   bool& hl, bool& hr, float& tnl, float& tfl, float& tnr, float& tfr,
+                                                   unsigned& exact_count) {
+    {
+        const float x0 = fmaf(w0.x, r.ix, r.nx), x1 = fmaf(w0.w, r.ix, r.nx);
+        const float y0 = fmaf(w0.y, r.iy, r.ny), y1 = fmaf(w1.x, r.iy, r.ny);
+        const float z0 = fmaf(w0.z, r.iz, r.nz), z1 = fmaf(w1.y, r.iz, r.nz);
+        tnl = maxn(maxn(minn(x0, x1), minn(y0, y1)), minn(z0, z1));
+        tfl = minn(minn(maxn(x0, x1), maxn(y0, y1)), maxn(z0, z1));
+    }
+    {
+        const float x0 = fmaf(w1.z, r.ix, r.nx), x1 = fmaf(w2.y, r.ix, r.nx);
+        const float y0 = fmaf(w1.w, r.iy, r.ny), y1 = fmaf(w2.z, r.iy, r.ny);
+        const float z0 = fmaf(w2.x, r.iz, r.nz), z1 = fmaf(w2.w, r.iz, r.nz);
+        tnr = maxn(maxn(minn(x0, x1), minn(y0, y1)), minn(z0, z1));
+        tfr = minn(minn(maxn(x0, x1), maxn(y0, y1)), maxn(z0, z1));
+    }
+    const float dl = tfl - tnl, dr = tfr - tnr;
+    hl = dl >= r.m; hr = dr >= r.m;
+    const bool ul = !(hl || dl < -r.m), ur = !(hr || dr < -r.m);
+    if (ul || ur) {
+        if (ul) { ++exact_count; hl = slab_exact_call(r.o, r.d, make_float4(w0.x, w0.y, w0.z, 0.f), make_float4(w0.w, w1.x, w1.y, 0.f)); }
+        if (ur) { ++exact_count; hr = slab_exact_call(r.o, r.d, make_float4(w1.z, w1.w, w2.x, 0.f), make_float4(w2.y, w2.z, w2.w, 0.f)); }
+    }
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -151,8 +176,8 @@ __device__ __forceinline__ void trace_closest(const KArgs& a, const FRay& r, Sta
             const float4* w = a.wide + 4 * (size_t)ref;
             const float4 w0 = ldg4(w), w1 = ldg4(w + 1), w2 = ldg4(w + 2), w3 = ldg4(w + 3);
             float tnl, tfl, tnr, tfr;
-            const bool hl = slab_filtered(r, w0.x, w0.y, w0.z, w0.w, w1.x, w1.y, tnl, tfl, exact_count);
-            const bool hr = slab_filtered(r, w1.z, w1.w, w2.x, w2.y, w2.z, w2.w, tnr, tfr, exact_count);
+            bool hl, hr;
+            slab_filtered_pair(r, w0, w1, w2, hl, hr, tnl, tfl, tnr, tfr, exact_count);
             const uint32_t rl = __float_as_uint(w3.x), rr = __float_as_uint(w3.y);
             if (hl) { if (hr) st.push(rr); ref = rl; }
             else if (hr) ref = rr;
@@ -183,8 +208,8 @@ __device__ __forceinline__ bool trace_any(const KArgs& a, const FRay& r, Stack& 
             const float4* w = a.wide + 4 * (size_t)ref;
             const float4 w0 = ldg4(w), w1 = ldg4(w + 1), w2 = ldg4(w + 2), w3 = ldg4(w + 3);
             float tnl, tfl, tnr, tfr;
-            const bool hl = slab_filtered(r, w0.x, w0.y, w0.z, w0.w, w1.x, w1.y, tnl, tfl, exact_count);
-            const bool hr = slab_filtered(r, w1.z, w1.w, w2.x, w2.y, w2.z, w2.w, tnr, tfr, exact_count);
+            bool hl, hr;
+            slab_filtered_pair(r, w0, w1, w2, hl, hr, tnl, tfl, tnr, tfr, exact_count);
             if (COUNT) *boxes += 2;
             const uint32_t rl = __float_as_uint(w3.x), rr = __float_as_uint(w3.y);
             if (hl && hr) {
@@ -309,10 +334,11 @@ __device__ __forceinline__ void phase_classify(const KArgs& a) {
 
 // Closest hit of one tile (lane = pixel) + the hit record + "can any shadow ray of this pixel reach
 // another object's root box" (the root test of :328).  Returns the ballot of interested lanes.
+template <bool TL = false>
 __device__ __forceinline__ unsigned primary_tile(const KArgs& a, Stack& st, unsigned tile, unsigned lane, Pixel& p, V3& d,
                                                  Hit& h, unsigned& hit_ballot, unsigned& exact_count) {
     long long tl_c0 = 0; unsigned long long tl_ns = 0;
-    if (a.debug_timeline == 1) { tl_c0 = clock64(); asm volatile("mov.u64 %0, %globaltimer;" : "=l"(tl_ns)); }
+    if (TL && a.debug_timeline == 1) { tl_c0 = clock64(); asm volatile("mov.u64 %0, %globaltimer;" : "=l"(tl_ns)); }
     p = pixel_of(a, tile, lane);
     d = primary_dir(a, p);
     const FRay r = make_fray(v3(0.f, 0.f, 0.f), d, a.coord_bound);
@@ -342,7 +368,7 @@ __device__ __forceinline__ unsigned primary_tile(const KArgs& a, Stack& st, unsi
     }
     hit_ballot = __ballot_sync(kFull, p.valid && h.tri >= 0);
     const unsigned int_ballot = __ballot_sync(kFull, interested);
-    if (a.debug_timeline == 1 && p.valid) {
+    if (TL && a.debug_timeline == 1 && p.valid) {
         __syncwarp();
         const size_t at = (size_t)p.py * a.width + p.px;
         unsigned smid; asm volatile("mov.u32 %0, %smid;" : "=r"(smid));
@@ -476,7 +502,22 @@ __device__ __forceinline__ unsigned long long ld_volatile_u64(const unsigned lon
     return *reinterpret_cast<const volatile unsigned long long*>(p);
 }
 
-template <bool COUNT>
+// Out-of-line shading for the fused kernel: the shading code needs 72 registers, the traversal loops 56; inlined
+// into one kernel under the 64-register cap the traversal loops would carry the spills.
+#ifndef SRT_SHADE_INLINE
+__device__ __noinline__ void shade_pixel_call(const KArgs& a, Pixel p, Hit h, V3 d, unsigned tile, unsigned lane) {
+    shade_pixel(a, p, h, d, false, tile, lane);
+}
+__device__ __noinline__ void shade_tile_call(const KArgs& a, unsigned tile, unsigned lane) { shade_tile_from_memory(a, tile, lane); }
+#else
+__device__ __forceinline__ void shade_pixel_call(const KArgs& a, Pixel p, Hit h, V3 d, unsigned tile, unsigned lane) {
+    shade_pixel(a, p, h, d, false, tile, lane);
+}
+__device__ __forceinline__ void shade_tile_call(const KArgs& a, unsigned tile, unsigned lane) { shade_tile_from_memory(a, tile, lane); }
+#endif
+
+// COUNT / TL: the instrumented builds (variants 104 / 102, 103); the product kernel carries none of their state.
+template <bool COUNT, bool TL>
 __global__ void __launch_bounds__(kThreads, SRT_MINBLOCKS) render_dataflow(const __grid_constant__ KArgs a) {
     extern __shared__ uint32_t smem[];
     const unsigned lane = threadIdx.x & 31;
@@ -488,7 +529,7 @@ __global__ void __launch_bounds__(kThreads, SRT_MINBLOCKS) render_dataflow(const
     // debug_timeline == 2: per-warp timestamps (start, primary queue empty, end) + item counts in the t plane
     unsigned long long ts0 = 0, ts1 = 0, ts2 = 0; unsigned n_p = 0, n_s = 0, n_c = 0;
     unsigned box_occluded = 0, box_free = 0;   // COUNT: shadow-stage box tests by rays that ended occluded / unoccluded
-    if (a.debug_timeline == 2) asm volatile("mov.u64 %0, %globaltimer;" : "=l"(ts0));
+    if (TL && a.debug_timeline == 2) asm volatile("mov.u64 %0, %globaltimer;" : "=l"(ts0));
 
     for (;;) {
       const unsigned qbase = next_item(&a.counters[CNT_TILE], lane, SRT_PCHUNK);
@@ -497,9 +538,9 @@ __global__ void __launch_bounds__(kThreads, SRT_MINBLOCKS) render_dataflow(const
         ++n_p;
         const unsigned tile = a.tile_order[q];
         Pixel p; V3 d; Hit h; unsigned hit_ballot;
-        const unsigned int_ballot = primary_tile(a, st, tile, lane, p, d, h, hit_ballot, exact_count);
+        const unsigned int_ballot = primary_tile<TL>(a, st, tile, lane, p, d, h, hit_ballot, exact_count);
         if (int_ballot == 0) {
-            shade_pixel(a, p, h, d, false, tile, lane);
+            shade_pixel_call(a, p, h, d, tile, lane);
         } else {
             __threadfence();                                   // this lane's hit record before the publication
             __syncwarp();
@@ -519,7 +560,7 @@ __global__ void __launch_bounds__(kThreads, SRT_MINBLOCKS) render_dataflow(const
       }
     }
 
-    if (a.debug_timeline == 2) asm volatile("mov.u64 %0, %globaltimer;" : "=l"(ts1));
+    if (TL && a.debug_timeline == 2) asm volatile("mov.u64 %0, %globaltimer;" : "=l"(ts1));
     if (a.n_objects >= 2 && N > 0) {
         bool finished = false;
         while (!finished) {
@@ -555,14 +596,14 @@ __global__ void __launch_bounds__(kThreads, SRT_MINBLOCKS) render_dataflow(const
             last = __shfl_sync(kFull, last, 0);
             if (last) {
                 __threadfence();
-                shade_tile_from_memory(a, tile, lane);
+                shade_tile_call(a, tile, lane);
                 ++n_c;
             }
           }
         }
     }
 
-    if (a.debug_timeline == 2 && a.t) {
+    if (TL && a.debug_timeline == 2 && a.t) {
         asm volatile("mov.u64 %0, %globaltimer;" : "=l"(ts2));
         __syncwarp();
         if (lane == 0) {
@@ -631,6 +672,74 @@ cudaError_t launch_build_wide(const float4* nodes, const srt_object* objects, ui
 
 size_t phased_smem_bytes(int stack_cap) { return (size_t)stack_cap * kThreads * sizeof(uint32_t); }
 
+// ---------------------------------------------------------------------------------------------
+// srt_eval_leaf: one thread per case, the SAME device functions the render kernels call.
+namespace {
+__global__ void eval_leaf_kernel(int op, const float* __restrict__ in, float* __restrict__ out, size_t n, int wi, int wo) {
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const float* x = in + i * wi;
+    float* y = out + i * wo;
+    switch (op) {
+    case SRT_LEAF_POWF: y[0] = srt_powf(x[0], x[1]); break;
+    case SRT_LEAF_SLAB: {
+        const V3 o = v3(x[0], x[1], x[2]), d = v3(x[3], x[4], x[5]);
+        float bound = 0.f;
+        for (int k = 6; k < 12; ++k) bound = fmaxf(bound, fabsf(x[k]));
+        const FRay r = make_fray(o, d, bound);
+        float tn, tf; unsigned exact_count = 0;
+        const bool f = slab_filtered(r, x[6], x[7], x[8], x[9], x[10], x[11], tn, tf, exact_count);
+        y[0] = slab_exact(o, d, make_float4(x[6], x[7], x[8], 0.f), make_float4(x[9], x[10], x[11], 0.f)) ? 1.f : 0.f;
+        y[1] = f ? 1.f : 0.f;
+        y[2] = (float)exact_count;
+        break;
+    }
+    case SRT_LEAF_TRIANGLE:
+        y[0] = moller_trumbore(v3(x[0], x[1], x[2]), v3(x[3], x[4], x[5]), make_float4(x[6], x[7], x[8], 0.f),
+                               make_float4(x[9], x[10], x[11], 0.f), make_float4(x[12], x[13], x[14], 0.f));
+        break;
+    case SRT_LEAF_PHONG: {
+        PhongPixel px;
+        const V3 d = v3(x[3], x[4], x[5]);
+        const float t = x[18];
+        px.n = v3(x[0], x[1], x[2]);
+        px.P = v3(add(0.f, mul(t, d.x)), add(0.f, mul(t, d.y)), add(0.f, mul(t, d.z)));   // :156 with origin (0,0,0)
+        px.v = normalize3(v3(-d.x, -d.y, -d.z));                                           // :190
+        px.oc = v3(x[12], x[13], x[14]);
+        px.ambientStrength = x[15]; px.specularStrength = x[16]; px.shininess = x[17];
+        const V3 c = phong(px, v3(x[6], x[7], x[8]), v3(x[9], x[10], x[11]));
+        y[0] = c.x; y[1] = c.y; y[2] = c.z;
+        break;
+    }
+    case SRT_LEAF_TONE: y[0] = (float)tone_quantise(x[0], x[1], x[2]); break;
+    default: break;
+    }
+}
+}  // namespace
+
+int leaf_in_width(int op) {
+    switch (op) {
+    case SRT_LEAF_POWF: return 2;
+    case SRT_LEAF_SLAB: return 12;
+    case SRT_LEAF_TRIANGLE: return 15;
+    case SRT_LEAF_PHONG: return 19;
+    case SRT_LEAF_TONE: return 3;
+    default: return 0;
+    }
+}
+int leaf_out_width(int op) {
+    switch (op) {
+    case SRT_LEAF_POWF: case SRT_LEAF_TRIANGLE: case SRT_LEAF_TONE: return 1;
+    case SRT_LEAF_SLAB: case SRT_LEAF_PHONG: return 3;
+    default: return 0;
+    }
+}
+cudaError_t launch_eval_leaf(int op, const float* in, float* out, size_t n, cudaStream_t stream) {
+    if (n == 0) return cudaSuccess;
+    eval_leaf_kernel<<<(unsigned)((n + 127) / 128), 128, 0, stream>>>(op, in, out, n, leaf_in_width(op), leaf_out_width(op));
+    return cudaGetLastError();
+}
+
 cudaError_t launch_render_phased(const KArgs& a, int variant, int sm_count, cudaStream_t stream, int* launches) {
     const int n_tiles = a.tiles_x * a.tiles_y;
     if (launches) *launches = 0;
@@ -638,15 +747,16 @@ cudaError_t launch_render_phased(const KArgs& a, int variant, int sm_count, cuda
     const size_t smem = phased_smem_bytes(a.stack_cap);
     static bool attr_set = false;
     if (!attr_set) {
-        cudaFuncSetAttribute(render_dataflow<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024);
-        cudaFuncSetAttribute(render_dataflow<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024);
+        cudaFuncSetAttribute(render_dataflow<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024);
+        cudaFuncSetAttribute(render_dataflow<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024);
+        cudaFuncSetAttribute(render_dataflow<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024);
         cudaFuncSetAttribute(render_phase<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024);
         cudaFuncSetAttribute(render_phase<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024);
         cudaFuncSetAttribute(render_phase<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024);
         attr_set = true;
     }
     int per_sm = 0;
-    cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, render_dataflow<false>, kThreads, smem);
+    cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, render_dataflow<false, false>, kThreads, smem);
     if (e != cudaSuccess) return e;
     if (per_sm < 1) return cudaErrorLaunchOutOfResources;
     // Persistent grid: exactly the resident capacity.  (The dataflow kernel's waiting warps only wait for
@@ -664,8 +774,9 @@ cudaError_t launch_render_phased(const KArgs& a, int variant, int sm_count, cuda
         if (launches) *launches = 4;
         return cudaGetLastError();
     }
-    if (a.debug_timeline == 3) render_dataflow<true><<<blocks, kThreads, smem, stream>>>(a);   // node_visits / tri_tests = shadow box tests of occluded / free rays
-    else render_dataflow<false><<<blocks, kThreads, smem, stream>>>(a);
+    if (a.debug_timeline == 3) render_dataflow<true, false><<<blocks, kThreads, smem, stream>>>(a);   // node_visits / tri_tests = shadow box tests of occluded / free rays
+    else if (a.debug_timeline != 0) render_dataflow<false, true><<<blocks, kThreads, smem, stream>>>(a);
+    else render_dataflow<false, false><<<blocks, kThreads, smem, stream>>>(a);
     if (launches) *launches = 2;
     return cudaGetLastError();
 }
