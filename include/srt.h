@@ -141,9 +141,11 @@ typedef struct srt_render_params {
     int32_t row_block, shard_index, shard_count;
 } srt_render_params;
 
-enum { SRT_VARIANT_DEFAULT = 0,   /* phased persistent kernel (falls back to SIMPLE for the legacy one-box path) */
+enum { SRT_VARIANT_DEFAULT = 0,   /* staged pipeline: classify, primary, shadow (overlapping the primary pass's tail by
+                                     programmatic dependent launch), shade; falls back to SIMPLE for the legacy one-box path */
        SRT_VARIANT_SIMPLE = 1,    /* one thread = one pixel, whole pixel per work item */
-       SRT_VARIANT_SPLIT = 3,     /* the phased kernel as separate launches, one per phase (profiling) */
+       SRT_VARIANT_FUSED = 2,     /* the stages fused into one persistent dataflow kernel */
+       SRT_VARIANT_SPLIT = 3,     /* the stages as strictly ordered launches (per-stage profiling) */
        SRT_VARIANT_COUNT = 100,   /* SIMPLE + node / triangle counters */
        SRT_VARIANT_TIMELINE = 101 /* SIMPLE + per-tile cost map in the id / t planes (debug) */ };
 
@@ -166,7 +168,7 @@ typedef struct srt_stats {
     uint64_t tri_tests;
     uint64_t exact_slab_tests;    /* phased kernel: slab tests the filter could not decide (ran the exact divisions) */
     float    kernel_ms;           /* CUDA-event time of the render kernel(s) */
-    int32_t  kernel_launches;     /* kernels launched by the last srt_render (1, or one per phase for SRT_VARIANT_SPLIT) */
+    int32_t  kernel_launches;     /* kernels launched by the last srt_render */
 } srt_stats;
 
 typedef struct srt_context srt_context;

@@ -23,6 +23,7 @@ SRT_ERR_UNSUPPORTED = -6
 
 VARIANT_DEFAULT = 0
 VARIANT_SIMPLE = 1
+VARIANT_FUSED = 2
 VARIANT_SPLIT = 3
 VARIANT_COUNT = 100
 VARIANT_TIMELINE = 101

@@ -105,6 +105,33 @@ Box bounds(const std::vector<Triangle>& tris, const uint32_t* order, size_t n) {
 
 struct SortKey { float key; uint32_t index; };
 
+// Per-triangle data the build touches at every level, packed (the Triangle objects are 180 bytes apart):
+// pointOne.xyz (the sort keys, Object.cpp:193-201) and the triangle's own box.
+struct TriLite { float key[3]; float lo[3], hi[3]; };
+
+struct BuildInput {
+    const std::vector<Triangle>* tris;
+    std::vector<TriLite> lite;
+    bool finite = true;        // no NaN / inf coordinate: min / max over per-triangle boxes is order-independent
+};
+
+// calculateBoundingBoxes over an index range via the per-triangle boxes.  min / max of finite floats do not depend
+// on the evaluation order except for the sign of a zero result (glm::min keeps the first of +0 / -0), so a zero
+// component — and any input with non-finite coordinates — takes the reference's own loop.
+Box bounds_fast(const BuildInput& in, const uint32_t* order, size_t n) {
+    if (!in.finite) return bounds(*in.tris, order, n);
+    float lo0 = FLT_MAX, lo1 = FLT_MAX, lo2 = FLT_MAX, hi0 = -FLT_MAX, hi1 = -FLT_MAX, hi2 = -FLT_MAX;
+    for (size_t i = 0; i < n; ++i) {
+        const TriLite& t = in.lite[order[i]];
+        lo0 = t.lo[0] < lo0 ? t.lo[0] : lo0; lo1 = t.lo[1] < lo1 ? t.lo[1] : lo1; lo2 = t.lo[2] < lo2 ? t.lo[2] : lo2;
+        hi0 = hi0 < t.hi[0] ? t.hi[0] : hi0; hi1 = hi1 < t.hi[1] ? t.hi[1] : hi1; hi2 = hi2 < t.hi[2] ? t.hi[2] : hi2;
+    }
+    if (lo0 == 0.0f || lo1 == 0.0f || lo2 == 0.0f || hi0 == 0.0f || hi1 == 0.0f || hi2 == 0.0f) return bounds(*in.tris, order, n);
+    Box b;
+    b.lo = vec3(lo0, lo1, lo2); b.hi = vec3(hi0, hi1, hi2);
+    return b;
+}
+
 Node* make_leaf(const std::vector<Triangle>& tris, const uint32_t* order, size_t n, const Box& b) {
     Node* leaf = new Node();
     leaf->minBox = b.lo; leaf->maxBox = b.hi;
@@ -116,8 +143,8 @@ Node* make_leaf(const std::vector<Triangle>& tris, const uint32_t* order, size_t
 // splitTrianglesForBox, Object.cpp:225-272, on an index range instead of Triangle vectors.
 // Same tree: the axis rule (:240-248), std::sort on pointOne.axis with '<' (same introsort, same
 // comparison outcomes => same permutation), halves n/2 | rest (:254-255), recursion iff size > 8.
-Node* split(const std::vector<Triangle>& tris, uint32_t* order, size_t n, const Box& box,
-            std::vector<SortKey>& scratch) {
+Node* split(const BuildInput& in, uint32_t* order, size_t n, const Box& box, std::vector<SortKey>& scratch) {
+    const std::vector<Triangle>& tris = *in.tris;
     Node* node = new Node();
     node->minBox = box.lo; node->maxBox = box.hi;
     const float sx = std::fabs(box.hi.x - box.lo.x);
@@ -126,18 +153,17 @@ Node* split(const std::vector<Triangle>& tris, uint32_t* order, size_t n, const 
     const int axis = (sx > sy && sx > sz) ? 0 : ((sy > sx && sy > sz) ? 1 : 2);
     scratch.resize(n);
     for (size_t i = 0; i < n; ++i) {
-        const vec4& p = tris[order[i]].pointOne;
-        scratch[i].key = axis == 0 ? p.x : (axis == 1 ? p.y : p.z);
+        scratch[i].key = in.lite[order[i]].key[axis];
         scratch[i].index = order[i];
     }
     std::sort(scratch.begin(), scratch.end(), [](const SortKey& a, const SortKey& b) { return a.key < b.key; });
     for (size_t i = 0; i < n; ++i) order[i] = scratch[i].index;
     const size_t nl = n / 2, nr = n - nl;
-    const Box bl = bounds(tris, order, nl);
-    const Box br = bounds(tris, order + nl, nr);
+    const Box bl = bounds_fast(in, order, nl);
+    const Box br = bounds_fast(in, order + nl, nr);
     const size_t stop = 8;                                    // triangleSizeStop, Object.cpp:261
-    node->left = nl > stop ? split(tris, order, nl, bl, scratch) : make_leaf(tris, order, nl, bl);
-    node->right = nr > stop ? split(tris, order + nl, nr, br, scratch) : make_leaf(tris, order + nl, nr, br);
+    node->left = nl > stop ? split(in, order, nl, bl, scratch) : make_leaf(tris, order, nl, bl);
+    node->right = nr > stop ? split(in, order + nl, nr, br, scratch) : make_leaf(tris, order + nl, nr, br);
     return node;
 }
 
@@ -174,7 +200,23 @@ void ObjectManager::createBoundingHierarchy(const std::string& objFilename) {
     minBox[objFilename] = all.lo;
     maxBox[objFilename] = all.hi;
     std::vector<SortKey> scratch;
-    Node* root = split(triangles, order.data(), order.size(), all, scratch);   // the root is always split once (:282)
+    BuildInput in;
+    in.tris = &triangles;
+    in.lite.resize(triangles.size());
+    for (size_t i = 0; i < triangles.size(); ++i) {
+        const Triangle& t = triangles[i];
+        TriLite& l = in.lite[i];
+        const float px[3] = {t.pointOne.x, t.pointTwo.x, t.pointThree.x};
+        const float py[3] = {t.pointOne.y, t.pointTwo.y, t.pointThree.y};
+        const float pz[3] = {t.pointOne.z, t.pointTwo.z, t.pointThree.z};
+        l.key[0] = px[0]; l.key[1] = py[0]; l.key[2] = pz[0];
+        l.lo[0] = std::min(px[0], std::min(px[1], px[2])); l.hi[0] = std::max(px[0], std::max(px[1], px[2]));
+        l.lo[1] = std::min(py[0], std::min(py[1], py[2])); l.hi[1] = std::max(py[0], std::max(py[1], py[2]));
+        l.lo[2] = std::min(pz[0], std::min(pz[1], pz[2])); l.hi[2] = std::max(pz[0], std::max(pz[1], pz[2]));
+        for (int k = 0; k < 3; ++k)
+            if (!(std::isfinite(px[k]) && std::isfinite(py[k]) && std::isfinite(pz[k]))) in.finite = false;
+    }
+    Node* root = split(in, order.data(), order.size(), all, scratch);   // the root is always split once (:282)
     Node*& slot = boundingVolumeHierarchy[objFilename];
     free_tree(slot);
     slot = root;

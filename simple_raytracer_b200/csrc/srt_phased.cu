@@ -32,7 +32,10 @@ using namespace srtd;
 
 namespace {
 
-constexpr int kThreads = 128;
+#ifndef SRT_THREADS
+#define SRT_THREADS 128
+#endif
+constexpr int kThreads = SRT_THREADS;
 #ifndef SRT_MINBLOCKS
 #define SRT_MINBLOCKS 8
 #endif
@@ -440,41 +443,93 @@ __device__ __forceinline__ void shade_tile_from_memory(const KArgs& a, unsigned 
     shade_pixel(a, p, h, primary_dir(a, p), mine, tile, lane);
 }
 
-// ---- the three phases as separate passes (SRT_VARIANT_SPLIT: one launch each, for profiling) -------
+// ---- the three stages as separate passes -----------------------------------------------------------
+// OVERLAP (the production pipeline): the shadow pass is launched with programmatic stream serialization,
+// so its CTAs become resident as soon as CTAs of the primary pass retire and fill the SMs that pass's long
+// tail tiles (bunny silhouette: 100-400 k cycles each) would leave idle.  The passes are then ordered by
+// data, not by the launch boundary: a primary tile is PUBLISHED (hit records + interest word, fence,
+// tagged list entry, fence, "tiles decided" count) and a shadow item waits for its list entry.  The
+// primary CTAs are all resident before the first shadow CTA exists (the grid is the resident capacity and
+// every CTA triggers the dependent launch first thing), and they never wait, so the waits cannot deadlock.
+__device__ __forceinline__ unsigned long long ld_volatile_u64(const unsigned long long* p) {
+    return *reinterpret_cast<const volatile unsigned long long*>(p);
+}
+
+template <bool OVERLAP>
 __device__ __forceinline__ void phase_primary(const KArgs& a, uint32_t* smem, unsigned& exact_count) {
+    if (OVERLAP) asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
     const unsigned lane = threadIdx.x & 31;
     const unsigned n_tiles = (unsigned)(a.tiles_x * a.tiles_y);
     Stack st; st.base = smem + threadIdx.x; st.sp = 0;
-    unsigned hits = 0;
+    unsigned hits = 0, decided = 0;
     for (;;) {
         const unsigned q = next_item(&a.counters[CNT_TILE], lane);
         if (q >= n_tiles) break;
         const unsigned tile = a.tile_order[q];
         Pixel p; V3 d; Hit h; unsigned hit_ballot;
         const unsigned int_ballot = primary_tile(a, st, tile, lane, p, d, h, hit_ballot, exact_count);
+        ++decided;
+        if (OVERLAP && int_ballot) __syncwarp();                 // the lanes' hit records happen-before lane 0's fence
         if (lane == 0) {
             hits += __popc(hit_ballot);
             a.tile_interest[tile] = int_ballot;
             if (int_ballot) {
                 const unsigned slot = (unsigned)atomicAdd(&a.counters[CNT_LIST], 1ull);
-                a.tile_list[slot] = ((unsigned long long)a.frame_seq << 32) | tile;
+                const unsigned long long entry = ((unsigned long long)a.frame_seq << 32) | tile;
+                if (OVERLAP) {
+                    __threadfence();                             // (cumulative) hit records + interest word before the entry
+                    *reinterpret_cast<volatile unsigned long long*>(a.tile_list + slot) = entry;
+                } else {
+                    a.tile_list[slot] = entry;
+                }
             }
         }
+    }
+    if (OVERLAP) {                                               // this warp's tiles are decided: entries before the count
+        __syncwarp();
+        if (lane == 0) { __threadfence(); atomicAdd(&a.counters[CNT_PDONE], (unsigned long long)decided); }
     }
     if (lane == 0 && hits) atomicAdd(&a.counters[CNT_HIT], (unsigned long long)hits);
 }
 
+template <bool OVERLAP>
 __device__ __forceinline__ void phase_shadow(const KArgs& a, uint32_t* smem, unsigned& exact_count) {
     const unsigned lane = threadIdx.x & 31;
-    const unsigned n_list = (unsigned)a.counters[CNT_LIST];
-    const unsigned n_items = n_list * (unsigned)a.light_count;
+    const unsigned N = (unsigned)a.light_count;
     Stack st; st.base = smem + threadIdx.x; st.sp = 0;
+    if (!OVERLAP) {
+        const unsigned n_items = (unsigned)a.counters[CNT_LIST] * N;
+        for (;;) {
+            const unsigned item = next_item(&a.counters[CNT_SHADOW], lane);
+            if (item >= n_items) break;
+            const unsigned slot = item / N;
+            shadow_item(a, st, (unsigned)(a.tile_list[slot] & 0xffffffffull), (int)(item - slot * N), lane, exact_count);
+        }
+        return;
+    }
+    const unsigned n_tiles = (unsigned)(a.tiles_x * a.tiles_y);
+    const unsigned long long seq = a.frame_seq;
     for (;;) {
         const unsigned item = next_item(&a.counters[CNT_SHADOW], lane);
-        if (item >= n_items) break;
-        const unsigned slot = item / (unsigned)a.light_count;
-        shadow_item(a, st, (unsigned)(a.tile_list[slot] & 0xffffffffull), (int)(item - slot * (unsigned)a.light_count), lane,
-                    exact_count);
+        const unsigned slot = item / N;
+        unsigned long long e = 0;
+        if (lane == 0 && slot < n_tiles) {
+            for (unsigned spins = 0;; ++spins) {
+                e = ld_volatile_u64(a.tile_list + slot);
+                if ((e >> 32) == seq) break;
+                if (spins > (1u << 23)) { atomicAdd(&a.counters[CNT_TIMEOUT], 1ull); break; }   // > 1 s: give up loudly
+                if (ld_volatile_u64(a.counters + CNT_PDONE) >= n_tiles) {          // every tile decided: final answer
+                    __threadfence();
+                    e = ld_volatile_u64(a.tile_list + slot);
+                    break;
+                }
+                __nanosleep(200);
+            }
+        }
+        e = __shfl_sync(kFull, e, 0);
+        if ((e >> 32) != seq) break;                               // beyond the last published tile: no more work
+        __threadfence();
+        shadow_item(a, st, (unsigned)(e & 0xffffffffull), (int)(item - slot * N), lane, exact_count);
     }
 }
 
@@ -498,9 +553,6 @@ __device__ __forceinline__ void phase_shade(const KArgs& a) {
 // tile's last shadow item shades that tile.  No grid-wide barrier: the long primary tiles at the end
 // of the queue (bunny silhouette: 400 us against a 300 us phase) overlap with shadow and shading
 // work instead of idling the machine (profiles/r01_phased_fused: 35 % of warp samples sat in barriers).
-__device__ __forceinline__ unsigned long long ld_volatile_u64(const unsigned long long* p) {
-    return *reinterpret_cast<const volatile unsigned long long*>(p);
-}
 
 // Out-of-line shading for the fused kernel: the shading code needs 72 registers, the traversal loops 56; inlined
 // into one kernel under the 64-register cap the traversal loops would carry the spills.
@@ -624,13 +676,13 @@ __global__ void __launch_bounds__(kThreads, SRT_MINBLOCKS) render_dataflow(const
 
 __global__ void __launch_bounds__(kThreads) classify_kernel(const __grid_constant__ KArgs a) { phase_classify(a); }
 
-// The stages as separate launches (profiling each on its own).
-template <int PHASE>
+// The stages as separate launches.
+template <int PHASE, bool OVERLAP>
 __global__ void __launch_bounds__(kThreads) render_phase(const __grid_constant__ KArgs a) {
     extern __shared__ uint32_t smem[];
     unsigned exact_count = 0;
-    if (PHASE == 0) phase_primary(a, smem, exact_count);
-    if (PHASE == 1) phase_shadow(a, smem, exact_count);
+    if (PHASE == 0) phase_primary<OVERLAP>(a, smem, exact_count);
+    if (PHASE == 1) phase_shadow<OVERLAP>(a, smem, exact_count);
     if (PHASE == 2) phase_shade(a);
     for (int s = 16; s > 0; s >>= 1) exact_count += __shfl_xor_sync(kFull, exact_count, s);
     if ((threadIdx.x & 31) == 0 && exact_count) atomicAdd(&a.counters[CNT_EXACT], (unsigned long long)exact_count);
@@ -740,6 +792,20 @@ cudaError_t launch_eval_leaf(int op, const float* in, float* out, size_t n, cuda
     return cudaGetLastError();
 }
 
+namespace {
+template <class K>
+cudaError_t persistent_blocks(K kernel, size_t smem, int sm_count, int n_tiles, int* blocks) {
+    int per_sm = 0;
+    cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, kThreads, smem);
+    if (e != cudaSuccess) return e;
+    if (per_sm < 1) return cudaErrorLaunchOutOfResources;
+    *blocks = sm_count * per_sm;                                   // persistent grid: exactly the resident capacity
+    const int need = (n_tiles + kThreads / 32 - 1) / (kThreads / 32);
+    if (*blocks > need) *blocks = need;
+    return cudaSuccess;
+}
+}  // namespace
+
 cudaError_t launch_render_phased(const KArgs& a, int variant, int sm_count, cudaStream_t stream, int* launches) {
     const int n_tiles = a.tiles_x * a.tiles_y;
     if (launches) *launches = 0;
@@ -750,30 +816,46 @@ cudaError_t launch_render_phased(const KArgs& a, int variant, int sm_count, cuda
         cudaFuncSetAttribute(render_dataflow<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024);
         cudaFuncSetAttribute(render_dataflow<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024);
         cudaFuncSetAttribute(render_dataflow<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024);
-        cudaFuncSetAttribute(render_phase<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024);
-        cudaFuncSetAttribute(render_phase<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024);
-        cudaFuncSetAttribute(render_phase<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024);
+        cudaFuncSetAttribute(render_phase<0, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024);
+        cudaFuncSetAttribute(render_phase<1, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024);
+        cudaFuncSetAttribute(render_phase<0, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024);
+        cudaFuncSetAttribute(render_phase<1, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024);
         attr_set = true;
     }
-    int per_sm = 0;
-    cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, render_dataflow<false, false>, kThreads, smem);
-    if (e != cudaSuccess) return e;
-    if (per_sm < 1) return cudaErrorLaunchOutOfResources;
-    // Persistent grid: exactly the resident capacity.  (The dataflow kernel's waiting warps only wait for
-    // warps that already hold a tile, so it would also be correct with a larger grid.)
-    int blocks = sm_count * per_sm;
-    const int need = (n_tiles + kThreads / 32 - 1) / (kThreads / 32);
-    if (blocks > need) blocks = need;
     int cblocks = (n_tiles + kThreads - 1) / kThreads;
     if (cblocks > sm_count * 8) cblocks = sm_count * 8;
     classify_kernel<<<cblocks, kThreads, 0, stream>>>(a);
-    if (variant == SRT_VARIANT_SPLIT) {
-        render_phase<0><<<blocks, kThreads, smem, stream>>>(a);
-        if (a.n_objects >= 2 && a.light_count > 0) render_phase<1><<<blocks, kThreads, smem, stream>>>(a);
-        render_phase<2><<<blocks, kThreads, smem, stream>>>(a);
-        if (launches) *launches = 4;
+    cudaError_t e;
+    const bool shadows = a.n_objects >= 2 && a.light_count > 0;
+    if (variant == SRT_VARIANT_DEFAULT || variant == SRT_VARIANT_SPLIT) {
+        const bool overlap = variant == SRT_VARIANT_DEFAULT;
+        int bp = 0, bs = 0, bc = 0;
+        if ((e = persistent_blocks(render_phase<0, false>, smem, sm_count, n_tiles, &bp)) != cudaSuccess) return e;
+        if ((e = persistent_blocks(render_phase<1, false>, smem, sm_count, n_tiles, &bs)) != cudaSuccess) return e;
+        if ((e = persistent_blocks(render_phase<2, false>, 0, sm_count, n_tiles, &bc)) != cudaSuccess) return e;
+        int n = 1;
+        if (overlap && shadows) {
+            render_phase<0, true><<<bp, kThreads, smem, stream>>>(a);
+            cudaLaunchConfig_t cfg = {};
+            cfg.gridDim = dim3((unsigned)bs); cfg.blockDim = dim3(kThreads); cfg.dynamicSmemBytes = smem; cfg.stream = stream;
+            cudaLaunchAttribute attr[1];
+            attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+            attr[0].val.programmaticStreamSerializationAllowed = 1;
+            cfg.attrs = attr; cfg.numAttrs = 1;
+            if ((e = cudaLaunchKernelEx(&cfg, render_phase<1, true>, a)) != cudaSuccess) return e;
+            n += 2;
+        } else {
+            render_phase<0, false><<<bp, kThreads, smem, stream>>>(a);
+            ++n;
+            if (shadows) { render_phase<1, false><<<bs, kThreads, smem, stream>>>(a); ++n; }
+        }
+        render_phase<2, false><<<bc, kThreads, 0, stream>>>(a);
+        ++n;
+        if (launches) *launches = n;
         return cudaGetLastError();
     }
+    int blocks = 0;
+    if ((e = persistent_blocks(render_dataflow<false, false>, smem, sm_count, n_tiles, &blocks)) != cudaSuccess) return e;
     if (a.debug_timeline == 3) render_dataflow<true, false><<<blocks, kThreads, smem, stream>>>(a);   // node_visits / tri_tests = shadow box tests of occluded / free rays
     else if (a.debug_timeline != 0) render_dataflow<false, true><<<blocks, kThreads, smem, stream>>>(a);
     else render_dataflow<false, false><<<blocks, kThreads, smem, stream>>>(a);

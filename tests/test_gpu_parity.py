@@ -27,8 +27,9 @@ CASES = [
 ]
 
 
-# kernel variants: 0 = phased persistent kernel (default), 3 = the same as three launches, 1 = simple
-@pytest.mark.parametrize("variant", [0, 3, 1], ids=["phased", "split", "simple"])
+# kernel variants: 0 = staged pipeline with overlapped passes (default), 2 = the stages fused into one dataflow kernel,
+# 3 = the stages as strictly ordered launches, 1 = simple (one thread = one pixel, exact divisions everywhere)
+@pytest.mark.parametrize("variant", [0, 2, 3, 1], ids=["pipeline", "fused", "split", "simple"])
 @pytest.mark.parametrize("key,W,H,focal,N", CASES, ids=[c[0] for c in CASES])
 def test_frame_parity(gpu_ctx, ref_scene, key, W, H, focal, N, variant):
     cfg = scenes.CONFIGS[key]
@@ -114,14 +115,14 @@ def test_oracle_matches_reference_on_gpu_box(ref_scene):
 
 
 def test_full_size_c3_variants_agree_and_sample_matches_oracle(gpu_ctx, ref_scene):
-    """BASELINE configs[2] at its full size (1920x1080, 16 lights): the three kernel variants give identical
+    """BASELINE configs[2] at its full size (1920x1080, 16 lights): the four kernel variants give identical
     bytes (the simple kernel evaluates every slab test with the exact divisions, the phased ones with the
     filter), and every 48th pixel column equals the oracle."""
     _b, arrays, light = ref_scene("C3")
     W, H, focal, N = 1920, 1080, 1080.0, 16
     sc = gpu_ctx.upload(arrays)
     outs = []
-    for variant in (0, 3, 1):
+    for variant in (0, 2, 3, 1):
         p = _abi.default_params(W, H, focal, light, N, True)
         p.variant = variant
         outs.append(gpu_ctx.render(sc, p))
@@ -129,7 +130,7 @@ def test_full_size_c3_variants_agree_and_sample_matches_oracle(gpu_ctx, ref_scen
     for o in outs[1:]:
         for k in ("rgb", "obj_id", "tri_id", "t"):
             assert np.array_equal(outs[0][k], o[k]), k
-    assert outs[0]["stats"]["kernel_launches"] == 2 and outs[1]["stats"]["kernel_launches"] == 4
+    assert [o["stats"]["kernel_launches"] for o in outs] == [4, 2, 4, 1]
     p = _abi.default_params(W, H, focal, light, N, True)
     want = pyoracle.oracle_render(arrays, p, col_begin=7, col_step=48)
     cols = np.arange(7, W, 48)
@@ -165,7 +166,7 @@ def test_full_size_c4_textured_4k(gpu_ctx, ref_scene):
     print(f"C4 4K: phased {a['stats']['kernel_ms']:.3f} ms, simple {c['stats']['kernel_ms']:.3f} ms, hit pixels {a['stats']['hit_pixels']}")
 
 
-@pytest.mark.parametrize("variant", [0, 1], ids=["phased", "simple"])
+@pytest.mark.parametrize("variant", [0, 2, 1], ids=["pipeline", "fused", "simple"])
 def test_interleaved_row_block_shards_equal_full_frame(gpu_ctx, ref_scene, variant):
     """Multi-GPU single-frame mode (row_block / shard_index / shard_count): the shards of 1, 3 and 8 'ranks',
     rendered one after the other into the same buffers, reproduce the unsharded frame byte for byte."""
