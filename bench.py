@@ -417,6 +417,37 @@ def run_b200_arm(args):
             ln["scene"].destroy()
         ctx_b.destroy()
 
+    # ---- the reference's own result format (ImageData: sparse float lists, column-major) through the C ABI ----
+    imagedata = None
+    if not args.no_e2e and rank == 0 and not args.still:
+        fp = capi.C.POINTER(capi.C.c_float)
+        pts = capi.PinnedArray((W * H, 2), np.float32)
+        col = capi.PinnedArray((W * H, 3), np.float32)
+        sc2 = ctx.upload(pinned[0][0])
+        n_out = capi.C.c_uint64(0)
+
+        def imagedata_step(s):
+            k = s % n_unique
+            sc2.update(pinned[k][0])
+            capi._check(capi.lib().srt_render_sparse(ctx.h, sc2.h, capi.C.byref(params[k]), capi.C.byref(n_out)))
+            capi._check(capi.lib().srt_fetch_sparse(ctx.h, pts.array.ctypes.data_as(fp), col.array.ctypes.data_as(fp), n_out.value))
+            return n_out.value
+
+        for s in range(Wm):
+            imagedata_step(s)
+        torch.cuda.synchronize()
+        t_a = time.perf_counter()
+        entries = sum(imagedata_step(Wm + s) for s in range(K))
+        torch.cuda.synchronize()
+        ms = 1e3 * (time.perf_counter() - t_a) / K
+        imagedata = {"ms_per_frame": ms, "frames_per_s": 1e3 / ms, "entries_per_frame": entries / K,
+                     "d2h_bytes_per_frame": 20 * entries / K,
+                     "what": "rank 0: srt_scene_update + srt_render_sparse (render, device-side compaction into the reference's "
+                             "ImageData layout, simple_raytracer.cpp:505-525) + srt_fetch_sparse into pinned host memory; synchronous "
+                             "calls, host wall clock"}
+        sc2.destroy()
+        pts.free(); col.free()
+
     # ---- image series including host prep (parse cache + prep thread pool + upload + render + download) ----
     series = None
     if args.series_frames != 0 and not args.still:
@@ -500,6 +531,8 @@ def run_b200_arm(args):
             line["roofline_l2"] = {"bound": "l2", "achieved": l2b / (kern_ms * 1e-3) / 1e9, "peak": l2_peak, "unit": "GB/s",
                                    "frac": l2b / (kern_ms * 1e-3) / 1e9 / l2_peak,
                                    "peak_source": "6300 B/cycle (microarchitecture guide, measured on B300) x SM clock"}
+        if imagedata:
+            line["e2e_imagedata"] = imagedata
         if e2e:
             line["e2e"] = {"value": rays_total / (e2e_ms * 1e-3) / 1e6, "unit": UNIT, "h2d_bytes_per_step": int(e2e[1]) * world,
                            "d2h_bytes_per_step": int(e2e[2]) * (1 if args.gather else world), "ms_per_step": e2e_ms / K,

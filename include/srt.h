@@ -203,6 +203,15 @@ int  srt_sync(srt_context* ctx);
 /* Statistics of the most recent srt_render on this context (synchronises the context). */
 int  srt_last_stats(srt_context* ctx, srt_stats* out);
 
+/* ---- render with the reference's own result format (struct ImageData :28, filled by :505-525) ----
+ * Renders like srt_render, then compacts on the device: only the pixels whose quantised colour is not (0,0,0)
+ * (:518), in the reference's column-major scan order (x outer :511, y inner :513); positions (x, y) and colours
+ * (r, g, b in 0..255) as floats, i.e. the memory layout of std::vector<glm::vec2> / std::vector<glm::vec3>.
+ * srt_render_sparse synchronises and returns the number of entries; srt_fetch_sparse copies up to `capacity`
+ * entries to host or device arrays (points_xy[2*i], colors_rgb[3*i]; either may be NULL). */
+int  srt_render_sparse(srt_context* ctx, const srt_scene* scene, const srt_render_params* params, uint64_t* count);
+int  srt_fetch_sparse(srt_context* ctx, float* points_xy, float* colors_rgb, uint64_t capacity);
+
 /* ---- helpers ---- */
 void srt_default_params(srt_render_params* p);             /* fills the reference's literals */
 /* Light staircase of softShadow :363-383: out[3*i..] for i < count, sequential fp32 adds. */

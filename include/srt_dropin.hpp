@@ -24,6 +24,7 @@
 #include <cstdint>
 #include <stdexcept>
 #include <string>
+#include <type_traits>
 #include <vector>
 
 #include "srt.h"
@@ -81,15 +82,27 @@ public:
         params.width = (int32_t)imageSize.x;
         params.height = (int32_t)imageSize.y;
         params.light_pos[0] = lightPos.x; params.light_pos[1] = lightPos.y; params.light_pos[2] = lightPos.z;
+        ImageDataT out;
+        using P = typename decltype(out.imagePoints)::value_type;
+        using Cl = typename decltype(out.imageColors)::value_type;
+        if (sizeof(P) == 2 * sizeof(float) && sizeof(Cl) == 3 * sizeof(float) && std::is_trivially_copyable<P>::value &&
+            std::is_trivially_copyable<Cl>::value) {
+            // glm::vec2 / glm::vec3 are packed floats: the device builds both lists (non-black filter :518,
+            // column-major order :511-513) and they are copied straight into the vectors' storage.
+            uint64_t n = 0;
+            check(srt_render_sparse(ctx_, scene_, &params, &n));
+            out.imagePoints.resize((size_t)n);
+            out.imageColors.resize((size_t)n);
+            check(srt_fetch_sparse(ctx_, reinterpret_cast<float*>(out.imagePoints.data()),
+                                   reinterpret_cast<float*>(out.imageColors.data()), n));
+            return out;
+        }
         const int32_t keep = params.no_sky_fill;
         params.no_sky_fill = 1;                // (0,0,0) marks "not drawn" exactly like :518
         std::vector<uint8_t> rgb;
         render(rgb);
         params.no_sky_fill = keep;
-        ImageDataT out;
         const int W = params.width, H = params.height;
-        using P = typename decltype(out.imagePoints)::value_type;
-        using Cl = typename decltype(out.imageColors)::value_type;
         for (int x = 0; x < W; ++x)            // :511 outer loop over columns
             for (int y = 0; y < H; ++y) {      // :513
                 const uint8_t* c = &rgb[((size_t)y * W + x) * 3];

@@ -22,7 +22,7 @@ EXPORTS = [
     "srt_context_set_stream", "srt_context_get_info", "srt_scene_upload", "srt_scene_update",
     "srt_scene_destroy", "srt_render", "srt_sync", "srt_last_stats", "srt_default_params",
     "srt_light_positions", "srt_host_alloc", "srt_host_free", "srt_device_alloc", "srt_device_free",
-    "srt_last_error", "srt_eval_leaf",
+    "srt_last_error", "srt_eval_leaf", "srt_render_sparse", "srt_fetch_sparse",
 ]
 
 
@@ -62,6 +62,8 @@ def lib():
         L.srt_default_params.argtypes = [C.POINTER(_abi.RenderParams)]
         L.srt_default_params.restype = None
         L.srt_light_positions.argtypes = [C.POINTER(_abi.RenderParams), C.POINTER(C.c_float)]
+        L.srt_render_sparse.argtypes = [vp, vp, C.POINTER(_abi.RenderParams), C.POINTER(C.c_uint64)]
+        L.srt_fetch_sparse.argtypes = [vp, C.POINTER(C.c_float), C.POINTER(C.c_float), C.c_uint64]
         L.srt_eval_leaf.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_float), C.POINTER(C.c_float), C.c_size_t]
         L.srt_host_alloc.argtypes = [C.c_size_t]
         L.srt_host_alloc.restype = vp
@@ -176,6 +178,16 @@ class Context:
                         tri.ctypes.data if ids else None, tt.ctypes.data if want_t else None)
         self.sync()
         return dict(rgb=rgb, obj_id=obj, tri_id=tri, t=tt, stats=self.last_stats())
+
+    def render_sparse(self, scene: Scene, params: _abi.RenderParams):
+        """The reference's ImageData: (points[n][2], colors[n][3]) of the drawn pixels, column-major order."""
+        n = C.c_uint64(0)
+        _check(lib().srt_render_sparse(self.h, scene.h, C.byref(params), C.byref(n)))
+        pts = np.zeros((n.value, 2), np.float32)
+        col = np.zeros((n.value, 3), np.float32)
+        fp = C.POINTER(C.c_float)
+        _check(lib().srt_fetch_sparse(self.h, pts.ctypes.data_as(fp), col.ctypes.data_as(fp), n.value))
+        return pts, col
 
     def sync(self):
         _check(lib().srt_sync(self.h))

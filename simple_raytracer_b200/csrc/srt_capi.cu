@@ -72,6 +72,10 @@ struct srt_context {
     DevBuf out_rgb, out_obj, out_tri, out_t;     // staging for HOST output pointers
     DevBuf hit_t, hit_tri, tile_interest, tile_list, tile_order, tile_done, shadow_mask;
     uint32_t frame_seq = 0;   // scratch of the phased kernel
+    DevBuf sparse_rgb, sparse_seg, sparse_points, sparse_colors, sparse_total;   // srt_render_sparse
+    unsigned long long* sparse_total_host = nullptr;   // pinned
+    uint64_t sparse_count = 0;
+    bool have_sparse = false;
     int last_launches = 0;
     // last render
     bool have_last = false;
@@ -148,6 +152,8 @@ void srt_context_destroy(srt_context* c) {
     c->hit_t.release(); c->hit_tri.release(); c->tile_interest.release(); c->tile_list.release(); c->tile_order.release(); c->tile_done.release(); c->shadow_mask.release();
     if (c->counters) cudaFree(c->counters);
     if (c->counters_host) cudaFreeHost(c->counters_host);
+    c->sparse_rgb.release(); c->sparse_seg.release(); c->sparse_points.release(); c->sparse_colors.release(); c->sparse_total.release();
+    if (c->sparse_total_host) cudaFreeHost(c->sparse_total_host);
     if (c->ev0) cudaEventDestroy(c->ev0);
     if (c->ev1) cudaEventDestroy(c->ev1);
     if (c->ev_copy) cudaEventDestroy(c->ev_copy);
@@ -553,6 +559,50 @@ int srt_render(srt_context* c, const srt_scene* s, const srt_render_params* p, c
     c->last_primary = my_rows * (uint64_t)p->width;
     c->last_lights = p->light_count;
     c->last_objects = s->n_objects;
+    return SRT_OK;
+}
+
+int srt_render_sparse(srt_context* c, const srt_scene* s, const srt_render_params* p, uint64_t* count) {
+    if (!c || !s || !p || !count) return fail(SRT_ERR_INVALID_ARG, "NULL argument");
+    if (p->row_block != 0 || p->shard_count > 1)
+        return fail(SRT_ERR_INVALID_ARG, "srt_render_sparse: interleaved row sharding is not supported (use row_begin / row_end)");
+    if (p->width <= 0 || p->height <= 0) return fail(SRT_ERR_INVALID_ARG, "bad image size %dx%d", p->width, p->height);
+    CU(cudaSetDevice(c->device));
+    const size_t npix = (size_t)p->width * p->height;
+    int rc;
+    if ((rc = c->sparse_rgb.reserve(npix * 3))) return rc;
+    srt_render_params q = *p;
+    q.no_sky_fill = 1;                                   // (0,0,0) marks "not drawn" exactly like :518
+    srt_frame fr = {(uint8_t*)c->sparse_rgb.p, nullptr, nullptr, nullptr};
+    if ((rc = srt_render(c, s, &q, &fr))) return rc;
+    int rb = p->row_begin, re = p->row_end;
+    if (rb == 0 && re == 0) re = p->height;
+    const size_t rows_px = (size_t)(re - rb) * p->width;
+    if ((rc = c->sparse_seg.reserve(srtk::sparse_segments(p->width, re - rb) * sizeof(uint32_t) + 4))) return rc;
+    if ((rc = c->sparse_points.reserve(rows_px * 2 * sizeof(float) + 4))) return rc;
+    if ((rc = c->sparse_colors.reserve(rows_px * 3 * sizeof(float) + 4))) return rc;
+    if ((rc = c->sparse_total.reserve(sizeof(unsigned long long)))) return rc;
+    if (!c->sparse_total_host) CU(cudaMallocHost(&c->sparse_total_host, sizeof(unsigned long long)));
+    cudaError_t e = srtk::launch_sparse_compact((const uint8_t*)c->sparse_rgb.p, p->width, rb, re, (uint32_t*)c->sparse_seg.p,
+                                                (float*)c->sparse_points.p, (float*)c->sparse_colors.p,
+                                                (unsigned long long*)c->sparse_total.p, c->stream);
+    if (e != cudaSuccess) return fail(SRT_ERR_CUDA, "sparse compaction launch: %s", cudaGetErrorString(e));
+    CU(cudaMemcpyAsync(c->sparse_total_host, c->sparse_total.p, sizeof(unsigned long long), cudaMemcpyDeviceToHost, c->stream));
+    CU(cudaStreamSynchronize(c->stream));
+    c->sparse_count = *c->sparse_total_host;
+    c->have_sparse = true;
+    *count = c->sparse_count;
+    return SRT_OK;
+}
+
+int srt_fetch_sparse(srt_context* c, float* points_xy, float* colors_rgb, uint64_t capacity) {
+    if (!c) return fail(SRT_ERR_INVALID_ARG, "NULL context");
+    if (!c->have_sparse) return fail(SRT_ERR_INVALID_ARG, "srt_fetch_sparse: no srt_render_sparse has been issued on this context");
+    CU(cudaSetDevice(c->device));
+    const uint64_t n = c->sparse_count < capacity ? c->sparse_count : capacity;
+    if (n && points_xy) CU(cudaMemcpyAsync(points_xy, c->sparse_points.p, n * 2 * sizeof(float), cudaMemcpyDefault, c->stream));
+    if (n && colors_rgb) CU(cudaMemcpyAsync(colors_rgb, c->sparse_colors.p, n * 3 * sizeof(float), cudaMemcpyDefault, c->stream));
+    CU(cudaStreamSynchronize(c->stream));
     return SRT_OK;
 }
 

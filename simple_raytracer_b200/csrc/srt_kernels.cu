@@ -176,6 +176,76 @@ __global__ void __launch_bounds__(128) render_simple(const __grid_constant__ KAr
 
 }  // namespace
 
+// ---------------------------------------------------------------------------------------------
+// Sparse output: the reference's ImageData (simple_raytracer.cpp:28, :505-525) — only the pixels whose quantised
+// colour is not (0,0,0) (:518), in its column-major scan order (x outer :511, y inner :513), positions and colours
+// as floats.  Three small kernels over the rendered RGB8 frame: count per (column, 32-row segment), exclusive scan
+// in (column-major) segment order, scatter.
+namespace {
+constexpr int kSegRows = 32;
+
+__device__ __forceinline__ bool drawn(const uint8_t* rgb, size_t at) { return (rgb[3 * at] | rgb[3 * at + 1] | rgb[3 * at + 2]) != 0; }
+
+__global__ void sparse_count_kernel(const uint8_t* __restrict__ rgb, int width, int row_begin, int row_end, int n_seg,
+                                    uint32_t* __restrict__ counts) {
+    const int x = blockIdx.x * blockDim.x + threadIdx.x, seg = blockIdx.y;
+    if (x >= width) return;
+    const int y0 = row_begin + seg * kSegRows, y1 = min(y0 + kSegRows, row_end);
+    uint32_t n = 0;
+    for (int y = y0; y < y1; ++y) n += drawn(rgb, (size_t)y * width + x) ? 1u : 0u;
+    counts[(size_t)x * n_seg + seg] = n;
+}
+
+// One block: exclusive scan of counts[0..n) in place, total to *total.
+__global__ void sparse_scan_kernel(uint32_t* __restrict__ counts, uint32_t n, unsigned long long* __restrict__ total) {
+    __shared__ uint32_t part[1024];
+    const uint32_t per = (n + blockDim.x - 1) / blockDim.x;
+    const uint32_t b = min(threadIdx.x * per, n), e = min(b + per, n);
+    uint32_t sum = 0;
+    for (uint32_t i = b; i < e; ++i) sum += counts[i];
+    part[threadIdx.x] = sum;
+    __syncthreads();
+    for (uint32_t off = 1; off < blockDim.x; off <<= 1) {               // Hillis-Steele over the per-thread sums
+        const uint32_t v = threadIdx.x >= off ? part[threadIdx.x - off] : 0u;
+        __syncthreads();
+        part[threadIdx.x] += v;
+        __syncthreads();
+    }
+    uint32_t run = part[threadIdx.x] - sum;                             // exclusive prefix of this thread's chunk
+    for (uint32_t i = b; i < e; ++i) { const uint32_t c = counts[i]; counts[i] = run; run += c; }
+    if (threadIdx.x == blockDim.x - 1) *total = part[threadIdx.x];
+}
+
+__global__ void sparse_write_kernel(const uint8_t* __restrict__ rgb, int width, int row_begin, int row_end, int n_seg,
+                                    const uint32_t* __restrict__ offsets, float* __restrict__ points, float* __restrict__ colors) {
+    const int x = blockIdx.x * blockDim.x + threadIdx.x, seg = blockIdx.y;
+    if (x >= width) return;
+    const int y0 = row_begin + seg * kSegRows, y1 = min(y0 + kSegRows, row_end);
+    size_t o = offsets[(size_t)x * n_seg + seg];
+    for (int y = y0; y < y1; ++y) {
+        const size_t at = (size_t)y * width + x;
+        if (!drawn(rgb, at)) continue;
+        points[2 * o] = (float)x; points[2 * o + 1] = (float)y;                       // glm::vec2(x, y)          :516
+        colors[3 * o] = (float)rgb[3 * at]; colors[3 * o + 1] = (float)rgb[3 * at + 1]; colors[3 * o + 2] = (float)rgb[3 * at + 2];
+        ++o;
+    }
+}
+}  // namespace
+
+size_t sparse_segments(int width, int rows) { return (size_t)width * (size_t)((rows + kSegRows - 1) / kSegRows); }
+
+cudaError_t launch_sparse_compact(const uint8_t* rgb, int width, int row_begin, int row_end, uint32_t* seg_counts, float* points,
+                                  float* colors, unsigned long long* total, cudaStream_t stream) {
+    const int rows = row_end - row_begin;
+    if (width <= 0 || rows <= 0) return cudaMemsetAsync(total, 0, sizeof(unsigned long long), stream);
+    const int n_seg = (rows + kSegRows - 1) / kSegRows;
+    const dim3 grid((unsigned)((width + 127) / 128), (unsigned)n_seg);
+    sparse_count_kernel<<<grid, 128, 0, stream>>>(rgb, width, row_begin, row_end, n_seg, seg_counts);
+    sparse_scan_kernel<<<1, 1024, 0, stream>>>(seg_counts, (uint32_t)((size_t)width * n_seg), total);
+    sparse_write_kernel<<<grid, 128, 0, stream>>>(rgb, width, row_begin, row_end, n_seg, seg_counts, points, colors);
+    return cudaGetLastError();
+}
+
 cudaError_t launch_render(const KArgs& a, int variant, int sm_count, cudaStream_t stream) {
     const int n_tiles = a.tiles_x * a.tiles_y;
     if (n_tiles <= 0) return cudaSuccess;

@@ -83,6 +83,11 @@ cudaError_t launch_build_wide(const float4* nodes, const srt_object* objects, ui
 // Shared memory the phased kernel needs per CTA for `stack_cap`, and whether it fits.
 size_t phased_smem_bytes(int stack_cap);
 // Single cooperative launch (variant SRT_VARIANT_DEFAULT) or three launches (SRT_VARIANT_SPLIT).
+// Sparse (ImageData-style) output of a rendered RGB8 frame: srt_render_sparse.  seg_counts: sparse_segments() words.
+size_t sparse_segments(int width, int rows);
+cudaError_t launch_sparse_compact(const uint8_t* rgb, int width, int row_begin, int row_end, uint32_t* seg_counts, float* points,
+                                  float* colors, unsigned long long* total, cudaStream_t stream);
+
 // Leaf evaluation hook (srt_eval_leaf): `in` / `out` are device arrays.
 int leaf_in_width(int op);
 int leaf_out_width(int op);

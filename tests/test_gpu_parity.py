@@ -210,6 +210,36 @@ def test_dropin_adapter_equals_verbatim_reference_function(ref_scene):
     assert np.count_nonzero(want_c != got_c) <= 3
 
 
+def test_sparse_output_equals_dense_frame(gpu_ctx, ref_scene):
+    """srt_render_sparse (device-side compaction into the reference's ImageData layout, :505-525): exactly the
+    non-black pixels of the dense frame rendered without sky fill, in column-major order, as floats — at odd
+    sizes, for a row range, and at the full 1080p size."""
+    _b, arrays, light = ref_scene("C3")
+    sc = gpu_ctx.upload(arrays)
+    for W, H, rows in ((150, 100, None), (97, 33, None), (64, 70, (13, 51)), (1920, 1080, None)):
+        p = _abi.default_params(W, H, float(H), light, 2, True)
+        if rows:
+            p.row_begin, p.row_end = rows
+        pts, col = gpu_ctx.render_sparse(sc, p)
+        p.no_sky_fill = 1
+        rgb = gpu_ctx.render(sc, p, ids=False, want_t=False)["rgb"]
+        r0, r1 = rows if rows else (0, H)
+        drawn = rgb.any(axis=2)
+        drawn[:r0] = False
+        drawn[r1:] = False
+        xs, ys = np.nonzero(drawn.T)                       # column-major: x outer, y inner
+        assert len(pts) == len(xs) and len(xs) > 0
+        assert np.array_equal(pts[:, 0], xs.astype(np.float32)) and np.array_equal(pts[:, 1], ys.astype(np.float32))
+        assert np.array_equal(col, rgb[ys, xs].astype(np.float32))
+    sc.destroy()
+    empty = _abi.FlatSceneArrays(np.zeros(0, _abi.NODE_DTYPE), np.zeros(0, _abi.GEOM_DTYPE), np.zeros(0, _abi.ATTR_DTYPE),
+                                 np.zeros(0, _abi.OBJECT_DTYPE), ())
+    sc = gpu_ctx.upload(empty)
+    pts, col = gpu_ctx.render_sparse(sc, _abi.default_params(40, 30, 30.0, light, 1, True))
+    assert len(pts) == 0 and len(col) == 0
+    sc.destroy()
+
+
 def test_series_driver_equals_frame_by_frame(gpu_ctx):
     """series.SeriesRenderer (asset cache + prep thread pool + scene update in place) renders the same bytes
     as building and uploading every frame from scratch."""
