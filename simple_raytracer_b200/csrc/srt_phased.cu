@@ -1,5 +1,5 @@
-// srt_phased.cu — the production render kernel (sm_100a): one persistent grid, three stages connected
-// by dataflow (no grid barrier).  See DESIGN.md §Kernels.
+// srt_phased.cu — the production render kernels (sm_100a): three stages, each a persistent grid of warps that
+// pull work items from atomic queues.  See DESIGN.md §4.
 //
 //   P  primary   work item = 8x4 pixel tile (one warp, lane = pixel): primary ray (:505-517), closest hit
 //                over every object's BVH (:405-431, :296-317, :42-75) -> hit record (t, triangle) in
@@ -14,6 +14,10 @@
 //   C  shade     work item = tile: base colour / texture (:350-361, :437-443), N x Phong (:144-200)
 //                with the /5 of occluded lights (:369), tone map, gamma, quantise, sky (:391-398,
 //                :447-449, :476-487).
+//
+// The default path launches the stages as separate kernels, the shadow pass overlapping the primary pass's tail
+// through programmatic dependent launch (render_phase<PHASE, OVERLAP>); render_dataflow is the same three stage
+// bodies fused into one kernel (SRT_VARIANT_FUSED).
 //
 // Arithmetic: everything that reaches an output (Moeller-Trumbore, hit point, Phong, tone map) is the
 // exact operation sequence of srt_device.cuh.  The slab test is evaluated with a FILTER: an
@@ -32,20 +36,9 @@ using namespace srtd;
 
 namespace {
 
-#ifndef SRT_THREADS
-#define SRT_THREADS 128
-#endif
-constexpr int kThreads = SRT_THREADS;
-#ifndef SRT_MINBLOCKS
-#define SRT_MINBLOCKS 8
-#endif
+constexpr int kThreads = 128;       // 4 warps per CTA (64 / 32 measured: +-1 %)
+constexpr int kFusedMinBlocks = 8;  // the fused kernel: 64 registers
 // queue entries a warp takes per atomic: consecutive tiles / consecutive lights of one tile (locality in the SM's L1)
-#ifndef SRT_PCHUNK
-#define SRT_PCHUNK 1
-#endif
-#ifndef SRT_SCHUNK
-#define SRT_SCHUNK 1
-#endif
 constexpr unsigned kFull = 0xffffffffu;
 
 // ---------------------------------------------------------------------------------------------
@@ -106,11 +99,7 @@ __device__ __forceinline__ FRay make_fray(V3 o, V3 d, float coord_bound) {
     return r;
 }
 
-#ifdef SRT_EXACT_NOINLINE
-__device__ __noinline__ bool slab_exact_call(V3 o, V3 d, float4 lo, float4 hi) { return slab_exact(o, d, lo, hi); }
-#else
 __device__ __forceinline__ bool slab_exact_call(V3 o, V3 d, float4 lo, float4 hi) { return slab_exact(o, d, lo, hi); }
-#endif
 
 // Returns the reference's decision for this box.  `tn_out` = approximate entry parameter (ordering only).
 __device__ __forceinline__ bool slab_filtered(const FRay& r, float lox, float loy, float loz, float hix, float hiy,
@@ -556,21 +545,14 @@ __device__ __forceinline__ void phase_shade(const KArgs& a) {
 
 // Out-of-line shading for the fused kernel: the shading code needs 72 registers, the traversal loops 56; inlined
 // into one kernel under the 64-register cap the traversal loops would carry the spills.
-#ifndef SRT_SHADE_INLINE
 __device__ __noinline__ void shade_pixel_call(const KArgs& a, Pixel p, Hit h, V3 d, unsigned tile, unsigned lane) {
     shade_pixel(a, p, h, d, false, tile, lane);
 }
 __device__ __noinline__ void shade_tile_call(const KArgs& a, unsigned tile, unsigned lane) { shade_tile_from_memory(a, tile, lane); }
-#else
-__device__ __forceinline__ void shade_pixel_call(const KArgs& a, Pixel p, Hit h, V3 d, unsigned tile, unsigned lane) {
-    shade_pixel(a, p, h, d, false, tile, lane);
-}
-__device__ __forceinline__ void shade_tile_call(const KArgs& a, unsigned tile, unsigned lane) { shade_tile_from_memory(a, tile, lane); }
-#endif
 
 // COUNT / TL: the instrumented builds (variants 104 / 102, 103); the product kernel carries none of their state.
 template <bool COUNT, bool TL>
-__global__ void __launch_bounds__(kThreads, SRT_MINBLOCKS) render_dataflow(const __grid_constant__ KArgs a) {
+__global__ void __launch_bounds__(kThreads, kFusedMinBlocks) render_dataflow(const __grid_constant__ KArgs a) {
     extern __shared__ uint32_t smem[];
     const unsigned lane = threadIdx.x & 31;
     const unsigned n_tiles = (unsigned)(a.tiles_x * a.tiles_y);
@@ -584,9 +566,9 @@ __global__ void __launch_bounds__(kThreads, SRT_MINBLOCKS) render_dataflow(const
     if (TL && a.debug_timeline == 2) asm volatile("mov.u64 %0, %globaltimer;" : "=l"(ts0));
 
     for (;;) {
-      const unsigned qbase = next_item(&a.counters[CNT_TILE], lane, SRT_PCHUNK);
-      if (qbase >= n_tiles) break;
-      for (unsigned q = qbase; q < qbase + SRT_PCHUNK && q < n_tiles; ++q) {
+      const unsigned q = next_item(&a.counters[CNT_TILE], lane);
+      if (q >= n_tiles) break;
+      {
         ++n_p;
         const unsigned tile = a.tile_order[q];
         Pixel p; V3 d; Hit h; unsigned hit_ballot;
@@ -616,8 +598,8 @@ __global__ void __launch_bounds__(kThreads, SRT_MINBLOCKS) render_dataflow(const
     if (a.n_objects >= 2 && N > 0) {
         bool finished = false;
         while (!finished) {
-          const unsigned sbase = next_item(&a.counters[CNT_SHADOW], lane, SRT_SCHUNK);
-          for (unsigned s = sbase; s < sbase + SRT_SCHUNK; ++s) {
+          const unsigned s = next_item(&a.counters[CNT_SHADOW], lane);
+          {
             const unsigned slot = s / N;
             const int light = (int)(s - slot * N);
             unsigned long long e = 0;

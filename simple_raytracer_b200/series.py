@@ -7,7 +7,8 @@ This driver keeps the per-frame work bit-identical and takes it off the critical
   * assets are parsed / decoded once (host.set_asset_cache: loading is deterministic);
   * frames are prepared `depth` ahead on a pool of host threads (the C++ scene calls release the GIL);
   * the prepared, flattened scene is uploaded straight from the C++-owned arrays (no Python copy), rendered,
-    and the frame is read back — on the context's stream, one frame after the other.
+    and the frame is read back into pinned memory — asynchronously, on two contexts (streams) that alternate, so
+    the GPU leg of frame i runs while the driver waits for the prep of frame i+1.
 
 With several GPUs each rank runs this driver on its own frames (frame f -> rank f % world, multigpu.py).
 """
@@ -33,6 +34,24 @@ def prepare_frame(cfg: scenes.SceneConfig, angle_deg: float):
     return hs, desc, np.asarray(light, np.float32)
 
 
+class _Lane:
+    """One context + device scene + pinned host frame.  Two lanes alternate so that the upload / render / download
+    of frame i overlaps the wait for the host prep of frame i+1."""
+
+    def __init__(self, ctx: capi.Context, width: int, height: int, own_ctx: bool):
+        self.ctx, self.own_ctx = ctx, own_ctx
+        self.scene: Optional[capi.Scene] = None
+        self.frame = capi.PinnedArray((height, width, 3), np.uint8)
+
+    def close(self):
+        if self.scene is not None:
+            self.scene.destroy()
+            self.scene = None
+        self.frame.free()
+        if self.own_ctx:
+            self.ctx.destroy()
+
+
 class SeriesRenderer:
     def __init__(self, ctx: capi.Context, cfg: scenes.SceneConfig, width: int, height: int, focal: float,
                  light_count: int, workers: Optional[int] = None, depth: Optional[int] = None, variant: int = 0):
@@ -40,16 +59,42 @@ class SeriesRenderer:
         self.width, self.height, self.focal, self.light_count, self.variant = width, height, focal, light_count, variant
         self.workers = workers or max(1, len(os.sched_getaffinity(0)))
         self.depth = depth or 2 * self.workers
-        self.scene: Optional[capi.Scene] = None
+        self.lanes = [_Lane(ctx, width, height, False), _Lane(capi.Context(ctx.device), width, height, True)]
         host.set_asset_cache(True)
 
+    def _issue(self, lane: _Lane, desc, light):
+        """Upload + render + download of one frame on the lane's stream, asynchronous."""
+        if lane.scene is None:
+            h = capi.C.c_void_p()
+            capi._check(capi.lib().srt_scene_upload(lane.ctx.h, desc, capi.C.byref(h)))
+            lane.scene = capi.Scene(lane.ctx, h)
+        else:
+            lane.scene.update(desc.contents)
+        p = _abi.default_params(self.width, self.height, self.focal, light, self.light_count, self.cfg.use_bvh)
+        p.variant = self.variant
+        lane.ctx.render_raw(lane.scene, p, rgb=lane.frame.ptr)
+
     def frames(self, angles: Iterable[float], out: Optional[np.ndarray] = None) -> Iterator[Tuple[int, np.ndarray, dict]]:
-        """Yields (index, rgb[H][W][3] host array, timing) per frame, in order.  `out`: reuse one host buffer
-        (the yielded array is then only valid until the next iteration)."""
+        """Yields (index, rgb[H][W][3] host array, timing) per frame, in order.  The yielded array is the lane's
+        pinned frame (valid for the next two iterations), or `out` if given (valid until the next iteration)."""
         angles = list(angles)
         pool = ThreadPoolExecutor(max_workers=self.workers)
         pending = deque()
+        inflight = deque()                           # (index, lane, host scene, timing)
         nxt = 0
+
+        def retire():
+            i, lane, hs, tm = inflight.popleft()
+            t0 = time.perf_counter()
+            lane.ctx.sync()                          # frame i is in the lane's pinned buffer; `hs` may go away now
+            pool.submit(hs.close)                    # freeing 70 k triangles + the Node tree takes milliseconds: off the critical path
+            rgb = lane.frame.array
+            if out is not None:
+                np.copyto(out, rgb)
+                rgb = out
+            tm["gpu_ms"] += 1e3 * (time.perf_counter() - t0)
+            return i, rgb, tm
+
         try:
             while nxt < len(angles) and len(pending) < self.depth:
                 pending.append(pool.submit(prepare_frame, self.cfg, angles[nxt])); nxt += 1
@@ -59,26 +104,23 @@ class SeriesRenderer:
                 t1 = time.perf_counter()
                 if nxt < len(angles):
                     pending.append(pool.submit(prepare_frame, self.cfg, angles[nxt])); nxt += 1
-                if self.scene is None:
-                    h = capi.C.c_void_p()
-                    capi._check(capi.lib().srt_scene_upload(self.ctx.h, desc, capi.C.byref(h)))
-                    self.scene = capi.Scene(self.ctx, h)
-                else:
-                    self.scene.update(desc.contents)
-                p = _abi.default_params(self.width, self.height, self.focal, light, self.light_count, self.cfg.use_bvh)
-                p.variant = self.variant
-                rgb = out if out is not None else np.empty((self.height, self.width, 3), np.uint8)
-                self.ctx.render_raw(self.scene, p, rgb=rgb.ctypes.data)
-                self.ctx.sync()                      # the C++-owned arrays of `hs` may go away now
-                pool.submit(hs.close)                # freeing 70 k triangles + the Node tree takes milliseconds: off the critical path
+                if len(inflight) == len(self.lanes):
+                    yield retire()                   # frees the lane frame i is about to use
                 t2 = time.perf_counter()
-                yield i, rgb, dict(wait_prep_ms=1e3 * (t1 - t0), gpu_ms=1e3 * (t2 - t1))
+                lane = self.lanes[i % len(self.lanes)]
+                self._issue(lane, desc, light)
+                inflight.append((i, lane, hs, dict(wait_prep_ms=1e3 * (t1 - t0), gpu_ms=1e3 * (time.perf_counter() - t2))))
+            while inflight:
+                yield retire()
         finally:
+            for _i, lane, hs, _tm in inflight:
+                lane.ctx.sync()
+                hs.close()
             for f in pending:
                 f.cancel()
             pool.shutdown(wait=True, cancel_futures=True)
 
     def close(self):
-        if self.scene is not None:
-            self.scene.destroy()
-            self.scene = None
+        for lane in self.lanes:
+            lane.close()
+        self.lanes = []
