@@ -141,11 +141,13 @@ typedef struct srt_render_params {
     int32_t row_block, shard_index, shard_count;
 } srt_render_params;
 
-enum { SRT_VARIANT_DEFAULT = 0,   /* staged pipeline: classify, primary, shadow (overlapping the primary pass's tail by
-                                     programmatic dependent launch), shade; falls back to SIMPLE for the legacy one-box path */
+enum { SRT_VARIANT_DEFAULT = 0,   /* staged pipeline: classify, primary, shadow, shade as stream-ordered launches; falls back to
+                                     SIMPLE for the legacy one-box path */
        SRT_VARIANT_SIMPLE = 1,    /* one thread = one pixel, whole pixel per work item */
        SRT_VARIANT_FUSED = 2,     /* the stages fused into one persistent dataflow kernel */
-       SRT_VARIANT_SPLIT = 3,     /* the stages as strictly ordered launches (per-stage profiling) */
+       SRT_VARIANT_SPLIT = 3,     /* = DEFAULT (kept for callers that ask for per-stage launches explicitly) */
+       SRT_VARIANT_OVERLAP = 4,   /* DEFAULT with the shadow pass overlapping the primary pass's tail (programmatic
+                                     dependent launch, passes ordered by published tile entries) */
        SRT_VARIANT_COUNT = 100,   /* SIMPLE + node / triangle counters */
        SRT_VARIANT_TIMELINE = 101 /* SIMPLE + per-tile cost map in the id / t planes (debug) */ };
 

@@ -25,6 +25,7 @@ VARIANT_DEFAULT = 0
 VARIANT_SIMPLE = 1
 VARIANT_FUSED = 2
 VARIANT_SPLIT = 3
+VARIANT_OVERLAP = 4
 VARIANT_COUNT = 100
 VARIANT_TIMELINE = 101
 

@@ -505,10 +505,10 @@ int srt_render(srt_context* c, const srt_scene* s, const srt_render_params* p, c
         // nothing to intersect: still an image (all sky) — run the kernel with zero objects
     }
     // kernel selection: the phased kernel unless the scene / request needs the simple one
-    a.stack_cap = (int)(s->max_depth + s->n_objects + 2);
+    a.stack_cap = srtk::phased_stack_cap((int)s->max_depth, (int)s->n_objects);
     const bool tl = p->variant == 102 || p->variant == 103 || p->variant == 104;   // debug: per-tile cost map of the primary stage / per-warp timestamps
     a.debug_timeline = p->variant == 102 ? 1 : (p->variant == 103 ? 2 : (p->variant == 104 ? 3 : 0));
-    const bool want_phased = (p->variant == SRT_VARIANT_DEFAULT || p->variant == SRT_VARIANT_FUSED || p->variant == SRT_VARIANT_SPLIT || tl) && p->use_bvh &&
+    const bool want_phased = (p->variant == SRT_VARIANT_DEFAULT || p->variant == SRT_VARIANT_FUSED || p->variant == SRT_VARIANT_SPLIT || p->variant == SRT_VARIANT_OVERLAP || tl) && p->use_bvh &&
                              s->phased_ok && srtk::phased_smem_bytes(a.stack_cap) <= 96 * 1024;
     cudaError_t e;
     if (want_phased) {

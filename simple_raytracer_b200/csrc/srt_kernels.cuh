@@ -81,6 +81,7 @@ constexpr uint32_t kLeafMaxCount = 15, kLeafFirstBits = 27;
 cudaError_t launch_build_wide(const float4* nodes, const srt_object* objects, uint32_t n_nodes, uint32_t n_objects,
                               float4* wide, uint32_t* root_ref, cudaStream_t stream);
 // Shared memory the phased kernel needs per CTA for `stack_cap`, and whether it fits.
+int phased_stack_cap(int max_depth, int n_objects);   // stack of interior nodes + room for the leaf list
 size_t phased_smem_bytes(int stack_cap);
 // Single cooperative launch (variant SRT_VARIANT_DEFAULT) or three launches (SRT_VARIANT_SPLIT).
 // Sparse (ImageData-style) output of a rendered RGB8 frame: srt_render_sparse.  seg_counts: sparse_segments() words.

@@ -15,9 +15,9 @@
 //                with the /5 of occluded lights (:369), tone map, gamma, quantise, sky (:391-398,
 //                :447-449, :476-487).
 //
-// The default path launches the stages as separate kernels, the shadow pass overlapping the primary pass's tail
-// through programmatic dependent launch (render_phase<PHASE, OVERLAP>); render_dataflow is the same three stage
-// bodies fused into one kernel (SRT_VARIANT_FUSED).
+// The default path launches the stages as separate, stream-ordered kernels (render_phase<PHASE, OVERLAP>; OVERLAP
+// lets the shadow pass start in the primary pass's tail through programmatic dependent launch); render_dataflow
+// is the same three stage bodies fused into one kernel (SRT_VARIANT_FUSED).
 //
 // Arithmetic: everything that reaches an output (Moeller-Trumbore, hit point, Phong, tone map) is the
 // exact operation sequence of srt_device.cuh.  The slab test is evaluated with a FILTER: an
@@ -146,46 +146,72 @@ __device__ __forceinline__ void slab_filtered_pair(const FRay& r, const float4& 
 }
 
 // ---------------------------------------------------------------------------------------------
-// Traversal stack: per thread, in shared memory, one column per thread (bank = tid % 32).
+// Traversal stack + leaf list: per thread, in shared memory, one column per thread (bank = tid % 32).
+// The stack (interior nodes whose own box passed) grows from the bottom of the column, the list of leaves
+// waiting for their triangle tests from the top; the column has kLeafRoom entries more than the deepest stack.
+constexpr int kLeafRoom = 8;   // 0 / 2 / 4 / 8 / 16 measured: 8 (the list also uses whatever the stack leaves free)
 struct Stack {
     uint32_t* base;   // &smem[threadIdx.x]
     int sp;
     __device__ __forceinline__ void push(uint32_t v) { base[sp * kThreads] = v; ++sp; }
     __device__ __forceinline__ uint32_t pop() { if (sp == 0) return kRefNone; --sp; return base[sp * kThreads]; }
+    __device__ __forceinline__ void put_leaf(int cap, int& nl, uint32_t ref) { base[(cap - 1 - nl) * kThreads] = ref; ++nl; }
+    __device__ __forceinline__ uint32_t get_leaf(int cap, int i) const { return base[(cap - 1 - i) * kThreads]; }
 };
 
-__device__ __forceinline__ bool is_interior(uint32_t ref) { return ref < kRefNone; }
 __device__ __forceinline__ bool is_leaf(uint32_t ref) { return (ref >> 31) != 0u; }
 __device__ __forceinline__ uint32_t leaf_first(uint32_t ref) { return ref & ((1u << kLeafFirstBits) - 1u); }
 __device__ __forceinline__ uint32_t leaf_count(uint32_t ref) { return (ref >> kLeafFirstBits) & 15u; }
 
-// Closest hit over everything on the stack (refs of nodes whose own box already passed).
-// While-while: every lane descends until it holds a leaf (or nothing), then the warp intersects.
+// The closest-hit traversal separates box tests from triangle tests.  In a plain while-while loop a lane that
+// reaches a leaf idles until every other lane of the warp has reached one too, and lanes without a leaf idle
+// through the triangle tests (ncu: 22/32 active threads).  Here a leaf child is put on the lane's leaf list the
+// moment its box passes and the lane keeps descending; the triangle tests then run as ONE flat loop over
+// (leaf, triangle) per lane: 26.5/32 active threads, -20 % time for the primary pass.  (The same scheme as
+// speculative traversal for the any-hit rays — keep descending with up to 2-4 postponed leaves — raised their
+// thread efficiency from 15.7 to 19.5 of 32 but executed 15 % more instructions and needed either the larger
+// shared-memory column, halving the L1 hit rate, or registers; measured slower in both forms and not kept.)
+
+// Closest hit over everything on the stack (refs of nodes whose own box already passed).  The reference visits
+// EVERY reachable leaf (no pruning by distance, S5) and the closest hit is the order-independent min over
+// (t, visit index) (S6), so collecting leaves first changes nothing but the schedule.
 __device__ __forceinline__ void trace_closest(const KArgs& a, const FRay& r, Stack& st, Hit& h, unsigned& exact_count) {
+    const int cap = a.stack_cap;
+    int nl = 0;
     uint32_t ref = st.pop();
-    while (ref != kRefNone) {
-        while (is_interior(ref)) {
-            const float4* w = a.wide + 4 * (size_t)ref;
-            const float4 w0 = ldg4(w), w1 = ldg4(w + 1), w2 = ldg4(w + 2), w3 = ldg4(w + 3);
-            float tnl, tfl, tnr, tfr;
-            bool hl, hr;
-            slab_filtered_pair(r, w0, w1, w2, hl, hr, tnl, tfl, tnr, tfr, exact_count);
-            const uint32_t rl = __float_as_uint(w3.x), rr = __float_as_uint(w3.y);
-            if (hl) { if (hr) st.push(rr); ref = rl; }
-            else if (hr) ref = rr;
-            else ref = st.pop();
-        }
-        if (is_leaf(ref)) {
-            const uint32_t first = leaf_first(ref), cnt = leaf_count(ref);
-            for (uint32_t k = 0; k < cnt; ++k) {
-                const float4* g = a.geom + 3 * (size_t)(first + k);
-                const float t = moller_trumbore(r.o, r.d, ldg4(g), ldg4(g + 1), ldg4(g + 2));
-                const int32_t idx = (int32_t)(first + k);
-                // S6: first visited wins ties == smallest visit index wins ties
-                if (t != -INFINITY && (t < h.t || (t == h.t && idx < h.tri))) { h.t = t; h.tri = idx; }
+    for (;;) {
+        while (ref != kRefNone) {
+            if (is_leaf(ref)) {                                   // a root that is itself a leaf
+                st.put_leaf(cap, nl, ref);
+                ref = st.pop();
+            } else {
+                const float4* w = a.wide + 4 * (size_t)ref;
+                const float4 w0 = ldg4(w), w1 = ldg4(w + 1), w2 = ldg4(w + 2), w3 = ldg4(w + 3);
+                float tnl, tfl, tnr, tfr;
+                bool hl, hr;
+                slab_filtered_pair(r, w0, w1, w2, hl, hr, tnl, tfl, tnr, tfr, exact_count);
+                const uint32_t rl = __float_as_uint(w3.x), rr = __float_as_uint(w3.y);
+                if (hl && is_leaf(rl)) { st.put_leaf(cap, nl, rl); hl = false; }
+                if (hr && is_leaf(rr)) { st.put_leaf(cap, nl, rr); hr = false; }
+                if (hl) { if (hr) st.push(rr); ref = rl; }
+                else if (hr) ref = rr;
+                else ref = st.pop();
             }
-            ref = st.pop();
+            if (st.sp + nl + 3 > cap) break;                     // room for one push and two leaves, or test the leaves first
         }
+        uint32_t cur = 0, end = 0;
+        int li = 0;
+        for (;;) {
+            while (cur == end && li < nl) { const uint32_t l = st.get_leaf(cap, li++); cur = leaf_first(l); end = cur + leaf_count(l); }
+            if (cur == end) break;
+            const float4* g = a.geom + 3 * (size_t)cur;
+            const float t = moller_trumbore(r.o, r.d, ldg4(g), ldg4(g + 1), ldg4(g + 2));
+            // S6: first visited wins ties == smallest visit index wins ties
+            if (t != -INFINITY && (t < h.t || (t == h.t && (int32_t)cur < h.tri))) { h.t = t; h.tri = (int32_t)cur; }
+            ++cur;
+        }
+        nl = 0;
+        if (ref == kRefNone) break;
     }
 }
 
@@ -196,7 +222,7 @@ template <bool COUNT = false>
 __device__ __forceinline__ bool trace_any(const KArgs& a, const FRay& r, Stack& st, unsigned& exact_count, unsigned* boxes = nullptr) {
     uint32_t ref = st.pop();
     while (ref != kRefNone) {
-        while (is_interior(ref)) {
+        while (ref < kRefNone) {
             const float4* w = a.wide + 4 * (size_t)ref;
             const float4 w0 = ldg4(w), w1 = ldg4(w + 1), w2 = ldg4(w + 2), w3 = ldg4(w + 3);
             float tnl, tfl, tnr, tfr;
@@ -432,14 +458,16 @@ __device__ __forceinline__ void shade_tile_from_memory(const KArgs& a, unsigned 
     shade_pixel(a, p, h, primary_dir(a, p), mine, tile, lane);
 }
 
-// ---- the three stages as separate passes -----------------------------------------------------------
-// OVERLAP (the production pipeline): the shadow pass is launched with programmatic stream serialization,
+// ---- the three stages as separate passes (the production pipeline) -------------------------------------
+// OVERLAP (SRT_VARIANT_OVERLAP): the shadow pass is launched with programmatic stream serialization,
 // so its CTAs become resident as soon as CTAs of the primary pass retire and fill the SMs that pass's long
 // tail tiles (bunny silhouette: 100-400 k cycles each) would leave idle.  The passes are then ordered by
 // data, not by the launch boundary: a primary tile is PUBLISHED (hit records + interest word, fence,
 // tagged list entry, fence, "tiles decided" count) and a shadow item waits for its list entry.  The
 // primary CTAs are all resident before the first shadow CTA exists (the grid is the resident capacity and
 // every CTA triggers the dependent launch first thing), and they never wait, so the waits cannot deadlock.
+// Measured: +2 % with the first primary kernel, -2.5 % with the current one (the fences and the tagged entries cost
+// more than the tail they hide), so the default keeps the launches strictly ordered.
 __device__ __forceinline__ unsigned long long ld_volatile_u64(const unsigned long long* p) {
     return *reinterpret_cast<const volatile unsigned long long*>(p);
 }
@@ -704,6 +732,7 @@ cudaError_t launch_build_wide(const float4* nodes, const srt_object* objects, ui
     return cudaGetLastError();
 }
 
+int phased_stack_cap(int max_depth, int n_objects) { return max_depth + n_objects + 2 + kLeafRoom; }
 size_t phased_smem_bytes(int stack_cap) { return (size_t)stack_cap * kThreads * sizeof(uint32_t); }
 
 // ---------------------------------------------------------------------------------------------
@@ -793,6 +822,7 @@ cudaError_t launch_render_phased(const KArgs& a, int variant, int sm_count, cuda
     if (launches) *launches = 0;
     if (n_tiles <= 0) return cudaSuccess;
     const size_t smem = phased_smem_bytes(a.stack_cap);
+    const size_t smem_s = phased_smem_bytes(a.stack_cap - kLeafRoom);   // the shadow pass keeps its leaves in registers
     static bool attr_set = false;
     if (!attr_set) {
         cudaFuncSetAttribute(render_dataflow<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024);
@@ -809,17 +839,17 @@ cudaError_t launch_render_phased(const KArgs& a, int variant, int sm_count, cuda
     classify_kernel<<<cblocks, kThreads, 0, stream>>>(a);
     cudaError_t e;
     const bool shadows = a.n_objects >= 2 && a.light_count > 0;
-    if (variant == SRT_VARIANT_DEFAULT || variant == SRT_VARIANT_SPLIT) {
-        const bool overlap = variant == SRT_VARIANT_DEFAULT;
+    if (variant == SRT_VARIANT_DEFAULT || variant == SRT_VARIANT_SPLIT || variant == SRT_VARIANT_OVERLAP) {
+        const bool overlap = variant == SRT_VARIANT_OVERLAP;
         int bp = 0, bs = 0, bc = 0;
         if ((e = persistent_blocks(render_phase<0, false>, smem, sm_count, n_tiles, &bp)) != cudaSuccess) return e;
-        if ((e = persistent_blocks(render_phase<1, false>, smem, sm_count, n_tiles, &bs)) != cudaSuccess) return e;
+        if ((e = persistent_blocks(render_phase<1, false>, smem_s, sm_count, n_tiles, &bs)) != cudaSuccess) return e;
         if ((e = persistent_blocks(render_phase<2, false>, 0, sm_count, n_tiles, &bc)) != cudaSuccess) return e;
         int n = 1;
         if (overlap && shadows) {
             render_phase<0, true><<<bp, kThreads, smem, stream>>>(a);
             cudaLaunchConfig_t cfg = {};
-            cfg.gridDim = dim3((unsigned)bs); cfg.blockDim = dim3(kThreads); cfg.dynamicSmemBytes = smem; cfg.stream = stream;
+            cfg.gridDim = dim3((unsigned)bs); cfg.blockDim = dim3(kThreads); cfg.dynamicSmemBytes = smem_s; cfg.stream = stream;
             cudaLaunchAttribute attr[1];
             attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
             attr[0].val.programmaticStreamSerializationAllowed = 1;
@@ -829,7 +859,7 @@ cudaError_t launch_render_phased(const KArgs& a, int variant, int sm_count, cuda
         } else {
             render_phase<0, false><<<bp, kThreads, smem, stream>>>(a);
             ++n;
-            if (shadows) { render_phase<1, false><<<bs, kThreads, smem, stream>>>(a); ++n; }
+            if (shadows) { render_phase<1, false><<<bs, kThreads, smem_s, stream>>>(a); ++n; }
         }
         render_phase<2, false><<<bc, kThreads, 0, stream>>>(a);
         ++n;

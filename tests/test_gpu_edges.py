@@ -58,7 +58,7 @@ def build_scene(tmp_path, rng, n_objects, tris_per_object, kind, scale=1.0):
     return hs
 
 
-def check(gpu_ctx, arrays, p, variants=(0, 2, 1)):
+def check(gpu_ctx, arrays, p, variants=(0, 2, 4, 1)):
     want = pyoracle.oracle_render(arrays, p)
     sc = gpu_ctx.upload(arrays)
     try:

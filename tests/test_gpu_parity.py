@@ -27,9 +27,9 @@ CASES = [
 ]
 
 
-# kernel variants: 0 = staged pipeline with overlapped passes (default), 2 = the stages fused into one dataflow kernel,
-# 3 = the stages as strictly ordered launches, 1 = simple (one thread = one pixel, exact divisions everywhere)
-@pytest.mark.parametrize("variant", [0, 2, 3, 1], ids=["pipeline", "fused", "split", "simple"])
+# kernel variants: 0 = staged pipeline (default), 2 = the stages fused into one dataflow kernel, 4 = the pipeline with
+# the shadow pass overlapping the primary pass, 1 = simple (one thread = one pixel, exact divisions everywhere)
+@pytest.mark.parametrize("variant", [0, 2, 4, 1], ids=["pipeline", "fused", "overlap", "simple"])
 @pytest.mark.parametrize("key,W,H,focal,N", CASES, ids=[c[0] for c in CASES])
 def test_frame_parity(gpu_ctx, ref_scene, key, W, H, focal, N, variant):
     cfg = scenes.CONFIGS[key]
@@ -122,7 +122,7 @@ def test_full_size_c3_variants_agree_and_sample_matches_oracle(gpu_ctx, ref_scen
     W, H, focal, N = 1920, 1080, 1080.0, 16
     sc = gpu_ctx.upload(arrays)
     outs = []
-    for variant in (0, 2, 3, 1):
+    for variant in (0, 2, 4, 1):
         p = _abi.default_params(W, H, focal, light, N, True)
         p.variant = variant
         outs.append(gpu_ctx.render(sc, p))
