@@ -507,7 +507,7 @@ def run_b200_arm(args):
             "roofline": {"bound": "hbm", "achieved": ach, "peak": hbm_peak, "unit": "GB/s", "frac": ach / hbm_peak,
                          # dram__bytes_read + write of the three render kernels of one frame (ncu --set full, caches cold for
                          # every kernel: profiles/r01_pipeline_stages_ncu_summary.txt); only meaningful for the default config
-                         "traffic": 35.9e6 if (args.config == "C3" and args.variant == 0) else None,
+                         "traffic": 35.2e6 if (args.config == "C3" and args.variant == 0) else None,
                          "traffic_source": "ncu capture of one mid-orbit frame, profiles/r01_pipeline_stages_ncu_summary.txt",
                          "peak_source": "measured (MEASURED_PEAKS.json)" if peaks else "fallback",
                          "note": "scene is L2-resident by design: compulsory HBM bytes = one scene read + one RGB8 frame write; "
