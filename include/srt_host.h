@@ -64,6 +64,9 @@ int  srt_host_flat_texture_name(srt_host_scene* s, int i, char* buf, int buflen)
 /* Process-wide cache of parsed OBJ/MTL files and decoded textures: the reference re-reads them on every frame
  * of its loop (simple_raytracer.cpp:537, :554); loading is deterministic, so cached loads are bit-identical.
  * Thread-safe; off by default; disabling clears the cache. */
+/* drawImage(..., saveImage = true) :461-498: the BMP CImg writes, from a dense sky-filled RGB8 frame (srt_render's
+ * output); byte-identical to the reference's file.  0 on success, -1 on I/O failure. */
+int  srt_host_write_bmp(const char* path, const uint8_t* rgb, int width, int height);
 void srt_host_set_asset_cache(int enabled);
 
 /* OBJ number parser (for tests): returns 1 and the value, or 0. */

@@ -153,6 +153,7 @@ def ref_lib():
         lib.ref_dropin_render.argtypes = [vp, i32, i32, _f32p, _f32p, _f32p, C.c_long, C.c_char_p, i32]
         lib.ref_verbatim_sparse.restype = C.c_long
         lib.ref_verbatim_sparse.argtypes = [vp, i32, i32, _f32p, _f32p, _f32p, C.c_long]
+        lib.ref_draw_image.argtypes = [i32, i32, _f32p, _f32p, C.c_long, i32]
         lib.ref_leaf_moller_trumbore.argtypes = [i32, _f32p, _f32p, _f32p, _f32p]
         lib.ref_leaf_slab.argtypes = [i32, _f32p, _f32p, _f32p, _f32p, C.POINTER(C.c_uint8)]
         lib.ref_leaf_slab_origin0.argtypes = [i32, _f32p, _f32p, _f32p, C.POINTER(C.c_uint8)]
@@ -169,6 +170,26 @@ _libm.cosf.restype = C.c_float
 _libm.cosf.argtypes = [C.c_float]
 _libm.sinf.restype = C.c_float
 _libm.sinf.argtypes = [C.c_float]
+
+
+def ref_draw_image(workdir, width, height, points, colors, angle=0) -> bytes:
+    """The reference's drawImage(..., saveImage=True) (:461-498) on the given ImageData lists; returns the bytes of the
+    BMP it wrote (images/generation/output<angle>.bmp under `workdir`)."""
+    import os
+    from pathlib import Path as _P
+    lib = ref_lib()
+    out_dir = _P(workdir) / "images" / "generation"
+    out_dir.mkdir(parents=True, exist_ok=True)
+    pts = np.ascontiguousarray(points, np.float32)
+    col = np.ascontiguousarray(colors, np.float32)
+    old = os.getcwd()
+    os.chdir(workdir)
+    try:
+        if lib.ref_draw_image(int(width), int(height), _fp(pts), _fp(col), len(pts), int(angle)) != 0:
+            raise RuntimeError("reference drawImage failed")
+    finally:
+        os.chdir(old)
+    return (out_dir / f"output{int(angle)}.bmp").read_bytes()
 
 
 @contextlib.contextmanager

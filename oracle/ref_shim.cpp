@@ -545,6 +545,22 @@ extern "C" long ref_dropin_render(void* h, int W, int Hh, const float* light4, f
         return -1;
     }
 }
+// The reference's drawImage(..., saveImage = true, displayImage = false) (:461-498) on caller-supplied lists: writes
+// images/generation/output<angle>.bmp under the CWD (the directory must exist, like for the reference's main()).
+extern "C" int ref_draw_image(int W, int Hh, const float* points2, const float* colors3, long n, int angle) {
+    std::vector<glm::vec2> pts((size_t)n);
+    std::vector<glm::vec3> cols((size_t)n);
+    for (long i = 0; i < n; ++i) {
+        pts[(size_t)i] = glm::vec2(points2[2 * i], points2[2 * i + 1]);
+        cols[(size_t)i] = glm::vec3(colors3[3 * i], colors3[3 * i + 1], colors3[3 * i + 2]);
+    }
+    try {
+        drawImage(glm::vec2((float)W, (float)Hh), pts, cols, angle, true, false);
+    } catch (...) {
+        return -1;
+    }
+    return 0;
+}
 // The verbatim function's sparse output, for comparison.
 extern "C" long ref_verbatim_sparse(void* h, int W, int Hh, const float* light4, float* points2, float* colors3, long cap) {
     RefScene* s = (RefScene*)h;

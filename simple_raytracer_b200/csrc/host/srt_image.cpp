@@ -48,4 +48,38 @@ unsigned char* decode_image_rgb8(const char* path, int* width, int* height) {
     return data;
 }
 
+// drawImage(..., saveImage = true) (simple_raytracer.cpp:461-498) writes the frame with CImg<unsigned char>::save_bmp.
+// The same file from a dense, sky-filled RGB8 frame (what srt_render returns): 54-byte header with the values
+// CImg writes (file size, data offset 0x36, info-header size 0x28, width, height, 1 plane, 24 bits, image size, and
+// its two 0x0100 resolution fields at 0x26 / 0x2A), then the rows bottom-up as B, G, R, each padded to 4 bytes.
+bool write_bmp(const char* path, const unsigned char* rgb, int width, int height) {
+    if (!path || !rgb || width <= 0 || height <= 0) return false;
+    FILE* f = std::fopen(path, "wb");
+    if (!f) return false;
+    const uint32_t w = (uint32_t)width, h = (uint32_t)height;
+    const uint32_t align = (4u - (3u * w) % 4u) % 4u, row = 3u * w + align, buf_size = row * h, file_size = 54u + buf_size;
+    unsigned char header[54] = {0};
+    auto put32 = [&](int at, uint32_t v) { for (int k = 0; k < 4; ++k) header[at + k] = (unsigned char)((v >> (8 * k)) & 0xFF); };
+    header[0] = 'B'; header[1] = 'M';
+    put32(0x02, file_size);
+    header[0x0A] = 0x36;
+    header[0x0E] = 0x28;
+    put32(0x12, w);
+    put32(0x16, h);
+    header[0x1A] = 1;
+    header[0x1C] = 24;
+    put32(0x22, buf_size);
+    header[0x27] = 0x1;
+    header[0x2B] = 0x1;
+    bool ok = std::fwrite(header, 1, 54, f) == 54;
+    std::string line(row, '\0');
+    for (int y = height - 1; y >= 0 && ok; --y) {
+        const unsigned char* src = rgb + (size_t)y * w * 3;
+        for (uint32_t x = 0; x < w; ++x) { line[3 * x] = (char)src[3 * x + 2]; line[3 * x + 1] = (char)src[3 * x + 1]; line[3 * x + 2] = (char)src[3 * x]; }
+        ok = std::fwrite(line.data(), 1, row, f) == row;
+    }
+    ok = (std::fclose(f) == 0) && ok;
+    return ok;
+}
+
 }  // namespace srt

@@ -107,6 +107,8 @@ void set_asset_cache(bool enabled);
 
 // --- image decoding (srt_image.cpp) -------------------------------------------------------------
 unsigned char* decode_image_rgb8(const char* path, int* width, int* height);
+// drawImage's saved file (:461-498, CImg save_bmp) from a dense sky-filled RGB8 frame; false on I/O failure.
+bool write_bmp(const char* path, const unsigned char* rgb, int width, int height);
 
 }  // namespace srt
 #endif

@@ -81,6 +81,7 @@ def _lib():
         L.srt_host_flat_max_depth.argtypes = [vp]
         L.srt_host_flat_texture_name.argtypes = [vp, i32, cp, i32]
         L.srt_host_parse_double.argtypes = [cp, C.POINTER(C.c_double)]
+        L.srt_host_write_bmp.argtypes = [cp, C.c_void_p, i32, i32]
         L.srt_host_set_asset_cache.argtypes = [i32]
         L.srt_host_set_asset_cache.restype = None
         _bound = True
@@ -252,6 +253,16 @@ class HostScene:
             names.append(buf.value.decode())
         return _abi.FlatSceneArrays.from_desc_pointer(d, self.object_names(), names,
                                                       self.lib.srt_host_flat_max_depth(self.h))
+
+
+def write_bmp(path, rgb: np.ndarray):
+    """drawImage(..., saveImage=True) (simple_raytracer.cpp:461-498): the BMP file CImg writes, from a dense sky-filled
+    RGB8 frame [H][W][3] — byte-identical to the reference's file."""
+    a = np.ascontiguousarray(rgb, np.uint8)
+    if a.ndim != 3 or a.shape[2] != 3:
+        raise ValueError("rgb must be [H][W][3] uint8")
+    if _lib().srt_host_write_bmp(str(path).encode(), a.ctypes.data, a.shape[1], a.shape[0]) != 0:
+        raise OSError(f"cannot write {path}")
 
 
 def set_asset_cache(enabled: bool):

@@ -54,8 +54,12 @@ class _Lane:
 
 class SeriesRenderer:
     def __init__(self, ctx: capi.Context, cfg: scenes.SceneConfig, width: int, height: int, focal: float,
-                 light_count: int, workers: Optional[int] = None, depth: Optional[int] = None, variant: int = 0):
+                 light_count: int, workers: Optional[int] = None, depth: Optional[int] = None, variant: int = 0,
+                 save_pattern: Optional[str] = None):
+        """save_pattern: e.g. "images/generation/output{index}.bmp" — every frame is also written as the BMP the
+        reference's drawImage saves (:488-494), on the worker pool, off the critical path."""
         self.ctx, self.cfg = ctx, cfg
+        self.save_pattern = save_pattern
         self.width, self.height, self.focal, self.light_count, self.variant = width, height, focal, light_count, variant
         self.workers = workers or max(1, len(os.sched_getaffinity(0)))
         self.depth = depth or 2 * self.workers
@@ -89,6 +93,8 @@ class SeriesRenderer:
             lane.ctx.sync()                          # frame i is in the lane's pinned buffer; `hs` may go away now
             pool.submit(hs.close)                    # freeing 70 k triangles + the Node tree takes milliseconds: off the critical path
             rgb = lane.frame.array
+            if self.save_pattern:
+                pool.submit(host.write_bmp, self.save_pattern.format(index=i, angle=angles[i]), rgb.copy())
             if out is not None:
                 np.copyto(out, rgb)
                 rgb = out

@@ -240,16 +240,22 @@ def test_sparse_output_equals_dense_frame(gpu_ctx, ref_scene):
     sc.destroy()
 
 
-def test_series_driver_equals_frame_by_frame(gpu_ctx):
+def test_series_driver_equals_frame_by_frame(gpu_ctx, tmp_path):
     """series.SeriesRenderer (asset cache + prep thread pool + scene update in place) renders the same bytes
     as building and uploading every frame from scratch."""
     from simple_raytracer_b200 import host, series
     cfg = scenes.CONFIGS["C3"]
     W, H, focal = scenes.scaled(cfg, 180)
     angles = [0.0, 1.5, 3.0, 40.5, 181.5]
-    sr = series.SeriesRenderer(gpu_ctx, cfg, W, H, focal, 4, workers=3)
+    sr = series.SeriesRenderer(gpu_ctx, cfg, W, H, focal, 4, workers=3, save_pattern=str(tmp_path / "output{index}.bmp"))
     got = {i: rgb.copy() for i, rgb, _tm in sr.frames(angles)}
     sr.close()
+    for i in got:                                          # the saved files: 24-bit BMP, bottom-up BGR (drawImage :488-494)
+        raw = (tmp_path / f"output{i}.bmp").read_bytes()
+        row = (3 * W + 3) // 4 * 4
+        assert raw[:2] == b"BM" and len(raw) == 54 + row * H
+        px = np.frombuffer(raw, np.uint8, offset=54).reshape(H, row)[::-1, :3 * W].reshape(H, W, 3)[:, :, ::-1]
+        assert np.array_equal(px, got[i])
     host.set_asset_cache(False)
     for i, ang in enumerate(angles):
         hs = host.HostScene(); view = cfg.build(hs, ang); light = scenes.light_view_space(hs, view)

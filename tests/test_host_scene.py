@@ -122,3 +122,23 @@ def test_transformation_matrices():
     assert np.allclose(I, np.eye(4), atol=1e-5)
     Mi = s.xf_mirror(1, 0, 0).reshape(4, 4)
     assert np.diag(Mi).tolist() == [-1, 1, 1, 1]
+
+
+@pytest.mark.ref
+def test_write_bmp_equals_reference_draw_image(tmp_path):
+    """host.write_bmp of a dense sky-filled frame == the file the reference's drawImage (:461-498, CImg save_bmp) writes
+    from the corresponding ImageData lists, byte for byte — at widths with and without row padding."""
+    from oracle import pyoracle
+    rng = np.random.default_rng(4)
+    for W, H in ((37, 21), (64, 48), (150, 5), (1, 1)):
+        rgb = rng.integers(0, 256, (H, W, 3), dtype=np.uint8)
+        rgb[rng.random((H, W)) < 0.3] = 0                                  # not drawn -> sky in both
+        ys, xs = np.nonzero(rgb.any(axis=2))
+        pts = np.stack([xs, ys], axis=1).astype(np.float32)
+        col = rgb[ys, xs].astype(np.float32)
+        want = pyoracle.ref_draw_image(tmp_path, W, H, pts, col, angle=W)
+        dense = rgb.copy()
+        dense[~rgb.any(axis=2)] = (173, 216, 230)                          # what srt_render returns (sky fill :476-487)
+        path = tmp_path / f"ours{W}.bmp"
+        host.write_bmp(path, dense)
+        assert path.read_bytes() == want, (W, H)
