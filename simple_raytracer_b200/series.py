@@ -124,7 +124,7 @@ class SeriesRenderer:
                 hs.close()
             for f in pending:
                 f.cancel()
-            pool.shutdown(wait=True, cancel_futures=True)
+            pool.shutdown(wait=True)                 # (queued frame writes and scene frees still run)
 
     def close(self):
         for lane in self.lanes:
