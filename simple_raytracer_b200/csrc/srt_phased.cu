@@ -466,8 +466,8 @@ __device__ __forceinline__ void shade_tile_from_memory(const KArgs& a, unsigned 
 // tagged list entry, fence, "tiles decided" count) and a shadow item waits for its list entry.  The
 // primary CTAs are all resident before the first shadow CTA exists (the grid is the resident capacity and
 // every CTA triggers the dependent launch first thing), and they never wait, so the waits cannot deadlock.
-// Measured: +2 % with the first primary kernel, -2.5 % with the current one (the fences and the tagged entries cost
-// more than the tail they hide), so the default keeps the launches strictly ordered.
+// Measured: +2 % on the orbit average, -5 % on C3 itself (short shadow pass, the publication protocol for nothing),
+// so the default keeps the launches strictly ordered.
 __device__ __forceinline__ unsigned long long ld_volatile_u64(const unsigned long long* p) {
     return *reinterpret_cast<const volatile unsigned long long*>(p);
 }
@@ -526,21 +526,40 @@ __device__ __forceinline__ void phase_shadow(const KArgs& a, uint32_t* smem, uns
     }
     const unsigned n_tiles = (unsigned)(a.tiles_x * a.tiles_y);
     const unsigned long long seq = a.frame_seq;
+    bool all_published = false;                                    // warp-uniform: the primary pass has finished
+    unsigned n_items = 0;
     for (;;) {
         const unsigned item = next_item(&a.counters[CNT_SHADOW], lane);
         const unsigned slot = item / N;
+        if (!all_published) {
+            unsigned long long done = 0;
+            if (lane == 0) done = ld_volatile_u64(a.counters + CNT_PDONE);
+            if (__shfl_sync(kFull, done, 0) >= n_tiles) {          // from here on: plain loads, no waiting, no fences
+                __threadfence();
+                all_published = true;
+                n_items = (unsigned)ld_volatile_u64(a.counters + CNT_LIST) * N;
+            }
+        }
+        if (all_published) {
+            if (item >= n_items) break;
+            shadow_item(a, st, (unsigned)(__ldcg(a.tile_list + slot) & 0xffffffffull), (int)(item - slot * N), lane, exact_count);
+            continue;
+        }
+        // the primary pass is still running: wait for this item's list entry
         unsigned long long e = 0;
         if (lane == 0 && slot < n_tiles) {
+            unsigned ns = 250;
             for (unsigned spins = 0;; ++spins) {
                 e = ld_volatile_u64(a.tile_list + slot);
                 if ((e >> 32) == seq) break;
-                if (spins > (1u << 23)) { atomicAdd(&a.counters[CNT_TIMEOUT], 1ull); break; }   // > 1 s: give up loudly
+                if (spins > (1u << 20)) { atomicAdd(&a.counters[CNT_TIMEOUT], 1ull); break; }   // > 1 s: give up loudly
                 if (ld_volatile_u64(a.counters + CNT_PDONE) >= n_tiles) {          // every tile decided: final answer
                     __threadfence();
                     e = ld_volatile_u64(a.tile_list + slot);
                     break;
                 }
-                __nanosleep(200);
+                __nanosleep(ns);                                   // back off: thousands of waiting warps poll two lines
+                if (ns < 2000) ns *= 2;
             }
         }
         e = __shfl_sync(kFull, e, 0);
