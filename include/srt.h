@@ -197,6 +197,49 @@ int  srt_scene_upload(srt_context* ctx, const srt_scene_desc* desc, srt_scene** 
 int  srt_scene_update(srt_context* ctx, srt_scene* scene, const srt_scene_desc* desc);
 void srt_scene_destroy(srt_scene* scene);
 
+/* ---- device scene prep: the per-frame host work of the reference's frame loop, on the device ----
+ * The reference re-transforms every object and rebuilds its bounding hierarchy on the host for every frame
+ * (main :553-618 -> ObjectManager::transformTriangles Object.cpp:183-190, createBoundingHierarchy Object.cpp:275-284
+ * -> splitTrianglesForBox :225-272, calculateBoundingBoxes :205-221).  These entry points keep the object-space
+ * mesh resident on the GPU and produce, from a list of matrices per object, exactly the arrays srt_flatten.hpp
+ * would produce from the reference's ObjectManager after the same calls: the same vertices (one fp32 mat4 * vec4 per
+ * transformTriangles call), the same tree (libstdc++'s std::sort permutation is reproduced, ties included), the same
+ * boxes, the same leaf order — bit for bit.  Only the texture slot numbers are the caller's (srt_mesh_desc::tex).
+ * Coordinates must be finite (srt_scene_prep_status reports SRT_ERR_UNSUPPORTED otherwise). */
+typedef struct srt_mesh srt_mesh;
+typedef struct srt_mesh_desc {
+    const float*   points;        /* [n_tris][3][4]  pointOne / pointTwo / pointThree (vec4) in objTriangles load order */
+    const float*   uv;            /* [n_tris][3][2]  colorOne/Two/ThreeCoordinate (texel space), or NULL = zeros      */
+    const int32_t* tex;           /* [n_tris]        texture slot of Triangle::textureName or -1; NULL = all -1       */
+    uint64_t       n_tris;
+} srt_mesh_desc;
+int  srt_mesh_upload(srt_context* ctx, const srt_mesh_desc* desc, srt_mesh** out);
+void srt_mesh_destroy(srt_mesh* mesh);
+int  srt_mesh_info(const srt_mesh* mesh, uint64_t* n_tris, uint64_t* n_nodes, uint32_t* max_depth);
+
+/* One entry per key of objTriangles, in that map's iteration order (like srt_object). */
+typedef struct srt_prep_object {
+    const srt_mesh* mesh;         /* the triangles loadObjFile / setTriangles put under this name                    */
+    const float*    matrices;     /* n_matrices x 16 floats, column-major (glm::mat4): the transformTriangles calls  */
+    uint32_t        n_matrices;   /*   made on this object since it was loaded, in call order                        */
+    float           color[3];     /* objColors[name]                                                                */
+    float           ambient, specular, shininess;   /* objProperties[name]                                          */
+} srt_prep_object;
+
+/* Transforms, builds and flattens on the context stream (asynchronous) into *scene — created when *scene is NULL,
+ * otherwise reused (its buffers grow as needed).  textures: uploaded when the scene is created or when non-NULL;
+ * pass NULL / 0 afterwards to keep them.  with_flat_lists: also fill the load-order lists of the legacy one-box
+ * path (use_bvh = 0). */
+int  srt_scene_prep(srt_context* ctx, const srt_prep_object* objects, uint32_t n_objects,
+                    const srt_texture_desc* textures, uint32_t n_textures, int with_flat_lists, srt_scene** scene);
+/* Synchronises the context; SRT_OK, or SRT_ERR_UNSUPPORTED when the last srt_scene_prep met a non-finite coordinate. */
+int  srt_scene_prep_status(srt_context* ctx, srt_scene* scene);
+/* Sizes and contents of a device scene (tests, debugging); any output pointer may be NULL. */
+int  srt_scene_counts(const srt_scene* scene, uint64_t* n_nodes, uint64_t* n_tris, uint64_t* n_flat, uint32_t* n_objects,
+                      uint32_t* max_depth);
+int  srt_scene_download(srt_context* ctx, const srt_scene* scene, srt_node* nodes, srt_tri_geom* geom, srt_tri_attr* attr,
+                        srt_tri_geom* flat_geom, srt_tri_attr* flat_attr, srt_object* objects);
+
 /* ---- render: the replacement for sendRaysAndIntersectPointsColors :505 ---- */
 /* Asynchronous on the context stream; call srt_sync before reading host outputs. */
 int  srt_render(srt_context* ctx, const srt_scene* scene, const srt_render_params* params,

@@ -40,6 +40,15 @@ int  srt_host_get_triangles(srt_host_scene* s, const char* name, float* out30, u
 /* Install already-decoded RGB8 pixels for a texture name (copied). */
 int  srt_host_set_texture(srt_host_scene* s, const char* name, const uint8_t* rgb, int width, int height);
 
+/* For the device scene prep (srt_scene_prep): texture slot of every triangle of `name` (slots numbered by first
+ * appearance in load order, -1 = untextured), slot names one per line in names_buf; returns the slot count, -1 for
+ * an unknown object, -2 when names_buf is too small. */
+int  srt_host_triangle_textures(srt_host_scene* s, const char* name, int32_t* slot_out, char* names_buf, int buflen);
+int  srt_host_texture_data(srt_host_scene* s, const char* texture_name, const uint8_t** rgb, int* width, int* height);
+/* Iteration order of ObjectManager::objTriangles for keys inserted in the given sequence (the object order of
+ * simple_raytracer.cpp:409 / :322): order_out[k] = index into names of the k-th key visited; duplicates count once. */
+int  srt_host_object_order(const char* const* names, int n, int* order_out);
+
 /* Transformation (Transformation.h:10-20) and the glm calls of main() */
 void srt_host_xf_scale(float sx, float sy, float sz, float* out16);
 void srt_host_xf_rotate_x(float radians, float* out16);

@@ -67,6 +67,15 @@ class RenderParams(C.Structure):
     ]
 
 
+class MeshDesc(C.Structure):
+    _fields_ = [("points", C.c_void_p), ("uv", C.c_void_p), ("tex", C.c_void_p), ("n_tris", C.c_uint64)]
+
+
+class PrepObject(C.Structure):
+    _fields_ = [("mesh", C.c_void_p), ("matrices", C.c_void_p), ("n_matrices", C.c_uint32),
+                ("color", C.c_float * 3), ("ambient", C.c_float), ("specular", C.c_float), ("shininess", C.c_float)]
+
+
 class Frame(C.Structure):
     _fields_ = [("rgb", C.c_void_p), ("obj_id", C.c_void_p), ("tri_id", C.c_void_p), ("t", C.c_void_p)]
 

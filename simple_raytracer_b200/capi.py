@@ -23,6 +23,8 @@ EXPORTS = [
     "srt_scene_destroy", "srt_render", "srt_sync", "srt_last_stats", "srt_default_params",
     "srt_light_positions", "srt_host_alloc", "srt_host_free", "srt_device_alloc", "srt_device_free",
     "srt_last_error", "srt_eval_leaf", "srt_render_sparse", "srt_fetch_sparse",
+    "srt_mesh_upload", "srt_mesh_destroy", "srt_mesh_info", "srt_scene_prep", "srt_scene_prep_status",
+    "srt_scene_counts", "srt_scene_download",
 ]
 
 
@@ -74,6 +76,16 @@ def lib():
         L.srt_device_free.argtypes = [vp, vp]
         L.srt_device_free.restype = None
         L.srt_last_error.restype = C.c_char_p
+        L.srt_mesh_upload.argtypes = [vp, C.POINTER(_abi.MeshDesc), C.POINTER(vp)]
+        L.srt_mesh_destroy.argtypes = [vp]
+        L.srt_mesh_destroy.restype = None
+        L.srt_mesh_info.argtypes = [vp, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64), C.POINTER(C.c_uint32)]
+        L.srt_scene_prep.argtypes = [vp, C.POINTER(_abi.PrepObject), C.c_uint32, C.POINTER(_abi.TextureDesc), C.c_uint32,
+                                     C.c_int, C.POINTER(vp)]
+        L.srt_scene_prep_status.argtypes = [vp, vp]
+        L.srt_scene_counts.argtypes = [vp, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64), C.POINTER(C.c_uint64),
+                                       C.POINTER(C.c_uint32), C.POINTER(C.c_uint32)]
+        L.srt_scene_download.argtypes = [vp, vp, vp, vp, vp, vp, vp, vp]
         _lib = L
     return _lib
 
@@ -126,9 +138,69 @@ class Scene:
         self._keep = (arrays_or_desc, d)
         _check(lib().srt_scene_update(self.ctx.h, self.h, C.byref(d)))
 
+    def counts(self) -> dict:
+        nn, nt, nf, no, md = C.c_uint64(), C.c_uint64(), C.c_uint64(), C.c_uint32(), C.c_uint32()
+        _check(lib().srt_scene_counts(self.h, C.byref(nn), C.byref(nt), C.byref(nf), C.byref(no), C.byref(md)))
+        return dict(n_nodes=nn.value, n_tris=nt.value, n_flat=nf.value, n_objects=no.value, max_depth=md.value)
+
+    def download(self) -> _abi.FlatSceneArrays:
+        """The device scene as host arrays (srt_scene_download; tests and debugging)."""
+        c = self.counts()
+        nodes = np.zeros(c["n_nodes"], _abi.NODE_DTYPE)
+        geom = np.zeros(c["n_tris"], _abi.GEOM_DTYPE)
+        attr = np.zeros(c["n_tris"], _abi.ATTR_DTYPE)
+        fgeom = np.zeros(c["n_flat"], _abi.GEOM_DTYPE)
+        fattr = np.zeros(c["n_flat"], _abi.ATTR_DTYPE)
+        objs = np.zeros(c["n_objects"], _abi.OBJECT_DTYPE)
+        _check(lib().srt_scene_download(self.ctx.h, self.h, nodes.ctypes.data, geom.ctypes.data, attr.ctypes.data,
+                                        fgeom.ctypes.data, fattr.ctypes.data, objs.ctypes.data))
+        return _abi.FlatSceneArrays(nodes, geom, attr, objs, (), fgeom if len(fgeom) else None,
+                                    fattr if len(fattr) else None, max_depth=c["max_depth"])
+
+    def prep_status(self):
+        """Synchronises; raises SrtError(SRT_ERR_UNSUPPORTED) if the last srt_scene_prep met a non-finite coordinate."""
+        _check(lib().srt_scene_prep_status(self.ctx.h, self.h))
+
     def destroy(self):
         if self.h:
             lib().srt_scene_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.destroy()
+        except Exception:
+            pass
+
+
+class Mesh:
+    """Object-space triangles resident on the GPU (srt_mesh): what loadObjFile put into objTriangles[name]."""
+
+    def __init__(self, ctx: "Context", points, uv=None, tex=None):
+        pts = np.ascontiguousarray(points, np.float32).reshape(-1, 12)
+        d = _abi.MeshDesc()
+        d.points = pts.ctypes.data
+        d.n_tris = len(pts)
+        if uv is not None:
+            uv = np.ascontiguousarray(uv, np.float32).reshape(-1, 6)
+            assert len(uv) == len(pts)
+            d.uv = uv.ctypes.data
+        if tex is not None:
+            tex = np.ascontiguousarray(tex, np.int32).reshape(-1)
+            assert len(tex) == len(pts)
+            d.tex = tex.ctypes.data
+        h = C.c_void_p()
+        _check(lib().srt_mesh_upload(ctx.h, C.byref(d), C.byref(h)))
+        self.ctx, self.h, self.n_tris = ctx, h, len(pts)
+
+    def info(self) -> dict:
+        nt, nn, md = C.c_uint64(), C.c_uint64(), C.c_uint32()
+        _check(lib().srt_mesh_info(self.h, C.byref(nt), C.byref(nn), C.byref(md)))
+        return dict(n_tris=nt.value, n_nodes=nn.value, max_depth=md.value)
+
+    def destroy(self):
+        if self.h:
+            lib().srt_mesh_destroy(self.h)
             self.h = None
 
     def __del__(self):
@@ -160,6 +232,36 @@ class Context:
         h = C.c_void_p()
         _check(lib().srt_scene_upload(self.h, C.byref(d), C.byref(h)))
         return Scene(self, h)
+
+    def prep_scene(self, objects, textures=None, with_flat_lists: bool = False, scene: Optional[Scene] = None) -> Scene:
+        """srt_scene_prep: transform + BVH build + flatten on the device, asynchronous.  objects: sequence of
+        (Mesh, matrices [k][16] float32, color, (ambient, specular, shininess)) in objTriangles iteration order;
+        textures: list of [H][W][3] uint8 arrays (None keeps the textures of an existing scene)."""
+        n = len(objects)
+        arr = (_abi.PrepObject * max(n, 1))()
+        keep = []
+        for i, (mesh, mats, color, props) in enumerate(objects):
+            m = np.ascontiguousarray(mats, np.float32).reshape(-1, 16)
+            keep.append(m)
+            arr[i].mesh = mesh.h
+            arr[i].matrices = m.ctypes.data if len(m) else None
+            arr[i].n_matrices = len(m)
+            arr[i].color[:] = [float(x) for x in color]
+            arr[i].ambient, arr[i].specular, arr[i].shininess = [float(x) for x in props]
+        tex_arr, n_tex = None, 0
+        if textures is not None:
+            tex_keep = [np.ascontiguousarray(t, np.uint8) for t in textures]
+            keep.append(tex_keep)
+            n_tex = len(tex_keep)
+            tex_arr = (_abi.TextureDesc * max(n_tex, 1))()
+            for i, t in enumerate(tex_keep):
+                tex_arr[i].rgb = t.ctypes.data
+                tex_arr[i].height, tex_arr[i].width = t.shape[0], t.shape[1]
+        h = scene.h if scene is not None else C.c_void_p()
+        _check(lib().srt_scene_prep(self.h, arr, n, tex_arr, n_tex, 1 if with_flat_lists else 0, C.byref(h)))
+        if scene is None:
+            scene = Scene(self, h)
+        return scene
 
     def render_raw(self, scene: Scene, params: _abi.RenderParams, rgb=None, obj_id=None, tri_id=None, t=None):
         """Pointers (ints) may be host or device addresses; asynchronous."""

@@ -3,6 +3,8 @@
 #include <cstdlib>
 #include <cstring>
 #include <string>
+#include <unordered_map>
+#include <vector>
 
 #include "srt_flatten.hpp"
 #include "srt_host.h"
@@ -110,6 +112,50 @@ int srt_host_set_texture(srt_host_scene* s, const char* name, const uint8_t* rgb
     s->om.textureDimensions[name] = srt::ivec2(width, height);
     s->flat_valid = false;
     return 0;
+}
+
+// Texture slot of every triangle of `name` (slots numbered by first appearance in load order, -1 = untextured);
+// the slot names go to names_buf, one per line.  Returns the number of slots, -1 for an unknown object, -2 if
+// names_buf is too small.
+int srt_host_triangle_textures(srt_host_scene* s, const char* name, int32_t* slot_out, char* names_buf, int buflen) {
+    auto it = s->om.objTriangles.find(name);
+    if (it == s->om.objTriangles.end()) return -1;
+    std::unordered_map<std::string, int32_t> slot;
+    std::string names;
+    size_t i = 0;
+    for (const srt::Triangle& t : it->second) {
+        int32_t k = -1;
+        if (!t.textureName.empty()) {
+            auto f = slot.find(t.textureName);
+            if (f == slot.end()) { k = (int32_t)slot.size(); slot.emplace(t.textureName, k); names += t.textureName; names += '\n'; }
+            else k = f->second;
+        }
+        if (slot_out) slot_out[i] = k;
+        ++i;
+    }
+    if (names_buf) {
+        if ((int)names.size() + 1 > buflen) return -2;
+        std::memcpy(names_buf, names.c_str(), names.size() + 1);
+    }
+    return (int)slot.size();
+}
+int srt_host_texture_data(srt_host_scene* s, const char* texture_name, const uint8_t** rgb, int* width, int* height) {
+    auto td = s->om.textureData.find(texture_name);
+    auto dim = s->om.textureDimensions.find(texture_name);
+    if (td == s->om.textureData.end() || !td->second || dim == s->om.textureDimensions.end()) return -1;
+    *rgb = td->second; *width = dim->second.x; *height = dim->second.y;
+    return 0;
+}
+// Iteration order of an unordered_map<std::string, ...> whose keys were inserted in the given sequence (S2: the
+// object order of simple_raytracer.cpp:409 / :322 is the iteration order of objTriangles).  order_out[k] = index
+// into names of the k-th key visited.
+int srt_host_object_order(const char* const* names, int n, int* order_out) {
+    std::unordered_map<std::string, std::vector<srt::Triangle>> m;     // same key / mapped types as ObjectManager::objTriangles
+    std::unordered_map<std::string, int> index;
+    for (int i = 0; i < n; ++i) { m[names[i]]; index.emplace(names[i], i); }
+    int k = 0;
+    for (const auto& pair : m) order_out[k++] = index[pair.first];
+    return k;
 }
 
 void srt_host_xf_scale(float sx, float sy, float sz, float* o) { store16(srt::Transformation::scaleObj(sx, sy, sz), o); }

@@ -13,8 +13,9 @@
 
 #include "srt.h"
 #include "srt_kernels.cuh"
+#include "srt_internal.hpp"
 
-namespace {
+namespace srti {
 
 thread_local std::string g_err;
 
@@ -28,74 +29,18 @@ int fail(int code, const char* fmt, ...) {
     return code;
 }
 
-#define CU(call)                                                                                   \
-    do {                                                                                           \
-        cudaError_t e__ = (call);                                                                  \
-        if (e__ != cudaSuccess)                                                                    \
-            return fail(e__ == cudaErrorMemoryAllocation ? SRT_ERR_OOM : SRT_ERR_CUDA, "%s: %s",   \
-                        #call, cudaGetErrorString(e__));                                           \
-    } while (0)
-
-struct DevBuf {
-    void* p = nullptr;
-    size_t cap = 0;
-    int reserve(size_t bytes) {
-        if (bytes <= cap) return SRT_OK;
-        if (p) cudaFree(p);
-        p = nullptr; cap = 0;
-        size_t want = bytes + bytes / 8 + 256;
-        cudaError_t e = cudaMalloc(&p, want);
-        if (e != cudaSuccess) return fail(SRT_ERR_OOM, "cudaMalloc(%zu): %s", want, cudaGetErrorString(e));
-        cap = want;
-        return SRT_OK;
-    }
-    void release() { if (p) cudaFree(p); p = nullptr; cap = 0; }
-};
-
 bool is_device_pointer(const void* p) {
     cudaPointerAttributes at;
     if (cudaPointerGetAttributes(&at, p) != cudaSuccess) { cudaGetLastError(); return false; }
     return at.type == cudaMemoryTypeDevice || at.type == cudaMemoryTypeManaged;
 }
 
-}  // namespace
+}  // namespace srti
 
-struct srt_context {
-    int device = 0;
-    cudaStream_t stream = nullptr;
-    bool own_stream = true;
-    int sm_count = 0, cc_major = 0, cc_minor = 0;
-    size_t l2_bytes = 0;
-    unsigned long long* counters = nullptr;      // device, srtk::CNT_WORDS
-    unsigned long long* counters_host = nullptr; // pinned
-    cudaEvent_t ev0 = nullptr, ev1 = nullptr, ev_copy = nullptr;
-    DevBuf out_rgb, out_obj, out_tri, out_t;     // staging for HOST output pointers
-    DevBuf hit_t, hit_tri, tile_interest, tile_list, tile_order, tile_done, shadow_mask;
-    uint32_t frame_seq = 0;   // scratch of the phased kernel
-    DevBuf sparse_rgb, sparse_seg, sparse_points, sparse_colors, sparse_total;   // srt_render_sparse
-    unsigned long long* sparse_total_host = nullptr;   // pinned
-    uint64_t sparse_count = 0;
-    bool have_sparse = false;
-    int last_launches = 0;
-    // last render
-    bool have_last = false;
-    uint64_t last_primary = 0;
-    int last_lights = 0;
-    uint32_t last_objects = 0;
-};
-
-struct srt_scene {
-    srt_context* ctx = nullptr;
-    DevBuf nodes, geom, attr, flat_geom, flat_attr, objects, texdesc;
-    DevBuf wide, root_ref;                        // device-internal traversal layout (srt_phased.cu)
-    bool phased_ok = false;                       // leaf sizes / index ranges fit the packed traversal refs
-    float coord_bound = 0.f;                      // max |coordinate| over the root boxes
-    std::vector<DevBuf> tex;
-    std::vector<srtk::TexDev> tex_host;
-    uint64_t n_nodes = 0, n_tris = 0, n_flat = 0;
-    uint32_t n_objects = 0, n_textures = 0;
-    uint32_t max_depth = 0;
-};
+using srti::fail;
+using srti::g_err;
+using srti::is_device_pointer;
+using srti::DevBuf;
 
 extern "C" {
 
@@ -350,6 +295,7 @@ int fill_scene(srt_context* c, srt_scene* s, const srt_scene_desc* d, bool textu
     s->phased_ok = d->n_objects > 0 && max_leaf <= srtk::kLeafMaxCount && d->n_tris < (1ull << srtk::kLeafFirstBits) &&
                    d->n_nodes < 0x40000000ull;
     s->coord_bound = 0.f;
+    s->coord_bound_dev = nullptr;
     for (uint32_t o = 0; o < d->n_objects; ++o) {
         const srt_node& rn = d->nodes[d->objects[o].root];
         for (int k = 0; k < 3; ++k) {
@@ -415,6 +361,7 @@ void srt_scene_destroy(srt_scene* s) {
     s->nodes.release(); s->geom.release(); s->attr.release(); s->flat_geom.release(); s->flat_attr.release();
     s->objects.release(); s->texdesc.release(); s->wide.release(); s->root_ref.release();
     for (auto& t : s->tex) t.release();
+    srti_prep_state_destroy(s->prep);
     delete s;
 }
 
@@ -532,6 +479,7 @@ int srt_render(srt_context* c, const srt_scene* s, const srt_render_params* p, c
         a.frame_seq = c->frame_seq; a.tile_order = (uint32_t*)c->tile_order.p;
         a.shadow_mask = (uint32_t*)c->shadow_mask.p;
         a.coord_bound = s->coord_bound;
+        a.coord_bound_dev = s->coord_bound_dev;
         e = srtk::launch_render_phased(a, p->variant, c->sm_count, c->stream, &c->last_launches);
     } else {
         e = srtk::launch_render(a, p->variant, c->sm_count, c->stream);

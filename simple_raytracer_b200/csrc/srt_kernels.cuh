@@ -55,6 +55,7 @@ struct KArgs {
     uint32_t* tile_order;       // [tiles] phase-P queue order: expected-heavy tiles first
     uint32_t* shadow_mask;      // [tiles][light_count] ballot of occluded lanes
     float coord_bound;          // max |coordinate| over all root boxes (margin of the filtered slab test)
+    const float* coord_bound_dev;   // non-null: read the bound from device memory instead (device-prepared scenes)
     int32_t stack_cap;          // per-thread traversal stack entries (shared memory)
     int32_t debug_timeline;     // 1: phase P overwrites the t / obj_id / tri_id planes with per-tile cycles / SM / start ns
 };

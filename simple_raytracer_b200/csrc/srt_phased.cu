@@ -75,6 +75,12 @@ __device__ __forceinline__ float maxn(float a, float b) { float r; asm("max.NaN.
 // rays, S3) stays on the filter: i = rcp(+-0) = +-inf and n = 0 give b*i = +-inf, which IS the
 // reference's b/0 (same sign rules), and 0*inf = NaN where the reference has 0/0.  The margin only
 // has to cover the axes with finite values.
+// The bound is a launch constant for uploaded scenes; a scene prepared on the device (srt_scene_prep) keeps it in
+// device memory, because no host code ever sees the boxes.
+__device__ __forceinline__ float coord_bound_of(const KArgs& a) {
+    return a.coord_bound_dev ? __ldg(a.coord_bound_dev) : a.coord_bound;
+}
+
 __device__ __forceinline__ FRay make_fray(V3 o, V3 d, float coord_bound) {
     FRay r;
     r.o = o; r.d = d;
@@ -359,7 +365,7 @@ __device__ __forceinline__ unsigned primary_tile(const KArgs& a, Stack& st, unsi
     if (TL && a.debug_timeline == 1) { tl_c0 = clock64(); asm volatile("mov.u64 %0, %globaltimer;" : "=l"(tl_ns)); }
     p = pixel_of(a, tile, lane);
     d = primary_dir(a, p);
-    const FRay r = make_fray(v3(0.f, 0.f, 0.f), d, a.coord_bound);
+    const FRay r = make_fray(v3(0.f, 0.f, 0.f), d, coord_bound_of(a));
     h.t = INFINITY; h.tri = -1; h.obj = -1;
     st.sp = 0;
     if (p.valid) push_roots(a, r, st, -1, exact_count);                       // :409 (S2 order via the S6 rule)
@@ -377,7 +383,7 @@ __device__ __forceinline__ unsigned primary_tile(const KArgs& a, Stack& st, unsi
             for (int i = 0; i < a.light_count && !interested; ++i) {
                 V3 so, sd;
                 shadow_ray(a, d, h.t, i, so, sd);
-                const FRay s = make_fray(so, sd, a.coord_bound);
+                const FRay s = make_fray(so, sd, coord_bound_of(a));
                 st.sp = 0;
                 interested = push_roots(a, s, st, h.obj, exact_count);
             }
@@ -414,7 +420,7 @@ __device__ __forceinline__ void shadow_item(const KArgs& a, Stack& st, unsigned 
         obj = __float_as_int(ldg4(a.geom + 3 * (size_t)tri).w);
         shadow_ray(a, primary_dir(a, p), t, light, so, sd);
     }
-    const FRay s = make_fray(so, sd, a.coord_bound);
+    const FRay s = make_fray(so, sd, coord_bound_of(a));
     if (mine) push_roots(a, s, st, obj, exact_count);
     unsigned boxes = 0;
     const bool occluded = trace_any<COUNT>(a, s, st, exact_count, &boxes);

@@ -84,6 +84,9 @@ def _lib():
         L.srt_host_write_bmp.argtypes = [cp, C.c_void_p, i32, i32]
         L.srt_host_set_asset_cache.argtypes = [i32]
         L.srt_host_set_asset_cache.restype = None
+        L.srt_host_triangle_textures.argtypes = [vp, cp, C.POINTER(C.c_int32), C.c_char_p, i32]
+        L.srt_host_texture_data.argtypes = [vp, cp, C.POINTER(vp), C.POINTER(i32), C.POINTER(i32)]
+        L.srt_host_object_order.argtypes = [C.POINTER(cp), i32, C.POINTER(i32)]
         _bound = True
     return L
 
@@ -186,6 +189,28 @@ class HostScene:
         self.lib.srt_host_get_triangles(self.h, name.encode(), _fp(out), flags.ctypes.data_as(C.POINTER(C.c_uint8)))
         return out, flags
 
+    def triangle_textures(self, name):
+        """(slot per triangle [n] int32, slot names) — slots numbered by first appearance in load order, -1 = untextured."""
+        n = self.lib.srt_host_triangle_count(self.h, name.encode())
+        if n < 0:
+            raise KeyError(name)
+        slots = np.full(n, -1, np.int32)
+        buf = C.create_string_buffer(1 << 16)
+        k = self.lib.srt_host_triangle_textures(self.h, name.encode(), slots.ctypes.data_as(C.POINTER(C.c_int32)), buf, len(buf))
+        if k < 0:
+            raise RuntimeError("srt_host_triangle_textures failed")
+        names = [x for x in buf.value.decode().split("\n") if x]
+        assert len(names) == k
+        return slots, names
+
+    def texture(self, texture_name) -> np.ndarray:
+        """Decoded RGB8 pixels [H][W][3] of a loaded texture (a copy)."""
+        ptr, w, h = C.c_void_p(), C.c_int(), C.c_int()
+        if self.lib.srt_host_texture_data(self.h, texture_name.encode(), C.byref(ptr), C.byref(w), C.byref(h)) != 0:
+            raise KeyError(texture_name)
+        buf = (C.c_uint8 * (w.value * h.value * 3)).from_address(ptr.value)
+        return np.frombuffer(buf, np.uint8).reshape(h.value, w.value, 3).copy()
+
     # -- Transformation / glm
     def _mat(self, fn, *args):
         out = np.zeros(16, np.float32)
@@ -253,6 +278,15 @@ class HostScene:
             names.append(buf.value.decode())
         return _abi.FlatSceneArrays.from_desc_pointer(d, self.object_names(), names,
                                                       self.lib.srt_host_flat_max_depth(self.h))
+
+
+def object_order(names):
+    """Iteration order of the reference's objTriangles map for keys first touched in the order `names` (S2)."""
+    uniq = list(dict.fromkeys(names))
+    arr = (C.c_char_p * max(len(uniq), 1))(*[n.encode() for n in uniq])
+    out = (C.c_int * max(len(uniq), 1))()
+    k = _lib().srt_host_object_order(arr, len(uniq), out)
+    return [uniq[out[i]] for i in range(k)]
 
 
 def write_bmp(path, rgb: np.ndarray):
