@@ -466,15 +466,27 @@ def run_b200_arm(args):
         t_s1 = time.time()
         sr.close()
         series = (t_s1 - t_s0, n_fr, threads, float(np.mean(waits)), gpu_leg)
+        # the same series with the per-frame prep on the GPU (srt_scene_prep): no host pool at all
+        sd = _series.SeriesRenderer(ctx, cfg, W, H, focal, N, workers=1, variant=args.variant, prep="device")
+        n_fd = 2 * n_fr
+        myd = [360.0 * (i * world + rank) / (n_fd * world) for i in range(n_fd)]
+        list(sd.frames(myd[:2]))                                       # warm-up: parse + upload the meshes once
+        barrier()
+        t_d0 = time.time()
+        tmd = [tm for (_i, _rgb, tm) in sd.frames(myd)]
+        torch.cuda.synchronize()
+        t_d1 = time.time()
+        series_dev = (t_d1 - t_d0, n_fd, float(np.mean([tm["issue_ms"] for tm in tmd])), sd.host_fallbacks)
+        sd.close()
 
     # ---- max over ranks, totals ----
-    agg = torch.tensor([total_ms, e2e[0] if e2e else 0.0, kern_ms, prep_ms, series[0] if series else 0.0],
-                       dtype=torch.float64, device=dev)
+    agg = torch.tensor([total_ms, e2e[0] if e2e else 0.0, kern_ms, prep_ms, series[0] if series else 0.0,
+                        series_dev[0] if series else 0.0], dtype=torch.float64, device=dev)
     tot = torch.tensor([float(rays_local)], dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(agg, op=dist.ReduceOp.MAX)
         dist.all_reduce(tot, op=dist.ReduceOp.SUM)
-    total_ms, e2e_ms, kern_ms_max, prep_ms_max, series_s = [float(x) for x in agg.tolist()]
+    total_ms, e2e_ms, kern_ms_max, prep_ms_max, series_s, series_dev_s = [float(x) for x in agg.tolist()]
     rays_total = float(tot.item())
 
     line = None
@@ -546,6 +558,12 @@ def run_b200_arm(args):
                 "what": "whole image-series pipeline per rank: cached assets, per-frame transform + BVH build + flatten on a host "
                         "thread pool (bit-identical to rebuilding from files), upload, render, download to pinned host memory on two "
                         "alternating contexts (the GPU leg overlaps the wait for the next frame's prep)"}
+            line["series_with_device_prep"] = {
+                "frames_per_s": world * series_dev[1] / series_dev_s, "frames": world * series_dev[1], "host_threads_per_rank": 1,
+                "mean_issue_ms": series_dev[2], "host_fallback_frames": series_dev[3],
+                "what": "the same pipeline with the per-frame prep on the GPU: meshes resident in object space, per frame the "
+                        "recorded scene script (matrices) -> srt_scene_prep (transformTriangles + createBoundingHierarchy + "
+                        "flatten as CUDA kernels, bit-identical to the host result) -> render -> download; one host thread"}
         if world == 1 and not args.no_cpu_baseline:
             try:
                 nv = 1 if args.still else 4

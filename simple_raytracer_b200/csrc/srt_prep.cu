@@ -369,6 +369,285 @@ __device__ void sort_rounds(const SortSpace& s) {
 __device__ __forceinline__ uint32_t lg2_floor(uint32_t n) { return 31u - __clz(n); }
 
 // ------------------------------------------------------------------------------------------------------------
+// Large nodes: the same introsort loop, one node's segment spread over many CTAs.  A round is three launches over
+// the tiles (1024 elements) of all segments longer than kWideSmall: count the elements not less / not greater than
+// the pivot per tile; rank them (a tile adds the counts of the tiles before it) and record their positions; swap the
+// pairs and, in the CTA that finishes a segment last, cut it and set up its two sides for the next round.  Shorter
+// segments, and whatever is left after the planned number of rounds, are finished by one CTA each.
+struct SortShared {
+    uint32_t qcount[2];
+    uint32_t warp_cnt[64];
+    uint32_t sh_k;
+};
+
+// median of (first + 1, mid, last - 1) to first, reading around L1 (other CTAs of this launch wrote these keys);
+// returns the pivot.
+__device__ float median_to_first_cg(float* key, uint32_t* idx, uint32_t first, uint32_t last) {
+    const uint32_t A = first + 1, B = first + (last - first) / 2, C = last - 1;
+    const float ka = __ldcg(key + A), kb = __ldcg(key + B), kc = __ldcg(key + C);
+    uint32_t m; float km;
+    if (ka < kb) { if (kb < kc) { m = B; km = kb; } else if (ka < kc) { m = C; km = kc; } else { m = A; km = ka; } }
+    else if (ka < kc) { m = A; km = ka; }
+    else if (kb < kc) { m = C; km = kc; }
+    else { m = B; km = kb; }
+    const float kf = __ldcg(key + first);
+    const uint32_t jf = __ldcg(idx + first), jm = __ldcg(idx + m);
+    key[first] = km; key[m] = kf;
+    idx[first] = jm; idx[m] = jf;
+    return km;
+}
+
+// One thread: queue [lo, hi) for round `round`, or hand it to the finishing CTAs.
+__device__ void wide_emit(const PrepArgs& a, const WideArgs& w, uint32_t lo, uint32_t hi, uint32_t d, uint32_t round, bool no_more_rounds) {
+    const uint32_t len = hi - lo;
+    if (len <= 16) return;
+    if (len <= kWideSmall || d == 0 || no_more_rounds) {
+        const uint32_t e = atomicAdd(w.fin_count, 1u);
+        if (e < w.max_fin) w.fin[e] = WideSmall{lo, hi, d}; else atomicOr(a.status, 2u);
+        return;
+    }
+    const uint32_t nt = (len - 1 + kWideTile - 1) / kWideTile;
+    const uint32_t t0 = atomicAdd(&w.rounds[round].ntiles, nt);
+    const uint32_t sid = atomicAdd(&w.rounds[round].nsegs, 1u);
+    if (sid >= w.max_segs || t0 + nt > w.max_tiles) { atomicOr(a.status, 2u); return; }
+    const float pivot = median_to_first_cg(a.key, a.idx, lo, hi);
+    w.segs[(size_t)(round & 1u) * w.max_segs + sid] = WideSeg{lo, hi, d, pivot, t0, nt, 0u, 0u};
+    uint2* ts = w.tile_seg + (size_t)(round & 1u) * w.max_tiles + t0;
+    for (uint32_t i = 0; i < nt; ++i) ts[i] = make_uint2(sid, i);
+}
+
+// keys of the level's nodes: pointOne.<axis> of every triangle in its current order
+__global__ void __launch_bounds__(256) wide_begin_kernel(const PrepArgs a, const WorkItem* __restrict__ items) {
+    const WorkItem it = items[blockIdx.y];
+    if (blockIdx.x * kWideTile >= it.count) return;
+    const PrepObject o = a.objects[it.obj];
+    const float4* n = a.nodes + 2 * ((size_t)o.node_base + it.node);
+    const float4 b0 = n[0], b1 = n[1];
+    const float sx = fabsf(__fsub_rn(b1.x, b0.x)), sy = fabsf(__fsub_rn(b1.y, b0.y)), sz = fabsf(__fsub_rn(b1.z, b0.z));
+    const uint32_t ax = (sx > sy && sx > sz) ? 0u : ((sy > sx && sy > sz) ? 1u : 2u);
+    const size_t gbase = (size_t)o.tri_base + it.start;
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+        const uint32_t li = blockIdx.x * kWideTile + u * 256u + threadIdx.x;
+        if (li < it.count) {
+            const uint32_t tri = a.order[gbase + li];
+            const float4 p1 = a.xpts[3 * ((size_t)o.tri_base + tri)];
+            a.idx[gbase + li] = tri;
+            a.key[gbase + li] = ax == 0 ? p1.x : (ax == 1 ? p1.y : p1.z);
+        }
+    }
+}
+
+__global__ void wide_init_kernel(const PrepArgs a, const WideArgs w, const WorkItem* __restrict__ items, const uint32_t n_items, const uint32_t rounds) {
+    for (uint32_t r = threadIdx.x; r <= (uint32_t)kWideMaxRounds; r += blockDim.x) w.rounds[r] = WideRound{0u, 0u};
+    if (threadIdx.x == 0) *w.fin_count = 0;
+    for (uint32_t i = threadIdx.x; i < n_items * 12u; i += blockDim.x) w.childacc[i] = seed_of((int)(i % 6u));
+    __syncthreads();
+    for (uint32_t i = threadIdx.x; i < n_items; i += blockDim.x) {
+        const WorkItem it = items[i];
+        const uint32_t lo = a.objects[it.obj].tri_base + it.start;
+        if (it.count > 16) wide_emit(a, w, lo, lo + it.count, 2u * lg2_floor(it.count), 0, rounds == 0);
+    }
+}
+
+__global__ void __launch_bounds__(256) wide_count_kernel(const PrepArgs a, const WideArgs w, const uint32_t round) {
+    const uint32_t t = blockIdx.x;
+    if (t >= w.rounds[round].ntiles) return;
+    const uint2 ts = w.tile_seg[(size_t)(round & 1u) * w.max_tiles + t];
+    const WideSeg S = w.segs[(size_t)(round & 1u) * w.max_segs + ts.x];
+    const uint32_t x0 = S.lo + 1 + ts.y * kWideTile, x1 = x0 + kWideTile < S.hi ? x0 + kWideTile : S.hi;
+    const float p = S.pivot;
+    uint32_t cl = 0, cr = 0;
+    for (uint32_t x = x0 + threadIdx.x; x < x1; x += 256) { const float k = a.key[x]; cl += !(k < p); cr += !(p < k); }
+    cl = __reduce_add_sync(kFull, cl); cr = __reduce_add_sync(kFull, cr);
+    __shared__ uint32_t sl[8], sr[8];
+    if ((threadIdx.x & 31u) == 0) { sl[threadIdx.x >> 5] = cl; sr[threadIdx.x >> 5] = cr; }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        uint32_t tl = 0, tr = 0;
+        for (int i = 0; i < 8; ++i) { tl += sl[i]; tr += sr[i]; }
+        w.tile_cnt[t] = make_uint2(tl, tr);
+    }
+}
+
+__global__ void __launch_bounds__(256) wide_scatter_kernel(const PrepArgs a, const WideArgs w, const uint32_t round) {
+    const uint32_t t = blockIdx.x;
+    if (t >= w.rounds[round].ntiles) return;
+    const unsigned lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+    const uint2 ts = w.tile_seg[(size_t)(round & 1u) * w.max_tiles + t];
+    const WideSeg S = w.segs[(size_t)(round & 1u) * w.max_segs + ts.x];
+    const uint32_t x0 = S.lo + 1 + ts.y * kWideTile + warp * 128u, xe = S.lo + 1 + (ts.y + 1) * kWideTile;
+    const uint32_t x1 = xe < S.hi ? xe : S.hi;
+    const float p = S.pivot;
+    __shared__ uint32_t sl[8], sr[8], base[2];
+    unsigned bl[4], br[4];
+    uint32_t wl = 0, wr = 0;
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+        const uint32_t x = x0 + 32u * u + lane;
+        const bool valid = x < x1;
+        const float k = valid ? a.key[x] : 0.f;
+        bl[u] = __ballot_sync(kFull, valid && !(k < p));
+        br[u] = __ballot_sync(kFull, valid && !(p < k));
+        wl += __popc(bl[u]); wr += __popc(br[u]);
+    }
+    if (lane == 0) { sl[warp] = wl; sr[warp] = wr; }
+    if (warp == 0) {                                             // ranks before this tile: the counts of the segment's earlier tiles
+        uint32_t pl = 0, pr = 0;
+        for (uint32_t i = lane; i < ts.y; i += 32) { const uint2 c = w.tile_cnt[S.tile_first + i]; pl += c.x; pr += c.y; }
+        pl = __reduce_add_sync(kFull, pl); pr = __reduce_add_sync(kFull, pr);
+        if (lane == 0) { base[0] = pl; base[1] = pr; }
+    }
+    __syncthreads();
+    uint32_t offl = base[0], offr = base[1];
+    for (unsigned i = 0; i < warp; ++i) { offl += sl[i]; offr += sr[i]; }
+    const unsigned lt = (1u << lane) - 1u;
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+        const uint32_t x = x0 + 32u * u + lane;
+        if ((bl[u] >> lane) & 1u) a.posl[S.lo + offl + __popc(bl[u] & lt)] = x;
+        if ((br[u] >> lane) & 1u) a.posr[S.lo + offr + __popc(br[u] & lt)] = x;
+        offl += __popc(bl[u]); offr += __popc(br[u]);
+    }
+}
+
+__global__ void __launch_bounds__(256) wide_swap_kernel(const PrepArgs a, const WideArgs w, const uint32_t round, const uint32_t last_round) {
+    const uint32_t t = blockIdx.x;
+    if (t >= w.rounds[round].ntiles) return;
+    const unsigned lane = threadIdx.x & 31u;
+    const uint2 ts = w.tile_seg[(size_t)(round & 1u) * w.max_tiles + t];
+    WideSeg* sp = w.segs + (size_t)(round & 1u) * w.max_segs + ts.x;
+    const uint32_t lo = sp->lo, hi = sp->hi, d = sp->d, tile_first = sp->tile_first, ntiles = sp->ntiles;
+    __shared__ uint32_t tot[2];
+    __shared__ int is_last;
+    if (threadIdx.x < 32) {
+        uint32_t pl = 0, pr = 0;
+        for (uint32_t i = lane; i < ntiles; i += 32) { const uint2 c = w.tile_cnt[tile_first + i]; pl += c.x; pr += c.y; }
+        pl = __reduce_add_sync(kFull, pl); pr = __reduce_add_sync(kFull, pr);
+        if (lane == 0) { tot[0] = pl; tot[1] = pr; }
+    }
+    __syncthreads();
+    const uint32_t TL = tot[0], TR = tot[1], mn = TL < TR ? TL : TR;
+    const uint32_t k1 = (ts.y + 1) * kWideTile < mn ? (ts.y + 1) * kWideTile : mn;
+    for (uint32_t k = ts.y * kWideTile + threadIdx.x; k < k1; k += 256) {
+        const uint32_t l = a.posl[lo + k], r = a.posr[lo + TR - 1 - k];
+        if (l < r) {
+            const float kl = a.key[l], kr = a.key[r];
+            const uint32_t il = a.idx[l], ir = a.idx[r];
+            a.key[l] = kr; a.key[r] = kl; a.idx[l] = ir; a.idx[r] = il;
+            const bool last_pair = (k + 1 == mn) || !(a.posl[lo + k + 1] < a.posr[lo + TR - 2 - k]);
+            if (last_pair) sp->K = k + 1;
+        }
+    }
+    __threadfence();
+    __syncthreads();
+    if (threadIdx.x == 0) is_last = atomicAdd(&sp->done, 1u) == ntiles - 1;
+    __syncthreads();
+    if (!is_last || threadIdx.x != 0) return;
+    __threadfence();
+    const uint32_t K = __ldcg(&sp->K);
+    uint32_t cut = kNoPos;
+    if (K < TL) cut = a.posl[lo + K];
+    if (K >= 1) { const uint32_t r = a.posr[lo + TR - K]; cut = r < cut ? r : cut; }
+    wide_emit(a, w, cut, hi, d - 1, round + 1, last_round != 0);
+    wide_emit(a, w, lo, cut, d - 1, round + 1, last_round != 0);
+}
+
+// The segments left to one CTA each: the rest of their introsort loop in shared memory (global memory if longer).
+__global__ void __launch_bounds__(kBuildThreads, 1) wide_finish_kernel(const PrepArgs a, const WideArgs w) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    SortShared& sh = *reinterpret_cast<SortShared*>(smem_raw);
+    Seg* q0 = reinterpret_cast<Seg*>(smem_raw + 512);
+    constexpr uint32_t kQ = kWideSmall / 16;
+    float* wsp = reinterpret_cast<float*>(smem_raw + 512 + 2 * kQ * sizeof(Seg));
+    const uint32_t n = *w.fin_count < w.max_fin ? *w.fin_count : w.max_fin;
+    for (uint32_t e = blockIdx.x; e < n; e += gridDim.x) {
+        const WideSmall f = w.fin[e];
+        const uint32_t len = f.hi - f.lo;
+        SortSpace s;
+        s.qcount = sh.qcount; s.warp_cnt = sh.warp_cnt; s.sh_k = &sh.sh_k;
+        const bool in_smem = len <= kWideSmall;
+        if (in_smem) {
+            s.key = wsp; s.idx = reinterpret_cast<uint32_t*>(wsp + kWideSmall);
+            s.posl = reinterpret_cast<uint32_t*>(wsp + 2 * kWideSmall); s.posr = reinterpret_cast<uint32_t*>(wsp + 3 * kWideSmall);
+            s.q[0] = q0; s.q[1] = q0 + kQ;
+            for (uint32_t i = threadIdx.x; i < len; i += kBuildThreads) { s.key[i] = a.key[f.lo + i]; s.idx[i] = a.idx[f.lo + i]; }
+            if (threadIdx.x == 0) { sh.qcount[0] = 1; sh.qcount[1] = 0; s.q[0][0] = Seg{0u, len, f.d}; }
+        } else {
+            s.key = a.key; s.idx = a.idx; s.posl = a.posl; s.posr = a.posr;
+            s.q[0] = reinterpret_cast<Seg*>(a.segq) + f.lo / 8;
+            s.q[1] = reinterpret_cast<Seg*>(a.segq) + a.segq_stride + f.lo / 8;
+            if (threadIdx.x == 0) { sh.qcount[0] = 1; sh.qcount[1] = 0; s.q[0][0] = Seg{f.lo, f.hi, f.d}; }
+        }
+        sort_rounds(s);
+        if (in_smem)
+            for (uint32_t i = threadIdx.x; i < len; i += kBuildThreads) { a.key[f.lo + i] = s.key[i]; a.idx[f.lo + i] = s.idx[i]; }
+        __syncthreads();
+    }
+}
+
+// __final_insertion_sort of the level's nodes (stable, window of 15) -> order[], and the child boxes as packed minima.
+__global__ void __launch_bounds__(256) wide_final_kernel(const PrepArgs a, const WideArgs w, const WorkItem* __restrict__ items) {
+    const WorkItem it = items[blockIdx.y];
+    if (blockIdx.x * kWideTile >= it.count) return;
+    const PrepObject o = a.objects[it.obj];
+    const uint32_t ns = o.tri_base + it.start, ne = ns + it.count, half = it.count / 2;
+    const unsigned lane = threadIdx.x & 31u;
+#pragma unroll 1
+    for (int u = 0; u < 4; ++u) {
+        const uint32_t x = ns + blockIdx.x * kWideTile + u * 256u + threadIdx.x;
+        const bool active = x < ne;
+        unsigned long long acc[6];
+#pragma unroll
+        for (int q = 0; q < 6; ++q) acc[q] = seed_of(q);
+        uint32_t child = 0;
+        if (active) {
+            const float k = a.key[x];
+            uint32_t dst = x;
+            const uint32_t y0 = x >= ns + 15 ? x - 15 : ns, y1 = x + 16 < ne ? x + 16 : ne;
+            for (uint32_t y = y0; y < x; ++y) dst -= (a.key[y] > k);
+            for (uint32_t y = x + 1; y < y1; ++y) dst += (a.key[y] < k);
+            const uint32_t tri = a.idx[x];
+            a.order[dst] = tri;
+            child = (dst - ns) < half ? 0u : 1u;
+            const uint32_t pos = dst - o.tri_base;                      // position in the object's order
+            const float2* lp = reinterpret_cast<const float2*>(a.lite + 6 * ((size_t)o.tri_base + tri));
+            const float2 v0 = lp[0], v1 = lp[1], v2 = lp[2];
+            const float v[6] = {v0.x, v0.y, v1.x, v1.y, v2.x, v2.y};
+#pragma unroll
+            for (int q = 0; q < 3; ++q) {
+                if (v[q] == v[q] && v[q] < FLT_MAX) acc[q] = pack_min(v[q], pos);
+                if (v[3 + q] == v[3 + q] && v[3 + q] > -FLT_MAX) acc[3 + q] = pack_max(v[3 + q], pos);
+            }
+        }
+        const unsigned m_act = __ballot_sync(kFull, active), m_one = __ballot_sync(kFull, active && child == 1u);
+        if (m_act == 0) continue;
+        unsigned long long* dstacc = w.childacc + (size_t)blockIdx.y * 12u;
+        if (m_one == 0 || m_one == m_act) {
+#pragma unroll
+            for (int q = 0; q < 6; ++q) {
+                const unsigned long long v = warp_min64(acc[q]);
+                if (lane == 0 && v != seed_of(q)) atomicMin(dstacc + (m_one ? 6 : 0) + q, v);
+            }
+        } else if (active) {
+#pragma unroll
+            for (int q = 0; q < 6; ++q) if (acc[q] != seed_of(q)) atomicMin(dstacc + child * 6u + q, acc[q]);
+        }
+    }
+}
+
+__global__ void wide_children_kernel(const PrepArgs a, const WideArgs w, const WorkItem* __restrict__ items, const uint32_t n_items) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= 2 * n_items) return;
+    const WorkItem it = items[i >> 1];
+    const PrepObject o = a.objects[it.obj];
+    float box[6];
+    for (int q = 0; q < 6; ++q) box[q] = decode_sorted(a, o, w.childacc[(size_t)i * 6u + q], q);
+    const uint32_t child = (i & 1u) ? o.topo[it.node].right : it.node + 1;
+    write_node(a, o, child, box);
+}
+
+// ------------------------------------------------------------------------------------------------------------
 struct Level {                     // nodes of the current level inside the CTA's range (shared memory), ascending by start
     uint32_t node[kNLMax], start[kNLMax], count[kNLMax];     // start: position relative to the CTA's range
     uint32_t axis[kNLMax];
@@ -600,8 +879,30 @@ size_t build_smem_bytes(bool subtree) {
     return subtree ? base + 4 * sizeof(float) * (size_t)kSubtreeMax : base;
 }
 
+size_t wide_finish_smem_bytes() { return 512 + 2 * (size_t)(kWideSmall / 16) * sizeof(Seg) + 4 * sizeof(float) * (size_t)kWideSmall; }
+
+cudaError_t launch_wide_level(const PrepArgs& a, const WideArgs& w, const WorkItem* items, uint32_t n_items, uint32_t max_count,
+                              uint32_t rounds, uint32_t tile_grid, int sm_count, cudaStream_t stream, int* launches) {
+    if (n_items == 0) return cudaSuccess;
+    const dim3 tiles((max_count + kWideTile - 1) / kWideTile, n_items);
+    wide_begin_kernel<<<tiles, 256, 0, stream>>>(a, items);
+    wide_init_kernel<<<1, 256, 0, stream>>>(a, w, items, n_items, rounds);
+    for (uint32_t r = 0; r < rounds; ++r) {
+        wide_count_kernel<<<tile_grid, 256, 0, stream>>>(a, w, r);
+        wide_scatter_kernel<<<tile_grid, 256, 0, stream>>>(a, w, r);
+        wide_swap_kernel<<<tile_grid, 256, 0, stream>>>(a, w, r, r + 1 == rounds ? 1u : 0u);
+    }
+    wide_finish_kernel<<<sm_count, kBuildThreads, wide_finish_smem_bytes(), stream>>>(a, w);
+    wide_final_kernel<<<tiles, 256, 0, stream>>>(a, w, items);
+    wide_children_kernel<<<(2 * n_items + 63) / 64, 64, 0, stream>>>(a, w, items, n_items);
+    if (launches) *launches += 5 + 3 * (int)rounds;
+    return cudaGetLastError();
+}
+
 cudaError_t prepare_kernels() {
-    return cudaFuncSetAttribute(build_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)build_smem_bytes(true));
+    cudaError_t e = cudaFuncSetAttribute(build_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)build_smem_bytes(true));
+    if (e != cudaSuccess) return e;
+    return cudaFuncSetAttribute(wide_finish_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)wide_finish_smem_bytes());
 }
 
 cudaError_t launch_transform(const PrepArgs& a, uint32_t max_tris, cudaStream_t stream) {

@@ -49,6 +49,33 @@ struct PrepArgs {
     unsigned long long* rootacc;   // [n_objects][6] packed (value code, position) minima of the object boxes
 };
 
+// ---- large nodes: the introsort loop of a node spread over many CTAs (one launch per step of a round) ----
+struct WideSeg {               // a segment being partitioned: [lo, hi) are scene positions, key[lo] holds the pivot
+    uint32_t lo, hi, d;
+    float pivot;
+    uint32_t tile_first, ntiles;
+    uint32_t K;                // pairs swapped (written by the CTA that holds the last swapping pair)
+    uint32_t done;             // tiles that finished the swap step
+};
+struct WideRound { uint32_t nsegs, ntiles; };
+struct WideSmall { uint32_t lo, hi, d; };    // a segment short enough for one CTA's shared memory (or out of depth / rounds)
+
+struct WideArgs {
+    WideSeg* segs;   uint32_t max_segs;      // [2][max_segs], by round parity
+    uint2* tile_seg; uint32_t max_tiles;     // [2][max_tiles]: (segment, tile index within the segment)
+    uint2* tile_cnt;                         // [max_tiles]: elements not less / not greater than the pivot
+    WideRound* rounds;                       // [kWideMaxRounds + 1]
+    WideSmall* fin;  uint32_t max_fin;       // segments left to one CTA each
+    uint32_t* fin_count;
+    unsigned long long* childacc;            // [items][2][6] packed minima of the child boxes
+};
+constexpr int kWideMaxRounds = 40;
+constexpr uint32_t kWideTile = 1024;         // elements per tile CTA
+constexpr uint32_t kWideSmall = 12288;       // a segment at most this long is finished by one CTA in shared memory
+
+cudaError_t launch_wide_level(const PrepArgs& a, const WideArgs& w, const WorkItem* items, uint32_t n_items, uint32_t max_count,
+                              uint32_t rounds, uint32_t tile_grid, int sm_count, cudaStream_t stream, int* launches);
+
 constexpr int kSubtreeMax = 4096;     // a node with at most this many triangles is built, with its whole subtree, by one CTA in shared memory
 constexpr int kBuildThreads = 1024;
 

@@ -4,6 +4,7 @@
 #include <cuda_runtime.h>
 
 #include <cfloat>
+#include <cstdlib>
 #include <cstring>
 #include <vector>
 
@@ -25,7 +26,8 @@ struct srt_mesh {
 };
 
 struct srt_prep_state {
-    DevBuf xpts, lite, order, key, idx, posl, posr, segq, blob, misc;
+    DevBuf xpts, lite, order, key, idx, posl, posr, segq, blob, misc, wide;
+    int last_launches = 0;
     std::vector<unsigned char> blob_host;
     // the recipe goes through pinned staging (a pageable cudaMemcpyAsync would first wait for the stream): two
     // buffers in turn, each guarded by the event of its last copy
@@ -74,7 +76,7 @@ size_t blob_put(std::vector<unsigned char>& b, const T* src, size_t n) {
 void srti_prep_state_destroy(srt_prep_state* p) {
     if (!p) return;
     p->xpts.release(); p->lite.release(); p->order.release(); p->key.release(); p->idx.release();
-    p->posl.release(); p->posr.release(); p->segq.release(); p->blob.release(); p->misc.release();
+    p->posl.release(); p->posr.release(); p->segq.release(); p->blob.release(); p->misc.release(); p->wide.release();
     if (p->status_host) cudaFreeHost(p->status_host);
     for (int k = 0; k < 2; ++k) {
         if (p->pin[k]) cudaFreeHost(p->pin[k]);
@@ -141,7 +143,9 @@ int srt_scene_prep(srt_context* c, const srt_prep_object* objs, uint32_t n_objec
     uint32_t max_depth = 0, max_tris = 0;
     for (uint32_t i = 0; i < n_objects; ++i) {
         const srt_prep_object& po = objs[i];
-        if (!po.mesh || po.mesh->ctx != c) return fail(SRT_ERR_INVALID_ARG, "object %u: mesh is NULL or belongs to another context", i);
+        // a mesh is immutable after its (synchronous) upload: any context of the same device may read it
+        if (!po.mesh || !po.mesh->ctx || po.mesh->ctx->device != c->device)
+            return fail(SRT_ERR_INVALID_ARG, "object %u: mesh is NULL or lives on another device", i);
         if (po.n_matrices && !po.matrices) return fail(SRT_ERR_INVALID_ARG, "object %u: matrices is NULL", i);
         n_tris += po.mesh->n_tris; n_nodes += po.mesh->topo_host.size(); n_mats += po.n_matrices;
         if (po.mesh->max_depth > max_depth) max_depth = po.mesh->max_depth;
@@ -311,12 +315,57 @@ int srt_scene_prep(srt_context* c, const srt_prep_object* objs, uint32_t n_objec
     a.key = (float*)ps.key.p; a.idx = (uint32_t*)ps.idx.p; a.posl = (uint32_t*)ps.posl.p; a.posr = (uint32_t*)ps.posr.p;
     a.segq = (uint32_t*)ps.segq.p; a.segq_stride = (uint32_t)segq_stride;
 
+    // workspace of the many-CTA path for the large nodes
+    size_t max_items = 1, n_big_total = 0;
+    for (const auto& lv : big) { if (lv.size() > max_items) max_items = lv.size(); n_big_total += lv.size(); }
+    srtp::WideArgs w;
+    std::memset(&w, 0, sizeof w);
+    w.max_segs = (uint32_t)(N / 4096 + 2 * max_items + 64);
+    w.max_tiles = (uint32_t)(N / srtp::kWideTile + w.max_segs + 64);
+    w.max_fin = (uint32_t)(N / 16 + max_items + 64);
+    {
+        size_t off = 0;
+        auto carve = [&](size_t bytes) { const size_t at = off; off = (off + bytes + 255) & ~size_t(255); return at; };
+        const size_t o_segs = carve(2 * (size_t)w.max_segs * sizeof(srtp::WideSeg));
+        const size_t o_tseg = carve(2 * (size_t)w.max_tiles * sizeof(uint2));
+        const size_t o_tcnt = carve((size_t)w.max_tiles * sizeof(uint2));
+        const size_t o_rnd = carve((srtp::kWideMaxRounds + 1) * sizeof(srtp::WideRound));
+        const size_t o_fin = carve((size_t)w.max_fin * sizeof(srtp::WideSmall));
+        const size_t o_cnt = carve(sizeof(uint32_t));
+        const size_t o_acc = carve(max_items * 12 * sizeof(unsigned long long));
+        if (n_big_total && (rc = ps.wide.reserve(off))) return bail(rc);
+        unsigned char* wb = (unsigned char*)ps.wide.p;
+        w.segs = (srtp::WideSeg*)(wb + o_segs); w.tile_seg = (uint2*)(wb + o_tseg); w.tile_cnt = (uint2*)(wb + o_tcnt);
+        w.rounds = (srtp::WideRound*)(wb + o_rnd); w.fin = (srtp::WideSmall*)(wb + o_fin); w.fin_count = (uint32_t*)(wb + o_cnt);
+        w.childacc = (unsigned long long*)(wb + o_acc);
+    }
+    static const bool single_cta_big = std::getenv("SRT_PREP_SINGLE_CTA") != nullptr;     // A/B: the one-CTA-per-node path
+    int launches = 0;
     cudaError_t e = srtp::launch_transform(a, max_tris, c->stream);
     if (e == cudaSuccess) e = srtp::launch_roots(a, c->stream);
-    for (size_t d = 0; d < big.size() && e == cudaSuccess; ++d)
-        e = srtp::launch_build(a, (const srtp::WorkItem*)(dblob + at_big[d]), (uint32_t)big[d].size(), false, c->stream);
+    launches += 2;
+    for (size_t d = 0; d < big.size() && e == cudaSuccess; ++d) {
+        if (big[d].empty()) continue;
+        if (single_cta_big) {
+            e = srtp::launch_build(a, (const srtp::WorkItem*)(dblob + at_big[d]), (uint32_t)big[d].size(), false, c->stream);
+            ++launches;
+            continue;
+        }
+        uint32_t maxc = 0;
+        size_t tiles = 8, total = 0;
+        for (const srtp::WorkItem& it : big[d]) { if (it.count > maxc) maxc = it.count; total += it.count; tiles += it.count / srtp::kWideTile + 1; }
+        tiles += 2 * (total / srtp::kWideSmall + big[d].size());
+        uint32_t rounds = 0;                                       // planned global rounds: until the segments fit one CTA, plus one
+        if (maxc > srtp::kWideSmall) { rounds = 1; for (uint64_t v = srtp::kWideSmall; v < maxc; v *= 2) ++rounds; }
+        if (rounds > (uint32_t)srtp::kWideMaxRounds - 1) rounds = srtp::kWideMaxRounds - 1;
+        if (tiles > w.max_tiles) tiles = w.max_tiles;
+        e = srtp::launch_wide_level(a, w, (const srtp::WorkItem*)(dblob + at_big[d]), (uint32_t)big[d].size(), maxc, rounds,
+                                    (uint32_t)tiles, c->sm_count, c->stream, &launches);
+    }
     if (e == cudaSuccess) e = srtp::launch_build(a, (const srtp::WorkItem*)(dblob + at_sub), (uint32_t)sub.size(), true, c->stream);
     if (e == cudaSuccess) e = srtp::launch_flatten(a, max_tris, with_flat_lists != 0, c->stream);
+    launches += 3;
+    ps.last_launches = launches;
     if (e == cudaSuccess && n_objects > 0)
         e = srtk::launch_build_wide((const float4*)s->nodes.p, (const srt_object*)s->objects.p, (uint32_t)n_nodes, n_objects,
                                     (float4*)s->wide.p, (uint32_t*)s->root_ref.p, c->stream);
@@ -337,6 +386,8 @@ int srt_scene_prep_status(srt_context* c, srt_scene* s) {
     if (!s->prep || !s->prep->status_host) return fail(SRT_ERR_INVALID_ARG, "scene was not prepared with srt_scene_prep");
     CU(cudaSetDevice(c->device));
     CU(cudaStreamSynchronize(c->stream));
+    if (*s->prep->status_host & 2u)
+        return fail(SRT_ERR_CUDA, "srt_scene_prep: internal work-list overflow (please report)");
     if (*s->prep->status_host & 1u)
         return fail(SRT_ERR_UNSUPPORTED, "srt_scene_prep: a transformed coordinate is not finite (std::sort's comparison is not a strict weak order on NaN keys); prepare this frame on the host");
     return SRT_OK;

@@ -135,8 +135,11 @@ class DeviceScene:
         raise AttributeError(item)
 
     # -- the device part
-    def commit(self, scene: Optional[capi.Scene] = None, with_flat_lists: bool = False) -> capi.Scene:
-        """Transform + build + flatten on the GPU (asynchronous on the context stream)."""
+    def commit(self, scene: Optional[capi.Scene] = None, with_flat_lists: bool = False,
+               ctx: Optional[capi.Context] = None) -> capi.Scene:
+        """Transform + build + flatten on the GPU, asynchronous on the stream of `ctx` (default: the scene's context,
+        else the cache's; any context of the device the meshes live on will do)."""
+        ctx = ctx or (scene.ctx if scene is not None else self.cache.ctx)
         recipe = []
         for name in self.object_names():
             o = self.objects[name]
@@ -148,6 +151,6 @@ class DeviceScene:
             mats = np.stack(o.matrices) if o.matrices else np.zeros((0, 16), np.float32)
             recipe.append((o.mesh, mats, self.colors.get(name, (0.0, 0.0, 0.0)), self.props.get(name, (0.0, 0.0, 0.0))))
         new_textures = scene is None or getattr(scene, "_n_textures", -1) != len(self.cache.textures)
-        out = self.cache.ctx.prep_scene(recipe, self.cache.textures if new_textures else None, with_flat_lists, scene)
+        out = ctx.prep_scene(recipe, self.cache.textures if new_textures else None, with_flat_lists, scene)
         out._n_textures = len(self.cache.textures)
         return out

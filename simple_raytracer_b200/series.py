@@ -10,6 +10,11 @@ This driver keeps the per-frame work bit-identical and takes it off the critical
     and the frame is read back into pinned memory — asynchronously, on two contexts (streams) that alternate, so
     the GPU leg of frame i runs while the driver waits for the prep of frame i+1.
 
+With `prep="device"` the per-frame host work disappears altogether: the meshes stay on the GPU in object space and
+every frame is one recorded scene script (a few matrices) + srt_scene_prep (transform, BVH build, flatten as CUDA
+kernels, bit-identical to the host result, prep.py) + render + download.  A frame the device path cannot take
+(non-finite coordinates) is redone through the host path.
+
 With several GPUs each rank runs this driver on its own frames (frame f -> rank f % world, multigpu.py).
 """
 from __future__ import annotations
@@ -22,7 +27,7 @@ from typing import Callable, Iterable, Iterator, Optional, Tuple
 
 import numpy as np
 
-from . import _abi, capi, host, scenes
+from . import _abi, capi, host, prep as _prep, scenes
 
 
 def prepare_frame(cfg: scenes.SceneConfig, angle_deg: float):
@@ -55,7 +60,7 @@ class _Lane:
 class SeriesRenderer:
     def __init__(self, ctx: capi.Context, cfg: scenes.SceneConfig, width: int, height: int, focal: float,
                  light_count: int, workers: Optional[int] = None, depth: Optional[int] = None, variant: int = 0,
-                 save_pattern: Optional[str] = None):
+                 save_pattern: Optional[str] = None, prep: str = "host"):
         """save_pattern: e.g. "images/generation/output{index}.bmp" — every frame is also written as the BMP the
         reference's drawImage saves (:488-494), on the worker pool, off the critical path."""
         self.ctx, self.cfg = ctx, cfg
@@ -65,6 +70,65 @@ class SeriesRenderer:
         self.depth = depth or 2 * self.workers
         self.lanes = [_Lane(ctx, width, height, False), _Lane(capi.Context(ctx.device), width, height, True)]
         host.set_asset_cache(True)
+        if prep not in ("host", "device"):
+            raise ValueError("prep must be 'host' or 'device'")
+        self.prep = prep
+        self.mesh_cache = _prep.MeshCache(ctx) if prep == "device" else None
+        self.host_fallbacks = 0
+
+    def _frames_device(self, angles, out):
+        """prep='device': record the scene script, prepare + render + download on the lane's stream."""
+        inflight = deque()                           # (index, lane, timing)
+        pool = ThreadPoolExecutor(max_workers=2) if self.save_pattern else None
+
+        def retire():
+            i, lane, tm = inflight.popleft()
+            t0 = time.perf_counter()
+            try:
+                lane.scene.prep_status()             # synchronises the lane
+            except capi.SrtError as e:
+                if e.code != _abi.SRT_ERR_UNSUPPORTED:
+                    raise
+                self.host_fallbacks += 1             # redo this frame through the host path
+                hs, desc, light = prepare_frame(self.cfg, angles[i])
+                lane.scene.destroy()
+                lane.scene = None
+                self._issue(lane, desc, light)
+                lane.ctx.sync()
+                hs.close()
+                lane.scene.destroy()
+                lane.scene = None
+            rgb = lane.frame.array
+            if pool is not None:
+                pool.submit(host.write_bmp, self.save_pattern.format(index=i, angle=angles[i]), rgb.copy())
+            if out is not None:
+                np.copyto(out, rgb)
+                rgb = out
+            tm["gpu_ms"] += 1e3 * (time.perf_counter() - t0)
+            return i, rgb, tm
+
+        try:
+            for i in range(len(angles)):
+                if len(inflight) == len(self.lanes):
+                    yield retire()
+                t0 = time.perf_counter()
+                lane = self.lanes[i % len(self.lanes)]
+                ds = _prep.DeviceScene(self.mesh_cache)
+                view = self.cfg.build(ds, angles[i])
+                light = scenes.light_view_space(ds, view) if view is not None else np.array(scenes.LIGHT_WORLD, np.float32)
+                lane.scene = ds.commit(scene=lane.scene, with_flat_lists=not self.cfg.use_bvh, ctx=lane.ctx)
+                ds.close()
+                p = _abi.default_params(self.width, self.height, self.focal, np.asarray(light, np.float32), self.light_count, self.cfg.use_bvh)
+                p.variant = self.variant
+                lane.ctx.render_raw(lane.scene, p, rgb=lane.frame.ptr)
+                inflight.append((i, lane, dict(wait_prep_ms=0.0, gpu_ms=0.0, issue_ms=1e3 * (time.perf_counter() - t0))))
+            while inflight:
+                yield retire()
+        finally:
+            for _i, lane, _tm in inflight:
+                lane.ctx.sync()
+            if pool is not None:
+                pool.shutdown(wait=True)
 
     def _issue(self, lane: _Lane, desc, light):
         """Upload + render + download of one frame on the lane's stream, asynchronous."""
@@ -82,6 +146,9 @@ class SeriesRenderer:
         """Yields (index, rgb[H][W][3] host array, timing) per frame, in order.  The yielded array is the lane's
         pinned frame (valid for the next two iterations), or `out` if given (valid until the next iteration)."""
         angles = list(angles)
+        if self.prep == "device":
+            yield from self._frames_device(angles, out)
+            return
         pool = ThreadPoolExecutor(max_workers=self.workers)
         pending = deque()
         inflight = deque()                           # (index, lane, host scene, timing)
@@ -130,3 +197,6 @@ class SeriesRenderer:
         for lane in self.lanes:
             lane.close()
         self.lanes = []
+        if self.mesh_cache is not None:
+            self.mesh_cache.close()
+            self.mesh_cache = None

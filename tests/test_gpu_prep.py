@@ -160,6 +160,23 @@ def test_device_prep_textured_multi_object(gpu_ctx, angle):
         cache.close()
 
 
+def test_series_driver_with_device_prep_equals_host_prep(gpu_ctx):
+    """The image-series driver end to end: frames prepared on the GPU are byte-identical to frames prepared on the host."""
+    from simple_raytracer_b200 import series
+    cfg = scenes.CONFIGS["C3"]
+    W, H, focal = scenes.scaled(cfg, 180)
+    angles = [0.0, 1.5, 91.5, 200.0, 358.5]
+    frames = {}
+    for mode in ("host", "device"):
+        sr = series.SeriesRenderer(gpu_ctx, cfg, W, H, focal, 4, workers=2, prep=mode)
+        frames[mode] = [rgb.copy() for (_i, rgb, _tm) in sr.frames(angles)]
+        assert sr.host_fallbacks == 0
+        sr.close()
+    for a, b in zip(frames["host"], frames["device"]):
+        assert np.array_equal(a, b)
+    assert len({f.tobytes() for f in frames["device"]}) == len(angles)      # and they are five different frames
+
+
 def write_obj(path, tris):
     with open(path, "w") as f:
         for t in tris.reshape(-1, 3):
@@ -189,6 +206,7 @@ def key_pattern(rng, n, kind):
 @pytest.mark.parametrize("kind,n", [
     ("random", 5000), ("few", 3000), ("ascending", 9001), ("descending_zeros", 12000), ("shared", 20000), ("zeros", 700),
     ("random", 17), ("random", 16), ("random", 9), ("random", 8), ("random", 3), ("random", 1), ("descending_zeros", 70000),
+    ("few", 70000), ("ascending", 50000), ("shared", 150000), ("random", 12289), ("random", 4097),
 ])
 def test_sort_permutation_on_key_patterns(gpu_ctx, tmp_path, kind, n):
     """One object whose root sorts on a prescribed key sequence; no transform, so keys are exactly these."""
