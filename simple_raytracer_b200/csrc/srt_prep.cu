@@ -166,9 +166,10 @@ struct Seg { uint32_t lo, hi, d; };
 struct SortSpace {                 // generic pointers: shared memory (subtree CTAs) or global scratch (large nodes)
     float* key; uint32_t* idx; uint32_t* posl; uint32_t* posr;
     Seg* q[2];
-    uint32_t* qcount;              // [2] in shared memory
+    uint32_t* qcount;              // [4] in shared memory: entries of q[0], q[1]; of those, segments of at least kBigSeg
     uint32_t* warp_cnt;            // [64] in shared memory (CTA-wide partition)
     uint32_t* sh_k;                // in shared memory
+    unsigned long long* dbg;       // optional: per round (segments << 40 | cycles), 64 slots (SRT_PREP_DEBUG)
 };
 
 __device__ __forceinline__ void swap_pair(const SortSpace& s, uint32_t x, uint32_t y) {
@@ -190,9 +191,15 @@ __device__ __forceinline__ void median_to_first(const SortSpace& s, uint32_t fir
     swap_pair(s, first, m);
 }
 
+__device__ __forceinline__ void push_segment(const SortSpace& s, int nq, uint32_t lo, uint32_t hi, uint32_t d) {
+    if (hi - lo <= 16) return;
+    const uint32_t e = atomicAdd(s.qcount + nq, 1u);
+    s.q[nq][e] = Seg{lo, hi, d};
+    if (hi - lo >= kBigSeg && d > 0) atomicAdd(s.qcount + 2 + nq, 1u);
+}
 __device__ __forceinline__ void push_children(const SortSpace& s, int nq, uint32_t first, uint32_t cut, uint32_t last, uint32_t d) {
-    if (last - cut > 16) { const uint32_t e = atomicAdd(s.qcount + nq, 1u); s.q[nq][e] = Seg{cut, last, d}; }
-    if (cut - first > 16) { const uint32_t e = atomicAdd(s.qcount + nq, 1u); s.q[nq][e] = Seg{first, cut, d}; }
+    push_segment(s, nq, cut, last, d);
+    push_segment(s, nq, first, cut, d);
 }
 
 // One Hoare partition (std::__unguarded_partition_pivot) by one warp.
@@ -203,20 +210,30 @@ __device__ void warp_partition(const SortSpace& s, Seg sg, int nq, unsigned lane
     const float p = s.key[first];
     const unsigned lt = (1u << lane) - 1u;
     uint32_t TL = 0, TR = 0;
-    for (uint32_t base = first + 1; base < last; base += 128) {          // four chunks per trip: the loads go out together
+    uint32_t base = first + 1;
+    for (; base + 128 <= last; base += 128) {                            // four chunks per trip: the loads go out together
         float k[4];
 #pragma unroll
-        for (int u = 0; u < 4; ++u) { const uint32_t x = base + 32u * u + lane; k[u] = x < last ? s.key[x] : 0.f; }
+        for (int u = 0; u < 4; ++u) k[u] = s.key[base + 32u * u + lane];
 #pragma unroll
         for (int u = 0; u < 4; ++u) {
             const uint32_t x = base + 32u * u + lane;
-            const bool valid = x < last;
-            const bool fl = valid && !(k[u] < p), fr = valid && !(p < k[u]);
+            const bool fl = !(k[u] < p), fr = !(p < k[u]);
             const unsigned bl = __ballot_sync(kFull, fl), br = __ballot_sync(kFull, fr);
             if (fl) s.posl[first + TL + __popc(bl & lt)] = x;
             if (fr) s.posr[first + TR + __popc(br & lt)] = x;
             TL += __popc(bl); TR += __popc(br);
         }
+    }
+    for (; base < last; base += 32) {
+        const uint32_t x = base + lane;
+        const bool valid = x < last;
+        const float k = valid ? s.key[x] : 0.f;
+        const bool fl = valid && !(k < p), fr = valid && !(p < k);
+        const unsigned bl = __ballot_sync(kFull, fl), br = __ballot_sync(kFull, fr);
+        if (fl) s.posl[first + TL + __popc(bl & lt)] = x;
+        if (fr) s.posr[first + TR + __popc(br & lt)] = x;
+        TL += __popc(bl); TR += __popc(br);
     }
     __syncwarp();
     const uint32_t mn = TL < TR ? TL : TR;
@@ -238,6 +255,74 @@ __device__ void warp_partition(const SortSpace& s, Seg sg, int nq, unsigned lane
         if (K >= 1) { const uint32_t r = s.posr[first + TR - K]; cut = r < cut ? r : cut; }
         push_children(s, nq, first, cut, last, sg.d - 1);
     }
+    __syncwarp();
+}
+
+// position of the n-th (n >= 1) set bit of mask counted from bit 0 / from bit 31; mask has at least n bits set
+__device__ __forceinline__ uint32_t nth_set_lo(uint32_t mask, uint32_t n) {
+    uint32_t pos = 0;
+#pragma unroll
+    for (int step = 16; step >= 1; step >>= 1)
+        if ((uint32_t)__popc(mask & ((1u << (pos + step)) - 1u)) < n) pos += step;
+    return pos;
+}
+__device__ __forceinline__ uint32_t nth_set_hi(uint32_t mask, uint32_t n) { return 31u - nth_set_lo(__brev(mask), n); }
+
+__device__ void serial_heapsort(const SortSpace& s, uint32_t f, long len);
+
+// The rest of the introsort loop of a segment of at most 32 elements, one element per lane, in registers: the same
+// median / pivot / pairing rules as warp_partition with ballots instead of position lists.
+__device__ void warp_small_sort(const SortSpace& s, Seg sg, unsigned lane) {
+    const uint32_t first = sg.lo, n = sg.hi - sg.lo;
+    float k = lane < n ? s.key[first + lane] : 0.f;
+    uint32_t id = lane < n ? s.idx[first + lane] : 0u;
+    const unsigned lt = (1u << lane) - 1u, gt = ~((2u << lane) - 1u);
+    uint32_t lo = 0, hi = n, d = sg.d;                     // at most one side of a cut is longer than 16: no stack needed
+    while (hi - lo > 16) {
+        if (d == 0) {                                       // depth limit: libstdc++'s heap sort, by one lane, in memory
+            if (lane >= lo && lane < hi) { s.key[first + lane] = k; s.idx[first + lane] = id; }
+            __syncwarp();
+            if (lane == 0) serial_heapsort(s, first + lo, (long)(hi - lo));
+            __syncwarp();
+            if (lane >= lo && lane < hi) { k = s.key[first + lane]; id = s.idx[first + lane]; }
+            break;
+        }
+        const uint32_t A = lo + 1, B = lo + (hi - lo) / 2, C = hi - 1;
+        const float ka = __shfl_sync(kFull, k, A), kb = __shfl_sync(kFull, k, B), kc = __shfl_sync(kFull, k, C);
+        uint32_t m;
+        if (ka < kb) { if (kb < kc) m = B; else if (ka < kc) m = C; else m = A; }
+        else if (ka < kc) m = A;
+        else if (kb < kc) m = C;
+        else m = B;
+        {
+            const float k_lo = __shfl_sync(kFull, k, lo), k_m = __shfl_sync(kFull, k, m);
+            const uint32_t i_lo = __shfl_sync(kFull, id, lo), i_m = __shfl_sync(kFull, id, m);
+            if (lane == lo) { k = k_m; id = i_m; } else if (lane == m) { k = k_lo; id = i_lo; }
+        }
+        const float p = __shfl_sync(kFull, k, lo);
+        const bool in = lane > lo && lane < hi;
+        const bool fl = in && !(k < p), fr = in && !(p < k);
+        const unsigned bl = __ballot_sync(kFull, fl), br = __ballot_sync(kFull, fr);
+        const uint32_t TL = __popc(bl), TR = __popc(br);
+        uint32_t partner = lane;
+        bool swl = false;
+        if (fl) {                                           // k-th from the left not less than the pivot <-> k-th from the right not greater
+            const uint32_t rk = __popc(bl & lt) + 1;
+            if (rk <= TR) { const uint32_t r = nth_set_hi(br, rk); if (lane < r) { partner = r; swl = true; } }
+        }
+        if (fr && !swl) {
+            const uint32_t rk = __popc(br & gt) + 1;
+            if (rk <= TL) { const uint32_t l = nth_set_lo(bl, rk); if (l < lane) partner = l; }
+        }
+        const uint32_t K = __popc(__ballot_sync(kFull, swl));
+        k = __shfl_sync(kFull, k, partner); id = __shfl_sync(kFull, id, partner);
+        uint32_t cut = kNoPos;
+        if (K < TL) cut = nth_set_lo(bl, K + 1);
+        if (K >= 1) { const uint32_t r = nth_set_hi(br, K); cut = r < cut ? r : cut; }
+        --d;
+        if (hi - cut > 16) lo = cut; else hi = cut;          // continue with the side that is still longer than 16 (if any)
+    }
+    if (lane < n) { s.key[first + lane] = k; s.idx[first + lane] = id; }
     __syncwarp();
 }
 
@@ -346,20 +431,29 @@ __device__ void serial_heapsort(const SortSpace& s, uint32_t f, long len) {
 // Runs the introsort loop of every segment queued in q[0] (all threads of the CTA).
 __device__ void sort_rounds(const SortSpace& s) {
     const unsigned tid = threadIdx.x, lane = tid & 31u, warp = tid >> 5;
-    int cur = 0;
+    int cur = 0, round = 0;
+    long long t_prev = s.dbg ? clock64() : 0;
     while (true) {
         __syncthreads();
         const uint32_t n = s.qcount[cur];
+        if (s.dbg && tid == 0 && round < 64) {
+            const long long t = clock64();
+            s.dbg[round] = ((unsigned long long)n << 40) | (unsigned long long)(t - t_prev);
+            t_prev = t;
+            ++round;
+        }
         if (n == 0) break;
-        if (tid == 0) s.qcount[cur ^ 1] = 0;
+        const uint32_t n_long = s.qcount[2 + cur];
+        if (tid == 0) { s.qcount[cur ^ 1] = 0; s.qcount[2 + (cur ^ 1)] = 0; }
         __syncthreads();
-        for (uint32_t e = 0; e < n; ++e) {                       // the long segments, one after the other, CTA-wide
+        for (uint32_t e = 0; n_long != 0 && e < n; ++e) {        // the long segments, one after the other, CTA-wide
             const Seg sg = s.q[cur][e];
             if (sg.hi - sg.lo >= kBigSeg && sg.d > 0) cta_partition(s, sg, cur ^ 1);
         }
         for (uint32_t e = warp; e < n; e += kBuildThreads / 32) {     // the others, one warp each
             const Seg sg = s.q[cur][e];
             if (sg.d == 0) { if (lane == 0) serial_heapsort(s, sg.lo, (long)(sg.hi - sg.lo)); }
+            else if (sg.hi - sg.lo <= 32) warp_small_sort(s, sg, lane);
             else if (sg.hi - sg.lo < kBigSeg) warp_partition(s, sg, cur ^ 1, lane);
         }
         cur ^= 1;
@@ -375,7 +469,7 @@ __device__ __forceinline__ uint32_t lg2_floor(uint32_t n) { return 31u - __clz(n
 // pairs and, in the CTA that finishes a segment last, cut it and set up its two sides for the next round.  Shorter
 // segments, and whatever is left after the planned number of rounds, are finished by one CTA each.
 struct SortShared {
-    uint32_t qcount[2];
+    uint32_t qcount[4];
     uint32_t warp_cnt[64];
     uint32_t sh_k;
 };
@@ -566,18 +660,20 @@ __global__ void __launch_bounds__(kBuildThreads, 1) wide_finish_kernel(const Pre
         const uint32_t len = f.hi - f.lo;
         SortSpace s;
         s.qcount = sh.qcount; s.warp_cnt = sh.warp_cnt; s.sh_k = &sh.sh_k;
+        s.dbg = (a.dbg && e < 8) ? a.dbg + 64 * e : nullptr;
+        if (s.dbg && threadIdx.x == 0) for (int i = 0; i < 64; ++i) s.dbg[i] = 0;
         const bool in_smem = len <= kWideSmall;
         if (in_smem) {
             s.key = wsp; s.idx = reinterpret_cast<uint32_t*>(wsp + kWideSmall);
             s.posl = reinterpret_cast<uint32_t*>(wsp + 2 * kWideSmall); s.posr = reinterpret_cast<uint32_t*>(wsp + 3 * kWideSmall);
             s.q[0] = q0; s.q[1] = q0 + kQ;
             for (uint32_t i = threadIdx.x; i < len; i += kBuildThreads) { s.key[i] = a.key[f.lo + i]; s.idx[i] = a.idx[f.lo + i]; }
-            if (threadIdx.x == 0) { sh.qcount[0] = 1; sh.qcount[1] = 0; s.q[0][0] = Seg{0u, len, f.d}; }
+            if (threadIdx.x == 0) { sh.qcount[0] = sh.qcount[1] = sh.qcount[2] = sh.qcount[3] = 0; push_segment(s, 0, 0u, len, f.d); }
         } else {
             s.key = a.key; s.idx = a.idx; s.posl = a.posl; s.posr = a.posr;
             s.q[0] = reinterpret_cast<Seg*>(a.segq) + f.lo / 8;
             s.q[1] = reinterpret_cast<Seg*>(a.segq) + a.segq_stride + f.lo / 8;
-            if (threadIdx.x == 0) { sh.qcount[0] = 1; sh.qcount[1] = 0; s.q[0][0] = Seg{f.lo, f.hi, f.d}; }
+            if (threadIdx.x == 0) { sh.qcount[0] = sh.qcount[1] = sh.qcount[2] = sh.qcount[3] = 0; push_segment(s, 0, f.lo, f.hi, f.d); }
         }
         sort_rounds(s);
         if (in_smem)
@@ -661,7 +757,7 @@ __device__ __forceinline__ int find_node(const Level& L, uint32_t m, uint32_t li
 
 struct BuildShared {
     Level lev[2];
-    uint32_t qcount[2];
+    uint32_t qcount[4];
     uint32_t warp_cnt[64];
     uint32_t sh_k;
     uint32_t next_m;
@@ -732,7 +828,7 @@ __global__ void __launch_bounds__(kBuildThreads, 1) build_kernel(const PrepArgs 
         s.q[0] = reinterpret_cast<Seg*>(a.segq) + gbase / 8;
         s.q[1] = reinterpret_cast<Seg*>(a.segq) + a.segq_stride + gbase / 8;
     }
-    s.qcount = sh.qcount; s.warp_cnt = sh.warp_cnt; s.sh_k = &sh.sh_k;
+    s.qcount = sh.qcount; s.warp_cnt = sh.warp_cnt; s.sh_k = &sh.sh_k; s.dbg = nullptr;
 
     int cl = 0;
     uint32_t m = 1;
@@ -748,7 +844,7 @@ __global__ void __launch_bounds__(kBuildThreads, 1) build_kernel(const PrepArgs 
             const float sx = fabsf(__fsub_rn(b1.x, b0.x)), sy = fabsf(__fsub_rn(b1.y, b0.y)), sz = fabsf(__fsub_rn(b1.z, b0.z));
             L.axis[j] = (sx > sy && sx > sz) ? 0u : ((sy > sx && sy > sz) ? 1u : 2u);
         }
-        if (tid == 0) { sh.qcount[0] = 0; sh.qcount[1] = 0; }
+        if (tid == 0) { sh.qcount[0] = 0; sh.qcount[1] = 0; sh.qcount[2] = 0; sh.qcount[3] = 0; }
         __syncthreads();
         // keys: pointOne.<axis> of the node's triangles in their current order (:241-247)
         for (uint32_t li = tid; li < it.count; li += kBuildThreads) {
@@ -762,7 +858,7 @@ __global__ void __launch_bounds__(kBuildThreads, 1) build_kernel(const PrepArgs 
         }
         for (uint32_t j = tid; j < m; j += kBuildThreads) {
             const uint32_t cnt = L.count[j];
-            if (cnt > 16) { const uint32_t e = atomicAdd(sh.qcount, 1u); s.q[0][e] = Seg{L.start[j], L.start[j] + cnt, 2u * lg2_floor(cnt)}; }
+            if (cnt > 16) push_segment(s, 0, L.start[j], L.start[j] + cnt, 2u * lg2_floor(cnt));
         }
         sort_rounds(s);            // starts and ends with a CTA barrier
         // __final_insertion_sort: stable, nothing leaves its (at most 16 long) segment

@@ -47,6 +47,7 @@ struct PrepArgs {
     uint32_t* segq;            // [2][N/8 + n][3] segment queues of those nodes
     uint32_t segq_stride;      // entries per queue
     unsigned long long* rootacc;   // [n_objects][6] packed (value code, position) minima of the object boxes
+    unsigned long long* dbg;       // optional timing slots of the finishing CTAs (SRT_PREP_DEBUG), else null
 };
 
 // ---- large nodes: the introsort loop of a node spread over many CTAs (one launch per step of a round) ----

@@ -4,6 +4,7 @@
 #include <cuda_runtime.h>
 
 #include <cfloat>
+#include <cstdio>
 #include <cstdlib>
 #include <cstring>
 #include <vector>
@@ -314,6 +315,8 @@ int srt_scene_prep(srt_context* c, const srt_prep_object* objs, uint32_t n_objec
     a.xpts = (float4*)ps.xpts.p; a.lite = (float*)ps.lite.p; a.order = (uint32_t*)ps.order.p;
     a.key = (float*)ps.key.p; a.idx = (uint32_t*)ps.idx.p; a.posl = (uint32_t*)ps.posl.p; a.posr = (uint32_t*)ps.posr.p;
     a.segq = (uint32_t*)ps.segq.p; a.segq_stride = (uint32_t)segq_stride;
+    static const bool debug_timing = std::getenv("SRT_PREP_DEBUG") != nullptr;
+    if (debug_timing) { if ((rc = ps.misc.reserve(8 * 64 * 8))) return bail(rc); a.dbg = (unsigned long long*)ps.misc.p; }
 
     // workspace of the many-CTA path for the large nodes
     size_t max_items = 1, n_big_total = 0;
@@ -355,8 +358,12 @@ int srt_scene_prep(srt_context* c, const srt_prep_object* objs, uint32_t n_objec
         size_t tiles = 8, total = 0;
         for (const srtp::WorkItem& it : big[d]) { if (it.count > maxc) maxc = it.count; total += it.count; tiles += it.count / srtp::kWideTile + 1; }
         tiles += 2 * (total / srtp::kWideSmall + big[d].size());
-        uint32_t rounds = 0;                                       // planned global rounds: until the segments fit one CTA, plus one
-        if (maxc > srtp::kWideSmall) { rounds = 1; for (uint64_t v = srtp::kWideSmall; v < maxc; v *= 2) ++rounds; }
+        // planned many-CTA rounds: until the segments fit one CTA if every pivot split evenly, plus three (a median of
+        // three rarely does; a round with nothing left to do costs three empty launches, a segment left too long costs
+        // a one-CTA sort in global memory)
+        uint32_t rounds = 0;
+        static const int slack = std::getenv("SRT_PREP_SLACK") ? std::atoi(std::getenv("SRT_PREP_SLACK")) : 3;
+        if (maxc > srtp::kWideSmall) { rounds = (uint32_t)slack; for (uint64_t v = srtp::kWideSmall; v < maxc; v *= 2) ++rounds; }
         if (rounds > (uint32_t)srtp::kWideMaxRounds - 1) rounds = srtp::kWideMaxRounds - 1;
         if (tiles > w.max_tiles) tiles = w.max_tiles;
         e = srtp::launch_wide_level(a, w, (const srtp::WorkItem*)(dblob + at_big[d]), (uint32_t)big[d].size(), maxc, rounds,
@@ -386,6 +393,15 @@ int srt_scene_prep_status(srt_context* c, srt_scene* s) {
     if (!s->prep || !s->prep->status_host) return fail(SRT_ERR_INVALID_ARG, "scene was not prepared with srt_scene_prep");
     CU(cudaSetDevice(c->device));
     CU(cudaStreamSynchronize(c->stream));
+    if (std::getenv("SRT_PREP_DEBUG") && s->prep->misc.p) {       // last level's finishing CTAs: per round, segments and cycles
+        unsigned long long h[8 * 64];
+        cudaMemcpy(h, s->prep->misc.p, sizeof h, cudaMemcpyDeviceToHost);
+        for (int e = 0; e < 8; ++e) {
+            std::fprintf(stderr, "finish cta %d:", e);
+            for (int r = 0; r < 64 && h[64 * e + r]; ++r) std::fprintf(stderr, " %llu/%llu", h[64 * e + r] >> 40, h[64 * e + r] & ((1ull << 40) - 1));
+            std::fprintf(stderr, "\n");
+        }
+    }
     if (*s->prep->status_host & 2u)
         return fail(SRT_ERR_CUDA, "srt_scene_prep: internal work-list overflow (please report)");
     if (*s->prep->status_host & 1u)
