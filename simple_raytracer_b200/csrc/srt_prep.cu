@@ -24,6 +24,7 @@
 //     __make_heap / __sort_heap sequence (rare: adversarial key patterns only).
 // The comparison outcomes are the host's (same fp32 keys), hence the same permutation, the same tree.
 #include <cfloat>
+#include <type_traits>
 
 #include "srt_prep.cuh"
 
@@ -34,7 +35,6 @@ constexpr unsigned kFull = 0xFFFFFFFFu;
 constexpr uint32_t kNoPos = 0xFFFFFFFFu;
 constexpr int kNLMax = 512;           // nodes of one level inside a subtree CTA (kSubtreeMax / 9 < 512)
 constexpr int kSmemQueue = 256;       // segments longer than 16 inside kSubtreeMax elements: < 4096 / 17
-constexpr uint32_t kBigSeg = 2048;    // segments at least this long are partitioned by the whole CTA
 static_assert(2 * kNLMax <= kBuildThreads, "one thread per child in the level compaction");
 
 // ---- monotone code of a float for (value, position) minima; +0 and -0 share one code (they compare equal) ----
@@ -163,26 +163,70 @@ __global__ void roots_kernel(const PrepArgs a) {
 // std::sort emulation
 struct Seg { uint32_t lo, hi, d; };
 
-struct SortSpace {                 // generic pointers: shared memory (subtree CTAs) or global scratch (large nodes)
-    float* key; uint32_t* idx; uint32_t* posl; uint32_t* posr;
-    Seg* q[2];
-    uint32_t* qcount;              // [4] in shared memory: entries of q[0], q[1]; of those, segments of at least kBigSeg
+// Where the sort workspace lives.  Shared memory is addressed through the shared window (ld.shared / st.shared):
+// the sort is a chain of dependent small accesses, and a generic load of shared memory costs several times an LDS.
+__device__ __forceinline__ float lds_f(uint32_t a) { float v; asm volatile("ld.shared.f32 %0, [%1];" : "=f"(v) : "r"(a)); return v; }
+__device__ __forceinline__ uint32_t lds_u(uint32_t a) { uint32_t v; asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(a)); return v; }
+__device__ __forceinline__ void sts_f(uint32_t a, float v) { asm volatile("st.shared.f32 [%0], %1;" ::"r"(a), "f"(v) : "memory"); }
+__device__ __forceinline__ void sts_u(uint32_t a, uint32_t v) { asm volatile("st.shared.u32 [%0], %1;" ::"r"(a), "r"(v) : "memory"); }
+
+struct SharedMem {                 // byte addresses in the shared window
+    static constexpr uint32_t kLong = 2048;        // CTA-wide partitions run one after the other: measured slower at 768
+    uint32_t key_, idx_, posl_, posr_, q_[2];
+    __device__ __forceinline__ float key(uint32_t i) const { return lds_f(key_ + 4u * i); }
+    __device__ __forceinline__ uint32_t idx(uint32_t i) const { return lds_u(idx_ + 4u * i); }
+    __device__ __forceinline__ uint32_t posl(uint32_t i) const { return lds_u(posl_ + 4u * i); }
+    __device__ __forceinline__ uint32_t posr(uint32_t i) const { return lds_u(posr_ + 4u * i); }
+    __device__ __forceinline__ void set_key(uint32_t i, float v) const { sts_f(key_ + 4u * i, v); }
+    __device__ __forceinline__ void set_idx(uint32_t i, uint32_t v) const { sts_u(idx_ + 4u * i, v); }
+    __device__ __forceinline__ void set_posl(uint32_t i, uint32_t v) const { sts_u(posl_ + 4u * i, v); }
+    __device__ __forceinline__ void set_posr(uint32_t i, uint32_t v) const { sts_u(posr_ + 4u * i, v); }
+    __device__ __forceinline__ Seg seg(int nq, uint32_t e) const {
+        const uint32_t a = q_[nq] + 12u * e;
+        return Seg{lds_u(a), lds_u(a + 4), lds_u(a + 8)};
+    }
+    __device__ __forceinline__ void set_seg(int nq, uint32_t e, Seg v) const {
+        const uint32_t a = q_[nq] + 12u * e;
+        sts_u(a, v.lo); sts_u(a + 4, v.hi); sts_u(a + 8, v.d);
+    }
+};
+struct GlobalMem {                 // global scratch (nodes too large for shared memory)
+    static constexpr uint32_t kLong = 2048;
+    float* key_; uint32_t* idx_; uint32_t* posl_; uint32_t* posr_; Seg* q_[2];
+    __device__ __forceinline__ float key(uint32_t i) const { return key_[i]; }
+    __device__ __forceinline__ uint32_t idx(uint32_t i) const { return idx_[i]; }
+    __device__ __forceinline__ uint32_t posl(uint32_t i) const { return posl_[i]; }
+    __device__ __forceinline__ uint32_t posr(uint32_t i) const { return posr_[i]; }
+    __device__ __forceinline__ void set_key(uint32_t i, float v) const { key_[i] = v; }
+    __device__ __forceinline__ void set_idx(uint32_t i, uint32_t v) const { idx_[i] = v; }
+    __device__ __forceinline__ void set_posl(uint32_t i, uint32_t v) const { posl_[i] = v; }
+    __device__ __forceinline__ void set_posr(uint32_t i, uint32_t v) const { posr_[i] = v; }
+    __device__ __forceinline__ Seg seg(int nq, uint32_t e) const { return q_[nq][e]; }
+    __device__ __forceinline__ void set_seg(int nq, uint32_t e, Seg v) const { q_[nq][e] = v; }
+};
+
+template <class M>
+struct SortSpace {
+    M m;
+    uint32_t* qcount;              // [4] in shared memory: entries of q[0], q[1]; of those, segments of at least M::kLong
     uint32_t* warp_cnt;            // [64] in shared memory (CTA-wide partition)
     uint32_t* sh_k;                // in shared memory
     unsigned long long* dbg;       // optional: per round (segments << 40 | cycles), 64 slots (SRT_PREP_DEBUG)
 };
 
-__device__ __forceinline__ void swap_pair(const SortSpace& s, uint32_t x, uint32_t y) {
-    const float kx = s.key[x], ky = s.key[y];
-    const uint32_t ix = s.idx[x], iy = s.idx[y];
-    s.key[x] = ky; s.key[y] = kx;
-    s.idx[x] = iy; s.idx[y] = ix;
+template <class M>
+__device__ __forceinline__ void swap_pair(const SortSpace<M>& s, uint32_t x, uint32_t y) {
+    const float kx = s.m.key(x), ky = s.m.key(y);
+    const uint32_t ix = s.m.idx(x), iy = s.m.idx(y);
+    s.m.set_key(x, ky); s.m.set_key(y, kx);
+    s.m.set_idx(x, iy); s.m.set_idx(y, ix);
 }
 
 // std::__move_median_to_first(first, first + 1, mid, last - 1) — bits/stl_algo.h
-__device__ __forceinline__ void median_to_first(const SortSpace& s, uint32_t first, uint32_t last) {
+template <class M>
+__device__ __forceinline__ void median_to_first(const SortSpace<M>& s, uint32_t first, uint32_t last) {
     const uint32_t A = first + 1, B = first + (last - first) / 2, C = last - 1;
-    const float ka = s.key[A], kb = s.key[B], kc = s.key[C];
+    const float ka = s.m.key(A), kb = s.m.key(B), kc = s.m.key(C);
     uint32_t m;
     if (ka < kb) { if (kb < kc) m = B; else if (ka < kc) m = C; else m = A; }
     else if (ka < kc) m = A;
@@ -191,48 +235,51 @@ __device__ __forceinline__ void median_to_first(const SortSpace& s, uint32_t fir
     swap_pair(s, first, m);
 }
 
-__device__ __forceinline__ void push_segment(const SortSpace& s, int nq, uint32_t lo, uint32_t hi, uint32_t d) {
+template <class M>
+__device__ __forceinline__ void push_segment(const SortSpace<M>& s, int nq, uint32_t lo, uint32_t hi, uint32_t d) {
     if (hi - lo <= 16) return;
     const uint32_t e = atomicAdd(s.qcount + nq, 1u);
-    s.q[nq][e] = Seg{lo, hi, d};
-    if (hi - lo >= kBigSeg && d > 0) atomicAdd(s.qcount + 2 + nq, 1u);
+    s.m.set_seg(nq, e, Seg{lo, hi, d});
+    if (hi - lo >= M::kLong && d > 0) atomicAdd(s.qcount + 2 + nq, 1u);
 }
-__device__ __forceinline__ void push_children(const SortSpace& s, int nq, uint32_t first, uint32_t cut, uint32_t last, uint32_t d) {
+template <class M>
+__device__ __forceinline__ void push_children(const SortSpace<M>& s, int nq, uint32_t first, uint32_t cut, uint32_t last, uint32_t d) {
     push_segment(s, nq, cut, last, d);
     push_segment(s, nq, first, cut, d);
 }
 
 // One Hoare partition (std::__unguarded_partition_pivot) by one warp.
-__device__ void warp_partition(const SortSpace& s, Seg sg, int nq, unsigned lane) {
+template <class M>
+__device__ void warp_partition(const SortSpace<M>& s, Seg sg, int nq, unsigned lane) {
     const uint32_t first = sg.lo, last = sg.hi;
     if (lane == 0) median_to_first(s, first, last);
     __syncwarp();
-    const float p = s.key[first];
+    const float p = s.m.key(first);
     const unsigned lt = (1u << lane) - 1u;
     uint32_t TL = 0, TR = 0;
     uint32_t base = first + 1;
     for (; base + 128 <= last; base += 128) {                            // four chunks per trip: the loads go out together
         float k[4];
 #pragma unroll
-        for (int u = 0; u < 4; ++u) k[u] = s.key[base + 32u * u + lane];
+        for (int u = 0; u < 4; ++u) k[u] = s.m.key(base + 32u * u + lane);
 #pragma unroll
         for (int u = 0; u < 4; ++u) {
             const uint32_t x = base + 32u * u + lane;
             const bool fl = !(k[u] < p), fr = !(p < k[u]);
             const unsigned bl = __ballot_sync(kFull, fl), br = __ballot_sync(kFull, fr);
-            if (fl) s.posl[first + TL + __popc(bl & lt)] = x;
-            if (fr) s.posr[first + TR + __popc(br & lt)] = x;
+            if (fl) s.m.set_posl(first + TL + __popc(bl & lt), x);
+            if (fr) s.m.set_posr(first + TR + __popc(br & lt), x);
             TL += __popc(bl); TR += __popc(br);
         }
     }
     for (; base < last; base += 32) {
         const uint32_t x = base + lane;
         const bool valid = x < last;
-        const float k = valid ? s.key[x] : 0.f;
+        const float k = valid ? s.m.key(x) : 0.f;
         const bool fl = valid && !(k < p), fr = valid && !(p < k);
         const unsigned bl = __ballot_sync(kFull, fl), br = __ballot_sync(kFull, fr);
-        if (fl) s.posl[first + TL + __popc(bl & lt)] = x;
-        if (fr) s.posr[first + TR + __popc(br & lt)] = x;
+        if (fl) s.m.set_posl(first + TL + __popc(bl & lt), x);
+        if (fr) s.m.set_posr(first + TR + __popc(br & lt), x);
         TL += __popc(bl); TR += __popc(br);
     }
     __syncwarp();
@@ -242,7 +289,7 @@ __device__ void warp_partition(const SortSpace& s, Seg sg, int nq, unsigned lane
         const uint32_t k = kb + lane;
         bool sw = false;
         uint32_t l = 0, r = 0;
-        if (k < mn) { l = s.posl[first + k]; r = s.posr[first + TR - 1 - k]; sw = l < r; }
+        if (k < mn) { l = s.m.posl(first + k); r = s.m.posr(first + TR - 1 - k); sw = l < r; }
         const unsigned b = __ballot_sync(kFull, sw);
         if (sw) swap_pair(s, l, r);
         K += __popc(b);
@@ -251,8 +298,8 @@ __device__ void warp_partition(const SortSpace& s, Seg sg, int nq, unsigned lane
     __syncwarp();
     if (lane == 0) {
         uint32_t cut = kNoPos;
-        if (K < TL) cut = s.posl[first + K];
-        if (K >= 1) { const uint32_t r = s.posr[first + TR - K]; cut = r < cut ? r : cut; }
+        if (K < TL) cut = s.m.posl(first + K);
+        if (K >= 1) { const uint32_t r = s.m.posr(first + TR - K); cut = r < cut ? r : cut; }
         push_children(s, nq, first, cut, last, sg.d - 1);
     }
     __syncwarp();
@@ -268,23 +315,25 @@ __device__ __forceinline__ uint32_t nth_set_lo(uint32_t mask, uint32_t n) {
 }
 __device__ __forceinline__ uint32_t nth_set_hi(uint32_t mask, uint32_t n) { return 31u - nth_set_lo(__brev(mask), n); }
 
-__device__ void serial_heapsort(const SortSpace& s, uint32_t f, long len);
+template <class M>
+__device__ void serial_heapsort(const SortSpace<M>& s, uint32_t f, long len);
 
 // The rest of the introsort loop of a segment of at most 32 elements, one element per lane, in registers: the same
 // median / pivot / pairing rules as warp_partition with ballots instead of position lists.
-__device__ void warp_small_sort(const SortSpace& s, Seg sg, unsigned lane) {
+template <class M>
+__device__ void warp_small_sort(const SortSpace<M>& s, Seg sg, unsigned lane) {
     const uint32_t first = sg.lo, n = sg.hi - sg.lo;
-    float k = lane < n ? s.key[first + lane] : 0.f;
-    uint32_t id = lane < n ? s.idx[first + lane] : 0u;
+    float k = lane < n ? s.m.key(first + lane) : 0.f;
+    uint32_t id = lane < n ? s.m.idx(first + lane) : 0u;
     const unsigned lt = (1u << lane) - 1u, gt = ~((2u << lane) - 1u);
     uint32_t lo = 0, hi = n, d = sg.d;                     // at most one side of a cut is longer than 16: no stack needed
     while (hi - lo > 16) {
         if (d == 0) {                                       // depth limit: libstdc++'s heap sort, by one lane, in memory
-            if (lane >= lo && lane < hi) { s.key[first + lane] = k; s.idx[first + lane] = id; }
+            if (lane >= lo && lane < hi) { s.m.set_key(first + lane, k); s.m.set_idx(first + lane, id); }
             __syncwarp();
             if (lane == 0) serial_heapsort(s, first + lo, (long)(hi - lo));
             __syncwarp();
-            if (lane >= lo && lane < hi) { k = s.key[first + lane]; id = s.idx[first + lane]; }
+            if (lane >= lo && lane < hi) { k = s.m.key(first + lane); id = s.m.idx(first + lane); }
             break;
         }
         const uint32_t A = lo + 1, B = lo + (hi - lo) / 2, C = hi - 1;
@@ -322,24 +371,25 @@ __device__ void warp_small_sort(const SortSpace& s, Seg sg, unsigned lane) {
         --d;
         if (hi - cut > 16) lo = cut; else hi = cut;          // continue with the side that is still longer than 16 (if any)
     }
-    if (lane < n) { s.key[first + lane] = k; s.idx[first + lane] = id; }
+    if (lane < n) { s.m.set_key(first + lane, k); s.m.set_idx(first + lane, id); }
     __syncwarp();
 }
 
 // The same partition by the whole CTA (kBuildThreads threads; every thread calls it with the same segment).
-__device__ void cta_partition(const SortSpace& s, Seg sg, int nq) {
+template <class M>
+__device__ void cta_partition(const SortSpace<M>& s, Seg sg, int nq) {
     const unsigned tid = threadIdx.x, lane = tid & 31u, warp = tid >> 5;
     const uint32_t first = sg.lo, last = sg.hi;
     if (tid == 0) { median_to_first(s, first, last); *s.sh_k = 0; }
     __syncthreads();
-    const float p = s.key[first];
+    const float p = s.m.key(first);
     const uint32_t lo = first + 1, len = last - lo;
     const uint32_t per = ((len + 31u) / 32u + 31u) & ~31u;          // slice per warp, a multiple of 32
     const uint32_t s0 = lo + warp * per < last ? lo + warp * per : last;
     const uint32_t s1 = s0 + per < last ? s0 + per : last;
     uint32_t tl = 0, tr = 0;
     for (uint32_t x = s0 + lane; x < s1; x += 32) {
-        const float k = s.key[x];
+        const float k = s.m.key(x);
         tl += !(k < p); tr += !(p < k);
     }
     tl = __reduce_add_sync(kFull, tl); tr = __reduce_add_sync(kFull, tr);
@@ -352,25 +402,25 @@ __device__ void cta_partition(const SortSpace& s, Seg sg, int nq) {
     for (uint32_t base = s0; base < s1; base += 128) {
         float k[4];
 #pragma unroll
-        for (int u = 0; u < 4; ++u) { const uint32_t x = base + 32u * u + lane; k[u] = x < s1 ? s.key[x] : 0.f; }
+        for (int u = 0; u < 4; ++u) { const uint32_t x = base + 32u * u + lane; k[u] = x < s1 ? s.m.key(x) : 0.f; }
 #pragma unroll
         for (int u = 0; u < 4; ++u) {
             const uint32_t x = base + 32u * u + lane;
             const bool valid = x < s1;
             const bool fl = valid && !(k[u] < p), fr = valid && !(p < k[u]);
             const unsigned bl = __ballot_sync(kFull, fl), br = __ballot_sync(kFull, fr);
-            if (fl) s.posl[first + bl0 + __popc(bl & lt)] = x;
-            if (fr) s.posr[first + br0 + __popc(br & lt)] = x;
+            if (fl) s.m.set_posl(first + bl0 + __popc(bl & lt), x);
+            if (fr) s.m.set_posr(first + br0 + __popc(br & lt), x);
             bl0 += __popc(bl); br0 += __popc(br);
         }
     }
     __syncthreads();
     const uint32_t mn = TL < TR ? TL : TR;
     for (uint32_t k = tid; k < mn; k += kBuildThreads) {
-        const uint32_t l = s.posl[first + k], r = s.posr[first + TR - 1 - k];
+        const uint32_t l = s.m.posl(first + k), r = s.m.posr(first + TR - 1 - k);
         if (l < r) {
             swap_pair(s, l, r);
-            const bool last_pair = (k + 1 == mn) || !(s.posl[first + k + 1] < s.posr[first + TR - 2 - k]);
+            const bool last_pair = (k + 1 == mn) || !(s.m.posl(first + k + 1) < s.m.posr(first + TR - 2 - k));
             if (last_pair) *s.sh_k = k + 1;
         }
     }
@@ -378,43 +428,45 @@ __device__ void cta_partition(const SortSpace& s, Seg sg, int nq) {
     if (tid == 0) {
         const uint32_t K = *s.sh_k;
         uint32_t cut = kNoPos;
-        if (K < TL) cut = s.posl[first + K];
-        if (K >= 1) { const uint32_t r = s.posr[first + TR - K]; cut = r < cut ? r : cut; }
+        if (K < TL) cut = s.m.posl(first + K);
+        if (K >= 1) { const uint32_t r = s.m.posr(first + TR - K); cut = r < cut ? r : cut; }
         push_children(s, nq, first, cut, last, sg.d - 1);
     }
     __syncthreads();
 }
 
 // std::__adjust_heap + std::__push_heap (bits/stl_heap.h) on key/idx pairs starting at `f`.
-__device__ void heap_adjust(const SortSpace& s, uint32_t f, long hole, long len, float vk, uint32_t vi) {
+template <class M>
+__device__ void heap_adjust(const SortSpace<M>& s, uint32_t f, long hole, long len, float vk, uint32_t vi) {
     const long top = hole;
     long sc = hole;
     while (sc < (len - 1) / 2) {
         sc = 2 * (sc + 1);
-        if (s.key[f + sc] < s.key[f + sc - 1]) sc--;
-        s.key[f + hole] = s.key[f + sc]; s.idx[f + hole] = s.idx[f + sc];
+        if (s.m.key(f + sc) < s.m.key(f + sc - 1)) sc--;
+        s.m.set_key(f + hole, s.m.key(f + sc)); s.m.set_idx(f + hole, s.m.idx(f + sc));
         hole = sc;
     }
     if ((len & 1) == 0 && sc == (len - 2) / 2) {
         sc = 2 * (sc + 1);
-        s.key[f + hole] = s.key[f + sc - 1]; s.idx[f + hole] = s.idx[f + sc - 1];
+        s.m.set_key(f + hole, s.m.key(f + sc - 1)); s.m.set_idx(f + hole, s.m.idx(f + sc - 1));
         hole = sc - 1;
     }
     long parent = (hole - 1) / 2;
-    while (hole > top && s.key[f + parent] < vk) {
-        s.key[f + hole] = s.key[f + parent]; s.idx[f + hole] = s.idx[f + parent];
+    while (hole > top && s.m.key(f + parent) < vk) {
+        s.m.set_key(f + hole, s.m.key(f + parent)); s.m.set_idx(f + hole, s.m.idx(f + parent));
         hole = parent;
         parent = (hole - 1) / 2;
     }
-    s.key[f + hole] = vk; s.idx[f + hole] = vi;
+    s.m.set_key(f + hole, vk); s.m.set_idx(f + hole, vi);
 }
 
 // std::__partial_sort(first, last, last) = __make_heap + __sort_heap: the depth-limit fallback of __introsort_loop.
-__device__ void serial_heapsort(const SortSpace& s, uint32_t f, long len) {
+template <class M>
+__device__ void serial_heapsort(const SortSpace<M>& s, uint32_t f, long len) {
     if (len >= 2) {
         long parent = (len - 2) / 2;
         while (true) {
-            heap_adjust(s, f, parent, len, s.key[f + parent], s.idx[f + parent]);
+            heap_adjust(s, f, parent, len, s.m.key(f + parent), s.m.idx(f + parent));
             if (parent == 0) break;
             parent--;
         }
@@ -422,14 +474,15 @@ __device__ void serial_heapsort(const SortSpace& s, uint32_t f, long len) {
     long last = len;
     while (last > 1) {
         --last;
-        const float vk = s.key[f + last]; const uint32_t vi = s.idx[f + last];
-        s.key[f + last] = s.key[f]; s.idx[f + last] = s.idx[f];
+        const float vk = s.m.key(f + last); const uint32_t vi = s.m.idx(f + last);
+        s.m.set_key(f + last, s.m.key(f)); s.m.set_idx(f + last, s.m.idx(f));
         heap_adjust(s, f, 0, last, vk, vi);
     }
 }
 
 // Runs the introsort loop of every segment queued in q[0] (all threads of the CTA).
-__device__ void sort_rounds(const SortSpace& s) {
+template <class M>
+__device__ void sort_rounds(const SortSpace<M>& s) {
     const unsigned tid = threadIdx.x, lane = tid & 31u, warp = tid >> 5;
     int cur = 0, round = 0;
     long long t_prev = s.dbg ? clock64() : 0;
@@ -447,14 +500,14 @@ __device__ void sort_rounds(const SortSpace& s) {
         if (tid == 0) { s.qcount[cur ^ 1] = 0; s.qcount[2 + (cur ^ 1)] = 0; }
         __syncthreads();
         for (uint32_t e = 0; n_long != 0 && e < n; ++e) {        // the long segments, one after the other, CTA-wide
-            const Seg sg = s.q[cur][e];
-            if (sg.hi - sg.lo >= kBigSeg && sg.d > 0) cta_partition(s, sg, cur ^ 1);
+            const Seg sg = s.m.seg(cur, e);
+            if (sg.hi - sg.lo >= M::kLong && sg.d > 0) cta_partition(s, sg, cur ^ 1);
         }
         for (uint32_t e = warp; e < n; e += kBuildThreads / 32) {     // the others, one warp each
-            const Seg sg = s.q[cur][e];
+            const Seg sg = s.m.seg(cur, e);
             if (sg.d == 0) { if (lane == 0) serial_heapsort(s, sg.lo, (long)(sg.hi - sg.lo)); }
             else if (sg.hi - sg.lo <= 32) warp_small_sort(s, sg, lane);
-            else if (sg.hi - sg.lo < kBigSeg) warp_partition(s, sg, cur ^ 1, lane);
+            else if (sg.hi - sg.lo < M::kLong) warp_partition(s, sg, cur ^ 1, lane);
         }
         cur ^= 1;
     }
@@ -655,29 +708,31 @@ __global__ void __launch_bounds__(kBuildThreads, 1) wide_finish_kernel(const Pre
     constexpr uint32_t kQ = kWideSmall / 16;
     float* wsp = reinterpret_cast<float*>(smem_raw + 512 + 2 * kQ * sizeof(Seg));
     const uint32_t n = *w.fin_count < w.max_fin ? *w.fin_count : w.max_fin;
+    const uint32_t sh_base = (uint32_t)__cvta_generic_to_shared(wsp);
     for (uint32_t e = blockIdx.x; e < n; e += gridDim.x) {
         const WideSmall f = w.fin[e];
         const uint32_t len = f.hi - f.lo;
-        SortSpace s;
-        s.qcount = sh.qcount; s.warp_cnt = sh.warp_cnt; s.sh_k = &sh.sh_k;
-        s.dbg = (a.dbg && e < 8) ? a.dbg + 64 * e : nullptr;
-        if (s.dbg && threadIdx.x == 0) for (int i = 0; i < 64; ++i) s.dbg[i] = 0;
-        const bool in_smem = len <= kWideSmall;
-        if (in_smem) {
-            s.key = wsp; s.idx = reinterpret_cast<uint32_t*>(wsp + kWideSmall);
-            s.posl = reinterpret_cast<uint32_t*>(wsp + 2 * kWideSmall); s.posr = reinterpret_cast<uint32_t*>(wsp + 3 * kWideSmall);
-            s.q[0] = q0; s.q[1] = q0 + kQ;
-            for (uint32_t i = threadIdx.x; i < len; i += kBuildThreads) { s.key[i] = a.key[f.lo + i]; s.idx[i] = a.idx[f.lo + i]; }
-            if (threadIdx.x == 0) { sh.qcount[0] = sh.qcount[1] = sh.qcount[2] = sh.qcount[3] = 0; push_segment(s, 0, 0u, len, f.d); }
+        unsigned long long* dbg = (a.dbg && e < 8) ? a.dbg + 64 * e : nullptr;
+        if (dbg && threadIdx.x == 0) for (int i = 0; i < 64; ++i) dbg[i] = 0;
+        if (threadIdx.x == 0) sh.qcount[0] = sh.qcount[1] = sh.qcount[2] = sh.qcount[3] = 0;
+        if (len <= kWideSmall) {
+            SortSpace<SharedMem> s;
+            s.qcount = sh.qcount; s.warp_cnt = sh.warp_cnt; s.sh_k = &sh.sh_k; s.dbg = dbg;
+            s.m.key_ = sh_base; s.m.idx_ = sh_base + 4u * kWideSmall; s.m.posl_ = sh_base + 8u * kWideSmall; s.m.posr_ = sh_base + 12u * kWideSmall;
+            s.m.q_[0] = (uint32_t)__cvta_generic_to_shared(q0); s.m.q_[1] = s.m.q_[0] + 12u * kQ;
+            for (uint32_t i = threadIdx.x; i < len; i += kBuildThreads) { s.m.set_key(i, a.key[f.lo + i]); s.m.set_idx(i, a.idx[f.lo + i]); }
+            if (threadIdx.x == 0) push_segment(s, 0, 0u, len, f.d);
+            sort_rounds(s);
+            for (uint32_t i = threadIdx.x; i < len; i += kBuildThreads) { a.key[f.lo + i] = s.m.key(i); a.idx[f.lo + i] = s.m.idx(i); }
         } else {
-            s.key = a.key; s.idx = a.idx; s.posl = a.posl; s.posr = a.posr;
-            s.q[0] = reinterpret_cast<Seg*>(a.segq) + f.lo / 8;
-            s.q[1] = reinterpret_cast<Seg*>(a.segq) + a.segq_stride + f.lo / 8;
-            if (threadIdx.x == 0) { sh.qcount[0] = sh.qcount[1] = sh.qcount[2] = sh.qcount[3] = 0; push_segment(s, 0, f.lo, f.hi, f.d); }
+            SortSpace<GlobalMem> s;
+            s.qcount = sh.qcount; s.warp_cnt = sh.warp_cnt; s.sh_k = &sh.sh_k; s.dbg = dbg;
+            s.m.key_ = a.key; s.m.idx_ = a.idx; s.m.posl_ = a.posl; s.m.posr_ = a.posr;
+            s.m.q_[0] = reinterpret_cast<Seg*>(a.segq) + f.lo / 8;
+            s.m.q_[1] = reinterpret_cast<Seg*>(a.segq) + a.segq_stride + f.lo / 8;
+            if (threadIdx.x == 0) push_segment(s, 0, f.lo, f.hi, f.d);
+            sort_rounds(s);
         }
-        sort_rounds(s);
-        if (in_smem)
-            for (uint32_t i = threadIdx.x; i < len; i += kBuildThreads) { a.key[f.lo + i] = s.key[i]; a.idx[f.lo + i] = s.idx[i]; }
         __syncthreads();
     }
 }
@@ -809,7 +864,9 @@ __device__ __forceinline__ void child_finish(const PrepArgs& a, const PrepObject
 
 // One CTA per work item.  subtree = 0: split ONE node (workspace in global scratch); 1: the node and everything below it
 // (workspace in shared memory).
-__global__ void __launch_bounds__(kBuildThreads, 1) build_kernel(const PrepArgs a, const WorkItem* __restrict__ items, const int subtree) {
+template <bool SUBTREE>
+__global__ void __launch_bounds__(kBuildThreads, 1) build_kernel(const PrepArgs a, const WorkItem* __restrict__ items) {
+    constexpr int subtree = SUBTREE ? 1 : 0;
     extern __shared__ __align__(16) unsigned char smem_raw[];
     BuildShared& sh = *reinterpret_cast<BuildShared*>(smem_raw);
     const unsigned tid = threadIdx.x, lane = tid & 31u, warp = tid >> 5;
@@ -817,16 +874,15 @@ __global__ void __launch_bounds__(kBuildThreads, 1) build_kernel(const PrepArgs 
     const PrepObject o = a.objects[it.obj];
     const size_t gbase = (size_t)o.tri_base + it.start;              // scene position of the CTA's range
 
-    SortSpace s;
-    if (subtree) {
-        float* w = reinterpret_cast<float*>(smem_raw + ((sizeof(BuildShared) + 15) & ~size_t(15)));
-        s.key = w; s.idx = reinterpret_cast<uint32_t*>(w + kSubtreeMax);
-        s.posl = reinterpret_cast<uint32_t*>(w + 2 * kSubtreeMax); s.posr = reinterpret_cast<uint32_t*>(w + 3 * kSubtreeMax);
-        s.q[0] = sh.smem_q[0]; s.q[1] = sh.smem_q[1];
+    SortSpace<typename std::conditional<SUBTREE, SharedMem, GlobalMem>::type> s;
+    if constexpr (SUBTREE) {
+        const uint32_t w = (uint32_t)__cvta_generic_to_shared(smem_raw + ((sizeof(BuildShared) + 15) & ~size_t(15)));
+        s.m.key_ = w; s.m.idx_ = w + 4u * kSubtreeMax; s.m.posl_ = w + 8u * kSubtreeMax; s.m.posr_ = w + 12u * kSubtreeMax;
+        s.m.q_[0] = (uint32_t)__cvta_generic_to_shared(sh.smem_q[0]); s.m.q_[1] = (uint32_t)__cvta_generic_to_shared(sh.smem_q[1]);
     } else {
-        s.key = a.key + gbase; s.idx = a.idx + gbase; s.posl = a.posl + gbase; s.posr = a.posr + gbase;
-        s.q[0] = reinterpret_cast<Seg*>(a.segq) + gbase / 8;
-        s.q[1] = reinterpret_cast<Seg*>(a.segq) + a.segq_stride + gbase / 8;
+        s.m.key_ = a.key + gbase; s.m.idx_ = a.idx + gbase; s.m.posl_ = a.posl + gbase; s.m.posr_ = a.posr + gbase;
+        s.m.q_[0] = reinterpret_cast<Seg*>(a.segq) + gbase / 8;
+        s.m.q_[1] = reinterpret_cast<Seg*>(a.segq) + a.segq_stride + gbase / 8;
     }
     s.qcount = sh.qcount; s.warp_cnt = sh.warp_cnt; s.sh_k = &sh.sh_k; s.dbg = nullptr;
 
@@ -853,8 +909,8 @@ __global__ void __launch_bounds__(kBuildThreads, 1) build_kernel(const PrepArgs 
             const uint32_t tri = a.order[gbase + li];
             const float4 p1 = a.xpts[3 * ((size_t)o.tri_base + tri)];
             const uint32_t ax = L.axis[j];
-            s.idx[li] = tri;
-            s.key[li] = ax == 0 ? p1.x : (ax == 1 ? p1.y : p1.z);
+            s.m.set_idx(li, tri);
+            s.m.set_key(li, ax == 0 ? p1.x : (ax == 1 ? p1.y : p1.z));
         }
         for (uint32_t j = tid; j < m; j += kBuildThreads) {
             const uint32_t cnt = L.count[j];
@@ -866,12 +922,12 @@ __global__ void __launch_bounds__(kBuildThreads, 1) build_kernel(const PrepArgs 
             const int j = find_node(L, m, li);
             if (j < 0) continue;
             const uint32_t ns = L.start[j], ne = ns + L.count[j];
-            const float k = s.key[li];
+            const float k = s.m.key(li);
             uint32_t dst = li;
             const uint32_t y0 = li >= ns + 15 ? li - 15 : ns, y1 = li + 16 < ne ? li + 16 : ne;
-            for (uint32_t y = y0; y < li; ++y) dst -= (s.key[y] > k);
-            for (uint32_t y = li + 1; y < y1; ++y) dst += (s.key[y] < k);
-            a.order[gbase + dst] = s.idx[li];
+            for (uint32_t y = y0; y < li; ++y) dst -= (s.m.key(y) > k);
+            for (uint32_t y = li + 1; y < y1; ++y) dst += (s.m.key(y) < k);
+            a.order[gbase + dst] = s.m.idx(li);
         }
         __syncthreads();
         // child boxes (:254-259) and the children's nodes
@@ -996,7 +1052,7 @@ cudaError_t launch_wide_level(const PrepArgs& a, const WideArgs& w, const WorkIt
 }
 
 cudaError_t prepare_kernels() {
-    cudaError_t e = cudaFuncSetAttribute(build_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)build_smem_bytes(true));
+    cudaError_t e = cudaFuncSetAttribute(build_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)build_smem_bytes(true));
     if (e != cudaSuccess) return e;
     return cudaFuncSetAttribute(wide_finish_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)wide_finish_smem_bytes());
 }
@@ -1015,7 +1071,8 @@ cudaError_t launch_roots(const PrepArgs& a, cudaStream_t stream) {
 
 cudaError_t launch_build(const PrepArgs& a, const WorkItem* items, uint32_t n_items, bool subtree, cudaStream_t stream) {
     if (n_items == 0) return cudaSuccess;
-    build_kernel<<<n_items, kBuildThreads, build_smem_bytes(subtree), stream>>>(a, items, subtree ? 1 : 0);
+    if (subtree) build_kernel<true><<<n_items, kBuildThreads, build_smem_bytes(true), stream>>>(a, items);
+    else build_kernel<false><<<n_items, kBuildThreads, build_smem_bytes(false), stream>>>(a, items);
     return cudaGetLastError();
 }
 
