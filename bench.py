@@ -57,6 +57,7 @@ def parse_args():
     ap.add_argument("--cpu-seconds", type=float, default=20.0, help="CPU work (core-seconds) of the cpu_baseline sample")
     ap.add_argument("--still", action="store_true", help="render frame 0 on every step (profiling)")
     ap.add_argument("--gather", action="store_true", help="e2e: gather every rank's frame to rank 0 over NCCL before the download")
+    ap.add_argument("--series-lanes", type=int, default=6, help="frames in flight (contexts / streams) of the device-prep series leg")
     ap.add_argument("--series-frames", type=int, default=-1,
                     help="frames of the pipelined image-series leg incl. host prep (-1: 3 x host threads, max 96; 0: skip)")
     return ap.parse_args()
@@ -467,7 +468,7 @@ def run_b200_arm(args):
         sr.close()
         series = (t_s1 - t_s0, n_fr, threads, float(np.mean(waits)), gpu_leg)
         # the same series with the per-frame prep on the GPU (srt_scene_prep): no host pool at all
-        sd = _series.SeriesRenderer(ctx, cfg, W, H, focal, N, workers=1, variant=args.variant, prep="device")
+        sd = _series.SeriesRenderer(ctx, cfg, W, H, focal, N, workers=1, variant=args.variant, prep="device", lanes=args.series_lanes)
         n_fd = 2 * n_fr
         myd = [360.0 * (i * world + rank) / (n_fd * world) for i in range(n_fd)]
         list(sd.frames(myd[:2]))                                       # warm-up: parse + upload the meshes once
@@ -560,7 +561,7 @@ def run_b200_arm(args):
                         "alternating contexts (the GPU leg overlaps the wait for the next frame's prep)"}
             line["series_with_device_prep"] = {
                 "frames_per_s": world * series_dev[1] / series_dev_s, "frames": world * series_dev[1], "host_threads_per_rank": 1,
-                "mean_issue_ms": series_dev[2], "host_fallback_frames": series_dev[3],
+                "mean_issue_ms": series_dev[2], "host_fallback_frames": series_dev[3], "lanes": args.series_lanes,
                 "what": "the same pipeline with the per-frame prep on the GPU: meshes resident in object space, per frame the "
                         "recorded scene script (matrices) -> srt_scene_prep (transformTriangles + createBoundingHierarchy + "
                         "flatten as CUDA kernels, bit-identical to the host result) -> render -> download; one host thread"}

@@ -60,7 +60,7 @@ class _Lane:
 class SeriesRenderer:
     def __init__(self, ctx: capi.Context, cfg: scenes.SceneConfig, width: int, height: int, focal: float,
                  light_count: int, workers: Optional[int] = None, depth: Optional[int] = None, variant: int = 0,
-                 save_pattern: Optional[str] = None, prep: str = "host"):
+                 save_pattern: Optional[str] = None, prep: str = "host", lanes: Optional[int] = None):
         """save_pattern: e.g. "images/generation/output{index}.bmp" — every frame is also written as the BMP the
         reference's drawImage saves (:488-494), on the worker pool, off the critical path."""
         self.ctx, self.cfg = ctx, cfg
@@ -68,7 +68,10 @@ class SeriesRenderer:
         self.width, self.height, self.focal, self.light_count, self.variant = width, height, focal, light_count, variant
         self.workers = workers or max(1, len(os.sched_getaffinity(0)))
         self.depth = depth or 2 * self.workers
-        self.lanes = [_Lane(ctx, width, height, False), _Lane(capi.Context(ctx.device), width, height, True)]
+        # lanes = contexts (streams) that take frames in turn.  Two are enough to overlap copies with renders; the device
+        # prep is a chain of short, latency-bound launches that fills few SMs, so more frames in flight overlap better.
+        n_lanes = lanes or (6 if prep == "device" else 2)
+        self.lanes = [_Lane(ctx, width, height, False)] + [_Lane(capi.Context(ctx.device), width, height, True) for _ in range(n_lanes - 1)]
         host.set_asset_cache(True)
         if prep not in ("host", "device"):
             raise ValueError("prep must be 'host' or 'device'")
@@ -144,7 +147,7 @@ class SeriesRenderer:
 
     def frames(self, angles: Iterable[float], out: Optional[np.ndarray] = None) -> Iterator[Tuple[int, np.ndarray, dict]]:
         """Yields (index, rgb[H][W][3] host array, timing) per frame, in order.  The yielded array is the lane's
-        pinned frame (valid for the next two iterations), or `out` if given (valid until the next iteration)."""
+        pinned frame (valid until as many further frames as there are lanes have been taken), or `out` if given (valid until the next iteration)."""
         angles = list(angles)
         if self.prep == "device":
             yield from self._frames_device(angles, out)
