@@ -469,9 +469,9 @@ def run_b200_arm(args):
         series = (t_s1 - t_s0, n_fr, threads, float(np.mean(waits)), gpu_leg)
         # the same series with the per-frame prep on the GPU (srt_scene_prep): no host pool at all
         sd = _series.SeriesRenderer(ctx, cfg, W, H, focal, N, workers=1, variant=args.variant, prep="device", lanes=args.series_lanes)
-        n_fd = 2 * n_fr
+        n_fd = max(2 * n_fr, 96)
         myd = [360.0 * (i * world + rank) / (n_fd * world) for i in range(n_fd)]
-        list(sd.frames(myd[:2]))                                       # warm-up: parse + upload the meshes once
+        list(sd.frames(myd[:2 * args.series_lanes]))                   # warm-up: meshes parsed + uploaded once, every lane's scene allocated
         barrier()
         t_d0 = time.time()
         tmd = [tm for (_i, _rgb, tm) in sd.frames(myd)]

@@ -79,6 +79,15 @@ public:
     template <class ImageDataT, class Vec2, class Vec4, class OM>
     ImageDataT sendRaysAndIntersectPointsColors(const Vec2& imageSize, const Vec4& lightPos, OM* objManager) {
         uploadScene(*objManager, params.use_bvh == 0);
+        return renderPrepared<ImageDataT>(imageSize, lightPos, scene_);
+    }
+
+    // The same call on a scene that is already on the device — uploaded by uploadScene, or built there by
+    // srt::DevicePrep::commit (srt_prep.hpp), which replaces the per-frame transformTriangles /
+    // createBoundingHierarchy calls of the reference's frame loop.
+    template <class ImageDataT, class Vec2, class Vec4>
+    ImageDataT renderPrepared(const Vec2& imageSize, const Vec4& lightPos, srt_scene* scene) {
+        if (!scene) throw std::runtime_error("srt::Renderer: no scene");
         params.width = (int32_t)imageSize.x;
         params.height = (int32_t)imageSize.y;
         params.light_pos[0] = lightPos.x; params.light_pos[1] = lightPos.y; params.light_pos[2] = lightPos.z;
@@ -90,7 +99,7 @@ public:
             // glm::vec2 / glm::vec3 are packed floats: the device builds both lists (non-black filter :518,
             // column-major order :511-513) and they are copied straight into the vectors' storage.
             uint64_t n = 0;
-            check(srt_render_sparse(ctx_, scene_, &params, &n));
+            check(srt_render_sparse(ctx_, scene, &params, &n));
             out.imagePoints.resize((size_t)n);
             out.imageColors.resize((size_t)n);
             check(srt_fetch_sparse(ctx_, reinterpret_cast<float*>(out.imagePoints.data()),
@@ -99,8 +108,11 @@ public:
         }
         const int32_t keep = params.no_sky_fill;
         params.no_sky_fill = 1;                // (0,0,0) marks "not drawn" exactly like :518
-        std::vector<uint8_t> rgb;
-        render(rgb);
+        const size_t npx = (size_t)params.width * (size_t)params.height;
+        std::vector<uint8_t> rgb(npx * 3);
+        srt_frame fr = {rgb.data(), nullptr, nullptr, nullptr};
+        check(srt_render(ctx_, scene, &params, &fr));
+        check(srt_sync(ctx_));
         params.no_sky_fill = keep;
         const int W = params.width, H = params.height;
         for (int x = 0; x < W; ++x)            // :511 outer loop over columns

@@ -151,6 +151,9 @@ def ref_lib():
         lib.ref_selfcheck.argtypes = [vp, i32, i32, _f32p]
         lib.ref_dropin_render.restype = C.c_long
         lib.ref_dropin_render.argtypes = [vp, i32, i32, _f32p, _f32p, _f32p, C.c_long, C.c_char_p, i32]
+        lib.ref_device_prep.restype = C.c_long
+        lib.ref_device_prep.argtypes = [vp, i32, C.POINTER(cp), _f32p, i32, i32, _f32p, _f32p, _f32p, C.c_long, vp, vp, vp, vp,
+                                        C.c_char_p, i32]
         lib.ref_verbatim_sparse.restype = C.c_long
         lib.ref_verbatim_sparse.argtypes = [vp, i32, i32, _f32p, _f32p, _f32p, C.c_long]
         lib.ref_draw_image.argtypes = [i32, i32, _f32p, _f32p, C.c_long, i32]
@@ -385,6 +388,28 @@ class RefBackend:
         else:
             n = self.lib.ref_verbatim_sparse(self.h, width, height, _fp(l4), _fp(pts), _fp(col), cap)
         return pts[:n].copy(), col[:n].copy()
+
+    def device_prep(self, calls, n_nodes, n_tris, width, height, light4):
+        """include/srt_prep.hpp (srt::DevicePrep) + srt::Renderer::renderPrepared compiled against the reference's own
+        types, on this scene's meshes AS LOADED: `calls` = [(name, m16), ...] are the transformTriangles calls of one
+        frame.  Returns (FlatSceneArrays built on the GPU, ImageData points, colours).  Needs a GPU."""
+        l4 = np.asarray(light4, np.float32)
+        names = (C.c_char_p * max(len(calls), 1))(*[n.encode() for n, _m in calls])
+        mats = np.ascontiguousarray(np.stack([_m16(m) for _n, m in calls]) if calls else np.zeros((0, 16), np.float32))
+        n_obj = self.lib.ref_object_count(self.h)
+        nodes = np.zeros(n_nodes, _abi.NODE_DTYPE)
+        geom = np.zeros(n_tris, _abi.GEOM_DTYPE)
+        attr = np.zeros(n_tris, _abi.ATTR_DTYPE)
+        objs = np.zeros(n_obj, _abi.OBJECT_DTYPE)
+        cap = width * height
+        pts = np.zeros((cap, 2), np.float32)
+        col = np.zeros((cap, 3), np.float32)
+        err = C.create_string_buffer(1024)
+        n = self.lib.ref_device_prep(self.h, len(calls), names, _fp(mats), width, height, _fp(l4), _fp(pts), _fp(col), cap,
+                                     nodes.ctypes.data, geom.ctypes.data, attr.ctypes.data, objs.ctypes.data, err, 1024)
+        if n < 0:
+            raise RuntimeError("srt_prep: " + err.value.decode(errors="replace"))
+        return _abi.FlatSceneArrays(nodes, geom, attr, objs), pts[:n].copy(), col[:n].copy()
 
     def selfcheck(self, width, height, light4):
         l4 = np.asarray(light4, np.float32)

@@ -286,3 +286,48 @@ def test_device_prep_equals_the_unmodified_reference(gpu_ctx, ref_scene):
             ds.close()
     finally:
         cache.close()
+
+
+class _Split:
+    """Scene backend that sends the load / colour / clone calls to `loaded` and `full`, the per-frame calls
+    (transformTriangles, createBoundingHierarchy) to `full` only, and records the transforms."""
+
+    def __init__(self, loaded, full):
+        self.loaded, self.full, self.calls = loaded, full, []
+
+    def transform(self, name, m16):
+        self.calls.append((name, np.asarray(m16, f32).copy()))
+        self.full.transform(name, m16)
+
+    def create_bounding_hierarchy(self, name):
+        self.full.create_bounding_hierarchy(name)
+
+    def __getattr__(self, item):
+        fa, fb = getattr(self.loaded, item), getattr(self.full, item)
+        if item in ("load_obj", "set_color", "set_properties", "clone"):
+            def both_(*args):
+                fa(*args)
+                return fb(*args)
+            return both_
+        return fb
+
+
+@pytest.mark.ref
+def test_cpp_device_prep_header_against_the_reference_types(gpu_ctx):
+    """include/srt_prep.hpp compiled against the reference's ObjectManager: the scene it builds on the GPU equals the
+    flattened result of the reference's own transformTriangles + createBoundingHierarchy, and renderPrepared returns
+    the ImageData of the verbatim sendRaysAndIntersectPointsColors (:505)."""
+    from oracle import pyoracle
+    cfg = scenes.CONFIGS["shipped"]
+    loaded, full = pyoracle.RefBackend(), pyoracle.RefBackend()
+    b = _Split(loaded, full)
+    view = cfg.build(b, 20.0)
+    light = scenes.light_view_space(full, view)
+    want = full.flatten()
+    got, pts, col = loaded.device_prep(b.calls, len(want.nodes), len(want.geom), cfg.width, cfg.height, light)
+    assert_same_scene(want, got, what="srt::DevicePrep on the reference's types")
+    wp, wc = full.sparse(cfg.width, cfg.height, light, dropin=False)
+    assert np.array_equal(wp, pts)
+    assert np.abs(wc - col).max() <= 1.0
+    loaded.close()
+    full.close()
