@@ -29,6 +29,8 @@ struct srt_mesh {
 struct srt_prep_state {
     DevBuf xpts, lite, order, key, idx, posl, posr, segq, blob, misc, wide;
     int last_launches = 0;
+    cudaGraphExec_t graph = nullptr;           // the frame's launch sequence, captured once per scene composition
+    std::vector<uint64_t> graph_sig;
     std::vector<unsigned char> blob_host;
     // the recipe goes through pinned staging (a pageable cudaMemcpyAsync would first wait for the stream): two
     // buffers in turn, each guarded by the event of its last copy
@@ -78,6 +80,7 @@ void srti_prep_state_destroy(srt_prep_state* p) {
     if (!p) return;
     p->xpts.release(); p->lite.release(); p->order.release(); p->key.release(); p->idx.release();
     p->posl.release(); p->posr.release(); p->segq.release(); p->blob.release(); p->misc.release(); p->wide.release();
+    if (p->graph) cudaGraphExecDestroy(p->graph);
     if (p->status_host) cudaFreeHost(p->status_host);
     for (int k = 0; k < 2; ++k) {
         if (p->pin[k]) cudaFreeHost(p->pin[k]);
@@ -282,23 +285,6 @@ int srt_scene_prep(srt_context* c, const srt_prep_object* objs, uint32_t n_objec
     for (size_t d = 0; d < big.size(); ++d) at_big[d] = blob_put(blob, big[d].data(), big[d].size());
     const size_t at_sub = blob_put(blob, sub.data(), sub.size());
     if ((rc = ps.blob.reserve(blob.size() + 16))) return bail(rc);
-    {
-        const int k = ps.turn;
-        ps.turn ^= 1;
-        if (!ps.pin_ev[k]) CU(cudaEventCreateWithFlags(&ps.pin_ev[k], cudaEventDisableTiming));
-        else CU(cudaEventSynchronize(ps.pin_ev[k]));               // the copy of two calls ago has long finished
-        if (ps.pin_cap[k] < blob.size()) {
-            if (ps.pin[k]) cudaFreeHost(ps.pin[k]);
-            ps.pin[k] = nullptr; ps.pin_cap[k] = 0;
-            const size_t want = blob.size() + blob.size() / 2 + 4096;
-            cudaError_t pe = cudaMallocHost(&ps.pin[k], want);
-            if (pe != cudaSuccess) return bail(fail(SRT_ERR_OOM, "cudaMallocHost(%zu): %s", want, cudaGetErrorString(pe)));
-            ps.pin_cap[k] = want;
-        }
-        std::memcpy(ps.pin[k], blob.data(), blob.size());
-        CU(cudaMemcpyAsync(ps.blob.p, ps.pin[k], blob.size(), cudaMemcpyHostToDevice, c->stream));
-        CU(cudaEventRecord(ps.pin_ev[k], c->stream));
-    }
     unsigned char* dblob = (unsigned char*)ps.blob.p;
 
     srtp::PrepArgs a;
@@ -343,41 +329,101 @@ int srt_scene_prep(srt_context* c, const srt_prep_object* objs, uint32_t n_objec
         w.childacc = (unsigned long long*)(wb + o_acc);
     }
     static const bool single_cta_big = std::getenv("SRT_PREP_SINGLE_CTA") != nullptr;     // A/B: the one-CTA-per-node path
+    static const bool use_graph = std::getenv("SRT_PREP_NO_GRAPH") == nullptr;
     int launches = 0;
-    cudaError_t e = srtp::launch_transform(a, max_tris, c->stream);
-    if (e == cudaSuccess) e = srtp::launch_roots(a, c->stream);
-    launches += 2;
-    for (size_t d = 0; d < big.size() && e == cudaSuccess; ++d) {
-        if (big[d].empty()) continue;
-        if (single_cta_big) {
-            e = srtp::launch_build(a, (const srtp::WorkItem*)(dblob + at_big[d]), (uint32_t)big[d].size(), false, c->stream);
-            ++launches;
-            continue;
+    // Everything the frame enqueues: the recipe upload, the kernels, the status read-back.
+    auto enqueue = [&](const unsigned char* pinned) -> cudaError_t {
+        cudaError_t e = cudaMemcpyAsync(ps.blob.p, pinned, blob.size(), cudaMemcpyHostToDevice, c->stream);
+        if (e == cudaSuccess) e = srtp::launch_transform(a, max_tris, c->stream);
+        if (e == cudaSuccess) e = srtp::launch_roots(a, c->stream);
+        launches = 2;
+        for (size_t d = 0; d < big.size() && e == cudaSuccess; ++d) {
+            if (big[d].empty()) continue;
+            if (single_cta_big) {
+                e = srtp::launch_build(a, (const srtp::WorkItem*)(dblob + at_big[d]), (uint32_t)big[d].size(), false, c->stream);
+                ++launches;
+                continue;
+            }
+            uint32_t maxc = 0;
+            size_t tiles = 8, total = 0;
+            for (const srtp::WorkItem& it : big[d]) { if (it.count > maxc) maxc = it.count; total += it.count; tiles += it.count / srtp::kWideTile + 1; }
+            tiles += 2 * (total / srtp::kWideSmall + big[d].size());
+            // planned many-CTA rounds: until the segments fit one CTA if every pivot split evenly, plus three (a median of
+            // three rarely does; a round with nothing left to do costs three empty launches, a segment left too long costs
+            // a one-CTA sort in global memory)
+            uint32_t rounds = 0;
+            static const int slack = std::getenv("SRT_PREP_SLACK") ? std::atoi(std::getenv("SRT_PREP_SLACK")) : 3;
+            if (maxc > srtp::kWideSmall) { rounds = (uint32_t)slack; for (uint64_t v = srtp::kWideSmall; v < maxc; v *= 2) ++rounds; }
+            if (rounds > (uint32_t)srtp::kWideMaxRounds - 1) rounds = srtp::kWideMaxRounds - 1;
+            if (tiles > w.max_tiles) tiles = w.max_tiles;
+            e = srtp::launch_wide_level(a, w, (const srtp::WorkItem*)(dblob + at_big[d]), (uint32_t)big[d].size(), maxc, rounds,
+                                        (uint32_t)tiles, c->sm_count, c->stream, &launches);
         }
-        uint32_t maxc = 0;
-        size_t tiles = 8, total = 0;
-        for (const srtp::WorkItem& it : big[d]) { if (it.count > maxc) maxc = it.count; total += it.count; tiles += it.count / srtp::kWideTile + 1; }
-        tiles += 2 * (total / srtp::kWideSmall + big[d].size());
-        // planned many-CTA rounds: until the segments fit one CTA if every pivot split evenly, plus three (a median of
-        // three rarely does; a round with nothing left to do costs three empty launches, a segment left too long costs
-        // a one-CTA sort in global memory)
-        uint32_t rounds = 0;
-        static const int slack = std::getenv("SRT_PREP_SLACK") ? std::atoi(std::getenv("SRT_PREP_SLACK")) : 3;
-        if (maxc > srtp::kWideSmall) { rounds = (uint32_t)slack; for (uint64_t v = srtp::kWideSmall; v < maxc; v *= 2) ++rounds; }
-        if (rounds > (uint32_t)srtp::kWideMaxRounds - 1) rounds = srtp::kWideMaxRounds - 1;
-        if (tiles > w.max_tiles) tiles = w.max_tiles;
-        e = srtp::launch_wide_level(a, w, (const srtp::WorkItem*)(dblob + at_big[d]), (uint32_t)big[d].size(), maxc, rounds,
-                                    (uint32_t)tiles, c->sm_count, c->stream, &launches);
+        if (e == cudaSuccess) e = srtp::launch_build(a, (const srtp::WorkItem*)(dblob + at_sub), (uint32_t)sub.size(), true, c->stream);
+        if (e == cudaSuccess) e = srtp::launch_flatten(a, max_tris, with_flat_lists != 0, c->stream);
+        if (e == cudaSuccess && n_objects > 0)
+            e = srtk::launch_build_wide((const float4*)s->nodes.p, (const srt_object*)s->objects.p, (uint32_t)n_nodes, n_objects,
+                                        (float4*)s->wide.p, (uint32_t*)s->root_ref.p, c->stream);
+        launches += 3;
+        if (e == cudaSuccess) e = cudaMemcpyAsync(ps.status_host, a.status, sizeof(uint32_t), cudaMemcpyDeviceToHost, c->stream);
+        return e;
+    };
+    auto stage = [&](int k) -> int {                               // recipe -> pinned buffer k (its previous copy must be over)
+        if (!ps.pin_ev[k]) CU(cudaEventCreateWithFlags(&ps.pin_ev[k], cudaEventDisableTiming));
+        else CU(cudaEventSynchronize(ps.pin_ev[k]));
+        if (ps.pin_cap[k] < blob.size()) {
+            if (ps.pin[k]) cudaFreeHost(ps.pin[k]);
+            ps.pin[k] = nullptr; ps.pin_cap[k] = 0;
+            const size_t want = blob.size() + blob.size() / 2 + 4096;
+            cudaError_t pe = cudaMallocHost(&ps.pin[k], want);
+            if (pe != cudaSuccess) return fail(SRT_ERR_OOM, "cudaMallocHost(%zu): %s", want, cudaGetErrorString(pe));
+            ps.pin_cap[k] = want;
+        }
+        std::memcpy(ps.pin[k], blob.data(), blob.size());
+        return SRT_OK;
+    };
+    cudaError_t e = cudaSuccess;
+    if (use_graph) {
+        // The launch sequence of a frame depends on the composition of the scene only (which meshes, how many
+        // matrices, where the buffers live), not on its contents: it is captured once into a CUDA graph and replayed
+        // — one launch instead of about eighty.  The recipe always travels through pinned buffer 0.
+        std::vector<uint64_t> sig;
+        auto put = [&](const void* ptr) { sig.push_back((uint64_t)(uintptr_t)ptr); };
+        put(s->nodes.p); put(s->geom.p); put(s->attr.p); put(s->flat_geom.p); put(s->flat_attr.p); put(s->objects.p);
+        put(s->wide.p); put(s->root_ref.p); put(ps.xpts.p); put(ps.lite.p); put(ps.order.p); put(ps.key.p); put(ps.idx.p);
+        put(ps.posl.p); put(ps.posr.p); put(ps.segq.p); put(ps.blob.p); put(ps.wide.p); put(ps.misc.p); put(c->stream);
+        sig.push_back(blob.size()); sig.push_back(n_objects); sig.push_back((uint64_t)(with_flat_lists != 0));
+        sig.push_back((uint64_t)single_cta_big);
+        for (uint32_t i = 0; i < n_objects; ++i) { put(objs[i].mesh); sig.push_back(objs[i].n_matrices); }
+        if ((rc = stage(0))) return bail(rc);
+        put(ps.pin[0]);
+        if (!ps.graph || sig != ps.graph_sig) {
+            if (ps.graph) { cudaGraphExecDestroy(ps.graph); ps.graph = nullptr; }
+            cudaGraph_t g = nullptr;
+            e = cudaStreamBeginCapture(c->stream, cudaStreamCaptureModeThreadLocal);
+            if (e == cudaSuccess) {
+                const cudaError_t e1 = enqueue(ps.pin[0]);
+                const cudaError_t e2 = cudaStreamEndCapture(c->stream, &g);
+                e = e1 != cudaSuccess ? e1 : e2;
+            }
+            if (e == cudaSuccess) e = cudaGraphInstantiate(&ps.graph, g, 0);
+            if (g) cudaGraphDestroy(g);
+            if (e != cudaSuccess) { ps.graph = nullptr; ps.graph_sig.clear(); cudaGetLastError(); return bail(fail(SRT_ERR_CUDA, "scene prep graph capture: %s", cudaGetErrorString(e))); }
+            ps.graph_sig = sig;
+        } else {
+            launches = ps.last_launches;
+        }
+        e = cudaGraphLaunch(ps.graph, c->stream);
+        if (e == cudaSuccess) e = cudaEventRecord(ps.pin_ev[0], c->stream);
+    } else {
+        const int k = ps.turn;
+        ps.turn ^= 1;
+        if ((rc = stage(k))) return bail(rc);
+        e = enqueue(ps.pin[k]);
+        if (e == cudaSuccess) e = cudaEventRecord(ps.pin_ev[k], c->stream);
     }
-    if (e == cudaSuccess) e = srtp::launch_build(a, (const srtp::WorkItem*)(dblob + at_sub), (uint32_t)sub.size(), true, c->stream);
-    if (e == cudaSuccess) e = srtp::launch_flatten(a, max_tris, with_flat_lists != 0, c->stream);
-    launches += 3;
-    ps.last_launches = launches;
-    if (e == cudaSuccess && n_objects > 0)
-        e = srtk::launch_build_wide((const float4*)s->nodes.p, (const srt_object*)s->objects.p, (uint32_t)n_nodes, n_objects,
-                                    (float4*)s->wide.p, (uint32_t*)s->root_ref.p, c->stream);
     if (e != cudaSuccess) return bail(fail(SRT_ERR_CUDA, "scene prep launch: %s", cudaGetErrorString(e)));
-    CU(cudaMemcpyAsync(ps.status_host, a.status, sizeof(uint32_t), cudaMemcpyDeviceToHost, c->stream));
+    ps.last_launches = launches;
 
     s->n_nodes = n_nodes; s->n_tris = n_tris; s->n_flat = n_flat; s->n_objects = n_objects;
     s->max_depth = max_depth;
