@@ -31,6 +31,7 @@ struct srt_prep_state {
     int last_launches = 0;
     cudaGraphExec_t graph = nullptr;           // the frame's launch sequence, captured once per scene composition
     std::vector<uint64_t> graph_sig;
+    bool graph_failed = false;                 // capture was refused once (e.g. a stream that cannot be captured)
     std::vector<unsigned char> blob_host;
     // the recipe goes through pinned staging (a pageable cudaMemcpyAsync would first wait for the stream): two
     // buffers in turn, each guarded by the event of its last copy
@@ -383,7 +384,11 @@ int srt_scene_prep(srt_context* c, const srt_prep_object* objs, uint32_t n_objec
         return SRT_OK;
     };
     cudaError_t e = cudaSuccess;
-    if (use_graph) {
+    // (the legacy default stream cannot be captured: a context bound to it launches kernel by kernel)
+    const bool graph_ok = use_graph && !ps.graph_failed && c->stream != nullptr && c->stream != cudaStreamLegacy &&
+                          c->stream != cudaStreamPerThread;
+    bool launched = false;
+    if (graph_ok) {
         // The launch sequence of a frame depends on the composition of the scene only (which meshes, how many
         // matrices, where the buffers live), not on its contents: it is captured once into a CUDA graph and replayed
         // — one launch instead of about eighty.  The recipe always travels through pinned buffer 0.
@@ -408,14 +413,29 @@ int srt_scene_prep(srt_context* c, const srt_prep_object* objs, uint32_t n_objec
             }
             if (e == cudaSuccess) e = cudaGraphInstantiate(&ps.graph, g, 0);
             if (g) cudaGraphDestroy(g);
-            if (e != cudaSuccess) { ps.graph = nullptr; ps.graph_sig.clear(); cudaGetLastError(); return bail(fail(SRT_ERR_CUDA, "scene prep graph capture: %s", cudaGetErrorString(e))); }
-            ps.graph_sig = sig;
+            if (e != cudaSuccess) {                                // not capturable here: plain launches from now on
+                cudaStreamCaptureStatus st = cudaStreamCaptureStatusNone;
+                if (cudaStreamIsCapturing(c->stream, &st) == cudaSuccess && st != cudaStreamCaptureStatusNone) {
+                    cudaGraph_t dead = nullptr;
+                    cudaStreamEndCapture(c->stream, &dead);
+                    if (dead) cudaGraphDestroy(dead);
+                }
+                cudaGetLastError();
+                ps.graph = nullptr; ps.graph_sig.clear(); ps.graph_failed = true;
+                e = cudaSuccess;
+            } else {
+                ps.graph_sig = sig;
+            }
         } else {
             launches = ps.last_launches;
         }
-        e = cudaGraphLaunch(ps.graph, c->stream);
-        if (e == cudaSuccess) e = cudaEventRecord(ps.pin_ev[0], c->stream);
-    } else {
+        if (ps.graph) {
+            e = cudaGraphLaunch(ps.graph, c->stream);
+            if (e == cudaSuccess) e = cudaEventRecord(ps.pin_ev[0], c->stream);
+            launched = true;
+        }
+    }
+    if (!launched) {
         const int k = ps.turn;
         ps.turn ^= 1;
         if ((rc = stage(k))) return bail(rc);

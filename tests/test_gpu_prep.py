@@ -177,6 +177,20 @@ def test_series_driver_with_device_prep_equals_host_prep(gpu_ctx):
     assert len({f.tobytes() for f in frames["device"]}) == len(angles)      # and they are five different frames
 
 
+def test_device_prep_on_a_context_bound_to_the_default_stream():
+    """The legacy default stream cannot be captured into a CUDA graph: such a context launches kernel by kernel."""
+    ctx = capi.Context(0, stream=0)
+    cache = prep.MeshCache(ctx)
+    try:
+        for angle in (10.0, 20.0, 30.0):
+            cfg, want, got, sc, light = both(ctx, cache, "C3", angle)
+            assert_same_scene(want, got, what=f"default stream @ {angle}")
+            sc.destroy()
+    finally:
+        cache.close()
+        ctx.destroy()
+
+
 def write_obj(path, tris):
     with open(path, "w") as f:
         for t in tris.reshape(-1, 3):

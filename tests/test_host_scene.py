@@ -142,3 +142,91 @@ def test_write_bmp_equals_reference_draw_image(tmp_path):
         path = tmp_path / f"ours{W}.bmp"
         host.write_bmp(path, dense)
         assert path.read_bytes() == want, (W, H)
+
+
+# ---- host side of the device scene prep (prep.py): everything that does not need the GPU -----------------------
+def test_object_order_is_the_reference_maps_iteration_order():
+    """S2: the object order of a recorded scene = iteration order of objTriangles for the same insertion sequence."""
+    from simple_raytracer_b200 import host, scenes
+    for key in ("C3", "C4", "spheres", "cubes4"):
+        hs = host.HostScene()
+        log = []
+
+        class Rec:
+            def __getattr__(self, item):
+                f = getattr(hs, item)
+                if item in ("load_obj", "clone"):
+                    def wrapped(*args):
+                        log.append(args[1] if item == "clone" else args[0])
+                        return f(*args)
+                    return wrapped
+                return f
+
+        scenes.CONFIGS[key].build(Rec(), 30.0)
+        assert host.object_order(log) == hs.object_names(), key
+        hs.close()
+
+
+def test_triangle_texture_slots_and_pixels():
+    from simple_raytracer_b200 import host
+    hs = host.HostScene()
+    hs.load_obj("./obj/house/house.obj")
+    slots, names = hs.triangle_textures("./obj/house/house.obj")
+    tris, flags = hs.triangles("./obj/house/house.obj")
+    assert len(slots) == len(tris) and len(names) >= 2
+    assert np.array_equal(slots >= 0, flags != 0)
+    assert set(np.unique(slots[slots >= 0])) == set(range(len(names)))
+    first_use = [int(np.nonzero(slots == k)[0][0]) for k in range(len(names))]
+    assert first_use == sorted(first_use)                       # slots numbered by first appearance in load order
+    px = hs.texture(names[0])
+    assert px.ndim == 3 and px.shape[2] == 3 and px.dtype == np.uint8
+    hs.close()
+
+
+def test_recorded_scene_script_matches_the_host_calls():
+    """prep.DeviceScene records what the host backend executes: same objects, same matrices in the same order, the
+    clone idiom copies the transforms made so far, colours / properties follow the reference's defaults."""
+    from simple_raytracer_b200 import host, prep, scenes
+
+    class NoGpuCache:                      # MeshCache without a device: meshes are placeholders
+        assets = None
+        textures = []
+
+        class M:
+            n_tris = 0
+
+        def mesh(self, path):
+            return self.M()
+
+    ds = prep.DeviceScene(NoGpuCache())
+    calls = []
+    hs = host.HostScene()
+
+    class Tee:
+        def __getattr__(self, item):
+            f = getattr(hs, item)
+            if item == "transform":
+                def wrapped(name, m):
+                    calls.append((name, np.asarray(m, np.float32).copy()))
+                    return f(name, m)
+                return wrapped
+            return f
+
+    scenes.CONFIGS["cubes4"].build(ds, 40.0)
+    scenes.CONFIGS["cubes4"].build(Tee(), 40.0)
+    assert ds.object_names() == hs.object_names()
+    # cube1..3 were cloned after the first scale of cube.obj: they inherit exactly that one matrix, then their own
+    own = {}
+    for name, m in calls:
+        own.setdefault(name, []).append(m)
+    for name in ("cube1.obj", "cube2.obj", "cube3.obj"):
+        got = ds.objects[name].matrices
+        want = [own["cube.obj"][0]] + own[name]
+        assert len(got) == len(want) and all(np.array_equal(a, b) for a, b in zip(got, want)), name
+    assert all(np.array_equal(a, b) for a, b in zip(ds.objects["cube.obj"].matrices, own["cube.obj"]))
+    assert ds.props["cube.obj"] == prep.LOAD_PROPERTIES and "cube1.obj" not in ds.props      # clone(..., False), :731
+    assert ds.colors["cube1.obj"] == (1.0, 0.0, 1.0)
+    with pytest.raises(KeyError):
+        ds.clone("nope.obj", "x.obj", False)
+    ds.close()
+    hs.close()
