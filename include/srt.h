@@ -139,7 +139,15 @@ typedef struct srt_render_params {
      * shard_index + shard_count, ...  Pixels are independent (:511-523), so the union of the shards is
      * byte-identical to one full render. */
     int32_t row_block, shard_index, shard_count;
+    /* Where the light_count light samples sit (NOT a parity mode unless 0):
+     * SRT_LIGHTS_STAIRCASE  the reference's deterministic sequence (:363-383), the default;
+     * SRT_LIGHTS_JITTERED   sample i = light_pos + extent * (u_x, u_y, u_z), extent = light_step * ceil(light_count / 3)
+     *                       (the box the staircase spans), u in [0,1) from a counter-based generator keyed by
+     *                       (light_seed, 3 i + axis): reproducible, independent of evaluation order. */
+    int32_t  light_mode;
+    uint32_t light_seed;
 } srt_render_params;
+enum { SRT_LIGHTS_STAIRCASE = 0, SRT_LIGHTS_JITTERED = 1 };
 
 enum { SRT_VARIANT_DEFAULT = 0,   /* staged pipeline: classify, primary, shadow, shade as stream-ordered launches; falls back to
                                      SIMPLE for the legacy one-box path */
@@ -259,7 +267,8 @@ int  srt_fetch_sparse(srt_context* ctx, float* points_xy, float* colors_rgb, uin
 
 /* ---- helpers ---- */
 void srt_default_params(srt_render_params* p);             /* fills the reference's literals */
-/* Light staircase of softShadow :363-383: out[3*i..] for i < count, sequential fp32 adds. */
+/* Light sample positions, out[3*i..] for i < count: the staircase of softShadow :363-383 (sequential fp32 adds) or
+ * the jittered samples of light_mode. */
 int  srt_light_positions(const srt_render_params* p, float* out_xyz);
 void* srt_host_alloc(size_t bytes);                        /* pinned host memory */
 void  srt_host_free(void* p);

@@ -63,6 +63,8 @@ def oracle_lib():
         lib.srt_oracle_phong.argtypes = [_f32p] * 5 + [C.c_float] * 4 + [_f32p]
         lib.srt_oracle_tonemap_quantise.argtypes = [_f32p, C.c_float, C.c_float, _f32p, C.POINTER(C.c_int32)]
         lib.srt_oracle_light_positions.argtypes = [_f32p, C.c_int, C.c_float, _f32p]
+        lib.srt_oracle_light_positions_mode.argtypes = [C.POINTER(_abi.RenderParams), _f32p]
+        lib.srt_oracle_light_positions_mode.restype = None
         _oracle = lib
     return _oracle
 

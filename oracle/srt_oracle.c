@@ -136,6 +136,24 @@ void srt_oracle_light_positions(const float light_pos[3], int count, float step,
     }
 }
 
+/* srt_render_params::light_mode (srt.h): the staircase, or the jittered samples (not a reference mode: restated
+ * from include/srt.h's definition so that the CUDA path can be checked in that mode too). */
+void srt_oracle_light_positions_mode(const srt_render_params* p, float* out) {
+    if (p->light_mode == SRT_LIGHTS_JITTERED) {
+        const volatile float extent = p->light_step * (float)((p->light_count + 2) / 3);
+        for (int i = 0; i < p->light_count; ++i)
+            for (int a = 0; a < 3; ++a) {
+                uint32_t x = (uint32_t)(3 * i + a) * 0x9E3779B9u + p->light_seed;
+                x ^= x >> 16; x *= 0x85EBCA6Bu; x ^= x >> 13; x *= 0xC2B2AE35u; x ^= x >> 16;
+                const volatile float u = (float)(x >> 8) * (1.0f / 16777216.0f);
+                const volatile float off = extent * u;
+                out[3 * i + a] = p->light_pos[a] + off;
+            }
+        return;
+    }
+    srt_oracle_light_positions(p->light_pos, p->light_count, p->light_step, out);
+}
+
 /* ------------------------------------------------------------------------------------------- */
 typedef struct {
     const srt_scene_desc* sc;
@@ -329,7 +347,7 @@ long srt_oracle_render(const srt_scene_desc* scene, const srt_render_params* par
     if (!params->use_bvh && (!scene->flat_geom || !scene->flat_attr)) return -1;
     oracle_job J;
     J.sc = scene; J.pr = params;
-    srt_oracle_light_positions(params->light_pos, params->light_count, params->light_step, J.lights);
+    srt_oracle_light_positions_mode(params, J.lights);
     /* loop bounds of :511/:513: int i = -imageSize.x / 2 (float -> int truncation) */
     J.i0 = (int)(-(float)params->width / 2);
     J.j0 = (int)(-(float)params->height / 2);

@@ -21,6 +21,9 @@ SRT_ERR_OOM = -4
 SRT_ERR_SCENE = -5
 SRT_ERR_UNSUPPORTED = -6
 
+LIGHTS_STAIRCASE = 0      # the reference's sequence (parity)
+LIGHTS_JITTERED = 1       # counter-based jittered samples in the staircase's box (not a reference mode)
+
 VARIANT_DEFAULT = 0
 VARIANT_SIMPLE = 1
 VARIANT_FUSED = 2
@@ -64,6 +67,7 @@ class RenderParams(C.Structure):
         ("use_bvh", C.c_int32), ("row_begin", C.c_int32), ("row_end", C.c_int32),
         ("variant", C.c_int32), ("no_sky_fill", C.c_int32), ("row_block", C.c_int32),
         ("shard_index", C.c_int32), ("shard_count", C.c_int32),
+        ("light_mode", C.c_int32), ("light_seed", C.c_uint32),
     ]
 
 

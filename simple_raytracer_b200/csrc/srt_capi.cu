@@ -147,6 +147,20 @@ int srt_light_positions(const srt_render_params* p, float* out) {
     if (!p || !out) return fail(SRT_ERR_INVALID_ARG, "NULL argument");
     if (p->light_count < 0 || p->light_count > SRT_MAX_LIGHTS)
         return fail(SRT_ERR_INVALID_ARG, "light_count %d outside [0,%d]", p->light_count, SRT_MAX_LIGHTS);
+    if (p->light_mode == SRT_LIGHTS_JITTERED) {
+        // counter-based: a murmur3 finaliser over a Weyl sequence keyed by the seed; 24 random bits per coordinate
+        const volatile float extent = p->light_step * (float)((p->light_count + 2) / 3);
+        for (int i = 0; i < p->light_count; ++i)
+            for (int a = 0; a < 3; ++a) {
+                uint32_t x = (uint32_t)(3 * i + a) * 0x9E3779B9u + p->light_seed;
+                x ^= x >> 16; x *= 0x85EBCA6Bu; x ^= x >> 13; x *= 0xC2B2AE35u; x ^= x >> 16;
+                const volatile float u = (float)(x >> 8) * (1.0f / 16777216.0f);
+                const volatile float off = extent * u;
+                out[3 * i + a] = p->light_pos[a] + off;
+            }
+        return SRT_OK;
+    }
+    if (p->light_mode != SRT_LIGHTS_STAIRCASE) return fail(SRT_ERR_INVALID_ARG, "unknown light_mode %d", p->light_mode);
     volatile float L[3] = {p->light_pos[0], p->light_pos[1], p->light_pos[2]};
     for (int i = 0; i < p->light_count; ++i) {
         out[3 * i] = L[0]; out[3 * i + 1] = L[1]; out[3 * i + 2] = L[2];

@@ -61,3 +61,34 @@ def test_no_device_fails_loudly():
         capi.Context(0)
     assert e.value.code == _abi.SRT_ERR_NO_DEVICE
     assert "no CPU fallback" in str(e.value)
+
+
+def test_light_sample_positions_staircase_and_jittered():
+    """srt_light_positions (host arithmetic of the product library, no GPU needed) against the oracle: the reference's
+    staircase (:363-383) and the counter-based jittered samples of light_mode (reproducible, inside the staircase's box)."""
+    import numpy as np
+    from oracle import pyoracle
+    from simple_raytracer_b200 import _abi, capi
+    olib = pyoracle.oracle_lib()
+    p = _abi.default_params(64, 64, 400.0, (500.0, -300.0, -200.0), 16, True)
+    for mode, seed in ((_abi.LIGHTS_STAIRCASE, 0), (_abi.LIGHTS_JITTERED, 0), (_abi.LIGHTS_JITTERED, 12345)):
+        p.light_mode, p.light_seed = mode, seed
+        got = capi.light_positions(p)
+        want = np.zeros((16, 3), np.float32)
+        olib.srt_oracle_light_positions_mode(p, want.ctypes.data_as(pyoracle._f32p))
+        assert np.array_equal(got, want), (mode, seed)
+        if mode == _abi.LIGHTS_JITTERED:
+            lo = np.array([500.0, -300.0, -200.0], np.float32)
+            assert (got >= lo).all() and (got < lo + 3.0 * 6).all()
+            assert len({tuple(r) for r in got}) == 16
+            assert np.array_equal(got, capi.light_positions(p))          # reproducible
+    p.light_mode, p.light_seed = _abi.LIGHTS_JITTERED, 1
+    a = capi.light_positions(p)
+    p.light_seed = 2
+    assert not np.array_equal(a, capi.light_positions(p))
+    p.light_mode = 7
+    try:
+        capi.light_positions(p)
+        assert False, "unknown light_mode accepted"
+    except capi.SrtError as e:
+        assert e.code == _abi.SRT_ERR_INVALID_ARG
