@@ -87,6 +87,13 @@ typedef struct srt_tri_attr {
     float pad1[2];
 } srt_tri_attr;                               /* 48 B */
 
+/* Optional, same order as geom: the per-vertex normals Triangle::normalOne/Two/Three exactly as loadObjFile stored
+ * them (Object.cpp:98-104) — the reference never transforms them (transformTriangles touches the points only).
+ * Needed only for srt_render_params::smooth_normals (interpolateNormal :132-140). */
+typedef struct srt_tri_vnormal {
+    float n[3][4];                            /* xyz of each vertex normal, w unused (0) */
+} srt_tri_vnormal;                            /* 48 B: three 16-byte loads */
+
 /* One entry per key of ObjectManager::objTriangles, in that unordered_map's ITERATION order
  * (simple_raytracer.cpp:409, :322) — the order decides exact-tie resolution. */
 typedef struct srt_object {
@@ -115,6 +122,9 @@ typedef struct srt_scene_desc {
     const srt_tri_attr* flat_attr; uint64_t n_flat;
     const srt_object*   objects;   uint32_t n_objects;
     const srt_texture_desc* textures; uint32_t n_textures;
+    /* Optional (NULL: the scene cannot be rendered with smooth_normals): vertex normals in leaf order / load order. */
+    const srt_tri_vnormal* vnormal;
+    const srt_tri_vnormal* flat_vnormal;
 } srt_scene_desc;
 
 /* Every literal of the reference's hot path, as a parameter (defaults = the literals). */
@@ -146,6 +156,10 @@ typedef struct srt_render_params {
      *                       (light_seed, 3 i + axis): reproducible, independent of evaluation order. */
     int32_t  light_mode;
     uint32_t light_seed;
+    /* 1: phongIllumination with the normal the reference ships commented out (:162): n = interpolateNormal(triangle,
+     * barycentricCoords) :132-140 — normalize(b.x * normalOne + b.y * normalTwo + b.z * normalThree) — instead of the
+     * flat calculateTriangleNormal (:164).  Needs a scene with vertex normals.  0 (default): the shipped behaviour. */
+    int32_t  smooth_normals;
 } srt_render_params;
 enum { SRT_LIGHTS_STAIRCASE = 0, SRT_LIGHTS_JITTERED = 1 };
 
@@ -220,6 +234,7 @@ typedef struct srt_mesh_desc {
     const float*   uv;            /* [n_tris][3][2]  colorOne/Two/ThreeCoordinate (texel space), or NULL = zeros      */
     const int32_t* tex;           /* [n_tris]        texture slot of Triangle::textureName or -1; NULL = all -1       */
     uint64_t       n_tris;
+    const float*   normals;       /* [n_tris][3][3]  normalOne / normalTwo / normalThree, or NULL (no smooth_normals)   */
 } srt_mesh_desc;
 int  srt_mesh_upload(srt_context* ctx, const srt_mesh_desc* desc, srt_mesh** out);
 void srt_mesh_destroy(srt_mesh* mesh);
@@ -247,6 +262,7 @@ int  srt_scene_counts(const srt_scene* scene, uint64_t* n_nodes, uint64_t* n_tri
                       uint32_t* max_depth);
 int  srt_scene_download(srt_context* ctx, const srt_scene* scene, srt_node* nodes, srt_tri_geom* geom, srt_tri_attr* attr,
                         srt_tri_geom* flat_geom, srt_tri_attr* flat_attr, srt_object* objects);
+int  srt_scene_download_vnormals(srt_context* ctx, const srt_scene* scene, srt_tri_vnormal* vnormal, srt_tri_vnormal* flat_vnormal);
 
 /* ---- render: the replacement for sendRaysAndIntersectPointsColors :505 ---- */
 /* Asynchronous on the context stream; call srt_sync before reading host outputs. */
@@ -288,8 +304,11 @@ const char* srt_last_error(void);
  *   SRT_LEAF_PHONG     in  n[3], d[3], light[3], light_color[3], obj_color[3],
  *                          ambient, specular, shininess, t                                 out rgb[3]              (:144-200)
  *   SRT_LEAF_TONE      in  c, tone_k, gamma                                                out q (0..255)          (:391-398, :447-449)
+ *   SRT_LEAF_SMOOTH_NORMAL in p0[3], e1[3], e2[3], n1[3], n2[3], n3[3], P[3]                       out n[3]
+ *                      (interpolateNormal :132-140 at the barycentric coordinates :79-117 of P)
  */
-enum { SRT_LEAF_POWF = 0, SRT_LEAF_SLAB = 1, SRT_LEAF_TRIANGLE = 2, SRT_LEAF_PHONG = 3, SRT_LEAF_TONE = 4 };
+enum { SRT_LEAF_POWF = 0, SRT_LEAF_SLAB = 1, SRT_LEAF_TRIANGLE = 2, SRT_LEAF_PHONG = 3, SRT_LEAF_TONE = 4,
+       SRT_LEAF_SMOOTH_NORMAL = 5 };
 int  srt_eval_leaf(srt_context* ctx, int op, const float* in, float* out, size_t n);
 
 #ifdef __cplusplus

@@ -37,6 +37,7 @@ struct FlatScene {
     std::vector<srt_tri_attr> attr;
     std::vector<srt_tri_geom> flat_geom;  // objTriangles load order (legacy one-box path), optional
     std::vector<srt_tri_attr> flat_attr;
+    std::vector<srt_tri_vnormal> vnormal, flat_vnormal;   // vertex normals (smooth_normals), same orders
     std::vector<srt_object>   objects;
     std::vector<srt_texture_desc> textures;
     std::vector<std::string>  object_names;
@@ -54,6 +55,8 @@ struct FlatScene {
         d.objects = objects.data();      d.n_objects = (uint32_t)objects.size();
         d.textures = textures.empty() ? nullptr : textures.data();
         d.n_textures = (uint32_t)textures.size();
+        d.vnormal = vnormal.size() == geom.size() && !vnormal.empty() ? vnormal.data() : nullptr;
+        d.flat_vnormal = flat_vnormal.size() == flat_geom.size() && !flat_vnormal.empty() ? flat_vnormal.data() : nullptr;
         return d;
     }
 };
@@ -93,6 +96,14 @@ inline void fill_triangle(const Tri& t, int32_t obj, int32_t tex, srt_tri_geom& 
     a.uv[1][0] = t.colorTwoCoordinate.x;   a.uv[1][1] = t.colorTwoCoordinate.y;
     a.uv[2][0] = t.colorThreeCoordinate.x; a.uv[2][1] = t.colorThreeCoordinate.y;
     a.pad1[0] = a.pad1[1] = 0.0f;
+}
+
+// Triangle::normalOne/Two/Three as stored (never transformed by the reference).
+template <class Tri>
+inline void fill_vnormal(const Tri& t, srt_tri_vnormal& v) {
+    v.n[0][0] = t.normalOne.x;   v.n[0][1] = t.normalOne.y;   v.n[0][2] = t.normalOne.z;   v.n[0][3] = 0.f;
+    v.n[1][0] = t.normalTwo.x;   v.n[1][1] = t.normalTwo.y;   v.n[1][2] = t.normalTwo.z;   v.n[1][3] = 0.f;
+    v.n[2][0] = t.normalThree.x; v.n[2][1] = t.normalThree.y; v.n[2][2] = t.normalThree.z; v.n[2][3] = 0.f;
 }
 
 template <class OM>
@@ -141,8 +152,9 @@ struct Flattener {
             for (const auto& t : n->triangles) {
                 int32_t tex = texture_of(t.textureName);
                 if (tex == -2) return false;
-                fs.geom.emplace_back(); fs.attr.emplace_back();
+                fs.geom.emplace_back(); fs.attr.emplace_back(); fs.vnormal.emplace_back();
                 fill_triangle(t, obj, tex, fs.geom.back(), fs.attr.back());
+                fill_vnormal(t, fs.vnormal.back());
             }
             fs.nodes[me].a = first;
             fs.nodes[me].b = SRT_LEAF_BIT | (uint32_t)n->triangles.size();
@@ -215,8 +227,9 @@ int flatten(OM& om, FlatScene& fs, bool with_flat_lists = false, std::string* er
                     if (err) *err = "object '" + name + "': " + fl.err;
                     return SRT_ERR_SCENE;
                 }
-                fs.flat_geom.emplace_back(); fs.flat_attr.emplace_back();
+                fs.flat_geom.emplace_back(); fs.flat_attr.emplace_back(); fs.flat_vnormal.emplace_back();
                 detail::fill_triangle(t, obj, tex, fs.flat_geom.back(), fs.flat_attr.back());
+                detail::fill_vnormal(t, fs.flat_vnormal.back());
             }
             if (pair.second.size() != o.tri_count) {
                 // createBoundingHierarchy copies objTriangles[name] (Object.cpp:277-281); a later

@@ -55,7 +55,7 @@ public:
         for (const auto& pair : om.objTriangles) {
             const std::string& name = pair.first;
             const auto& tris = pair.second;
-            std::vector<float> pts(tris.size() * 12), uv(tris.size() * 6);
+            std::vector<float> pts(tris.size() * 12), uv(tris.size() * 6), vn(tris.size() * 9);
             std::vector<int32_t> tex(tris.size(), -1);
             bool textured = false;
             size_t i = 0;
@@ -68,6 +68,10 @@ public:
                 c[0] = t.colorOneCoordinate.x;   c[1] = t.colorOneCoordinate.y;
                 c[2] = t.colorTwoCoordinate.x;   c[3] = t.colorTwoCoordinate.y;
                 c[4] = t.colorThreeCoordinate.x; c[5] = t.colorThreeCoordinate.y;
+                float* n = &vn[9 * i];
+                n[0] = t.normalOne.x;   n[1] = t.normalOne.y;   n[2] = t.normalOne.z;
+                n[3] = t.normalTwo.x;   n[4] = t.normalTwo.y;   n[5] = t.normalTwo.z;
+                n[6] = t.normalThree.x; n[7] = t.normalThree.y; n[8] = t.normalThree.z;
                 if (!t.textureName.empty()) { tex[i] = textureSlot(om, t.textureName); textured = true; }
                 ++i;
             }
@@ -75,6 +79,7 @@ public:
             d.points = pts.data(); d.n_tris = tris.size();
             d.uv = textured ? uv.data() : nullptr;
             d.tex = textured ? tex.data() : nullptr;
+            d.normals = vn.data();
             srt_mesh* m = nullptr;
             check(srt_mesh_upload(ctx_, &d, &m));
             auto old = meshes_.find(name);

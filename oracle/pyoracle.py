@@ -65,6 +65,8 @@ def oracle_lib():
         lib.srt_oracle_light_positions.argtypes = [_f32p, C.c_int, C.c_float, _f32p]
         lib.srt_oracle_light_positions_mode.argtypes = [C.POINTER(_abi.RenderParams), _f32p]
         lib.srt_oracle_light_positions_mode.restype = None
+        lib.srt_oracle_smooth_normal.argtypes = [_f32p, _f32p, _f32p, _f32p, _f32p, _f32p]
+        lib.srt_oracle_smooth_normal.restype = None
         _oracle = lib
     return _oracle
 
@@ -163,6 +165,7 @@ def ref_lib():
         lib.ref_leaf_slab.argtypes = [i32, _f32p, _f32p, _f32p, _f32p, C.POINTER(C.c_uint8)]
         lib.ref_leaf_slab_origin0.argtypes = [i32, _f32p, _f32p, _f32p, C.POINTER(C.c_uint8)]
         lib.ref_leaf_barycentric.argtypes = [i32, _f32p, _f32p, _f32p]
+        lib.ref_leaf_smooth_normal.argtypes = [i32, _f32p, _f32p, _f32p, _f32p]
         lib.ref_leaf_normal.argtypes = [i32, _f32p, _f32p]
         lib.ref_leaf_phong.argtypes = [i32] + [_f32p] * 7
         lib.ref_leaf_tonemap.argtypes = [i32, _f32p, _f32p, C.POINTER(C.c_int32)]

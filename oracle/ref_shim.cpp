@@ -348,6 +348,18 @@ void ref_leaf_barycentric(int n, const float* p12, const float* point3, float* o
         out3[3*i] = b.x; out3[3*i+1] = b.y; out3[3*i+2] = b.z;
     }
 }
+// interpolateNormal :132-140 at calculateBarycentricCoords(&t, point) :159 — the reference's own two functions; this
+// is the normal phongIllumination uses when its commented-out line :162 replaces :164.
+void ref_leaf_smooth_normal(int n, const float* p12, const float* normals9, const float* point3, float* out3) {
+    for (int i = 0; i < n; ++i) {
+        Triangle t = make_tri(p12 + 12 * i);
+        const float* m = normals9 + 9 * i;
+        t.normalOne = glm::vec3(m[0], m[1], m[2]); t.normalTwo = glm::vec3(m[3], m[4], m[5]); t.normalThree = glm::vec3(m[6], m[7], m[8]);
+        glm::vec3 b = calculateBarycentricCoords(&t, glm::vec3(point3[3*i], point3[3*i+1], point3[3*i+2]));
+        glm::vec3 v = interpolateNormal(t, b);
+        out3[3*i] = v.x; out3[3*i+1] = v.y; out3[3*i+2] = v.z;
+    }
+}
 void ref_leaf_normal(int n, const float* p12, float* out3) {
     for (int i = 0; i < n; ++i) {
         Triangle t = make_tri(p12 + 12 * i);

@@ -90,6 +90,16 @@ void srt_oracle_barycentric(const float p0[3], const float e1[3], const float e2
     out[0] = u; out[1] = v; out[2] = w;
 }
 
+/* interpolateNormal :132-140 at the barycentric coordinates of `point` (:159): the normal phongIllumination uses when
+ * its commented-out line :162 replaces :164.  n9 = normalOne, normalTwo, normalThree as loaded. */
+void srt_oracle_smooth_normal(const float p0[3], const float e1[3], const float e2[3], const float n9[9],
+                              const float point[3], float out[3]) {
+    float bc[3], s[3];
+    srt_oracle_barycentric(p0, e1, e2, point, bc);
+    for (int c = 0; c < 3; ++c) s[c] = (bc[0] * n9[c] + bc[1] * n9[3 + c]) + bc[2] * n9[6 + c];
+    normalize3(s, out);
+}
+
 /* phongIllumination, :144-200 with n = calculateTriangleNormal :32-37 precomputed. */
 void srt_oracle_phong(const float n[3], const float d[3], const float light[3], const float lc[3],
                       const float oc[3], float ambientStrength, float specularStrength, float shininess,
@@ -268,6 +278,14 @@ static void shade(const oracle_job* J, const oracle_hit* h, const float d[3], in
         base[0] = tx->rgb[idx + 0] / 255.0f; base[1] = tx->rgb[idx + 1] / 255.0f; base[2] = tx->rgb[idx + 2] / 255.0f;
         C->texel_fetches++;
     }
+    float nrm[3] = {a->n[0], a->n[1], a->n[2]};                              /* :164 */
+    if (pr->smooth_normals) {                                                /* :162 */
+        const srt_tri_vnormal* vn = use_flat ? &sc->flat_vnormal[h->tri] : &sc->vnormal[h->tri];
+        const float n9[9] = {vn->n[0][0], vn->n[0][1], vn->n[0][2], vn->n[1][0], vn->n[1][1], vn->n[1][2],
+                             vn->n[2][0], vn->n[2][1], vn->n[2][2]};
+        const float P[3] = {0.0f + t * d[0], 0.0f + t * d[1], 0.0f + t * d[2]};
+        srt_oracle_smooth_normal(g->p0, g->e1, g->e2, n9, P, nrm);
+    }
     float color[3] = {0.f, 0.f, 0.f};
     const float so[3] = {d[0] * t, d[1] * t, d[2] * t};                      /* :326 */
     for (int i = 0; i < pr->light_count; ++i) {                              /* :366 */
@@ -280,7 +298,7 @@ static void shade(const oracle_job* J, const oracle_hit* h, const float d[3], in
             if (sh) C->occluded++;
         }
         float c[3];
-        srt_oracle_phong(a->n, d, L, pr->light_color, base, ob->ambient, ob->specular, ob->shininess, t, c);
+        srt_oracle_phong(nrm, d, L, pr->light_color, base, ob->ambient, ob->specular, ob->shininess, t, c);
         C->lights_evaluated++;
         if (sh) { c[0] /= pr->shadow_div; c[1] /= pr->shadow_div; c[2] /= pr->shadow_div; }   /* :369 */
         color[0] += c[0]; color[1] += c[1]; color[2] += c[2];                /* :370 */
@@ -345,6 +363,7 @@ long srt_oracle_render(const srt_scene_desc* scene, const srt_render_params* par
     if (!scene || !params || !out) return -1;
     if (params->light_count < 0 || params->light_count > SRT_MAX_LIGHTS) return -1;
     if (!params->use_bvh && (!scene->flat_geom || !scene->flat_attr)) return -1;
+    if (params->smooth_normals && scene->n_objects > 0 && !(params->use_bvh ? scene->vnormal : scene->flat_vnormal)) return -1;
     oracle_job J;
     J.sc = scene; J.pr = params;
     srt_oracle_light_positions_mode(params, J.lights);

@@ -44,6 +44,7 @@ void  srt_oracle_phong(const float n[3], const float d[3], const float light[3],
                        float out[3]);
 void  srt_oracle_tonemap_quantise(const float color[3], float tone_k, float gamma, float out[3], int32_t q[3]);
 void  srt_oracle_light_positions(const float light_pos[3], int count, float step, float* out_xyz);
+void  srt_oracle_smooth_normal(const float p0[3], const float e1[3], const float e2[3], const float n9[9], const float point[3], float out[3]);
 void  srt_oracle_light_positions_mode(const srt_render_params* params, float* out_xyz);
 
 #ifdef __cplusplus

@@ -40,6 +40,8 @@ ATTR_DTYPE = np.dtype([("n", "<f4", 3), ("pad0", "<f4"), ("uv", "<f4", (3, 2)), 
 OBJECT_DTYPE = np.dtype([("color", "<f4", 3), ("ambient", "<f4"), ("specular", "<f4"), ("shininess", "<f4"),
                          ("root", "<u4"), ("tri_first", "<u4"), ("tri_count", "<u4"), ("flat_first", "<u4"),
                          ("box_min", "<f4", 3), ("box_max", "<f4", 3)])
+VNORMAL_DTYPE = np.dtype([("n", "<f4", (3, 4))])
+assert VNORMAL_DTYPE.itemsize == 48
 assert NODE_DTYPE.itemsize == 32 and GEOM_DTYPE.itemsize == 48 and ATTR_DTYPE.itemsize == 48
 assert OBJECT_DTYPE.itemsize == 64
 
@@ -55,6 +57,7 @@ class SceneDesc(C.Structure):
         ("flat_geom", C.c_void_p), ("flat_attr", C.c_void_p), ("n_flat", C.c_uint64),
         ("objects", C.c_void_p), ("n_objects", C.c_uint32),
         ("textures", C.POINTER(TextureDesc)), ("n_textures", C.c_uint32),
+        ("vnormal", C.c_void_p), ("flat_vnormal", C.c_void_p),
     ]
 
 
@@ -67,12 +70,13 @@ class RenderParams(C.Structure):
         ("use_bvh", C.c_int32), ("row_begin", C.c_int32), ("row_end", C.c_int32),
         ("variant", C.c_int32), ("no_sky_fill", C.c_int32), ("row_block", C.c_int32),
         ("shard_index", C.c_int32), ("shard_count", C.c_int32),
-        ("light_mode", C.c_int32), ("light_seed", C.c_uint32),
+        ("light_mode", C.c_int32), ("light_seed", C.c_uint32), ("smooth_normals", C.c_int32),
     ]
 
 
 class MeshDesc(C.Structure):
-    _fields_ = [("points", C.c_void_p), ("uv", C.c_void_p), ("tex", C.c_void_p), ("n_tris", C.c_uint64)]
+    _fields_ = [("points", C.c_void_p), ("uv", C.c_void_p), ("tex", C.c_void_p), ("n_tris", C.c_uint64),
+                ("normals", C.c_void_p)]
 
 
 class PrepObject(C.Structure):
@@ -117,7 +121,7 @@ class FlatSceneArrays:
     """Owner of the numpy arrays behind a SceneDesc (keeps them alive while C reads them)."""
 
     def __init__(self, nodes, geom, attr, objects, textures=(), flat_geom=None, flat_attr=None,
-                 object_names=(), texture_names=(), max_depth=0):
+                 object_names=(), texture_names=(), max_depth=0, vnormal=None, flat_vnormal=None):
         self.nodes = np.ascontiguousarray(nodes, dtype=NODE_DTYPE)
         self.geom = np.ascontiguousarray(geom, dtype=GEOM_DTYPE)
         self.attr = np.ascontiguousarray(attr, dtype=ATTR_DTYPE)
@@ -125,6 +129,8 @@ class FlatSceneArrays:
         self.textures = [np.ascontiguousarray(t, dtype=np.uint8) for t in textures]   # each [H][W][3]
         self.flat_geom = None if flat_geom is None else np.ascontiguousarray(flat_geom, dtype=GEOM_DTYPE)
         self.flat_attr = None if flat_attr is None else np.ascontiguousarray(flat_attr, dtype=ATTR_DTYPE)
+        self.vnormal = None if vnormal is None else np.ascontiguousarray(vnormal, dtype=VNORMAL_DTYPE)
+        self.flat_vnormal = None if flat_vnormal is None else np.ascontiguousarray(flat_vnormal, dtype=VNORMAL_DTYPE)
         self.object_names = list(object_names)
         self.texture_names = list(texture_names)
         self.max_depth = int(max_depth)
@@ -143,6 +149,10 @@ class FlatSceneArrays:
             d.n_flat = len(self.flat_geom)
         d.objects = self.objects.ctypes.data
         d.n_objects = len(self.objects)
+        if self.vnormal is not None and len(self.vnormal) == len(self.geom) and len(self.geom):
+            d.vnormal = self.vnormal.ctypes.data
+        if self.flat_vnormal is not None and d.n_flat and len(self.flat_vnormal) == d.n_flat:
+            d.flat_vnormal = self.flat_vnormal.ctypes.data
         if self.textures:
             arr = (TextureDesc * len(self.textures))()
             for i, t in enumerate(self.textures):
@@ -182,5 +192,7 @@ class FlatSceneArrays:
             t = d.textures[i]
             buf = (C.c_uint8 * (t.width * t.height * 3)).from_address(t.rgb)
             texs.append(np.frombuffer(buf, dtype=np.uint8).reshape(t.height, t.width, 3).copy())
+        vn = grab(d.vnormal, d.n_tris, VNORMAL_DTYPE) if d.vnormal else None
+        fvn = grab(d.flat_vnormal, d.n_flat, VNORMAL_DTYPE) if (d.flat_vnormal and d.n_flat) else None
         return FlatSceneArrays(nodes, geom, attr, objects, texs, flat_geom, flat_attr, object_names,
-                               texture_names, max_depth)
+                               texture_names, max_depth, vn, fvn)

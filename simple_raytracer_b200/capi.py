@@ -24,7 +24,7 @@ EXPORTS = [
     "srt_light_positions", "srt_host_alloc", "srt_host_free", "srt_device_alloc", "srt_device_free",
     "srt_last_error", "srt_eval_leaf", "srt_render_sparse", "srt_fetch_sparse",
     "srt_mesh_upload", "srt_mesh_destroy", "srt_mesh_info", "srt_scene_prep", "srt_scene_prep_status",
-    "srt_scene_counts", "srt_scene_download",
+    "srt_scene_counts", "srt_scene_download", "srt_scene_download_vnormals",
 ]
 
 
@@ -86,6 +86,7 @@ def lib():
         L.srt_scene_counts.argtypes = [vp, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64), C.POINTER(C.c_uint64),
                                        C.POINTER(C.c_uint32), C.POINTER(C.c_uint32)]
         L.srt_scene_download.argtypes = [vp, vp, vp, vp, vp, vp, vp, vp]
+        L.srt_scene_download_vnormals.argtypes = [vp, vp, vp, vp]
         _lib = L
     return _lib
 
@@ -154,8 +155,12 @@ class Scene:
         objs = np.zeros(c["n_objects"], _abi.OBJECT_DTYPE)
         _check(lib().srt_scene_download(self.ctx.h, self.h, nodes.ctypes.data, geom.ctypes.data, attr.ctypes.data,
                                         fgeom.ctypes.data, fattr.ctypes.data, objs.ctypes.data))
+        vn = np.zeros(c["n_tris"], _abi.VNORMAL_DTYPE)
+        fvn = np.zeros(c["n_flat"], _abi.VNORMAL_DTYPE)
+        have_vn = lib().srt_scene_download_vnormals(self.ctx.h, self.h, vn.ctypes.data, fvn.ctypes.data) == 0
         return _abi.FlatSceneArrays(nodes, geom, attr, objs, (), fgeom if len(fgeom) else None,
-                                    fattr if len(fattr) else None, max_depth=c["max_depth"])
+                                    fattr if len(fattr) else None, max_depth=c["max_depth"],
+                                    vnormal=vn if have_vn else None, flat_vnormal=fvn if (have_vn and len(fvn)) else None)
 
     def prep_status(self):
         """Synchronises; raises SrtError(SRT_ERR_UNSUPPORTED) if the last srt_scene_prep met a non-finite coordinate."""
@@ -176,7 +181,7 @@ class Scene:
 class Mesh:
     """Object-space triangles resident on the GPU (srt_mesh): what loadObjFile put into objTriangles[name]."""
 
-    def __init__(self, ctx: "Context", points, uv=None, tex=None):
+    def __init__(self, ctx: "Context", points, uv=None, tex=None, normals=None):
         pts = np.ascontiguousarray(points, np.float32).reshape(-1, 12)
         d = _abi.MeshDesc()
         d.points = pts.ctypes.data
@@ -189,6 +194,10 @@ class Mesh:
             tex = np.ascontiguousarray(tex, np.int32).reshape(-1)
             assert len(tex) == len(pts)
             d.tex = tex.ctypes.data
+        if normals is not None:
+            normals = np.ascontiguousarray(normals, np.float32).reshape(-1, 9)
+            assert len(normals) == len(pts)
+            d.normals = normals.ctypes.data
         h = C.c_void_p()
         _check(lib().srt_mesh_upload(ctx.h, C.byref(d), C.byref(h)))
         self.ctx, self.h, self.n_tris = ctx, h, len(pts)
@@ -313,8 +322,9 @@ class Context:
             pass
 
 
-LEAF_POWF, LEAF_SLAB, LEAF_TRIANGLE, LEAF_PHONG, LEAF_TONE = range(5)
-_LEAF_WIDTHS = {LEAF_POWF: (2, 1), LEAF_SLAB: (12, 3), LEAF_TRIANGLE: (15, 1), LEAF_PHONG: (19, 3), LEAF_TONE: (3, 1)}
+LEAF_POWF, LEAF_SLAB, LEAF_TRIANGLE, LEAF_PHONG, LEAF_TONE, LEAF_SMOOTH_NORMAL = range(6)
+_LEAF_WIDTHS = {LEAF_POWF: (2, 1), LEAF_SLAB: (12, 3), LEAF_TRIANGLE: (15, 1), LEAF_PHONG: (19, 3), LEAF_TONE: (3, 1),
+                LEAF_SMOOTH_NORMAL: (21, 3)}
 
 
 def eval_leaf(ctx: "Context", op: int, cases) -> np.ndarray:

@@ -303,6 +303,10 @@ int fill_scene(srt_context* c, srt_scene* s, const srt_scene_desc* d, bool textu
     if ((rc = copy_in(c, s->flat_geom, d->flat_geom, d->n_flat * sizeof(srt_tri_geom)))) return rc;
     if ((rc = copy_in(c, s->flat_attr, d->flat_attr, d->n_flat * sizeof(srt_tri_attr)))) return rc;
     if ((rc = copy_in(c, s->objects, d->objects, d->n_objects * sizeof(srt_object)))) return rc;
+    s->has_vnormal = d->vnormal != nullptr && d->n_tris > 0;
+    s->has_flat_vnormal = d->flat_vnormal != nullptr && d->n_flat > 0;
+    if (s->has_vnormal && (rc = copy_in(c, s->vnormal, d->vnormal, d->n_tris * sizeof(srt_tri_vnormal)))) return rc;
+    if (s->has_flat_vnormal && (rc = copy_in(c, s->flat_vnormal, d->flat_vnormal, d->n_flat * sizeof(srt_tri_vnormal)))) return rc;
     s->n_nodes = d->n_nodes; s->n_tris = d->n_tris; s->n_flat = d->n_flat; s->n_objects = d->n_objects;
     s->max_depth = depth;
     // device-internal traversal layout of the phased kernel: child boxes side by side, packed refs
@@ -374,6 +378,7 @@ void srt_scene_destroy(srt_scene* s) {
     if (s->ctx) { cudaSetDevice(s->ctx->device); cudaStreamSynchronize(s->ctx->stream); }
     s->nodes.release(); s->geom.release(); s->attr.release(); s->flat_geom.release(); s->flat_attr.release();
     s->objects.release(); s->texdesc.release(); s->wide.release(); s->root_ref.release();
+    s->vnormal.release(); s->flat_vnormal.release();
     for (auto& t : s->tex) t.release();
     srti_prep_state_destroy(s->prep);
     delete s;
@@ -397,6 +402,8 @@ int srt_render(srt_context* c, const srt_scene* s, const srt_render_params* p, c
     if (rb < 0 || re > p->height || rb > re) return fail(SRT_ERR_INVALID_ARG, "bad row range [%d,%d)", rb, re);
     if (!p->use_bvh && s->n_objects > 0 && s->n_flat == 0)
         return fail(SRT_ERR_INVALID_ARG, "use_bvh=0 (legacy one-box path) needs a scene flattened with load-order lists");
+    if (p->smooth_normals && s->n_objects > 0 && !(p->use_bvh ? s->has_vnormal : s->has_flat_vnormal))
+        return fail(SRT_ERR_INVALID_ARG, "smooth_normals needs a scene with vertex normals (srt_scene_desc::vnormal / srt_mesh_desc::normals)");
     CU(cudaSetDevice(c->device));
 
     srtk::KArgs a;
@@ -406,6 +413,9 @@ int srt_render(srt_context* c, const srt_scene* s, const srt_render_params* p, c
     a.attr = (const float4*)s->attr.p;
     a.flat_geom = (const float4*)s->flat_geom.p;
     a.flat_attr = (const float4*)s->flat_attr.p;
+    a.vnormal = s->has_vnormal ? (const float4*)s->vnormal.p : nullptr;
+    a.flat_vnormal = s->has_flat_vnormal ? (const float4*)s->flat_vnormal.p : nullptr;
+    a.smooth_normals = p->smooth_normals ? 1 : 0;
     a.objects = (const srt_object*)s->objects.p;
     a.textures = (const srtk::TexDev*)s->texdesc.p;
     a.n_objects = s->n_objects;

@@ -72,6 +72,8 @@ struct srt_context {
 struct srt_scene {
     srt_context* ctx = nullptr;
     srti::DevBuf nodes, geom, attr, flat_geom, flat_attr, objects, texdesc;
+    srti::DevBuf vnormal, flat_vnormal;           // optional vertex normals (smooth_normals)
+    bool has_vnormal = false, has_flat_vnormal = false;
     srti::DevBuf wide, root_ref;                        // device-internal traversal layout (srt_phased.cu)
     bool phased_ok = false;                       // leaf sizes / index ranges fit the packed traversal refs
     float coord_bound = 0.f;                      // max |coordinate| over the root boxes

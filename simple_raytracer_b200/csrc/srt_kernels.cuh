@@ -23,6 +23,9 @@ struct KArgs {
     const float4* attr;         // srt_tri_attr as 3 x float4
     const float4* flat_geom;    // load order (legacy one-box path) or null
     const float4* flat_attr;
+    const float4* vnormal;      // srt_tri_vnormal as 3 x float4 (leaf order) or null
+    const float4* flat_vnormal;
+    int32_t smooth_normals;     // 1: interpolateNormal :132-140 instead of the flat normal
     const srt_object* objects;
     const TexDev* textures;
     uint32_t n_objects;

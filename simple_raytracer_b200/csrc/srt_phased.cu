@@ -800,6 +800,12 @@ __global__ void eval_leaf_kernel(int op, const float* __restrict__ in, float* __
         break;
     }
     case SRT_LEAF_TONE: y[0] = (float)tone_quantise(x[0], x[1], x[2]); break;
+    case SRT_LEAF_SMOOTH_NORMAL: {
+        const V3 n = smooth_normal(v3(x[0], x[1], x[2]), v3(x[3], x[4], x[5]), v3(x[6], x[7], x[8]), make_float4(x[9], x[10], x[11], 0.f),
+                                   make_float4(x[12], x[13], x[14], 0.f), make_float4(x[15], x[16], x[17], 0.f), v3(x[18], x[19], x[20]));
+        y[0] = n.x; y[1] = n.y; y[2] = n.z;
+        break;
+    }
     default: break;
     }
 }
@@ -812,13 +818,14 @@ int leaf_in_width(int op) {
     case SRT_LEAF_TRIANGLE: return 15;
     case SRT_LEAF_PHONG: return 19;
     case SRT_LEAF_TONE: return 3;
+    case SRT_LEAF_SMOOTH_NORMAL: return 21;
     default: return 0;
     }
 }
 int leaf_out_width(int op) {
     switch (op) {
     case SRT_LEAF_POWF: case SRT_LEAF_TRIANGLE: case SRT_LEAF_TONE: return 1;
-    case SRT_LEAF_SLAB: case SRT_LEAF_PHONG: return 3;
+    case SRT_LEAF_SLAB: case SRT_LEAF_PHONG: case SRT_LEAF_SMOOTH_NORMAL: return 3;
     default: return 0;
     }
 }

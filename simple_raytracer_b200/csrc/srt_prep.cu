@@ -1012,15 +1012,26 @@ __device__ __forceinline__ void fill_triangle(const PrepArgs& a, const PrepObjec
     attr[2] = make_float4(t2.x, t2.y, 0.f, 0.f);
 }
 
+__device__ __forceinline__ void fill_vnormal(const PrepObject& o, uint32_t tri, float4* out) {
+    float n[9] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+    if (o.vn) for (int k = 0; k < 9; ++k) n[k] = o.vn[9 * (size_t)tri + k];
+    out[0] = make_float4(n[0], n[1], n[2], 0.f);
+    out[1] = make_float4(n[3], n[4], n[5], 0.f);
+    out[2] = make_float4(n[6], n[7], n[8], 0.f);
+}
+
 __global__ void __launch_bounds__(256) flatten_kernel(const PrepArgs a, const int flat_lists) {
     const PrepObject o = a.objects[blockIdx.y];
     const uint32_t j = blockIdx.x * 256u + threadIdx.x;
     if (j >= o.n_tris) return;
     const size_t g = (size_t)o.tri_base + j;
-    fill_triangle(a, o, blockIdx.y, a.order[g], a.geom + 3 * g, a.attr + 3 * g);
+    const uint32_t tri = a.order[g];
+    fill_triangle(a, o, blockIdx.y, tri, a.geom + 3 * g, a.attr + 3 * g);
+    fill_vnormal(o, tri, a.vnormal + 3 * g);
     if (flat_lists) {
         const size_t f = (size_t)o.flat_first + j;
         fill_triangle(a, o, blockIdx.y, j, a.flat_geom + 3 * f, a.flat_attr + 3 * f);
+        fill_vnormal(o, j, a.flat_vnormal + 3 * f);
     }
 }
 

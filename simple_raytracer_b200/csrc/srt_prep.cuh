@@ -21,6 +21,7 @@ struct PrepObject {            // one object of the frame (device copy of srt_pr
     const float4*   pts;       // mesh: [n_tris][3] points as loaded
     const float2*   uv;        // mesh: [n_tris][3] texel coordinates or null
     const int32_t*  tex;       // mesh: [n_tris] texture index or null
+    const float*    vn;        // mesh: [n_tris][9] vertex normals as loaded, or null (zeros, like a mesh without vn lines)
     const TopoNode* topo;      // mesh: [n_nodes]
     uint32_t n_tris, n_nodes;
     uint32_t tri_base, node_base, flat_first;
@@ -36,6 +37,7 @@ struct PrepArgs {
     const float* matrices;     // 16 floats each, column-major
     // scene arrays (outputs)
     float4* nodes; float4* geom; float4* attr; float4* flat_geom; float4* flat_attr;
+    float4* vnormal; float4* flat_vnormal;     // vertex normals in leaf / load order (copied, never transformed)
     srt_object* scene_objects;
     float* coord_bound;        // max |coordinate| over the root boxes
     uint32_t* status;          // bit 0: a transformed coordinate is not finite

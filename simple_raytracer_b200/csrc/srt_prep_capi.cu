@@ -18,8 +18,8 @@ using srti::fail;
 
 struct srt_mesh {
     srt_context* ctx = nullptr;
-    DevBuf pts, uv, tex, topo;
-    bool has_uv = false, has_tex = false;
+    DevBuf pts, uv, tex, topo, vn;
+    bool has_uv = false, has_tex = false, has_vn = false;
     uint64_t n_tris = 0;
     std::vector<srtp::TopoNode> topo_host;
     uint32_t max_depth = 0;
@@ -112,6 +112,7 @@ int srt_mesh_upload(srt_context* c, const srt_mesh_desc* d, srt_mesh** out) {
             if (d->tex[i] > m->max_tex) m->max_tex = d->tex[i];
         }
     }
+    if (!rc && d->normals) { rc = upload(c, m->vn, d->normals, d->n_tris * 9 * sizeof(float)); m->has_vn = d->n_tris > 0; }
     if (!rc) rc = upload(c, m->topo, m->topo_host.data(), m->topo_host.size() * sizeof(srtp::TopoNode));
     if (!rc) {
         cudaError_t e = cudaStreamSynchronize(c->stream);           // the host arrays may be freed on return
@@ -125,7 +126,7 @@ int srt_mesh_upload(srt_context* c, const srt_mesh_desc* d, srt_mesh** out) {
 void srt_mesh_destroy(srt_mesh* m) {
     if (!m) return;
     if (m->ctx) { cudaSetDevice(m->ctx->device); cudaStreamSynchronize(m->ctx->stream); }
-    m->pts.release(); m->uv.release(); m->tex.release(); m->topo.release();
+    m->pts.release(); m->uv.release(); m->tex.release(); m->topo.release(); m->vn.release();
     delete m;
 }
 
@@ -210,6 +211,8 @@ int srt_scene_prep(srt_context* c, const srt_prep_object* objs, uint32_t n_objec
     if ((rc = s->attr.reserve(N * sizeof(srt_tri_attr)))) return bail(rc);
     if ((rc = s->flat_geom.reserve(n_flat * sizeof(srt_tri_geom)))) return bail(rc);
     if ((rc = s->flat_attr.reserve(n_flat * sizeof(srt_tri_attr)))) return bail(rc);
+    if ((rc = s->vnormal.reserve(N * sizeof(srt_tri_vnormal)))) return bail(rc);
+    if ((rc = s->flat_vnormal.reserve(n_flat * sizeof(srt_tri_vnormal)))) return bail(rc);
     if ((rc = s->objects.reserve((size_t)n_objects * sizeof(srt_object)))) return bail(rc);
     if ((rc = s->wide.reserve(n_nodes * 64))) return bail(rc);
     if ((rc = s->root_ref.reserve((size_t)n_objects * sizeof(uint32_t)))) return bail(rc);
@@ -236,6 +239,7 @@ int srt_scene_prep(srt_context* c, const srt_prep_object* objs, uint32_t n_objec
         q.pts = (const float4*)m.pts.p;
         q.uv = m.has_uv ? (const float2*)m.uv.p : nullptr;
         q.tex = m.has_tex ? (const int32_t*)m.tex.p : nullptr;
+        q.vn = m.has_vn ? (const float*)m.vn.p : nullptr;
         q.topo = (const srtp::TopoNode*)m.topo.p;
         q.n_tris = (uint32_t)m.n_tris; q.n_nodes = (uint32_t)m.topo_host.size();
         q.tri_base = tri_base; q.node_base = node_base;
@@ -295,6 +299,7 @@ int srt_scene_prep(srt_context* c, const srt_prep_object* objs, uint32_t n_objec
     a.matrices = (const float*)(dblob + at_mat);
     a.nodes = (float4*)s->nodes.p; a.geom = (float4*)s->geom.p; a.attr = (float4*)s->attr.p;
     a.flat_geom = (float4*)s->flat_geom.p; a.flat_attr = (float4*)s->flat_attr.p;
+    a.vnormal = (float4*)s->vnormal.p; a.flat_vnormal = (float4*)s->flat_vnormal.p;
     a.scene_objects = (srt_object*)s->objects.p;
     a.rootacc = (unsigned long long*)(dblob + at_seeds);
     a.coord_bound = (float*)(dblob + at_seeds + 6 * (size_t)n_objects * 8);
@@ -395,7 +400,7 @@ int srt_scene_prep(srt_context* c, const srt_prep_object* objs, uint32_t n_objec
         std::vector<uint64_t> sig;
         auto put = [&](const void* ptr) { sig.push_back((uint64_t)(uintptr_t)ptr); };
         put(s->nodes.p); put(s->geom.p); put(s->attr.p); put(s->flat_geom.p); put(s->flat_attr.p); put(s->objects.p);
-        put(s->wide.p); put(s->root_ref.p); put(ps.xpts.p); put(ps.lite.p); put(ps.order.p); put(ps.key.p); put(ps.idx.p);
+        put(s->wide.p); put(s->root_ref.p); put(s->vnormal.p); put(s->flat_vnormal.p); put(ps.xpts.p); put(ps.lite.p); put(ps.order.p); put(ps.key.p); put(ps.idx.p);
         put(ps.posl.p); put(ps.posr.p); put(ps.segq.p); put(ps.blob.p); put(ps.wide.p); put(ps.misc.p); put(c->stream);
         sig.push_back(blob.size()); sig.push_back(n_objects); sig.push_back((uint64_t)(with_flat_lists != 0));
         sig.push_back((uint64_t)single_cta_big);
@@ -448,6 +453,7 @@ int srt_scene_prep(srt_context* c, const srt_prep_object* objs, uint32_t n_objec
     s->n_nodes = n_nodes; s->n_tris = n_tris; s->n_flat = n_flat; s->n_objects = n_objects;
     s->max_depth = max_depth;
     s->phased_ok = n_objects > 0;                                  // leaves hold at most 8 triangles by construction
+    s->has_vnormal = N > 0; s->has_flat_vnormal = n_flat > 0;      // (zeros for a mesh uploaded without normals)
     s->coord_bound = 0.f;
     s->coord_bound_dev = a.coord_bound;
     *scene = s;
@@ -482,6 +488,21 @@ int srt_scene_counts(const srt_scene* s, uint64_t* n_nodes, uint64_t* n_tris, ui
     if (n_flat) *n_flat = s->n_flat;
     if (n_objects) *n_objects = s->n_objects;
     if (max_depth) *max_depth = s->max_depth;
+    return SRT_OK;
+}
+
+int srt_scene_download_vnormals(srt_context* c, const srt_scene* s, srt_tri_vnormal* vnormal, srt_tri_vnormal* flat_vnormal) {
+    if (!c || !s || s->ctx != c) return fail(SRT_ERR_INVALID_ARG, "scene does not belong to this context");
+    CU(cudaSetDevice(c->device));
+    if (vnormal && s->n_tris) {
+        if (!s->has_vnormal) return fail(SRT_ERR_INVALID_ARG, "scene has no vertex normals");
+        CU(cudaMemcpyAsync(vnormal, s->vnormal.p, s->n_tris * sizeof(srt_tri_vnormal), cudaMemcpyDeviceToHost, c->stream));
+    }
+    if (flat_vnormal && s->n_flat) {
+        if (!s->has_flat_vnormal) return fail(SRT_ERR_INVALID_ARG, "scene has no load-order vertex normals");
+        CU(cudaMemcpyAsync(flat_vnormal, s->flat_vnormal.p, s->n_flat * sizeof(srt_tri_vnormal), cudaMemcpyDeviceToHost, c->stream));
+    }
+    CU(cudaStreamSynchronize(c->stream));
     return SRT_OK;
 }
 

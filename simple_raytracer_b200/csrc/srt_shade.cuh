@@ -11,6 +11,15 @@ struct Hit { float t; int32_t tri; int32_t obj; };
 
 __device__ __forceinline__ float4 ldg4(const float4* p) { return __ldg(p); }
 
+// interpolateNormal :132-140 at calculateBarycentricCoords(triangle, P) :159: (b.x * n1 + b.y * n2) + b.z * n3, normalised.
+__device__ __forceinline__ V3 smooth_normal(V3 p0, V3 e1, V3 e2, float4 n1, float4 n2, float4 n3, V3 P) {
+    const V3 bc = barycentric(p0, e1, e2, P);
+    const V3 s = v3(add(add(mul(bc.x, n1.x), mul(bc.y, n2.x)), mul(bc.z, n3.x)),
+                    add(add(mul(bc.x, n1.y), mul(bc.y, n2.y)), mul(bc.z, n3.y)),
+                    add(add(mul(bc.x, n1.z), mul(bc.y, n2.z)), mul(bc.z, n3.z)));
+    return normalize3(s);
+}
+
 // Base colour (:437-443, :350-361) and the light-independent part of phongIllumination.
 __device__ __forceinline__ PhongPixel prepare_pixel(const KArgs& a, const Hit& h, V3 d, bool use_flat) {
     const float4* gp = (use_flat ? a.flat_geom : a.geom) + 3 * (size_t)h.tri;
@@ -19,12 +28,17 @@ __device__ __forceinline__ PhongPixel prepare_pixel(const KArgs& a, const Hit& h
     const float4 a0 = ldg4(ap);
     const srt_object& ob = a.objects[h.obj];
     PhongPixel px;
-    px.n = v3(a0.x, a0.y, a0.z);
+    px.n = v3(a0.x, a0.y, a0.z);                                          // calculateTriangleNormal :164
     // ray->origin + distance * ray->direction, origin = (0,0,0)          :156 / :351
     px.P = v3(add(0.0f, mul(h.t, d.x)), add(0.0f, mul(h.t, d.y)), add(0.0f, mul(h.t, d.z)));
     px.v = normalize3(v3(-d.x, -d.y, -d.z));                              // :190
     px.oc = v3(ob.color[0], ob.color[1], ob.color[2]);                    // :439
     px.ambientStrength = ob.ambient; px.specularStrength = ob.specular; px.shininess = ob.shininess;
+    if (a.smooth_normals) {                                               // the commented-out line :162
+        const float4* np = (use_flat ? a.flat_vnormal : a.vnormal) + 3 * (size_t)h.tri;
+        px.n = smooth_normal(v3(g0.x, g0.y, g0.z), v3(g1.x, g1.y, g1.z), v3(g2.x, g2.y, g2.z), ldg4(np), ldg4(np + 1),
+                             ldg4(np + 2), px.P);
+    }
     const int32_t tex = __float_as_int(g1.w);
     if (tex >= 0) {                                                       // :350
         const float4 a1 = ldg4(ap + 1), a2 = ldg4(ap + 2);

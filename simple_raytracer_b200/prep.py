@@ -47,7 +47,7 @@ class MeshCache:
                 remap[k] = self.texture_names.index(name)
             tex = remap[slots] if len(names) else None
             uv = tris[:, 21:27] if len(names) else None
-            m = capi.Mesh(self.ctx, tris[:, 0:12], uv, tex)
+            m = capi.Mesh(self.ctx, tris[:, 0:12], uv, tex, normals=tris[:, 12:21])
         finally:
             hs.close()
         self.meshes[path] = m

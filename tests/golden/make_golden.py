@@ -118,6 +118,27 @@ def make_leaf_kat():
     print("leaf_kat.npz:", n, "cases;", int(np.isfinite(t).sum()), "triangle hits,", int(slab.sum()), "box hits")
 
 
+def make_smooth_normal_kat():
+    """leaf_smooth_normal.npz: the reference's interpolateNormal :132-140 at calculateBarycentricCoords :79-117 of the
+    committed leaf cases' points, with seeded vertex normals (unit, unnormalised, zero and degenerate ones)."""
+    lib = pyoracle.ref_lib()
+    kat = np.load(HERE / "leaf_kat.npz")
+    T, Pt = np.ascontiguousarray(kat["tri"]), np.ascontiguousarray(kat["point"])
+    n = len(T)
+    rng = np.random.default_rng(20240611)
+    N = rng.normal(0, 1, (n, 3, 3))
+    unit = rng.random(n) < 0.7
+    N[unit] /= np.linalg.norm(N[unit], axis=2, keepdims=True)
+    N[rng.random(n) < 0.02] = 0.0                       # a mesh without vn lines: normalize(0) = NaN, like the reference
+    same = rng.random(n) < 0.05
+    N[same, 1] = N[same, 0]; N[same, 2] = N[same, 0]    # flat-shaded export: three equal normals
+    N = np.ascontiguousarray(N.reshape(n, 9).astype(f32))
+    out = np.zeros((n, 3), f32)
+    lib.ref_leaf_smooth_normal(n, fp(T), fp(N), fp(Pt), fp(out))
+    np.savez_compressed(HERE / "leaf_smooth_normal.npz", tri=T, point=Pt, normals=N, out=out)
+    print("leaf_smooth_normal.npz:", n, "cases;", int(np.isfinite(out).all(axis=1).sum()), "finite")
+
+
 # (key, width, height, focal, lights, embed the flattened scene?)
 FRAMES = [
     ("C1", 96, 96, 75.0, 1, True),
@@ -153,5 +174,10 @@ def make_frames():
 
 
 if __name__ == "__main__":
-    make_leaf_kat()
-    make_frames()
+    import sys
+    if "--smooth-normal-only" in sys.argv:
+        make_smooth_normal_kat()
+    else:
+        make_leaf_kat()
+        make_smooth_normal_kat()
+        make_frames()

@@ -122,3 +122,12 @@ def test_powf_is_correctly_rounded_and_agrees_with_libm(gpu_ctx):
     sg = capi.eval_leaf(gpu_ctx, capi.LEAF_POWF, np.stack([sx, sy], axis=1))[:, 0]
     sh = np.array([libm.powf(float(a), float(b)) for a, b in zip(sx, sy)], f32)
     assert same_bits(sg, sh).all(), (sg, sh)
+
+
+def test_smooth_normal_equals_reference(gpu_ctx):
+    """interpolateNormal :132-140 at calculateBarycentricCoords :79-117 on the device against the reference's own two
+    functions (tests/golden/leaf_smooth_normal.npz): bit-identical, NaN for a mesh without normals like the reference."""
+    g = np.load(GOLDEN / "leaf_smooth_normal.npz")
+    p0, e1, e2 = tri_edges(g["tri"])
+    got = capi.eval_leaf(gpu_ctx, capi.LEAF_SMOOTH_NORMAL, np.hstack([p0, e1, e2, g["normals"], g["point"]]))
+    assert same_bits(got, g["out"]).all()

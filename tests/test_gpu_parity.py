@@ -10,7 +10,7 @@ import pytest
 
 from conftest import compare_images
 from oracle import pyoracle
-from simple_raytracer_b200 import _abi, scenes
+from simple_raytracer_b200 import _abi, capi, scenes
 
 pytestmark = [pytest.mark.gpu, pytest.mark.ref]
 
@@ -283,4 +283,39 @@ def test_jittered_light_samples_match_the_oracle_and_are_reproducible(gpu_ctx, r
     assert not np.array_equal(got["rgb"], base)
     p.light_seed = 43
     assert not np.array_equal(got["rgb"], gpu_ctx.render(sc, p)["rgb"])
+    sc.destroy()
+
+
+@pytest.mark.parametrize("key,lights", [("spheres", 4), ("C1", 1), ("C4", 2)])
+def test_smooth_normal_mode_matches_the_oracle(gpu_ctx, key, lights):
+    """smooth_normals = 1 (phongIllumination with its commented-out line :162: n = interpolateNormal)
+    on scenes whose meshes carry vertex normals: every kernel variant against the oracle; ids and t do not move."""
+    from simple_raytracer_b200 import host
+    cfg = scenes.CONFIGS[key]
+    hs = host.HostScene()
+    view = cfg.build(hs, 15.0)
+    light = scenes.light_view_space(hs, view) if view is not None else np.array(scenes.LIGHT_WORLD, np.float32)
+    arrays = hs.flatten(with_flat_lists=not cfg.use_bvh)
+    hs.close()
+    W, H, focal = scenes.scaled(cfg, 96)
+    p = _abi.default_params(W, H, focal, light, lights, cfg.use_bvh)
+    sc = gpu_ctx.upload(arrays)
+    flat = gpu_ctx.render(sc, p)
+    p.smooth_normals = 1
+    want = pyoracle.oracle_render(arrays, p)
+    for variant in ((0, 2, 4, 1) if cfg.use_bvh else (1,)):
+        p.variant = variant
+        got = gpu_ctx.render(sc, p)
+        assert np.array_equal(got["tri_id"], want["tri_id"]) and np.array_equal(got["t"], want["t"]), variant
+        assert np.abs(got["rgb"].astype(np.int32) - want["rgb"].astype(np.int32)).max() <= 1, variant
+    assert np.array_equal(got["tri_id"], flat["tri_id"]) and not np.array_equal(got["rgb"], flat["rgb"])
+    sc.destroy()
+    # a scene uploaded without vertex normals is refused, not shaded with garbage
+    bare = _abi.FlatSceneArrays(arrays.nodes, arrays.geom, arrays.attr, arrays.objects, arrays.textures, arrays.flat_geom,
+                                arrays.flat_attr)
+    sc = gpu_ctx.upload(bare)
+    p.variant = 0
+    with pytest.raises(capi.SrtError) as e:
+        gpu_ctx.render(sc, p)
+    assert e.value.code == _abi.SRT_ERR_INVALID_ARG
     sc.destroy()

@@ -43,6 +43,9 @@ def assert_same_scene(want: _abi.FlatSceneArrays, got: _abi.FlatSceneArrays, wan
     assert n == 0, f"{what}: {n} of {len(g_want)} triangles differ (leaf order), first {at}: want {g_want[at]} got {g_got[at]}"
     n, at = first_diff(want.attr, got.attr)
     assert n == 0, f"{what}: {n} attribute records differ, first {at}"
+    if want.vnormal is not None and got.vnormal is not None:
+        n, at = first_diff(want.vnormal, got.vnormal)
+        assert n == 0, f"{what}: {n} vertex-normal records differ, first {at}"
     if want.flat_geom is not None:
         assert got.flat_geom is not None and len(got.flat_geom) == len(want.flat_geom), what + ": load-order lists"
         fw, fg = want.flat_geom.copy(), got.flat_geom.copy()
@@ -104,6 +107,27 @@ def test_device_prepared_scene_renders_the_same_frame(gpu_ctx):
             for plane in ("rgb", "obj_id", "tri_id", "t"):
                 assert np.array_equal(a[plane], b[plane]), (variant, plane)
             assert a["stats"]["hit_pixels"] == b["stats"]["hit_pixels"] > 0
+        up.destroy()
+        sc.destroy()
+    finally:
+        cache.close()
+
+
+def test_device_prepared_scene_renders_smooth_normals(gpu_ctx):
+    """Vertex normals travel with the mesh and are re-ordered with the leaves: a device-prepared scene renders the
+    smooth-normal mode like the uploaded one."""
+    cache = prep.MeshCache(gpu_ctx)
+    try:
+        cfg, want, got, sc, light = both(gpu_ctx, cache, "spheres", 0.0)
+        assert want.vnormal is not None and got.vnormal is not None
+        p = _abi.default_params(180, 120, 120.0, light, 4, True)
+        p.smooth_normals = 1
+        up = gpu_ctx.upload(want)
+        a = gpu_ctx.render(up, p)
+        b = gpu_ctx.render(sc, p)
+        for plane in ("rgb", "obj_id", "tri_id", "t"):
+            assert np.array_equal(a[plane], b[plane]), plane
+        assert a["stats"]["hit_pixels"] > 0
         up.destroy()
         sc.destroy()
     finally:

@@ -133,3 +133,40 @@ def test_oracle_vs_live_reference_and_selfcheck(ref_scene):
         for k in ("rgb", "obj_id", "tri_id"):
             assert np.array_equal(want[k], got[k]), k
         assert same_bits(want["t"], got["t"])
+
+
+def test_smooth_normal_kat():
+    """interpolateNormal :132-140 at calculateBarycentricCoords :79-117: the oracle against the reference's own two
+    functions (tests/golden/leaf_smooth_normal.npz, generated by make_golden.py through oracle/_ref)."""
+    lib = pyoracle.oracle_lib()
+    g = np.load(GOLDEN / "leaf_smooth_normal.npz")
+    p0, e1, e2 = tri_edges(g["tri"])
+    n = len(p0)
+    got = np.zeros((n, 3), f32)
+    for i in range(n):
+        out = np.zeros(3, f32)
+        lib.srt_oracle_smooth_normal(fp(p0[i]), fp(e1[i]), fp(e2[i]), fp(np.ascontiguousarray(g["normals"][i])),
+                                     fp(np.ascontiguousarray(g["point"][i])), fp(out))
+        got[i] = out
+    assert same_bits(got, g["out"])
+    assert np.isfinite(g["out"]).all(axis=1).sum() > 2000
+
+
+def test_smooth_normal_frames_in_the_oracle():
+    """smooth_normals = 1 changes the shading and nothing else."""
+    from simple_raytracer_b200 import _abi, host, scenes
+    cfg = scenes.CONFIGS["spheres"]
+    hs = host.HostScene()
+    cfg.build(hs, 0.0)
+    arrays = hs.flatten()
+    hs.close()
+    assert arrays.vnormal is not None and len(arrays.vnormal) == len(arrays.geom)
+    assert np.abs(np.linalg.norm(arrays.vnormal["n"][:, :, :3], axis=2) - 1.0).max() < 1e-3     # sphere.obj ships unit normals
+    p = _abi.default_params(90, 60, 60.0, scenes.LIGHT_WORLD, 4, True)
+    flat = pyoracle.oracle_render(arrays, p)
+    p.smooth_normals = 1
+    smooth = pyoracle.oracle_render(arrays, p)
+    assert np.array_equal(flat["tri_id"], smooth["tri_id"]) and np.array_equal(flat["t"], smooth["t"])
+    hit = flat["tri_id"] >= 0
+    assert hit.sum() > 300 and (flat["rgb"][hit] != smooth["rgb"][hit]).any(axis=1).mean() > 0.5
+    assert np.array_equal(flat["rgb"][~hit], smooth["rgb"][~hit])
