@@ -244,7 +244,7 @@ def key_pattern(rng, n, kind):
 @pytest.mark.parametrize("kind,n", [
     ("random", 5000), ("few", 3000), ("ascending", 9001), ("descending_zeros", 12000), ("shared", 20000), ("zeros", 700),
     ("random", 17), ("random", 16), ("random", 9), ("random", 8), ("random", 3), ("random", 1), ("descending_zeros", 70000),
-    ("few", 70000), ("ascending", 50000), ("shared", 150000), ("random", 12289), ("random", 4097),
+    ("few", 70000), ("ascending", 50000), ("shared", 150000), ("random", 12289), ("random", 4097), ("shared", 400000),
 ])
 def test_sort_permutation_on_key_patterns(gpu_ctx, tmp_path, kind, n):
     """One object whose root sorts on a prescribed key sequence; no transform, so keys are exactly these."""
