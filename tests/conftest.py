@@ -88,8 +88,8 @@ _fixture_scene_cache = {}
 
 def scene_for_fixture(key, fx):
     """(arrays, light) for golden frame `key`: the embedded scene when the fixture carries one, else built
-    with this repo's host mirror from the staged assets (textured C4: through oracle/_ref, because the
-    mirror triangulates 7 n-gon faces of house.obj differently — DESIGN.md)."""
+    with this repo's host mirror from the staged assets (byte-identical to the reference-built scene, textured C4
+    included: tests/test_host_scene.py)."""
     from oracle import pyoracle
     from simple_raytracer_b200 import host, scenes
     if key in _fixture_scene_cache:
@@ -98,16 +98,11 @@ def scene_for_fixture(key, fx):
         out = (flat_from_fixture(fx), np.asarray(fx["light"], np.float32))
     else:
         cfg = scenes.CONFIGS[key]
-        if cfg.needs_textures:
-            if not pyoracle.ref_available():
-                pytest.skip("textured golden needs oracle/_ref (reference-built scene)")
-            b = pyoracle.RefBackend()
-        else:
-            try:
-                host.assets_dir()
-            except FileNotFoundError:
-                pytest.skip("staged assets not present")
-            b = host.HostScene()
+        try:
+            host.assets_dir()
+        except FileNotFoundError:
+            pytest.skip("staged assets not present")
+        b = host.HostScene()
         view = cfg.build(b, 0.0)
         light = scenes.light_view_space(b, view) if view is not None else np.array(scenes.LIGHT_WORLD, np.float32)
         out = (b.flatten(with_flat_lists=not cfg.use_bvh), np.asarray(light, np.float32))

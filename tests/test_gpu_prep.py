@@ -161,8 +161,7 @@ def test_device_prep_reuses_the_scene_across_frames(gpu_ctx):
 
 @pytest.mark.parametrize("angle", [0.0, 141.0])
 def test_device_prep_textured_multi_object(gpu_ctx, angle):
-    """C4 layout through the product's own OBJ reader on both sides (the earcut difference of house.obj against
-    tinyobjloader is a property of the reader, not of the prep)."""
+    """C4 layout (four textured meshes, house.obj with its ear-clipped faces) through the product's own OBJ reader."""
     cache = prep.MeshCache(gpu_ctx)
     try:
         cfg = scenes.CONFIGS["C4"]

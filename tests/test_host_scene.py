@@ -88,8 +88,8 @@ def test_mirror_flattens_byte_identical_to_reference(key):
 
 @pytest.mark.ref
 def test_mirror_series_frame_and_textured_scene():
-    """A rotated series frame (C5) is byte-identical; the textured scene is identical except house.obj,
-    whose 7 n-gon faces the mirror fan-triangulates (the reference uses earcut) — DESIGN.md open item."""
+    """A rotated series frame (C5) and the textured scene (C4) are byte-identical — including house.obj, whose
+    7 faces of more than four vertices go through the ear clipper (srt_polygon.cpp, tiny_obj_loader.h:1618)."""
     cfg = scenes.CONFIGS["C3"]
     rb = pyoracle.RefBackend(); cfg.build(rb, 37.5); ra = rb.flatten()
     hb = host.HostScene(); cfg.build(hb, 37.5); ha = hb.flatten()
@@ -101,10 +101,8 @@ def test_mirror_series_frame_and_textured_scene():
     assert ra.object_names == ha.object_names and ra.texture_names == ha.texture_names
     assert all(np.array_equal(a, b) for a, b in zip(ra.textures, ha.textures))       # sidecars == stb_image pixels
     assert np.array_equal(ra.objects.view(np.uint8), ha.objects.view(np.uint8))
-    house = ra.object_names.index("./obj/house/house.obj")
-    other = ra.geom["obj"] != house
-    assert np.array_equal(ra.geom[other].view(np.uint8), ha.geom[other].view(np.uint8))
-    assert np.array_equal(ra.attr[other].view(np.uint8), ha.attr[other].view(np.uint8))
+    for k in ("nodes", "geom", "attr"):
+        assert np.array_equal(getattr(ra, k).view(np.uint8), getattr(ha, k).view(np.uint8)), k
 
 
 def test_transformation_matrices():
@@ -230,3 +228,65 @@ def test_recorded_scene_script_matches_the_host_calls():
         ds.clone("nope.obj", "x.obj", False)
     ds.close()
     hs.close()
+
+
+def _polygon_faces(rng):
+    """Faces of 5-120 vertices in random planes (80 and more make the library index its nodes along a z-order curve): convex, star-shaped, combs, with repeated / collinear points, slightly
+    non-planar, self-crossing (the ear clipper's fallbacks), in a plane facing x, and collinear (dropped)."""
+    faces = []
+
+    def place(xy, wobble=0.0, facing_x=False):
+        xy = np.asarray(xy, np.float64)
+        if facing_x:
+            u, v, o = np.array([0, 1.0, 0]), np.array([0, 0, 1.0]), np.array([2.0, 0, 0])
+        else:
+            q, _ = np.linalg.qr(rng.normal(size=(3, 3)))
+            u, v, o = q[0], q[1], rng.normal(size=3) * 3
+        p = o + xy[:, :1] * u + xy[:, 1:] * v
+        if wobble:
+            p = p + rng.normal(size=p.shape) * wobble
+        faces.append(p.astype(np.float32))
+
+    for n in (5, 6, 7, 8, 11, 16, 33, 60, 80, 120):
+        ang = np.linspace(0, 2 * np.pi, n, endpoint=False)
+        place(np.c_[np.cos(ang), np.sin(ang)] * 2.0)                                     # convex
+        place(np.c_[np.cos(-ang), np.sin(-ang)] * 2.0, facing_x=True)                    # other winding, normal along x
+        r = np.where(np.arange(n) % 2 == 0, 2.0, 0.7)
+        place(np.c_[np.cos(ang) * r, np.sin(ang) * r])                                   # star
+        r = rng.uniform(0.3, 2.0, n)
+        place(np.c_[np.cos(ang) * r, np.sin(ang) * r], wobble=0.01)                      # star-shaped, off-plane
+        place(rng.uniform(-2, 2, (n, 2)))                                                # self-crossing
+    for teeth in (2, 3, 7):                                                              # comb: many reflex corners, collinear base
+        xs = np.arange(2 * teeth + 1, dtype=np.float64)
+        top = np.c_[xs, np.where(np.arange(2 * teeth + 1) % 2 == 0, 2.0, 0.5)]
+        base = np.c_[xs[::-1], np.zeros(2 * teeth + 1)]
+        place(np.r_[top, base])
+    sq = np.array([[0, 0], [1, 0], [2, 0], [2, 0], [2, 2], [1, 2], [0, 2], [0, 1]], np.float64)
+    place(sq); place(sq[::-1])                                                           # repeated + collinear points
+    place(np.array([[0, 0], [2, 2], [2, 0], [0, 2], [1, 3]], np.float64))                # bow tie with a cap
+    place(np.c_[np.arange(6.0), np.arange(6.0) * 0.5])                                   # collinear: zero normal
+    place(np.zeros((5, 2)))                                                              # one point five times
+    return faces
+
+
+@pytest.mark.ref
+def test_polygon_faces_triangulate_like_the_reference_loader(tmp_path):
+    """srt_polygon.cpp against tinyobjloader + mapbox earcut as the reference builds them (simple_raytracer.cpp:15-16):
+    same triangles in the same order for every face, bit for bit."""
+    rng = np.random.default_rng(20240611)
+    for rep in range(4):
+        faces = _polygon_faces(rng)
+        path = tmp_path / f"polys{rep}.obj"
+        with open(path, "w") as f:
+            base = 1
+            for p in faces:
+                for x, y, z in p:
+                    f.write(f"v {float(x)!r} {float(y)!r} {float(z)!r}\n")
+                f.write("f " + " ".join(str(base + k) for k in range(len(p))) + "\n")
+                base += len(p)
+        rb = pyoracle.RefBackend(); hb = host.HostScene()
+        n_ref = rb.load_obj(str(path)); n_ours = hb.load_obj(str(path))
+        assert n_ref == n_ours and n_ours > 0
+        rt, rf = rb.triangles(str(path)); ht, hf = hb.triangles(str(path))
+        assert rt.shape == ht.shape and len(rt) > 500
+        assert np.array_equal(rt.view(np.uint32), ht.view(np.uint32)) and np.array_equal(rf, hf)
