@@ -160,8 +160,25 @@ typedef struct srt_render_params {
      * barycentricCoords) :132-140 — normalize(b.x * normalOne + b.y * normalTwo + b.z * normalThree) — instead of the
      * flat calculateTriangleNormal (:164).  Needs a scene with vertex normals.  0 (default): the shipped behaviour. */
     int32_t  smooth_normals;
+    /* Quality switches the reference lacks.  All 0 = the shipped behaviour; none is a parity mode
+     * (the oracle restates them, tests compare against that):
+     * normalise_lights  1: the sum over the light samples (:370) is divided by light_count before tone mapping.
+     * shadow_segment    1: an occluder counts only where it lies between the point and the light sample,
+     *                   shadow_eps <= t <= 1 along shadowRay = light - point (:325-327); 0: any t >= 0 (an object
+     *                   BEHIND the light darkens the point, as shipped).
+     * texture_mode      how the interpolated texel coordinate (x, y) (:123-125; the scene carries the reference's
+     *                   per-vertex TEXEL coordinates, Object.cpp:113-119) addresses the image:
+     *                   SRT_TEX_TRUNCATE  texel ((int)x, (int)y) through the linear index of :357, index clamped to the image
+     *                                     where the reference would read out of bounds;
+     *                   SRT_TEX_NEAREST   texel (floor x mod width, floor y mod height): each axis wraps on its own;
+     *                   SRT_TEX_BILINEAR  blend of the four texels around (x, y) by its fractional parts, same wrapping. */
+    int32_t  normalise_lights;
+    int32_t  shadow_segment;
+    float    shadow_eps;
+    int32_t  texture_mode;
 } srt_render_params;
 enum { SRT_LIGHTS_STAIRCASE = 0, SRT_LIGHTS_JITTERED = 1 };
+enum { SRT_TEX_TRUNCATE = 0, SRT_TEX_NEAREST = 1, SRT_TEX_BILINEAR = 2 };
 
 enum { SRT_VARIANT_DEFAULT = 0,   /* staged pipeline: classify, primary, shadow, shade as stream-ordered launches; falls back to
                                      SIMPLE for the legacy one-box path */

@@ -67,6 +67,8 @@ def oracle_lib():
         lib.srt_oracle_light_positions_mode.restype = None
         lib.srt_oracle_smooth_normal.argtypes = [_f32p, _f32p, _f32p, _f32p, _f32p, _f32p]
         lib.srt_oracle_smooth_normal.restype = None
+        lib.srt_oracle_texture_sample.argtypes = [C.c_void_p, C.c_int32, C.c_int32, C.c_float, C.c_float, C.c_int32, _f32p]
+        lib.srt_oracle_texture_sample.restype = None
         _oracle = lib
     return _oracle
 

@@ -222,8 +222,11 @@ static void closest_in_object_flat(const oracle_job* J, uint32_t obj, const floa
 }
 
 /* shadowIntersection :321-342: any Moeller-Trumbore hit (any t >= 0) on a candidate triangle of
- * any OTHER object; the own object's traversal (:328, discarded at :331) is skipped. */
+ * any OTHER object; the own object's traversal (:328, discarded at :331) is skipped.
+ * srt_render_params::shadow_segment (not a reference mode): only hits with shadow_eps <= t <= 1 count. */
 static int shadowed(const oracle_job* J, int32_t own, const float so[3], const float sd[3], srt_oracle_counters* C) {
+    const int segment = J->pr->shadow_segment != 0;
+    const float t_lo = J->pr->shadow_eps, t_hi = 1.0f;
     const srt_node* nodes = J->sc->nodes;
     const srt_tri_geom* geom = J->sc->geom;
     for (uint32_t obj = 0; obj < J->sc->n_objects; ++obj) {
@@ -242,7 +245,8 @@ static int shadowed(const oracle_job* J, int32_t own, const float so[3], const f
                     for (uint32_t k = 0; k < cnt; ++k) {
                         const srt_tri_geom* g = &geom[n->a + k];
                         C->tri_tests_shadow++;
-                        if (srt_oracle_moller_trumbore(so, sd, g->p0, g->e1, g->e2) != -INFINITY) return 1;
+                        const float ts = srt_oracle_moller_trumbore(so, sd, g->p0, g->e1, g->e2);
+                        if (ts != -INFINITY && (!segment || (!(ts < t_lo) && !(ts > t_hi)))) return 1;
                     }
                     break;
                 }
@@ -252,6 +256,37 @@ static int shadowed(const oracle_job* J, int32_t own, const float so[3], const f
         }
     }
     return 0;
+}
+
+/* srt_render_params::texture_mode NEAREST / BILINEAR (not reference modes; srt.h): (x, y) is the interpolated texel
+ * coordinate; every axis wraps on its own (floor, then mod).  Bilinear: the texel values / 255 are blended in x, then in
+ * y, with the fractional parts of (x, y): (c00 * (1 - fx) + c10 * fx) * (1 - fy) + (c01 * (1 - fx) + c11 * fx) * fy. */
+static int wrap_index(float f, int n) {
+    if (!(f > -1.0e9f && f < 1.0e9f)) return 0;          /* NaN / huge: texel 0 */
+    int i = (int)f % n;
+    if (i < 0) i += n;
+    return i;
+}
+void srt_oracle_texture_sample(const uint8_t* rgb, int32_t width, int32_t height, float x, float y, int32_t mode, float out[3]) {
+    const float x0f = floorf(x), y0f = floorf(y);
+    const int x0 = wrap_index(x0f, width), y0 = wrap_index(y0f, height);
+    if (mode == SRT_TEX_NEAREST) {
+        const uint8_t* p = rgb + ((long)y0 * width + x0) * 3;
+        out[0] = p[0] / 255.0f; out[1] = p[1] / 255.0f; out[2] = p[2] / 255.0f;
+        return;
+    }
+    const int x1 = x0 + 1 == width ? 0 : x0 + 1, y1 = y0 + 1 == height ? 0 : y0 + 1;
+    float fx = x - x0f, fy = y - y0f;
+    if (!(fx >= 0.0f && fx <= 1.0f)) fx = 0.0f;
+    if (!(fy >= 0.0f && fy <= 1.0f)) fy = 0.0f;
+    const float gx = 1.0f - fx, gy = 1.0f - fy;
+    const uint8_t* p00 = rgb + ((long)y0 * width + x0) * 3; const uint8_t* p10 = rgb + ((long)y0 * width + x1) * 3;
+    const uint8_t* p01 = rgb + ((long)y1 * width + x0) * 3; const uint8_t* p11 = rgb + ((long)y1 * width + x1) * 3;
+    for (int c = 0; c < 3; ++c) {
+        const float top = (p00[c] / 255.0f) * gx + (p10[c] / 255.0f) * fx;
+        const float bot = (p01[c] / 255.0f) * gx + (p11[c] / 255.0f) * fx;
+        out[c] = top * gy + bot * fy;
+    }
 }
 
 /* softShadow :348-401 for the winning hit, then quantisation :447-449. */
@@ -271,11 +306,15 @@ static void shade(const oracle_job* J, const oracle_hit* h, const float d[3], in
         srt_oracle_barycentric(g->p0, g->e1, g->e2, P, bc);
         const float ux = bc[0] * a->uv[0][0] + bc[1] * a->uv[1][0] + bc[2] * a->uv[2][0];   /* :123-125 */
         const float uy = bc[0] * a->uv[0][1] + bc[1] * a->uv[1][1] + bc[2] * a->uv[2][1];
-        long idx = ((long)((int)uy * tx->width + (int)ux)) * 3;              /* :357 */
-        const long last = ((long)tx->width * tx->height - 1) * 3;
-        if (idx < 0) idx = 0;                 /* the reference reads out of bounds here (UB); clamp */
-        if (idx > last) idx = last;
-        base[0] = tx->rgb[idx + 0] / 255.0f; base[1] = tx->rgb[idx + 1] / 255.0f; base[2] = tx->rgb[idx + 2] / 255.0f;
+        if (pr->texture_mode == SRT_TEX_TRUNCATE) {
+            long idx = ((long)((int)uy * tx->width + (int)ux)) * 3;          /* :357 */
+            const long last = ((long)tx->width * tx->height - 1) * 3;
+            if (idx < 0) idx = 0;             /* the reference reads out of bounds here (UB); clamp */
+            if (idx > last) idx = last;
+            base[0] = tx->rgb[idx + 0] / 255.0f; base[1] = tx->rgb[idx + 1] / 255.0f; base[2] = tx->rgb[idx + 2] / 255.0f;
+        } else {
+            srt_oracle_texture_sample(tx->rgb, tx->width, tx->height, ux, uy, pr->texture_mode, base);
+        }
         C->texel_fetches++;
     }
     float nrm[3] = {a->n[0], a->n[1], a->n[2]};                              /* :164 */
@@ -302,6 +341,10 @@ static void shade(const oracle_job* J, const oracle_hit* h, const float d[3], in
         C->lights_evaluated++;
         if (sh) { c[0] /= pr->shadow_div; c[1] /= pr->shadow_div; c[2] /= pr->shadow_div; }   /* :369 */
         color[0] += c[0]; color[1] += c[1]; color[2] += c[2];                /* :370 */
+    }
+    if (pr->normalise_lights && pr->light_count > 0) {                       /* not a reference mode */
+        const float n = (float)pr->light_count;
+        color[0] /= n; color[1] /= n; color[2] /= n;
     }
     float tm[3]; int32_t q[3];
     srt_oracle_tonemap_quantise(color, pr->tone_k, pr->gamma, tm, q);

@@ -42,6 +42,7 @@ void  srt_oracle_barycentric(const float p0[3], const float e1[3], const float e
 void  srt_oracle_phong(const float n[3], const float d[3], const float light[3], const float light_color[3],
                        const float obj_color[3], float ambient, float specular, float shininess, float t,
                        float out[3]);
+void  srt_oracle_texture_sample(const uint8_t* rgb, int32_t width, int32_t height, float x, float y, int32_t mode, float out[3]);
 void  srt_oracle_tonemap_quantise(const float color[3], float tone_k, float gamma, float out[3], int32_t q[3]);
 void  srt_oracle_light_positions(const float light_pos[3], int count, float step, float* out_xyz);
 void  srt_oracle_smooth_normal(const float p0[3], const float e1[3], const float e2[3], const float n9[9], const float point[3], float out[3]);

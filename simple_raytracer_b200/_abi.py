@@ -23,6 +23,7 @@ SRT_ERR_UNSUPPORTED = -6
 
 LIGHTS_STAIRCASE = 0      # the reference's sequence (parity)
 LIGHTS_JITTERED = 1       # counter-based jittered samples in the staircase's box (not a reference mode)
+TEX_TRUNCATE, TEX_NEAREST, TEX_BILINEAR = 0, 1, 2     # srt_render_params::texture_mode
 
 VARIANT_DEFAULT = 0
 VARIANT_SIMPLE = 1
@@ -71,6 +72,7 @@ class RenderParams(C.Structure):
         ("variant", C.c_int32), ("no_sky_fill", C.c_int32), ("row_block", C.c_int32),
         ("shard_index", C.c_int32), ("shard_count", C.c_int32),
         ("light_mode", C.c_int32), ("light_seed", C.c_uint32), ("smooth_normals", C.c_int32),
+        ("normalise_lights", C.c_int32), ("shadow_segment", C.c_int32), ("shadow_eps", C.c_float), ("texture_mode", C.c_int32),
     ]
 
 

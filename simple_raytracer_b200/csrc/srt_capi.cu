@@ -404,6 +404,10 @@ int srt_render(srt_context* c, const srt_scene* s, const srt_render_params* p, c
         return fail(SRT_ERR_INVALID_ARG, "use_bvh=0 (legacy one-box path) needs a scene flattened with load-order lists");
     if (p->smooth_normals && s->n_objects > 0 && !(p->use_bvh ? s->has_vnormal : s->has_flat_vnormal))
         return fail(SRT_ERR_INVALID_ARG, "smooth_normals needs a scene with vertex normals (srt_scene_desc::vnormal / srt_mesh_desc::normals)");
+    if (p->texture_mode < SRT_TEX_TRUNCATE || p->texture_mode > SRT_TEX_BILINEAR)
+        return fail(SRT_ERR_INVALID_ARG, "unknown texture_mode %d", p->texture_mode);
+    if (p->shadow_segment && !(p->shadow_eps >= 0.0f && p->shadow_eps <= 1.0f))
+        return fail(SRT_ERR_INVALID_ARG, "shadow_eps %g outside [0,1]", (double)p->shadow_eps);
     CU(cudaSetDevice(c->device));
 
     srtk::KArgs a;
@@ -416,6 +420,10 @@ int srt_render(srt_context* c, const srt_scene* s, const srt_render_params* p, c
     a.vnormal = s->has_vnormal ? (const float4*)s->vnormal.p : nullptr;
     a.flat_vnormal = s->has_flat_vnormal ? (const float4*)s->flat_vnormal.p : nullptr;
     a.smooth_normals = p->smooth_normals ? 1 : 0;
+    a.normalise_lights = p->normalise_lights ? 1 : 0;
+    a.texture_mode = p->texture_mode;
+    a.shadow_t_lo = p->shadow_segment ? p->shadow_eps : -INFINITY;
+    a.shadow_t_hi = p->shadow_segment ? 1.0f : INFINITY;
     a.objects = (const srt_object*)s->objects.p;
     a.textures = (const srtk::TexDev*)s->texdesc.p;
     a.n_objects = s->n_objects;

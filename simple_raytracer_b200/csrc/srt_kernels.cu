@@ -91,7 +91,8 @@ __device__ __forceinline__ bool any_hit_in_tree(const KArgs& a, uint32_t root, V
                 for (uint32_t k = 0; k < cnt; ++k) {
                     const float4* g = a.geom + 3 * (size_t)(na + k);
                     if (COUNT) ++tris_seen;
-                    if (moller_trumbore(o, d, ldg4(g), ldg4(g + 1), ldg4(g + 2)) != -INFINITY) return true;
+                    const float ts = moller_trumbore(o, d, ldg4(g), ldg4(g + 1), ldg4(g + 2));
+                    if (ts != -INFINITY && !(ts < a.shadow_t_lo) && !(ts > a.shadow_t_hi)) return true;
                 }
             } else {
                 stack[sp++] = na;
@@ -151,6 +152,7 @@ __global__ void __launch_bounds__(128) render_simple(const __grid_constant__ KAr
                 if (shadowed) { c.x = dvd(c.x, a.shadow_div); c.y = dvd(c.y, a.shadow_div); c.z = dvd(c.z, a.shadow_div); }  // :369
                 color.x = add(color.x, c.x); color.y = add(color.y, c.y); color.z = add(color.z, c.z);   // :370
             }
+            if (a.normalise_lights) color = average_lights(color, a.light_count);
         }
         store_pixel(a, px, py, hit, color, h);
         if (TIMELINE) {   // debugging aid: per-tile cost map instead of the id / t planes

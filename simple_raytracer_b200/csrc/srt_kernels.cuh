@@ -26,6 +26,9 @@ struct KArgs {
     const float4* vnormal;      // srt_tri_vnormal as 3 x float4 (leaf order) or null
     const float4* flat_vnormal;
     int32_t smooth_normals;     // 1: interpolateNormal :132-140 instead of the flat normal
+    int32_t normalise_lights;   // 1: light sum / light_count before tone mapping
+    int32_t texture_mode;       // SRT_TEX_*
+    float shadow_t_lo, shadow_t_hi;   // an occluder counts for t in [lo, hi]: (-inf, +inf) as shipped, (eps, 1) with shadow_segment
     const srt_object* objects;
     const TexDev* textures;
     uint32_t n_objects;

@@ -224,7 +224,9 @@ __device__ __forceinline__ void trace_closest(const KArgs& a, const FRay& r, Sta
 // Any hit (shadowIntersection :321-342): true as soon as one candidate triangle reports t >= 0.
 // Order is free for a boolean; children are visited nearest-entry-first, boxes wholly behind the
 // origin last, so occluded rays usually stop after a few leaves.
-template <bool COUNT = false>
+// RANGED (srt_render_params::shadow_segment): only hits with shadow_t_lo <= t <= shadow_t_hi count; the box tests stay
+// the unbounded ones (a superset).  Compiled separately so that the shipped rule pays nothing for the switch.
+template <bool COUNT = false, bool RANGED = false>
 __device__ __forceinline__ bool trace_any(const KArgs& a, const FRay& r, Stack& st, unsigned& exact_count, unsigned* boxes = nullptr) {
     uint32_t ref = st.pop();
     while (ref != kRefNone) {
@@ -249,7 +251,8 @@ __device__ __forceinline__ bool trace_any(const KArgs& a, const FRay& r, Stack& 
             bool found = false;
             for (uint32_t k = 0; k < cnt; ++k) {
                 const float4* g = a.geom + 3 * (size_t)(first + k);
-                if (moller_trumbore(r.o, r.d, ldg4(g), ldg4(g + 1), ldg4(g + 2)) != -INFINITY) found = true;
+                const float ts = moller_trumbore(r.o, r.d, ldg4(g), ldg4(g + 1), ldg4(g + 2));
+                if (ts != -INFINITY && (!RANGED || (!(ts < a.shadow_t_lo) && !(ts > a.shadow_t_hi)))) found = true;
             }
             if (found) return true;
             ref = st.pop();
@@ -423,7 +426,8 @@ __device__ __forceinline__ void shadow_item(const KArgs& a, Stack& st, unsigned 
     const FRay s = make_fray(so, sd, coord_bound_of(a));
     if (mine) push_roots(a, s, st, obj, exact_count);
     unsigned boxes = 0;
-    const bool occluded = trace_any<COUNT>(a, s, st, exact_count, &boxes);
+    const bool ranged = a.shadow_t_hi != INFINITY;     // uniform over the launch
+    const bool occluded = ranged ? trace_any<COUNT, true>(a, s, st, exact_count, &boxes) : trace_any<COUNT, false>(a, s, st, exact_count, &boxes);
     if (COUNT) { if (occluded) *box_occluded += boxes; else *box_free += boxes; }
     const unsigned ballot = __ballot_sync(kFull, mine && occluded);
     if (lane == 0) a.shadow_mask[(size_t)tile * a.light_count + light] = ballot;
@@ -446,6 +450,7 @@ __device__ __forceinline__ void shade_pixel(const KArgs& a, const Pixel& p, cons
             if (shadowed) { c.x = dvd(c.x, a.shadow_div); c.y = dvd(c.y, a.shadow_div); c.z = dvd(c.z, a.shadow_div); }  // :369
             color.x = add(color.x, c.x); color.y = add(color.y, c.y); color.z = add(color.z, c.z);   // :370
         }
+        if (a.normalise_lights) color = average_lights(color, a.light_count);
     }
     store_pixel(a, p.px, p.py, hit, color, h, false);   // ids / t planes were written with the hit record
 }

@@ -20,6 +20,38 @@ __device__ __forceinline__ V3 smooth_normal(V3 p0, V3 e1, V3 e2, float4 n1, floa
     return normalize3(s);
 }
 
+// srt_render_params::normalise_lights: the light sum divided by the number of samples.
+__device__ __forceinline__ V3 average_lights(V3 c, int n) {
+    const float f = (float)n;
+    return n > 0 ? v3(dvd(c.x, f), dvd(c.y, f), dvd(c.z, f)) : c;
+}
+
+// srt_render_params::texture_mode NEAREST / BILINEAR (srt.h): wrapped addressing of the texel coordinate (x, y).
+__device__ __forceinline__ int wrap_index(float f, int n) {
+    if (!(f > -1.0e9f && f < 1.0e9f)) return 0;
+    int i = (int)f % n;
+    return i < 0 ? i + n : i;
+}
+__device__ __forceinline__ V3 texel(const TexDev& tx, int x, int y) {
+    const uint8_t* p = tx.rgb + ((long long)y * tx.width + x) * 3;
+    return v3(dvd((float)p[0], 255.0f), dvd((float)p[1], 255.0f), dvd((float)p[2], 255.0f));
+}
+__device__ __forceinline__ float blend2(float c0, float w0, float c1, float w1) { return add(mul(c0, w0), mul(c1, w1)); }
+__device__ __forceinline__ V3 texture_sample(const TexDev& tx, float x, float y, int mode) {
+    const float x0f = floorf(x), y0f = floorf(y);
+    const int x0 = wrap_index(x0f, tx.width), y0 = wrap_index(y0f, tx.height);
+    if (mode == SRT_TEX_NEAREST) return texel(tx, x0, y0);
+    const int x1 = x0 + 1 == tx.width ? 0 : x0 + 1, y1 = y0 + 1 == tx.height ? 0 : y0 + 1;
+    float fx = sub(x, x0f), fy = sub(y, y0f);
+    if (!(fx >= 0.0f && fx <= 1.0f)) fx = 0.0f;
+    if (!(fy >= 0.0f && fy <= 1.0f)) fy = 0.0f;
+    const float gx = sub(1.0f, fx), gy = sub(1.0f, fy);
+    const V3 c00 = texel(tx, x0, y0), c10 = texel(tx, x1, y0), c01 = texel(tx, x0, y1), c11 = texel(tx, x1, y1);
+    return v3(blend2(blend2(c00.x, gx, c10.x, fx), gy, blend2(c01.x, gx, c11.x, fx), fy),
+              blend2(blend2(c00.y, gx, c10.y, fx), gy, blend2(c01.y, gx, c11.y, fx), fy),
+              blend2(blend2(c00.z, gx, c10.z, fx), gy, blend2(c01.z, gx, c11.z, fx), fy));
+}
+
 // Base colour (:437-443, :350-361) and the light-independent part of phongIllumination.
 __device__ __forceinline__ PhongPixel prepare_pixel(const KArgs& a, const Hit& h, V3 d, bool use_flat) {
     const float4* gp = (use_flat ? a.flat_geom : a.geom) + 3 * (size_t)h.tri;
@@ -48,11 +80,15 @@ __device__ __forceinline__ PhongPixel prepare_pixel(const KArgs& a, const Hit& h
         const float ux = add(add(mul(bc.x, a1.x), mul(bc.y, a1.z)), mul(bc.z, a2.x));
         const float uy = add(add(mul(bc.x, a1.y), mul(bc.y, a1.w)), mul(bc.z, a2.y));
         const TexDev tx = a.textures[tex];
-        long long idx = ((long long)(__float2int_rz(uy) * tx.width + __float2int_rz(ux))) * 3;   // :357
-        const long long last = ((long long)tx.width * tx.height - 1) * 3;
-        idx = idx < 0 ? 0 : (idx > last ? last : idx);   // the reference reads out of bounds here (UB): clamp
-        px.oc = v3(dvd((float)tx.rgb[idx + 0], 255.0f), dvd((float)tx.rgb[idx + 1], 255.0f),
-                   dvd((float)tx.rgb[idx + 2], 255.0f));                  // :358-360
+        if (a.texture_mode == SRT_TEX_TRUNCATE) {
+            long long idx = ((long long)(__float2int_rz(uy) * tx.width + __float2int_rz(ux))) * 3;   // :357
+            const long long last = ((long long)tx.width * tx.height - 1) * 3;
+            idx = idx < 0 ? 0 : (idx > last ? last : idx);   // the reference reads out of bounds here (UB): clamp
+            px.oc = v3(dvd((float)tx.rgb[idx + 0], 255.0f), dvd((float)tx.rgb[idx + 1], 255.0f),
+                       dvd((float)tx.rgb[idx + 2], 255.0f));              // :358-360
+        } else {
+            px.oc = texture_sample(tx, ux, uy, a.texture_mode);
+        }
     }
     return px;
 }

@@ -319,3 +319,67 @@ def test_smooth_normal_mode_matches_the_oracle(gpu_ctx, key, lights):
         gpu_ctx.render(sc, p)
     assert e.value.code == _abi.SRT_ERR_INVALID_ARG
     sc.destroy()
+
+
+def _host_scene(key, angle=15.0):
+    from simple_raytracer_b200 import host
+    cfg = scenes.CONFIGS[key]
+    hs = host.HostScene()
+    view = cfg.build(hs, angle)
+    light = scenes.light_view_space(hs, view) if view is not None else np.array(scenes.LIGHT_WORLD, np.float32)
+    arrays = hs.flatten(with_flat_lists=not cfg.use_bvh)
+    hs.close()
+    return cfg, arrays, np.asarray(light, np.float32)
+
+
+@pytest.mark.parametrize("key,lights", [("spheres", 6), ("C3", 8), ("C4", 3)])
+@pytest.mark.parametrize("switch", ["normalise", "segment", "nearest", "bilinear", "all"])
+def test_quality_switches_match_the_oracle(gpu_ctx, key, lights, switch):
+    """SURVEY.md §8f row 4 switches (normalise_lights, shadow_segment + shadow_eps, texture_mode; none is a reference
+    mode): every kernel variant against the oracle's restatement; hits (ids, t) never move; all off = the shipped frame."""
+    cfg, arrays, light = _host_scene(key)
+    if switch in ("nearest", "bilinear") and not cfg.needs_textures:
+        pytest.skip("scene has no textures")
+    W, H, focal = scenes.scaled(cfg, 96)
+    p = _abi.default_params(W, H, focal, light, lights, cfg.use_bvh)
+    p.no_sky_fill = 1                                      # a hit that shades to black stays black (:518 turns it into sky)
+    if switch in ("segment", "all"):                       # a light INSIDE the scene: some geometry lies behind it
+        mid = arrays.objects["box_min"].min(axis=0) * 0.5 + arrays.objects["box_max"].max(axis=0) * 0.5
+        for k in range(3):
+            p.light_pos[k] = float(mid[k])
+    sc = gpu_ctx.upload(arrays)
+    shipped = gpu_ctx.render(sc, p)
+    if switch in ("normalise", "all"): p.normalise_lights = 1
+    if switch in ("segment", "all"): p.shadow_segment, p.shadow_eps = 1, 1e-4
+    if switch == "nearest": p.texture_mode = _abi.TEX_NEAREST
+    if switch in ("bilinear", "all"): p.texture_mode = _abi.TEX_BILINEAR
+    want = pyoracle.oracle_render(arrays, p)
+    for variant in ((0, 2, 4, 1) if cfg.use_bvh else (1,)):
+        p.variant = variant
+        got = gpu_ctx.render(sc, p)
+        assert np.array_equal(got["tri_id"], want["tri_id"]) and np.array_equal(got["t"], want["t"]), variant
+        assert np.abs(got["rgb"].astype(np.int32) - want["rgb"].astype(np.int32)).max() <= 1, variant
+    assert np.array_equal(got["tri_id"], shipped["tri_id"])
+    hit = shipped["tri_id"] >= 0
+    if switch == "segment":                                # fewer occluders count: no hit pixel gets darker
+        assert (got["rgb"][hit].astype(np.int32) >= shipped["rgb"][hit].astype(np.int32) - 1).all()
+        assert key != "spheres" or not np.array_equal(got["rgb"], shipped["rgb"])
+    if switch == "normalise":
+        assert (got["rgb"][hit].astype(np.int32) <= shipped["rgb"][hit].astype(np.int32)).all()
+        assert not np.array_equal(got["rgb"], shipped["rgb"])
+    if switch == "nearest":                                # in-range texel coordinates address the same texel
+        assert (got["rgb"] == shipped["rgb"]).all(axis=2).mean() > 0.98
+    sc.destroy()
+
+
+def test_quality_switch_arguments_are_checked(gpu_ctx):
+    cfg, arrays, light = _host_scene("spheres")
+    sc = gpu_ctx.upload(arrays)
+    for name, value in (("texture_mode", 3), ("texture_mode", -1), ("shadow_eps", 2.0), ("shadow_eps", float("nan"))):
+        p = _abi.default_params(64, 48, 48.0, light, 2, True)
+        p.shadow_segment = 1
+        setattr(p, name, value)
+        with pytest.raises(capi.SrtError) as e:
+            gpu_ctx.render(sc, p)
+        assert e.value.code == _abi.SRT_ERR_INVALID_ARG
+    sc.destroy()

@@ -170,3 +170,64 @@ def test_smooth_normal_frames_in_the_oracle():
     hit = flat["tri_id"] >= 0
     assert hit.sum() > 300 and (flat["rgb"][hit] != smooth["rgb"][hit]).any(axis=1).mean() > 0.5
     assert np.array_equal(flat["rgb"][~hit], smooth["rgb"][~hit])
+
+
+def test_texture_sample_modes_of_the_oracle():
+    """texture_mode NEAREST / BILINEAR (srt.h; not reference modes): wrapped addressing, exact at texel corners, the mean
+    half way, constant on a constant image."""
+    import ctypes as C
+    from simple_raytracer_b200 import _abi
+    lib = pyoracle.oracle_lib()
+    rng = np.random.default_rng(3)
+    Wt, Ht = 5, 3
+    img = rng.integers(0, 256, (Ht, Wt, 3), dtype=np.uint8)
+
+    def sample(x, y, mode, image=img):
+        out = np.zeros(3, np.float32)
+        lib.srt_oracle_texture_sample(image.ctypes.data_as(C.c_void_p), image.shape[1], image.shape[0], float(x), float(y), mode,
+                                      out.ctypes.data_as(C.POINTER(C.c_float)))
+        return out
+
+    f = lambda v: (v.astype(np.float32) / np.float32(255.0))
+    for x in range(-7, 9):
+        for y in range(-5, 7):
+            want = f(img[y % Ht, x % Wt])
+            assert np.array_equal(sample(x, y, _abi.TEX_NEAREST), want)
+            assert np.array_equal(sample(x + 0.75, y + 0.25, _abi.TEX_NEAREST), want)
+            assert np.array_equal(sample(x, y, _abi.TEX_BILINEAR), want)           # weights (1, 0): the corner texel itself
+            mid = sample(x + 0.5, y, _abi.TEX_BILINEAR)
+            assert np.allclose(mid, (want + f(img[y % Ht, (x + 1) % Wt])) / 2, atol=1e-6)
+            mid = sample(x, y + 0.5, _abi.TEX_BILINEAR)
+            assert np.allclose(mid, (want + f(img[(y + 1) % Ht, x % Wt])) / 2, atol=1e-6)
+    flat = np.full((4, 4, 3), 200, np.uint8)
+    assert np.allclose(sample(1.3, 2.9, _abi.TEX_BILINEAR, flat), 200 / 255, atol=1e-6)
+    for bad in (float("nan"), float("inf"), -float("inf"), 3e30):                  # never out of the image
+        assert np.isfinite(sample(bad, 1.0, _abi.TEX_BILINEAR)).all() and np.isfinite(sample(1.0, bad, _abi.TEX_NEAREST)).all()
+
+
+def test_quality_switches_in_the_oracle():
+    """normalise_lights, shadow_segment: what they change and what they leave alone (all off = the golden-checked path)."""
+    from simple_raytracer_b200 import _abi, host, scenes
+    cfg = scenes.CONFIGS["spheres"]
+    hs = host.HostScene()
+    cfg.build(hs, 0.0)
+    arrays = hs.flatten()
+    hs.close()
+    W, H, focal = 90, 60, 60.0
+    p = _abi.default_params(W, H, focal, scenes.LIGHT_WORLD, 1, True)
+    one = pyoracle.oracle_render(arrays, p)
+    p.normalise_lights = 1
+    assert np.array_equal(pyoracle.oracle_render(arrays, p)["rgb"], one["rgb"])      # a sum of one sample divided by one
+    p.light_count, p.light_step = 6, 0.0                                               # six samples at the same place
+    assert np.abs(pyoracle.oracle_render(arrays, p)["rgb"].astype(int) - one["rgb"].astype(int)).max() <= 1
+    # a light in the middle of the scene: geometry behind it shadows as shipped, not with shadow_segment
+    mid = arrays.objects["box_min"].min(axis=0) * 0.5 + arrays.objects["box_max"].max(axis=0) * 0.5
+    p = _abi.default_params(W, H, focal, mid, 1, True)
+    p.no_sky_fill = 1                                      # a hit that shades to black stays black (:518 turns it into sky)
+    shipped = pyoracle.oracle_render(arrays, p)
+    p.shadow_segment, p.shadow_eps = 1, 1e-4
+    seg = pyoracle.oracle_render(arrays, p)
+    assert np.array_equal(shipped["tri_id"], seg["tri_id"]) and np.array_equal(shipped["t"], seg["t"])
+    hit = shipped["tri_id"] >= 0
+    assert (seg["rgb"][hit].astype(int) >= shipped["rgb"][hit].astype(int)).all()
+    assert (seg["rgb"][hit] != shipped["rgb"][hit]).any(axis=1).sum() > 20
