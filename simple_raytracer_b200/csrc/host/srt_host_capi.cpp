@@ -100,6 +100,21 @@ int srt_host_get_triangles(srt_host_scene* s, const char* name, float* out30, ui
     }
     return (int)i;
 }
+int srt_host_decode_image(const char* path, int use_sidecar, uint8_t* out, size_t cap, int* width, int* height) {
+    int w = 0, h = 0;
+    unsigned char* px = srt::decode_image_file(path, &w, &h, use_sidecar != 0);
+    if (!px) return -1;
+    if (width) *width = w;
+    if (height) *height = h;
+    int rc = 0;
+    if (out) {
+        const size_t bytes = (size_t)w * (size_t)h * 3;
+        if (cap < bytes) rc = -2; else std::memcpy(out, px, bytes);
+    }
+    std::free(px);
+    return rc;
+}
+
 int srt_host_set_texture(srt_host_scene* s, const char* name, const uint8_t* rgb, int width, int height) {
     if (!rgb || width <= 0 || height <= 0) { s->error = "bad texture"; return -1; }
     const size_t bytes = (size_t)width * (size_t)height * 3;

@@ -1,14 +1,15 @@
 // srt_image.cpp — texture pixels for ObjectManager::loadObjFile (the reference calls
 // stbi_load(path, &w, &h, &ch, 3) at Object.cpp:57).
 //
-// This repository carries no JPEG / PNG decoder of its own yet.  Texture pixels come from a
-// pre-decoded sidecar file `<texture path>.rgb8` that oracle/stage_assets.py writes next to every
-// texture when it stages the reference's mesh / texture data (it decodes with the reference's own
-// stb_image through oracle/_ref, so the pixels are bit-identical to what the reference renders
-// with — JPEG decoders differ in their IDCT / upsampling, so "some other decoder" would not do).
+// PNG and JPEG files — the two formats the reference's assets use — are decoded by this repository's own decoders
+// (srt_png.cpp, srt_jpeg.cpp), which restate the format rules and stb_image's conversions so that the pixels are
+// the ones the reference renders with (JPEG decoders differ in their IDCT / upsampling / colour conversion, so "some
+// other decoder" would not do).  Any other format, or a file variant those decoders do not cover, falls back to a
+// pre-decoded sidecar `<texture path>.rgb8` (oracle/stage_assets.py writes one next to every texture when it stages
+// the reference's data, decoded with the reference's own stb_image through oracle/_ref).
 // Sidecar layout: 4 bytes "SRT8", int32 width, int32 height (little endian), then
 // height*width*3 bytes RGB, rows top-down — exactly the buffer stbi_load(..., 3) returns.
-// Without a sidecar the function returns nullptr, which loadObjFile reports the way the reference
+// When neither works the function returns nullptr, which loadObjFile reports the way the reference
 // reports a failed stbi_load (Object.cpp:63-65: message, continue); a scene that then references
 // the texture is rejected by the flattener (SRT_ERR_SCENE) instead of crashing.
 // Callers that already hold decoded RGB8 pixels can install ObjectManager::textureDecoder.
@@ -17,15 +18,44 @@
 #include <cstdlib>
 #include <cstring>
 #include <string>
+#include <vector>
 
 #include "srt_scene.hpp"
 
 namespace srt {
 
-unsigned char* decode_image_rgb8(const char* path, int* width, int* height) {
+namespace {
+// The file through our own decoders; nullptr when it is neither PNG nor JPEG or cannot be decoded.
+unsigned char* decode_known_format(const char* path, int* width, int* height) {
+    FILE* f = std::fopen(path, "rb");
+    if (!f) return nullptr;
+    std::vector<uint8_t> file;
+    unsigned char chunk[1 << 16];
+    for (size_t got; (got = std::fread(chunk, 1, sizeof chunk, f)) > 0;) file.insert(file.end(), chunk, chunk + got);
+    std::fclose(f);
+    std::vector<uint8_t> rgb;
+    int w = 0, h = 0;
+    const bool ok = (file.size() > 8 && file[0] == 0x89) ? decode_png(file.data(), file.size(), &w, &h, rgb)
+                  : (file.size() > 4 && file[0] == 0xFF && file[1] == 0xD8) ? decode_jpeg(file.data(), file.size(), &w, &h, rgb)
+                  : false;
+    if (!ok || w <= 0 || h <= 0 || rgb.size() != (size_t)w * h * 3) return nullptr;
+    unsigned char* out = (unsigned char*)std::malloc(rgb.size());
+    if (!out) return nullptr;
+    std::memcpy(out, rgb.data(), rgb.size());
+    if (width) *width = w;
+    if (height) *height = h;
+    return out;
+}
+}  // namespace
+
+unsigned char* decode_image_rgb8(const char* path, int* width, int* height) { return decode_image_file(path, width, height, true); }
+
+unsigned char* decode_image_file(const char* path, int* width, int* height, bool use_sidecar) {
     if (width) *width = 0;
     if (height) *height = 0;
     if (!path) return nullptr;
+    if (unsigned char* own = decode_known_format(path, width, height)) return own;
+    if (!use_sidecar) return nullptr;
     const std::string side = std::string(path) + ".rgb8";
     FILE* f = std::fopen(side.c_str(), "rb");
     if (!f) return nullptr;

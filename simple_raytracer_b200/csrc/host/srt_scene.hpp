@@ -16,6 +16,8 @@
 #ifndef SRT_SCENE_HPP_
 #define SRT_SCENE_HPP_
 
+#include <cstddef>
+#include <cstdint>
 #include <string>
 #include <unordered_map>
 #include <vector>
@@ -107,6 +109,11 @@ void set_asset_cache(bool enabled);
 
 // --- image decoding (srt_image.cpp) -------------------------------------------------------------
 unsigned char* decode_image_rgb8(const char* path, int* width, int* height);
+unsigned char* decode_image_file(const char* path, int* width, int* height, bool use_sidecar);
+// Decoders of our own for the two formats the reference's assets use, to the pixels stbi_load(..., 3) returns
+// (srt_png.cpp, srt_jpeg.cpp).  false: not that format, damaged, or a variant the decoder does not cover.
+bool decode_png(const uint8_t* data, size_t n, int* width, int* height, std::vector<uint8_t>& rgb);
+bool decode_jpeg(const uint8_t* data, size_t n, int* width, int* height, std::vector<uint8_t>& rgb);
 // drawImage's saved file (:461-498, CImg save_bmp) from a dense sky-filled RGB8 frame; false on I/O failure.
 bool write_bmp(const char* path, const unsigned char* rgb, int width, int height);
 

@@ -86,6 +86,7 @@ def _lib():
         L.srt_host_set_asset_cache.restype = None
         L.srt_host_triangle_textures.argtypes = [vp, cp, C.POINTER(C.c_int32), C.c_char_p, i32]
         L.srt_host_texture_data.argtypes = [vp, cp, C.POINTER(vp), C.POINTER(i32), C.POINTER(i32)]
+        L.srt_host_decode_image.argtypes = [cp, i32, vp, C.c_size_t, C.POINTER(i32), C.POINTER(i32)]
         L.srt_host_object_order.argtypes = [C.POINTER(cp), i32, C.POINTER(i32)]
         _bound = True
     return L
@@ -297,6 +298,18 @@ def write_bmp(path, rgb: np.ndarray):
         raise ValueError("rgb must be [H][W][3] uint8")
     if _lib().srt_host_write_bmp(str(path).encode(), a.ctypes.data, a.shape[1], a.shape[0]) != 0:
         raise OSError(f"cannot write {path}")
+
+
+def decode_image(path, use_sidecar: bool = True) -> np.ndarray:
+    """A texture file as the [H, W, 3] uint8 pixels stbi_load(path, ..., 3) returns (Object.cpp:57): PNG / JPEG through the
+    library's own decoders; other formats through a `.rgb8` sidecar unless use_sidecar is False."""
+    w, h = C.c_int32(0), C.c_int32(0)
+    if _lib().srt_host_decode_image(str(path).encode(), int(use_sidecar), None, 0, C.byref(w), C.byref(h)) != 0:
+        raise ValueError(f"cannot decode {path}")
+    out = np.zeros((h.value, w.value, 3), np.uint8)
+    if _lib().srt_host_decode_image(str(path).encode(), int(use_sidecar), out.ctypes.data, out.nbytes, C.byref(w), C.byref(h)) != 0:
+        raise ValueError(f"cannot decode {path}")
+    return out
 
 
 def set_asset_cache(enabled: bool):

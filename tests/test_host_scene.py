@@ -290,3 +290,150 @@ def test_polygon_faces_triangulate_like_the_reference_loader(tmp_path):
         rt, rf = rb.triangles(str(path)); ht, hf = hb.triangles(str(path))
         assert rt.shape == ht.shape and len(rt) > 500
         assert np.array_equal(rt.view(np.uint32), ht.view(np.uint32)) and np.array_equal(rf, hf)
+
+
+def _ref_decode(path):
+    import ctypes as C
+    lib = pyoracle.ref_lib()
+    lib.ref_decode_texture.argtypes = [C.c_char_p, C.c_void_p, C.c_int, C.POINTER(C.c_int), C.POINTER(C.c_int)]
+    w, h = C.c_int(0), C.c_int(0)
+    if lib.ref_decode_texture(str(path).encode(), None, 0, C.byref(w), C.byref(h)) != 0:
+        return None
+    buf = np.zeros((h.value, w.value, 3), np.uint8)
+    assert lib.ref_decode_texture(str(path).encode(), buf.ctypes.data, buf.nbytes, C.byref(w), C.byref(h)) == 0
+    return buf
+
+
+@pytest.mark.ref
+def test_texture_files_decode_like_the_reference_stb_image():
+    """Every texture of the reference's assets (PNG RGB / RGBA; JPEG baseline 4:4:4 and 4:2:0 with restart intervals,
+    one progressive) through our own decoders (srt_png.cpp, srt_jpeg.cpp; no sidecar) == stbi_load(..., 3) as the
+    reference calls it (Object.cpp:57), bit for bit."""
+    files = sorted(list(host.assets_dir().glob("obj/*/*.png")) + list(host.assets_dir().glob("obj/*/*.jpg")))
+    assert len(files) >= 10
+    for f in files:
+        want = _ref_decode(f)
+        assert want is not None, f
+        got = host.decode_image(f, use_sidecar=False)
+        assert got.shape == want.shape and np.array_equal(got, want), f.name
+
+
+def _write_png(path, samples, depth, ctype, interlace, rng, palette=None):
+    """Minimal PNG writer for the decoder test: samples [H, W, C] integers of `depth` bits, random filter per row."""
+    import struct, zlib
+    H, W, Cn = samples.shape
+
+    def pack_rows(img):                                     # -> list of byte rows
+        h, w, _ = img.shape
+        flat = img.reshape(h, w * Cn).astype(np.uint32)
+        if depth == 16:
+            return [np.stack([r >> 8, r & 255], axis=1).astype(np.uint8).reshape(-1) for r in flat]
+        if depth == 8:
+            return [r.astype(np.uint8) for r in flat]
+        per = 8 // depth
+        rows = []
+        for r in flat:
+            pad = (-len(r)) % per
+            r = np.concatenate([r, np.zeros(pad, np.uint32)]).reshape(-1, per)
+            rows.append(sum(r[:, k] << (8 - depth * (k + 1)) for k in range(per)).astype(np.uint8))
+        return rows
+
+    def filtered(img):
+        bpp = max(1, Cn * depth // 8)
+        out, prev = bytearray(), None
+        for row in pack_rows(img):
+            cur = row.astype(np.int32)
+            up = prev if prev is not None else np.zeros_like(cur)
+            left = np.concatenate([np.zeros(bpp, np.int32), cur[:-bpp]]) if len(cur) > bpp else np.zeros_like(cur)
+            ul = np.concatenate([np.zeros(bpp, np.int32), up[:-bpp]]) if len(cur) > bpp else np.zeros_like(cur)
+            f = int(rng.integers(0, 5))
+            p = left + up - ul
+            pa, pb, pc = np.abs(p - left), np.abs(p - up), np.abs(p - ul)
+            paeth = np.where((pa <= pb) & (pa <= pc), left, np.where(pb <= pc, up, ul))
+            pred = [0, left, up, (left + up) >> 1, paeth][f]
+            out.append(f)
+            out += ((cur - pred) & 255).astype(np.uint8).tobytes()
+            prev = cur
+        return bytes(out)
+
+    if interlace:
+        raw = b""
+        for x0, y0, dx, dy in ((0, 0, 8, 8), (4, 0, 8, 8), (0, 4, 4, 8), (2, 0, 4, 4), (0, 2, 2, 4), (1, 0, 2, 2), (0, 1, 1, 2)):
+            sub = samples[y0::dy, x0::dx]
+            if sub.shape[0] and sub.shape[1]:
+                raw += filtered(sub)
+    else:
+        raw = filtered(samples)
+
+    def chunk(tag, body):
+        return struct.pack(">I", len(body)) + tag + body + struct.pack(">I", zlib.crc32(tag + body))
+
+    comp = zlib.compressobj(int(rng.integers(0, 10)))
+    z = comp.compress(raw) + comp.flush()
+    cut = len(z) // 3
+    blob = b"\x89PNG\r\n\x1a\n" + chunk(b"IHDR", struct.pack(">IIBBBBB", W, H, depth, ctype, 0, 0, int(interlace)))
+    if palette is not None:
+        blob += chunk(b"PLTE", palette.astype(np.uint8).tobytes())
+    blob += chunk(b"tEXt", b"k\0v") + chunk(b"IDAT", z[:cut]) + chunk(b"IDAT", z[cut:]) + chunk(b"IEND", b"")
+    path.write_bytes(blob)
+
+
+@pytest.mark.ref
+def test_generated_png_variants_decode_like_the_reference(tmp_path):
+    """Every colour type x bit depth the format allows, with and without Adam7, odd sizes, all five filters, stored /
+    fixed / dynamic deflate blocks, IDAT split in two: srt_png.cpp == the reference's stb_image."""
+    rng = np.random.default_rng(7)
+    kinds = [(0, d) for d in (1, 2, 4, 8, 16)] + [(2, 8), (2, 16)] + [(3, d) for d in (1, 2, 4, 8)] + [(4, 8), (4, 16), (6, 8), (6, 16)]
+    n = 0
+    for ctype, depth in kinds:
+        Cn = {0: 1, 2: 3, 3: 1, 4: 2, 6: 4}[ctype]
+        for W, H in ((1, 1), (5, 3), (9, 17), (33, 8), (64, 40)):
+            for interlace in (False, True):
+                smooth = rng.integers(0, 2)
+                img = rng.integers(0, 1 << depth, (H, W, Cn))
+                if smooth:                                   # compressible content: dynamic blocks with long matches
+                    img = (np.add.outer(np.arange(H), np.arange(W))[:, :, None] // 3 + np.arange(Cn)) % (1 << depth)
+                palette = rng.integers(0, 256, (1 << min(depth, 8), 3)) if ctype == 3 else None
+                path = tmp_path / f"t{ctype}_{depth}_{W}x{H}_{int(interlace)}.png"
+                _write_png(path, img, depth, ctype, interlace, rng, palette)
+                want = _ref_decode(path)
+                assert want is not None, path.name
+                got = host.decode_image(path, use_sidecar=False)
+                assert got.shape == want.shape and np.array_equal(got, want), path.name
+                n += 1
+    assert n == len(kinds) * 10
+    bad = tmp_path / "bad.png"
+    bad.write_bytes(path.read_bytes()[:60])
+    with pytest.raises(ValueError):
+        host.decode_image(bad, use_sidecar=False)
+
+
+@pytest.mark.ref
+def test_generated_jpeg_variants_decode_like_the_reference(tmp_path):
+    """JPEG files written by Pillow's libjpeg — grey / 4:4:4 / 4:2:2 / 4:2:0 / 4:1:1, baseline and progressive, optimised
+    tables, restart intervals, sizes that are not multiples of the MCU, several qualities: srt_jpeg.cpp == stb_image."""
+    Image = pytest.importorskip("PIL.Image")
+    rng = np.random.default_rng(11)
+    n = 0
+    for W, H in ((1, 1), (7, 5), (16, 16), (17, 33), (100, 3), (131, 67)):
+        yy, xx = np.mgrid[0:H, 0:W]
+        base = np.stack([(xx * 255 // max(W - 1, 1)), (yy * 255 // max(H - 1, 1)), ((xx + yy) * 5) % 256], axis=2)
+        img = np.clip(base + rng.integers(-40, 40, (H, W, 3)), 0, 255).astype(np.uint8)
+        for mode, sub in (("L", None), ("RGB", "4:4:4"), ("RGB", "4:2:2"), ("RGB", "4:2:0"), ("RGB", "4:1:1")):
+            for progressive in (False, True):
+                for quality, extra in ((30, {}), (75, {"optimize": True}), (95, {"restart_marker_blocks": 3}), (100, {"restart_marker_rows": 1})):
+                    im = Image.fromarray(img if mode == "RGB" else img[:, :, 0], mode)
+                    path = tmp_path / f"j_{W}x{H}_{mode}_{(sub or 'g').replace(':', '')}_{int(progressive)}_{quality}.jpg"
+                    kw = dict(quality=quality, progressive=progressive, **extra)
+                    if sub:
+                        kw["subsampling"] = sub
+                    try:
+                        im.save(path, "JPEG", **kw)
+                    except (TypeError, ValueError, KeyError):
+                        continue
+                    want = _ref_decode(path)
+                    assert want is not None, path.name
+                    got = host.decode_image(path, use_sidecar=False)
+                    assert got.shape == want.shape and np.array_equal(got, want), path.name
+                    n += 1
+    assert n >= 100
