@@ -59,8 +59,8 @@ struct Bits {
 };
 
 struct HuffTable {
-    bool defined = false;
     int maxcode[18]; int valptr[17]; int mincode[17]; uint8_t values[256];
+    HuffTable() { for (int l = 0; l < 18; ++l) maxcode[l] = -1; std::memset(valptr, 0, sizeof valptr); std::memset(mincode, 0, sizeof mincode); }   // undefined table: every code is invalid
     bool build(const int counts[16], const uint8_t* vals, int nvals) {
         int code = 0, k = 0;
         for (int l = 1; l <= 16; ++l) {
@@ -73,7 +73,6 @@ struct HuffTable {
         maxcode[17] = 0x7fffffff;
         if (k != nvals || k > 256) return false;
         std::memcpy(values, vals, nvals);
-        defined = true;
         return true;
     }
     int decode(Bits& br) const {
@@ -92,6 +91,8 @@ inline int extend(Bits& br, int s) {
     const int v = br.bits(s);
     return v < (1 << (s - 1)) ? v - (1 << s) + 1 : v;
 }
+
+inline bool fits_short(int64_t v) { return v >= -32768 && v <= 32767; }
 
 struct Component {
     int id = 0, h = 1, v = 1, tq = 0, hd = 0, ha = 0;
@@ -128,6 +129,7 @@ bool Decoder::block_baseline(Component& c, int16_t* d) {
     const int t = dc[c.hd].decode(br);
     if (t < 0 || t > 15) return false;
     c.dc_pred += extend(br, t);
+    if (!fits_short((int64_t)c.dc_pred * q[0])) return false;          // stb_image refuses such a stream too (:2224)
     d[0] = (int16_t)(c.dc_pred * q[0]);
     for (int k = 1; k < 64;) {
         const int rs = ac[c.ha].decode(br);
@@ -149,6 +151,7 @@ bool Decoder::block_dc_progressive(Component& c, int16_t* d) {
         const int t = dc[c.hd].decode(br);
         if (t < 0 || t > 15) return false;
         c.dc_pred += extend(br, t);
+        if (!fits_short((int64_t)c.dc_pred * (1 << succ_low))) return false;
         d[0] = (int16_t)(c.dc_pred * (1 << succ_low));
     } else if (br.bit()) {
         d[0] = (int16_t)(d[0] + (int16_t)(1 << succ_low));
@@ -206,22 +209,25 @@ bool Decoder::block_ac_progressive(Component& c, int16_t* d) {
 }
 
 // ---- inverse DCT (stb_image.h:2452-2523) ----------------------------------------------------------
-inline uint8_t clamp255(int x) { return (uint8_t)(x < 0 ? 0 : x > 255 ? 255 : x); }
+inline uint8_t clamp255(int64_t x) { return (uint8_t)(x < 0 ? 0 : x > 255 ? 255 : x); }
 constexpr int fix(double x) { return (int)(x * 4096 + 0.5); }
 
-struct Butterfly { int x0, x1, x2, x3, t0, t1, t2, t3; };
-inline Butterfly butterfly(int s0, int s1, int s2, int s3, int s4, int s5, int s6, int s7) {
+// 64-bit intermediates: the same values as stb_image's 32-bit ones on every valid stream, and defined behaviour (no
+// signed overflow) on damaged ones.
+typedef int64_t wide;
+struct Butterfly { wide x0, x1, x2, x3, t0, t1, t2, t3; };
+inline Butterfly butterfly(wide s0, wide s1, wide s2, wide s3, wide s4, wide s5, wide s6, wide s7) {
     Butterfly b;
-    int p1 = (s2 + s6) * fix(0.5411961f);
-    int t2 = p1 + s6 * fix(-1.847759065f);
-    int t3 = p1 + s2 * fix(0.765366865f);
-    int t0 = (s0 + s4) * 4096, t1 = (s0 - s4) * 4096;
+    wide p1 = (s2 + s6) * fix(0.5411961f);
+    wide t2 = p1 + s6 * fix(-1.847759065f);
+    wide t3 = p1 + s2 * fix(0.765366865f);
+    wide t0 = (s0 + s4) * 4096, t1 = (s0 - s4) * 4096;
     b.x0 = t0 + t3; b.x3 = t0 - t3; b.x1 = t1 + t2; b.x2 = t1 - t2;
     t0 = s7; t1 = s5; t2 = s3; t3 = s1;
-    int p3 = t0 + t2, p4 = t1 + t3;
+    wide p3 = t0 + t2, p4 = t1 + t3;
     p1 = t0 + t3;
-    int p2 = t1 + t2;
-    const int p5 = (p3 + p4) * fix(1.175875602f);
+    wide p2 = t1 + t2;
+    const wide p5 = (p3 + p4) * fix(1.175875602f);
     t0 = t0 * fix(0.298631336f); t1 = t1 * fix(2.053119869f); t2 = t2 * fix(3.072711026f); t3 = t3 * fix(1.501321110f);
     p1 = p5 + p1 * fix(-0.899976223f); p2 = p5 + p2 * fix(-2.562915447f);
     p3 = p3 * fix(-1.961570560f); p4 = p4 * fix(-0.390180644f);
@@ -230,9 +236,9 @@ inline Butterfly butterfly(int s0, int s1, int s2, int s3, int s4, int s5, int s
 }
 
 void idct_block(uint8_t* out, int stride, const int16_t* d) {
-    int val[64];
+    wide val[64];
     for (int i = 0; i < 8; ++i) {
-        const int16_t* c = d + i; int* v = val + i;
+        const int16_t* c = d + i; wide* v = val + i;
         if (c[8] == 0 && c[16] == 0 && c[24] == 0 && c[32] == 0 && c[40] == 0 && c[48] == 0 && c[56] == 0) {
             const int dcterm = c[0] * 4;
             for (int r = 0; r < 8; ++r) v[8 * r] = dcterm;
@@ -246,9 +252,9 @@ void idct_block(uint8_t* out, int stride, const int16_t* d) {
         }
     }
     for (int i = 0; i < 8; ++i) {
-        const int* v = val + 8 * i; uint8_t* o = out + (size_t)stride * i;
+        const wide* v = val + 8 * i; uint8_t* o = out + (size_t)stride * i;
         Butterfly b = butterfly(v[0], v[1], v[2], v[3], v[4], v[5], v[6], v[7]);
-        const int bias = 65536 + (128 << 17);
+        const wide bias = 65536 + (128 << 17);
         b.x0 += bias; b.x1 += bias; b.x2 += bias; b.x3 += bias;
         o[0] = clamp255((b.x0 + b.t3) >> 17); o[7] = clamp255((b.x0 - b.t3) >> 17);
         o[1] = clamp255((b.x1 + b.t2) >> 17); o[6] = clamp255((b.x1 - b.t2) >> 17);
@@ -388,6 +394,7 @@ bool decode_jpeg(const uint8_t* data, size_t n, int* width, int* height, std::ve
             z.progressive = m == 0xC2;
             z.height = be16(seg + 1); z.width = be16(seg + 3); z.ncomp = seg[5];
             if (seg[0] != 8 || z.width == 0 || z.height == 0 || (z.ncomp != 1 && z.ncomp != 3)) return false;
+            if ((int64_t)z.width * z.height > ((int64_t)1 << 28)) return false;
             if (body != 6 + 3 * z.ncomp) return false;
             for (int i = 0; i < z.ncomp; ++i) {
                 Component& c = z.comp[i];

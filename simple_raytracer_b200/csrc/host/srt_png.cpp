@@ -67,10 +67,10 @@ const uint8_t kLenExtra[29] = {0, 0, 0, 0, 0, 0, 0, 0, 1, 1, 1, 1, 2, 2, 2, 2, 3
 const uint16_t kDistBase[30] = {1, 2, 3, 4, 5, 7, 9, 13, 17, 25, 33, 49, 65, 97, 129, 193, 257, 385, 513, 769, 1025, 1537, 2049, 3073, 4097, 6145, 8193, 12289, 16385, 24577};
 const uint8_t kDistExtra[30] = {0, 0, 0, 0, 1, 1, 2, 2, 3, 3, 4, 4, 5, 5, 6, 6, 7, 7, 8, 8, 9, 9, 10, 10, 11, 11, 12, 12, 13, 13};
 
-bool inflate_block(BitReader& br, const Huffman& lit, const Huffman& dist, std::vector<uint8_t>& out) {
+bool inflate_block(BitReader& br, const Huffman& lit, const Huffman& dist, std::vector<uint8_t>& out, size_t limit) {
     for (;;) {
         const int s = lit.decode(br);
-        if (s < 0 || br.overrun) return false;
+        if (s < 0 || br.overrun || out.size() > limit) return false;
         if (s < 256) { out.push_back((uint8_t)s); continue; }
         if (s == 256) return true;
         if (s > 285) return false;
@@ -84,7 +84,8 @@ bool inflate_block(BitReader& br, const Huffman& lit, const Huffman& dist, std::
     }
 }
 
-bool zlib_inflate(const uint8_t* data, size_t n, std::vector<uint8_t>& out) {
+// `limit`: the most bytes the caller can use; a stream that produces more is refused (no decompression bombs).
+bool zlib_inflate(const uint8_t* data, size_t n, std::vector<uint8_t>& out, size_t limit) {
     if (n < 2 || (data[0] & 15) != 8 || ((data[0] << 8) | data[1]) % 31 != 0 || (data[1] & 32)) return false;
     BitReader br{data + 2, n - 2};
     Huffman lit, dist;
@@ -95,7 +96,7 @@ bool zlib_inflate(const uint8_t* data, size_t n, std::vector<uint8_t>& out) {
             if (br.at + 4 > br.n) return false;
             const uint32_t len = br.p[br.at] | (br.p[br.at + 1] << 8), nlen = br.p[br.at + 2] | (br.p[br.at + 3] << 8);
             br.at += 4;
-            if ((len ^ 0xffffu) != nlen || br.at + len > br.n) return false;
+            if ((len ^ 0xffffu) != nlen || br.at + len > br.n || out.size() + len > limit) return false;
             out.insert(out.end(), br.p + br.at, br.p + br.at + len);
             br.at += len;
         } else if (type == 1) {
@@ -103,7 +104,7 @@ bool zlib_inflate(const uint8_t* data, size_t n, std::vector<uint8_t>& out) {
             for (int i = 0; i < 288; ++i) l[i] = i < 144 ? 8 : i < 256 ? 9 : i < 280 ? 7 : 8;
             uint8_t d5[30]; std::memset(d5, 5, sizeof d5);
             lit.build(l, 288); dist.build(d5, 30);
-            if (!inflate_block(br, lit, dist, out)) return false;
+            if (!inflate_block(br, lit, dist, out, limit)) return false;
         } else if (type == 2) {
             const int nlen = (int)br.bits(5) + 257, ndist = (int)br.bits(5) + 1, ncode = (int)br.bits(4) + 4;
             static const uint8_t order[19] = {16, 17, 18, 0, 8, 7, 9, 6, 10, 5, 11, 4, 12, 3, 13, 2, 14, 1, 15};
@@ -125,7 +126,7 @@ bool zlib_inflate(const uint8_t* data, size_t n, std::vector<uint8_t>& out) {
                 while (rep--) lens[i++] = v;
             }
             if (!lit.build(lens, nlen) || !dist.build(lens + nlen, ndist)) return false;
-            if (!inflate_block(br, lit, dist, out)) return false;
+            if (!inflate_block(br, lit, dist, out, limit)) return false;
         } else {
             return false;
         }
@@ -222,9 +223,9 @@ bool decode_png(const uint8_t* data, size_t n, int* width, int* height, std::vec
     }
     if (ctype < 0 || idat.empty() || (ctype == 3 && palette.empty())) return false;
     std::vector<uint8_t> raw;
-    raw.reserve(((size_t)w * 8 + 1) * h / 2);
-    if (!zlib_inflate(idat.data(), idat.size(), raw)) return false;
     const int channels = ctype == 0 ? 1 : ctype == 2 ? 3 : ctype == 3 ? 1 : ctype == 4 ? 2 : 4;
+    const size_t most = (((size_t)w * channels * depth + 7) / 8 + 1) * h + (interlace ? 7 * (size_t)h + 64 : 0);   // Adam7: a filter byte per sub-row
+    if (!zlib_inflate(idat.data(), idat.size(), raw, most + 258)) return false;
     std::vector<uint8_t> samples((size_t)w * h * channels), part;
     if (!interlace) {
         if (!unfilter_image(raw.data(), raw.size(), w, h, channels, depth, ctype == 0, samples)) return false;
