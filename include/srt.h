@@ -308,6 +308,11 @@ void  srt_host_free(void* p);
 void* srt_device_alloc(srt_context* ctx, size_t bytes);
 void  srt_device_free(srt_context* ctx, void* p);
 const char* srt_last_error(void);
+/* Measurement helper (roofline denominator, SURVEY.md §8d: "L2, to be pinned by a measured L2-read microbenchmark on the
+ * box"): every SM streams a `bytes`-sized device buffer `repeats` times with 16-byte loads; returns the read rate of the
+ * passes after the first in GB/s (CUDA events on the context's stream).  bytes <= L2 size measures L2 -> SM bandwidth,
+ * bytes >> L2 size HBM.  Not on the render path. */
+int  srt_measure_read_bandwidth(srt_context* ctx, size_t bytes, int repeats, double* gb_per_s);
 
 /* ---- leaf evaluation (test hook; not on the render path) ----
  * Runs ONE device leaf function of the render kernels on n independent cases so that tests can hold it against

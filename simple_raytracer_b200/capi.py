@@ -24,7 +24,7 @@ EXPORTS = [
     "srt_light_positions", "srt_host_alloc", "srt_host_free", "srt_device_alloc", "srt_device_free",
     "srt_last_error", "srt_eval_leaf", "srt_render_sparse", "srt_fetch_sparse",
     "srt_mesh_upload", "srt_mesh_destroy", "srt_mesh_info", "srt_scene_prep", "srt_scene_prep_status",
-    "srt_scene_counts", "srt_scene_download", "srt_scene_download_vnormals",
+    "srt_scene_counts", "srt_scene_download", "srt_scene_download_vnormals", "srt_measure_read_bandwidth",
 ]
 
 
@@ -66,6 +66,7 @@ def lib():
         L.srt_light_positions.argtypes = [C.POINTER(_abi.RenderParams), C.POINTER(C.c_float)]
         L.srt_render_sparse.argtypes = [vp, vp, C.POINTER(_abi.RenderParams), C.POINTER(C.c_uint64)]
         L.srt_fetch_sparse.argtypes = [vp, C.POINTER(C.c_float), C.POINTER(C.c_float), C.c_uint64]
+        L.srt_measure_read_bandwidth.argtypes = [C.c_void_p, C.c_size_t, C.c_int, C.POINTER(C.c_double)]
         L.srt_eval_leaf.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_float), C.POINTER(C.c_float), C.c_size_t]
         L.srt_host_alloc.argtypes = [C.c_size_t]
         L.srt_host_alloc.restype = vp
@@ -299,6 +300,12 @@ class Context:
         fp = C.POINTER(C.c_float)
         _check(lib().srt_fetch_sparse(self.h, pts.ctypes.data_as(fp), col.ctypes.data_as(fp), n.value))
         return pts, col
+
+    def measure_read_bandwidth(self, nbytes: int, repeats: int = 20) -> float:
+        """GB/s at which all SMs stream an `nbytes` device buffer (<= L2 size: L2 -> SM bandwidth; >> L2: HBM)."""
+        out = C.c_double(0.0)
+        _check(lib().srt_measure_read_bandwidth(self.h, int(nbytes), int(repeats), C.byref(out)))
+        return out.value
 
     def sync(self):
         _check(lib().srt_sync(self.h))

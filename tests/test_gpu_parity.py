@@ -383,3 +383,13 @@ def test_quality_switch_arguments_are_checked(gpu_ctx):
             gpu_ctx.render(sc, p)
         assert e.value.code == _abi.SRT_ERR_INVALID_ARG
     sc.destroy()
+
+
+def test_read_bandwidth_helper(gpu_ctx):
+    """srt_measure_read_bandwidth (the measured L2 denominator of bench.py's roofline_l2): an L2-resident buffer streams
+    faster than one far larger than L2, and both rates are plausible for a B200."""
+    l2 = max(gpu_ctx.measure_read_bandwidth(32 << 20, 20) for _ in range(2))
+    hbm = max(gpu_ctx.measure_read_bandwidth(2 << 30, 3) for _ in range(2))
+    assert 1000.0 < hbm < 9000.0 and hbm < l2 < 40000.0
+    with pytest.raises(capi.SrtError):
+        gpu_ctx.measure_read_bandwidth(16, 1)
