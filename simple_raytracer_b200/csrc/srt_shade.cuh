@@ -74,7 +74,7 @@ __device__ __forceinline__ PhongPixel prepare_pixel(const KArgs& a, const Hit& h
     const int32_t tex = __float_as_int(g1.w);
     if (tex >= 0) {                                                       // :350
         const float4 a1 = ldg4(ap + 1), a2 = ldg4(ap + 2);
-        // uv[0] = (a0.w? no) — layout: n.xyz pad | uv0.x uv0.y uv1.x uv1.y | uv2.x uv2.y pad pad
+        // srt_tri_attr as three float4: n.xyz pad | uv0.x uv0.y uv1.x uv1.y | uv2.x uv2.y pad pad
         const V3 bc = barycentric(v3(g0.x, g0.y, g0.z), v3(g1.x, g1.y, g1.z), v3(g2.x, g2.y, g2.z), px.P);
         // getTextureCoordinate :123-125: (b.x*A + b.y*B) + b.z*C per component
         const float ux = add(add(mul(bc.x, a1.x), mul(bc.y, a1.z)), mul(bc.z, a2.x));

@@ -368,3 +368,40 @@ def test_cpp_device_prep_header_against_the_reference_types(gpu_ctx):
     assert np.abs(wc - col).max() <= 1.0
     loaded.close()
     full.close()
+
+
+def test_device_prep_is_repeatable_under_load(gpu_ctx):
+    """Race hunt without a sanitizer: the same frames prepared 60 times each, alternating between two compositions (so the
+    cached launch graphs are swapped every time) while a second context renders on another stream — every download is
+    byte-identical to the host build.  A missing fence or barrier in the multi-CTA sort shows up here as a rare mismatch."""
+    cache = prep.MeshCache(gpu_ctx)
+    other = capi.Context(0)
+    cases = []
+    try:
+        for key, angle in (("C3", 33.0), ("C4", 141.0)):
+            cfg = scenes.CONFIGS[key]
+            hs = host.HostScene()
+            view = cfg.build(hs, angle)
+            want = hs.flatten()
+            light = scenes.light_view_space(hs, view)
+            hs.close()
+            cases.append((cfg, angle, want, light))
+        busy = other.upload(cases[0][2])
+        pb = _abi.default_params(480, 270, 270.0, cases[0][3], 16, True)
+        sc = {0: None, 1: None}
+        for rep in range(60):
+            for i, (cfg, angle, want, _light) in enumerate(cases):
+                if rep % 3 == 0:
+                    other.render(busy, pb, ids=False, want_t=False)
+                ds = prep.DeviceScene(cache)
+                cfg.build(ds, angle)
+                sc[i] = ds.commit(scene=sc[i])
+                ds.close()
+                sc[i].prep_status()
+                assert_same_scene(want, sc[i].download(), want.texture_names, cache.texture_names, what=f"repeat {rep}, scene {i}")
+        busy.destroy()
+        for s in sc.values():
+            s.destroy()
+    finally:
+        other.destroy()
+        cache.close()
