@@ -393,3 +393,22 @@ def test_read_bandwidth_helper(gpu_ctx):
     assert 1000.0 < hbm < 9000.0 and hbm < l2 < 40000.0
     with pytest.raises(capi.SrtError):
         gpu_ctx.measure_read_bandwidth(16, 1)
+
+
+def test_every_variant_is_repeatable(gpu_ctx):
+    """Race hunt without a sanitizer: 40 renders per kernel variant (the fused and overlapping ones order their stages by
+    published tile entries, fences and spin-waits) — every frame identical to the first, all variants identical to each other."""
+    cfg, arrays, light = _host_scene("C3", 200.0)            # 200 deg: most shadow rays cross the bunny
+    W, H, focal = scenes.scaled(cfg, 270)
+    p = _abi.default_params(W, H, focal, light, 16, True)
+    sc = gpu_ctx.upload(arrays)
+    first = None
+    for variant in (0, 2, 4, 1):
+        p.variant = variant
+        for rep in range(40 if variant != 1 else 3):
+            got = gpu_ctx.render(sc, p)
+            if first is None:
+                first = {k: v.copy() for k, v in got.items()}
+            for k in ("rgb", "tri_id", "t"):
+                assert np.array_equal(got[k], first[k]), (variant, rep, k)
+    sc.destroy()
