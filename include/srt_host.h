@@ -80,6 +80,8 @@ int  srt_host_flat_texture_name(srt_host_scene* s, int i, char* buf, int buflen)
 /* drawImage(..., saveImage = true) :461-498: the BMP CImg writes, from a dense sky-filled RGB8 frame (srt_render's
  * output); byte-identical to the reference's file.  0 on success, -1 on I/O failure. */
 int  srt_host_write_bmp(const char* path, const uint8_t* rgb, int width, int height);
+/* Not a reference format: the same dense RGB8 frame as a PNG file (8-bit RGB, lossless). */
+int  srt_host_write_png(const char* path, const uint8_t* rgb, int width, int height);
 void srt_host_set_asset_cache(int enabled);
 
 /* OBJ number parser (for tests): returns 1 and the value, or 0. */

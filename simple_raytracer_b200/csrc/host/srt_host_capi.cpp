@@ -211,6 +211,10 @@ int srt_host_flat_texture_name(srt_host_scene* s, int i, char* buf, int buflen) 
     return (int)s->flat.texture_names[(size_t)i].size();
 }
 
+int srt_host_write_png(const char* path, const uint8_t* rgb, int width, int height) {
+    return srt::write_png(path, rgb, width, height) ? 0 : -1;
+}
+
 int srt_host_write_bmp(const char* path, const uint8_t* rgb, int width, int height) {
     return srt::write_bmp(path, rgb, width, height) ? 0 : -1;
 }

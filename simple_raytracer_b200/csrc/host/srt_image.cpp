@@ -112,4 +112,14 @@ bool write_bmp(const char* path, const unsigned char* rgb, int width, int height
     return ok;
 }
 
+bool write_png(const char* path, const unsigned char* rgb, int width, int height) {
+    std::vector<uint8_t> file;
+    if (!path || !encode_png(rgb, width, height, file)) return false;
+    FILE* f = std::fopen(path, "wb");
+    if (!f) return false;
+    bool ok = std::fwrite(file.data(), 1, file.size(), f) == file.size();
+    ok = (std::fclose(f) == 0) && ok;
+    return ok;
+}
+
 }  // namespace srt

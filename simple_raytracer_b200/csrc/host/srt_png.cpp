@@ -9,6 +9,7 @@
 //   * zlib stream = concatenated IDAT chunks, inflate with stored / fixed / dynamic blocks (RFC 1950 / 1951).
 // CRCs and the Adler-32 are not checked (stb_image does not check them either).  Own implementation; tested against
 // the reference's decoder on its texture files and on generated images of every colour type (tests/test_host_scene.py).
+#include <algorithm>
 #include <cstdint>
 #include <cstdlib>
 #include <cstring>
@@ -258,6 +259,121 @@ bool decode_png(const uint8_t* data, size_t n, int* width, int* height, std::vec
     }
     if (width) *width = (int)w;
     if (height) *height = (int)h;
+    return true;
+}
+
+// ---- PNG output ("optional PNG" beside the reference's BMP) ---------------------------------
+// 8-bit RGB, non-interlaced; every row takes the filter (0-4) with the smallest sum of absolute residuals; one zlib
+// stream of fixed-Huffman blocks with a greedy hash-chain LZ77 (window 32 KiB).  Lossless, so any decoder returns the
+// frame bytes; not a reference format (the reference saves BMP, drawImage :488-494).
+namespace {
+
+struct BitWriter {
+    std::vector<uint8_t>& out; uint32_t hold = 0; int have = 0;
+    explicit BitWriter(std::vector<uint8_t>& o) : out(o) {}
+    void put(uint32_t v, int n) { hold |= v << have; have += n; while (have >= 8) { out.push_back((uint8_t)hold); hold >>= 8; have -= 8; } }
+    void put_code(uint32_t code, int n) { uint32_t r = 0; for (int i = 0; i < n; ++i) r |= ((code >> i) & 1u) << (n - 1 - i); put(r, n); }   // Huffman codes go MSB first
+    void flush() { if (have) { out.push_back((uint8_t)hold); hold = 0; have = 0; } }
+};
+
+void put_fixed_literal(BitWriter& bw, int s) {               // RFC 1951 3.2.6
+    if (s < 144) bw.put_code(0x30 + s, 8);
+    else if (s < 256) bw.put_code(0x190 + (s - 144), 9);
+    else if (s < 280) bw.put_code(s - 256, 7);
+    else bw.put_code(0xC0 + (s - 280), 8);
+}
+
+void deflate_fixed(const std::vector<uint8_t>& in, std::vector<uint8_t>& out) {
+    BitWriter bw(out);
+    bw.put(1, 1); bw.put(1, 2);                              // one final block, fixed codes
+    const size_t n = in.size();
+    const int kHashBits = 15, kChain = 24;
+    std::vector<int32_t> head((size_t)1 << kHashBits, -1), prev(n, -1);
+    auto hash = [&](size_t i) { return ((uint32_t)(in[i] | (in[i + 1] << 8) | (in[i + 2] << 16)) * 2654435761u) >> (32 - kHashBits); };
+    size_t i = 0;
+    while (i < n) {
+        int best_len = 0; size_t best_dist = 0;
+        if (i + 3 <= n) {
+            const uint32_t h = hash(i);
+            int32_t c = head[h];
+            for (int steps = 0; c >= 0 && steps < kChain && i - (size_t)c <= 32768; c = prev[c], ++steps) {
+                int l = 0;
+                const int lim = (int)std::min<size_t>(258, n - i);
+                while (l < lim && in[c + l] == in[i + l]) ++l;
+                if (l > best_len) { best_len = l; best_dist = i - (size_t)c; if (l == lim) break; }
+            }
+        }
+        if (best_len >= 3) {
+            int ls = 28; while (kLenBase[ls] > best_len) --ls;
+            put_fixed_literal(bw, 257 + ls);
+            bw.put((uint32_t)(best_len - kLenBase[ls]), kLenExtra[ls]);
+            int ds = 29; while (kDistBase[ds] > best_dist) --ds;
+            bw.put_code((uint32_t)ds, 5);
+            bw.put((uint32_t)(best_dist - kDistBase[ds]), kDistExtra[ds]);
+        } else {
+            put_fixed_literal(bw, in[i]);
+            best_len = 1;
+        }
+        for (int k = 0; k < best_len; ++k, ++i)
+            if (i + 3 <= n) { const uint32_t h = hash(i); prev[i] = head[h]; head[h] = (int32_t)i; }
+    }
+    put_fixed_literal(bw, 256);
+    bw.flush();
+}
+
+uint32_t crc32_of(const uint8_t* p, size_t n, uint32_t crc = 0) {
+    static uint32_t table[256]; static bool ready = false;
+    if (!ready) { for (uint32_t i = 0; i < 256; ++i) { uint32_t c = i; for (int k = 0; k < 8; ++k) c = (c & 1) ? 0xEDB88320u ^ (c >> 1) : c >> 1; table[i] = c; } ready = true; }
+    crc = ~crc;
+    for (size_t i = 0; i < n; ++i) crc = table[(crc ^ p[i]) & 255] ^ (crc >> 8);
+    return ~crc;
+}
+
+void put_chunk(std::vector<uint8_t>& file, const char* tag, const std::vector<uint8_t>& body) {
+    auto be = [&](uint32_t v) { for (int k = 3; k >= 0; --k) file.push_back((uint8_t)(v >> (8 * k))); };
+    be((uint32_t)body.size());
+    const size_t from = file.size();
+    file.insert(file.end(), tag, tag + 4);
+    file.insert(file.end(), body.begin(), body.end());
+    be(crc32_of(file.data() + from, file.size() - from));
+}
+
+}  // namespace
+
+bool encode_png(const uint8_t* rgb, int width, int height, std::vector<uint8_t>& file) {
+    if (!rgb || width <= 0 || height <= 0 || (int64_t)width * height > ((int64_t)1 << 28)) return false;
+    const size_t row = (size_t)width * 3;
+    std::vector<uint8_t> raw; raw.reserve((row + 1) * height);
+    std::vector<uint8_t> cand(row), best(row);
+    for (int y = 0; y < height; ++y) {
+        const uint8_t* cur = rgb + row * y; const uint8_t* up = y ? cur - row : nullptr;
+        long best_cost = -1; int best_f = 0;
+        for (int f = 0; f < 5; ++f) {
+            long cost = 0;
+            for (size_t i = 0; i < row; ++i) {
+                const int a = i >= 3 ? cur[i - 3] : 0, b = up ? up[i] : 0, c = (up && i >= 3) ? up[i - 3] : 0;
+                const int pred = f == 0 ? 0 : f == 1 ? a : f == 2 ? b : f == 3 ? (a + b) >> 1 : paeth(a, b, c);
+                cand[i] = (uint8_t)(cur[i] - pred);
+                cost += cand[i] < 128 ? cand[i] : 256 - cand[i];
+            }
+            if (best_cost < 0 || cost < best_cost) { best_cost = cost; best_f = f; best.swap(cand); }
+        }
+        raw.push_back((uint8_t)best_f);
+        raw.insert(raw.end(), best.begin(), best.end());
+    }
+    uint32_t s1 = 1, s2 = 0;                                 // Adler-32 of the uncompressed stream
+    for (size_t i = 0; i < raw.size();) { const size_t end = std::min(raw.size(), i + 5552); for (; i < end; ++i) { s1 += raw[i]; s2 += s1; } s1 %= 65521; s2 %= 65521; }
+    std::vector<uint8_t> z = {0x78, 0x01};
+    deflate_fixed(raw, z);
+    for (int k = 3; k >= 0; --k) z.push_back((uint8_t)(((s2 << 16) | s1) >> (8 * k)));
+    static const uint8_t sig[8] = {0x89, 'P', 'N', 'G', 0x0d, 0x0a, 0x1a, 0x0a};
+    file.assign(sig, sig + 8);
+    std::vector<uint8_t> hdr(13, 0);
+    for (int k = 0; k < 4; ++k) { hdr[k] = (uint8_t)((uint32_t)width >> (8 * (3 - k))); hdr[4 + k] = (uint8_t)((uint32_t)height >> (8 * (3 - k))); }
+    hdr[8] = 8; hdr[9] = 2;
+    put_chunk(file, "IHDR", hdr);
+    put_chunk(file, "IDAT", z);
+    put_chunk(file, "IEND", {});
     return true;
 }
 

@@ -116,6 +116,9 @@ bool decode_png(const uint8_t* data, size_t n, int* width, int* height, std::vec
 bool decode_jpeg(const uint8_t* data, size_t n, int* width, int* height, std::vector<uint8_t>& rgb);
 // drawImage's saved file (:461-498, CImg save_bmp) from a dense sky-filled RGB8 frame; false on I/O failure.
 bool write_bmp(const char* path, const unsigned char* rgb, int width, int height);
+// Not in the reference (it saves BMP only): the same frame as an 8-bit RGB PNG (srt_png.cpp).
+bool encode_png(const uint8_t* rgb, int width, int height, std::vector<uint8_t>& file);
+bool write_png(const char* path, const unsigned char* rgb, int width, int height);
 
 }  // namespace srt
 #endif

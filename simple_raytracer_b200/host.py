@@ -82,6 +82,7 @@ def _lib():
         L.srt_host_flat_texture_name.argtypes = [vp, i32, cp, i32]
         L.srt_host_parse_double.argtypes = [cp, C.POINTER(C.c_double)]
         L.srt_host_write_bmp.argtypes = [cp, C.c_void_p, i32, i32]
+        L.srt_host_write_png.argtypes = [cp, C.c_void_p, i32, i32]
         L.srt_host_set_asset_cache.argtypes = [i32]
         L.srt_host_set_asset_cache.restype = None
         L.srt_host_triangle_textures.argtypes = [vp, cp, C.POINTER(C.c_int32), C.c_char_p, i32]
@@ -298,6 +299,20 @@ def write_bmp(path, rgb: np.ndarray):
         raise ValueError("rgb must be [H][W][3] uint8")
     if _lib().srt_host_write_bmp(str(path).encode(), a.ctypes.data, a.shape[1], a.shape[0]) != 0:
         raise OSError(f"cannot write {path}")
+
+
+def write_png(path, rgb: np.ndarray):
+    """The same dense RGB8 frame as an 8-bit RGB PNG (lossless; not a reference format — the reference saves BMP)."""
+    a = np.ascontiguousarray(rgb, np.uint8)
+    if a.ndim != 3 or a.shape[2] != 3:
+        raise ValueError("rgb must be [H][W][3] uint8")
+    if _lib().srt_host_write_png(str(path).encode(), a.ctypes.data, a.shape[1], a.shape[0]) != 0:
+        raise OSError(f"cannot write {path}")
+
+
+def write_image(path, rgb: np.ndarray):
+    """write_png for a path ending in .png, else the reference's BMP."""
+    (write_png if str(path).lower().endswith(".png") else write_bmp)(path, rgb)
 
 
 def decode_image(path, use_sidecar: bool = True) -> np.ndarray:

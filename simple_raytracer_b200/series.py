@@ -103,7 +103,7 @@ class SeriesRenderer:
                 lane.scene = None
             rgb = lane.frame.array
             if pool is not None:
-                pool.submit(host.write_bmp, self.save_pattern.format(index=i, angle=angles[i]), rgb.copy())
+                pool.submit(host.write_image, self.save_pattern.format(index=i, angle=angles[i]), rgb.copy())
             if out is not None:
                 np.copyto(out, rgb)
                 rgb = out
@@ -164,7 +164,7 @@ class SeriesRenderer:
             pool.submit(hs.close)                    # freeing 70 k triangles + the Node tree takes milliseconds: off the critical path
             rgb = lane.frame.array
             if self.save_pattern:
-                pool.submit(host.write_bmp, self.save_pattern.format(index=i, angle=angles[i]), rgb.copy())
+                pool.submit(host.write_image, self.save_pattern.format(index=i, angle=angles[i]), rgb.copy())
             if out is not None:
                 np.copyto(out, rgb)
                 rgb = out

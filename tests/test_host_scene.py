@@ -481,3 +481,29 @@ def test_damaged_texture_files_fail_cleanly(tmp_path):
             except ValueError:
                 failed += 1
     assert failed > 50 and decoded + failed == 150 * len(files)
+
+
+def test_png_output_round_trips(tmp_path):
+    """host.write_png (8-bit RGB, fixed-Huffman deflate with LZ77 matches, per-row filter choice): our own decoder, Pillow and
+    — where it is built — the reference's stb_image all return the frame bytes."""
+    rng = np.random.default_rng(9)
+    frames = [rng.integers(0, 256, (1, 1, 3), dtype=np.uint8), rng.integers(0, 256, (37, 53, 3), dtype=np.uint8),
+              np.zeros((64, 300, 3), np.uint8), np.full((5, 7, 3), 255, np.uint8)]
+    yy, xx = np.mgrid[0:270, 0:480]
+    smooth = np.stack([xx * 255 // 479, yy * 255 // 269, (xx + yy) % 256], axis=2).astype(np.uint8)
+    smooth[100:140, 200:300] = (173, 216, 230)              # a flat sky-coloured patch: long matches
+    frames.append(smooth)
+    for i, f in enumerate(frames):
+        path = tmp_path / f"o{i}.png"
+        host.write_png(path, f)
+        assert np.array_equal(host.decode_image(path, use_sidecar=False), f)
+        try:
+            from PIL import Image
+            assert np.array_equal(np.asarray(Image.open(path).convert("RGB")), f)
+        except ImportError:
+            pass
+        if pyoracle.ref_available():
+            assert np.array_equal(_ref_decode(path), f)
+    assert (tmp_path / "o4.png").stat().st_size < smooth.nbytes // 3      # it does compress
+    host.write_image(tmp_path / "x.bmp", smooth)
+    assert (tmp_path / "x.bmp").read_bytes()[:2] == b"BM"
