@@ -19,7 +19,7 @@ LIB_PATH = Path(_os.environ.get("SRT_LIB") or (Path(__file__).resolve().parent /
 
 EXPORTS = [
     "srt_abi_version", "srt_device_count", "srt_context_create", "srt_context_destroy",
-    "srt_context_set_stream", "srt_context_get_info", "srt_scene_upload", "srt_scene_update",
+    "srt_context_set_stream", "srt_context_set_bands", "srt_context_get_info", "srt_scene_upload", "srt_scene_update",
     "srt_scene_destroy", "srt_render", "srt_sync", "srt_last_stats", "srt_default_params",
     "srt_light_positions", "srt_host_alloc", "srt_host_free", "srt_device_alloc", "srt_device_free",
     "srt_last_error", "srt_eval_leaf", "srt_render_sparse", "srt_fetch_sparse",
@@ -52,6 +52,7 @@ def lib():
         L.srt_context_destroy.argtypes = [vp]
         L.srt_context_destroy.restype = None
         L.srt_context_set_stream.argtypes = [vp, vp]
+        L.srt_context_set_bands.argtypes = [vp, C.c_int]
         L.srt_context_get_info.argtypes = [vp, C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_int),
                                            C.POINTER(C.c_size_t)]
         L.srt_scene_upload.argtypes = [vp, C.POINTER(_abi.SceneDesc), C.POINTER(vp)]
@@ -231,6 +232,14 @@ class Context:
         self.stream = stream              # None: the context's own stream
         if stream is not None:
             _check(lib().srt_context_set_stream(self.h, C.c_void_p(stream)))
+
+    def set_bands(self, bands: int) -> int:
+        """Row bands per frame of the default pipeline (2: one frame's halves overlap on two streams; 1: in one piece, for
+        callers that keep several frames in flight on several contexts).  Returns the previous value."""
+        before = lib().srt_context_set_bands(self.h, int(bands))
+        if before < 0:
+            _check(before)
+        return before
 
     def info(self):
         sm, ma, mi, l2 = C.c_int(), C.c_int(), C.c_int(), C.c_size_t()

@@ -64,6 +64,13 @@ struct srt_context {
     int last_launches = 0;
     // last render
     bool have_last = false;
+    // Two-band rendering (srt_render): the lower half of the rows is rendered by a child context on its own stream, so
+    // that the stages of the two halves overlap (one half's shadow pass runs in the other half's primary-pass tail).
+    srt_context* band = nullptr;      // child (owned); its `parent` points back
+    srt_context* parent = nullptr;
+    cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
+    bool last_banded = false;
+    int bands = 2;
     uint64_t last_primary = 0;
     int last_lights = 0;
     uint32_t last_objects = 0;

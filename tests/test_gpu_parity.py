@@ -130,7 +130,7 @@ def test_full_size_c3_variants_agree_and_sample_matches_oracle(gpu_ctx, ref_scen
     for o in outs[1:]:
         for k in ("rgb", "obj_id", "tri_id", "t"):
             assert np.array_equal(outs[0][k], o[k]), k
-    assert [o["stats"]["kernel_launches"] for o in outs] == [4, 2, 4, 1]
+    assert [o["stats"]["kernel_launches"] for o in outs] == [8, 2, 4, 1]     # the default pipeline renders two row bands of 4 launches each
     p = _abi.default_params(W, H, focal, light, N, True)
     want = pyoracle.oracle_render(arrays, p, col_begin=7, col_step=48)
     cols = np.arange(7, W, 48)
@@ -411,4 +411,28 @@ def test_every_variant_is_repeatable(gpu_ctx):
                 first = {k: v.copy() for k, v in got.items()}
             for k in ("rgb", "tri_id", "t"):
                 assert np.array_equal(got[k], first[k]), (variant, rep, k)
+    sc.destroy()
+
+
+@pytest.mark.parametrize("key,W,H", [("C3", 333, 203), ("C4", 256, 130), ("spheres", 200, 128)])
+def test_two_row_bands_equal_one_piece(gpu_ctx, key, W, H):
+    """srt_context_set_bands: the default pipeline renders a frame of >= 128 rows as two row bands on two streams; the
+    frame, the id / t planes and the counted hit pixels are those of the one-piece render (pixels are independent, :511-523)."""
+    cfg, arrays, light = _host_scene(key)
+    p = _abi.default_params(W, H, float(H), light, 5, True)
+    sc = gpu_ctx.upload(arrays)
+    assert gpu_ctx.set_bands(1) == 2                       # two bands are the default
+    one = gpu_ctx.render(sc, p)
+    assert gpu_ctx.set_bands(2) == 1
+    two = gpu_ctx.render(sc, p)
+    again = gpu_ctx.render(sc, p)
+    for k in ("rgb", "obj_id", "tri_id", "t"):
+        assert np.array_equal(one[k], two[k]) and np.array_equal(two[k], again[k]), k
+    assert one["stats"]["hit_pixels"] == two["stats"]["hit_pixels"] and one["stats"]["primary_rays"] == two["stats"]["primary_rays"] == W * H
+    assert two["stats"]["kernel_launches"] == 2 * one["stats"]["kernel_launches"] or one["stats"]["kernel_launches"] < 4
+    p.row_begin, p.row_end = 8, H - 3                      # a row range is split the same way
+    part = gpu_ctx.render(sc, p)
+    assert np.array_equal(part["tri_id"][8:H - 3], one["tri_id"][8:H - 3]) and np.array_equal(part["rgb"][8:H - 3], one["rgb"][8:H - 3])
+    with pytest.raises(capi.SrtError):
+        gpu_ctx.set_bands(3)
     sc.destroy()
