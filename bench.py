@@ -335,6 +335,24 @@ def run_b200_arm(args):
         rays0 = ray_count(W, H, N, hits_of(k0), n_obj)
         c3_still = {"ms_per_frame": ms0, "value": rays0 / (ms0 * 1e-3) / 1e6, "unit": UNIT, "rays_per_frame": rays0,
                     "what": "frame 0 of the orbit = BASELINE configs[2] (C3) itself, same timing method"}
+    # the same K frames with two row bands per frame (srt_context_set_bands: opt-in, one frame at a time)
+    two_bands = None
+    if rank == 0 and not args.still and args.variant == 0:
+        ctx.set_bands(2)
+        try:
+            for s in range(3):
+                flush.zero_(); render_step(Wm + s)
+            evb = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(K)]
+            for s in range(K):
+                flush.zero_()
+                evb[s][0].record(); render_step(Wm + s); evb[s][1].record()
+            torch.cuda.synchronize()
+            msb = float(sum(a.elapsed_time(b) for a, b in evb))
+            two_bands = {"value": rays_local / (msb * 1e-3) / 1e6, "unit": UNIT, "ms_per_step": msb / K,
+                         "what": "rank 0, the same K frames and timing as `value`, after srt_context_set_bands(ctx, 2): the upper and "
+                                 "lower half of every frame render on two streams and overlap each other's stages (same bytes)"}
+        finally:
+            ctx.set_bands(1)
     # algorithmic work of frame Wm (the first timed one) under the REFERENCE's traversal rules, counted by the
     # instrumented CUDA kernel (SRT_VARIANT_COUNT; tests check its counters against the oracle's)
     work = None
@@ -557,6 +575,8 @@ def run_b200_arm(args):
                                    + (" (all frames gathered to rank 0 over NCCL first)" if args.gather else "")}
         if c3_still:
             line["c3_frame0"] = c3_still
+        if two_bands:
+            line["value_two_bands"] = two_bands
         if series:
             line["series_with_host_prep"] = {
                 "frames_per_s": world * series[1] / series_s, "frames": world * series[1], "host_threads_per_rank": series[2],

@@ -222,10 +222,10 @@ int  srt_context_create(int device, srt_context** out);
 void srt_context_destroy(srt_context* ctx);
 /* Use an existing cudaStream_t (e.g. torch's current stream) instead of the context's own. */
 int  srt_context_set_stream(srt_context* ctx, void* cuda_stream);
-/* Row bands per frame of the default pipeline: 2 (default) renders the upper and the lower half of the rows on two
- * streams so that their stages overlap (one frame at a time: -11 % time); 1 renders in one piece — the choice when
- * several contexts already keep frames in flight concurrently (an image series), where the second band only adds
- * launches.  Returns the previous value, or a negative srt_status. */
+/* Row bands per frame of the default pipeline: 1 (default) renders a frame in one piece; 2 renders the upper and the
+ * lower half of the rows on two streams so that their stages overlap — for callers that render ONE frame at a time
+ * (-11 % time per frame; the same bytes).  Callers that already keep several frames in flight on several contexts (an
+ * image series) gain nothing from it.  Returns the previous value, or a negative srt_status. */
 int  srt_context_set_bands(srt_context* ctx, int bands);
 int  srt_context_get_info(srt_context* ctx, int* sm_count, int* cc_major, int* cc_minor,
                           size_t* l2_bytes);

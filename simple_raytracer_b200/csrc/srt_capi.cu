@@ -557,13 +557,12 @@ static int render_impl(srt_context* c, const srt_scene* s, const srt_render_para
 // shadow -> shade on its own counters and scratch, and the device interleaves them — one band's shadow pass fills the
 // SMs the other band's primary pass leaves idle in its tail, and stages with different instruction mixes share the
 // issue slots.  Pixels are independent (:511-523), so the frame is the same bytes; measured -11 % time per frame
-// over the C3 orbit.  SRT_BANDS=1 in the environment renders in one piece.
+// over the C3 orbit.  Opt-in per context: srt_context_set_bands(ctx, 2).
 int srt_render(srt_context* c, const srt_scene* s, const srt_render_params* p, const srt_frame* out) {
     if (!c || !s || !p || !out) return fail(SRT_ERR_INVALID_ARG, "NULL argument");
-    static const bool bands_off = [] { const char* e = std::getenv("SRT_BANDS"); return e && e[0] == '1'; }();
     int rb = p->row_begin, re = p->row_end;
     if (rb == 0 && re == 0) re = p->height;
-    const bool banded = !bands_off && c->bands == 2 && !c->parent && (p->variant == SRT_VARIANT_DEFAULT || p->variant == SRT_VARIANT_SPLIT) && p->use_bvh &&
+    const bool banded = c->bands == 2 && !c->parent && (p->variant == SRT_VARIANT_DEFAULT || p->variant == SRT_VARIANT_SPLIT) && p->use_bvh &&
                         p->row_block == 0 && p->shard_count <= 1 && s->n_objects > 0 && rb >= 0 && re <= p->height && re - rb >= 128;
     c->last_banded = false;
     if (!banded) return render_impl(c, s, p, out);

@@ -70,7 +70,7 @@ struct srt_context {
     srt_context* parent = nullptr;
     cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
     bool last_banded = false;
-    int bands = 2;
+    int bands = 1;                    // srt_context_set_bands
     uint64_t last_primary = 0;
     int last_lights = 0;
     uint32_t last_objects = 0;

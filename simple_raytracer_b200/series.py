@@ -149,7 +149,8 @@ class SeriesRenderer:
         """Yields (index, rgb[H][W][3] host array, timing) per frame, in order.  The yielded array is the lane's
         pinned frame (valid until as many further frames as there are lanes have been taken), or `out` if given (valid until the next iteration)."""
         angles = list(angles)
-        # several lanes already keep frames in flight concurrently: a second row band per frame would only add launches
+        # several lanes already keep frames in flight concurrently: a second row band per frame (a caller may have asked for
+        # it on the shared context) would only add launches
         before = [lane.ctx.set_bands(1) for lane in self.lanes] if len(self.lanes) > 1 else []
         try:
             yield from self._frames(angles, out)
