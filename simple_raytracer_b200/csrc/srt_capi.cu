@@ -7,6 +7,7 @@
 #include <cmath>
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <string>
 #include <vector>
@@ -75,6 +76,9 @@ int srt_context_create(int device, srt_context** out) {
         return fail(SRT_ERR_UNSUPPORTED, "device %d is sm_%d%d; this library carries sm_100a code only", device,
                     prop.major, prop.minor);
     srt_context* c = new srt_context();
+    // SRT_DEFAULT_BANDS=1|2: A/B switch for the row-band default (srt_context_set_bands overrides it per context)
+    static const int env_bands = [] { const char* e = std::getenv("SRT_DEFAULT_BANDS"); return e ? std::atoi(e) : 0; }();
+    if (env_bands == 1 || env_bands == 2) c->bands = env_bands;
     c->device = device;
     c->sm_count = prop.multiProcessorCount;
     c->cc_major = prop.major; c->cc_minor = prop.minor;

@@ -261,8 +261,23 @@ def test_series_driver_equals_frame_by_frame(gpu_ctx, tmp_path):
         hs = host.HostScene(); view = cfg.build(hs, ang); light = scenes.light_view_space(hs, view)
         sc = gpu_ctx.upload(hs.flatten())
         want = gpu_ctx.render(sc, _abi.default_params(W, H, focal, light, 4, True), ids=False, want_t=False)["rgb"]
+        if not np.array_equal(got[i], want):                # say which side is wrong, and where
+            fresh = capi.Context(0)
+            fresh.set_bands(1)
+            sc2 = fresh.upload(hs.flatten())
+            truth = fresh.render(sc2, _abi.default_params(W, H, focal, light, 4, True), ids=False, want_t=False)["rgb"]
+            again = gpu_ctx.render(sc, _abi.default_params(W, H, focal, light, 4, True), ids=False, want_t=False)["rgb"]
+            sc2.destroy(); fresh.destroy()
+            def where(a, b):
+                ys, xs = np.nonzero((a != b).any(axis=2))
+                return f"{len(ys)} px, rows {ys.min()}..{ys.max()}, cols {xs.min()}..{xs.max()}" if len(ys) else "equal"
+            import os
+            os.makedirs("gpurun_out", exist_ok=True)
+            np.savez_compressed(f"gpurun_out/series_mismatch_{os.getpid()}_{i}.npz", series=got[i], single=want, truth=truth, again=again)
+            sc.destroy()
+            raise AssertionError(f"frame {i} (angle {ang}): series vs single: {where(got[i], want)}; series vs truth: {where(got[i], truth)}; "
+                                 f"single vs truth: {where(want, truth)}; single-again vs truth: {where(again, truth)}")
         sc.destroy()
-        assert np.array_equal(got[i], want), f"frame {i}"
 
 
 def test_jittered_light_samples_match_the_oracle_and_are_reproducible(gpu_ctx, ref_scene):
@@ -421,8 +436,9 @@ def test_two_row_bands_equal_one_piece(gpu_ctx, key, W, H):
     cfg, arrays, light = _host_scene(key)
     p = _abi.default_params(W, H, float(H), light, 5, True)
     sc = gpu_ctx.upload(arrays)
+    default = gpu_ctx.set_bands(1)
     one = gpu_ctx.render(sc, p)
-    assert gpu_ctx.set_bands(2) == 1                       # one piece is the default
+    assert gpu_ctx.set_bands(2) == 1
     try:
         two = gpu_ctx.render(sc, p)
         again = gpu_ctx.render(sc, p)
@@ -431,7 +447,7 @@ def test_two_row_bands_equal_one_piece(gpu_ctx, key, W, H):
         with pytest.raises(capi.SrtError):
             gpu_ctx.set_bands(3)
     finally:
-        assert gpu_ctx.set_bands(1) == 2
+        assert gpu_ctx.set_bands(default) == 2
     for k in ("rgb", "obj_id", "tri_id", "t"):
         assert np.array_equal(one[k], two[k]) and np.array_equal(two[k], again[k]), k
     assert one["stats"]["hit_pixels"] == two["stats"]["hit_pixels"] and one["stats"]["primary_rays"] == two["stats"]["primary_rays"] == W * H
