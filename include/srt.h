@@ -237,7 +237,11 @@ int  srt_context_get_info(srt_context* ctx, int* sm_count, int* cc_major, int* c
 int  srt_scene_upload(srt_context* ctx, const srt_scene_desc* desc, srt_scene** out);
 /* Re-upload new contents into an existing scene object (per-frame scenes of an image series);
  * device buffers are reused when large enough.  The copy is asynchronous on the context stream
- * when the host arrays are pinned (srt_host_alloc). */
+ * when the host arrays are pinned (srt_host_alloc).
+ * Textures: desc->textures == NULL keeps the resident table (n_textures must equal the resident count).  Otherwise the
+ * table of `desc` becomes the scene's table: every slot is compared with the resident one (host pointer, size, a sampled
+ * fingerprint of the texels) and only slots that differ are copied again — the triangles' `tex` indices of `desc` always
+ * refer to the table passed with them.  srt_flatten.hpp numbers textures by name, so the slots of a series do not move. */
 int  srt_scene_update(srt_context* ctx, srt_scene* scene, const srt_scene_desc* desc);
 void srt_scene_destroy(srt_scene* scene);
 

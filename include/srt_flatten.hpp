@@ -16,6 +16,7 @@
 #ifndef SRT_FLATTEN_HPP_
 #define SRT_FLATTEN_HPP_
 
+#include <algorithm>
 #include <cmath>
 #include <cstdint>
 #include <cstring>
@@ -171,6 +172,29 @@ struct Flattener {
     }
 };
 
+// Texture slots were handed out in first-encounter order of the leaf walk, and that order moves with the camera (the
+// hierarchy is rebuilt from view-space vertices every frame).  Renumber them by texture NAME so that the same set of
+// textures always gets the same slots: a scene updated in place (srt_scene_update) then keeps a valid texture table.
+inline void canonical_texture_slots(FlatScene& fs) {
+    const size_t n = fs.textures.size();
+    if (n < 2) return;
+    std::vector<int32_t> order(n);
+    for (size_t i = 0; i < n; ++i) order[i] = (int32_t)i;
+    std::sort(order.begin(), order.end(), [&](int32_t a, int32_t b) { return fs.texture_names[(size_t)a] < fs.texture_names[(size_t)b]; });
+    std::vector<int32_t> slot_of(n);
+    std::vector<srt_texture_desc> tex(n);
+    std::vector<std::string> names(n);
+    for (size_t k = 0; k < n; ++k) {
+        slot_of[(size_t)order[k]] = (int32_t)k;
+        tex[k] = fs.textures[(size_t)order[k]];
+        names[k] = fs.texture_names[(size_t)order[k]];
+    }
+    fs.textures.swap(tex);
+    fs.texture_names.swap(names);
+    for (auto& g : fs.geom) if (g.tex >= 0) g.tex = slot_of[(size_t)g.tex];
+    for (auto& g : fs.flat_geom) if (g.tex >= 0) g.tex = slot_of[(size_t)g.tex];
+}
+
 template <class M, class K>
 inline bool lookup3(M& m, const K& key, float out[3]) {
     auto it = m.find(key);
@@ -242,6 +266,7 @@ int flatten(OM& om, FlatScene& fs, bool with_flat_lists = false, std::string* er
         fs.object_names.push_back(name);
         ++obj;
     }
+    detail::canonical_texture_slots(fs);
     return SRT_OK;
 }
 

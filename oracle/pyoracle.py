@@ -105,6 +105,26 @@ class RefRenderArgs(C.Structure):
 
 
 _ref = None
+_ref_dropin = None
+REF_DROPIN_SO = HERE / "_ref" / "libsrt_ref_dropin.so"
+
+
+def ref_dropin_lib():
+    """libsrt_ref_dropin.so: the product's drop-in headers compiled against the reference's types.  The ONLY test library
+    that links the product (libsrt_b200.so); loaded by the drop-in tests alone, never by the oracle / CPU-baseline legs."""
+    global _ref_dropin
+    if _ref_dropin is None:
+        if not REF_DROPIN_SO.exists():
+            raise FileNotFoundError(f"{REF_DROPIN_SO} missing: needs /root/reference and `make -C oracle ref`")
+        lib = C.CDLL(str(REF_DROPIN_SO))
+        vp, cp, i32 = C.c_void_p, C.c_char_p, C.c_int
+        lib.ref_dropin_render.restype = C.c_long
+        lib.ref_dropin_render.argtypes = [vp, i32, i32, _f32p, _f32p, _f32p, C.c_long, C.c_char_p, i32]
+        lib.ref_device_prep.restype = C.c_long
+        lib.ref_device_prep.argtypes = [vp, i32, C.POINTER(cp), _f32p, i32, i32, _f32p, _f32p, _f32p, C.c_long, vp, vp, vp, vp,
+                                        C.c_char_p, i32]
+        _ref_dropin = lib
+    return _ref_dropin
 
 
 def ref_available() -> bool:
@@ -155,11 +175,6 @@ def ref_lib():
         lib.ref_render_verbatim.restype = C.c_long
         lib.ref_render_verbatim.argtypes = [vp, i32, i32, _f32p, vp, C.POINTER(C.c_double)]
         lib.ref_selfcheck.argtypes = [vp, i32, i32, _f32p]
-        lib.ref_dropin_render.restype = C.c_long
-        lib.ref_dropin_render.argtypes = [vp, i32, i32, _f32p, _f32p, _f32p, C.c_long, C.c_char_p, i32]
-        lib.ref_device_prep.restype = C.c_long
-        lib.ref_device_prep.argtypes = [vp, i32, C.POINTER(cp), _f32p, i32, i32, _f32p, _f32p, _f32p, C.c_long, vp, vp, vp, vp,
-                                        C.c_char_p, i32]
         lib.ref_verbatim_sparse.restype = C.c_long
         lib.ref_verbatim_sparse.argtypes = [vp, i32, i32, _f32p, _f32p, _f32p, C.c_long]
         lib.ref_draw_image.argtypes = [i32, i32, _f32p, _f32p, C.c_long, i32]
@@ -389,7 +404,7 @@ class RefBackend:
         col = np.zeros((cap, 3), np.float32)
         if dropin:
             err = C.create_string_buffer(1024)
-            n = self.lib.ref_dropin_render(self.h, width, height, _fp(l4), _fp(pts), _fp(col), cap, err, 1024)
+            n = ref_dropin_lib().ref_dropin_render(self.h, width, height, _fp(l4), _fp(pts), _fp(col), cap, err, 1024)
             if n < 0:
                 raise RuntimeError("srt_dropin: " + err.value.decode(errors="replace"))
         else:
@@ -412,7 +427,7 @@ class RefBackend:
         pts = np.zeros((cap, 2), np.float32)
         col = np.zeros((cap, 3), np.float32)
         err = C.create_string_buffer(1024)
-        n = self.lib.ref_device_prep(self.h, len(calls), names, _fp(mats), width, height, _fp(l4), _fp(pts), _fp(col), cap,
+        n = ref_dropin_lib().ref_device_prep(self.h, len(calls), names, _fp(mats), width, height, _fp(l4), _fp(pts), _fp(col), cap,
                                      nodes.ctypes.data, geom.ctypes.data, attr.ctypes.data, objs.ctypes.data, err, 1024)
         if n < 0:
             raise RuntimeError("srt_prep: " + err.value.decode(errors="replace"))

@@ -18,31 +18,9 @@
 //     winning (object, triangle, t) is recorded.
 // ref_selfcheck() proves the restated loops reproduce the verbatim function bit-for-bit at the
 // shipped constants.
-#include <atomic>
-#include <cstdint>
-#include <cstdlib>
-#include <cstring>
-#include <string>
-#include <thread>
-#include <unistd.h>
-
-#define main reference_main_never_called
-#include "simple_raytracer.cpp"   // the reference TU, found through -I$(REF)
-#undef main
-
-#include "srt_flatten.hpp"        // product header (duck-typed on the reference's member names)
+#include "ref_scene.hpp"
 
 namespace {
-
-struct RefScene {
-    ObjectManager om;
-    srt::FlatScene flat;
-    bool flat_valid = false;
-    // leaf Node* -> first index in the flattened (leaf-order) triangle array
-    std::unordered_map<const Node*, int> leaf_base;
-    std::vector<std::string> names;                 // objTriangles iteration order
-    std::string last_error;
-};
 
 void free_tree(Node* n) {
     if (!n) return;
@@ -534,60 +512,6 @@ extern "C" int ref_decode_texture(const char* path, unsigned char* out, int cap,
     return (out && n > cap) ? -2 : 0;
 }
 
-// ---- the drop-in adapter (include/srt_dropin.hpp) compiled against the REFERENCE's own types -------
-// Test only: proves that srt::Renderer::sendRaysAndIntersectPointsColors is a drop-in for :505 — same
-// ImageData type, same sparse column-major contents — by running it on the reference's ObjectManager.
-#include "srt_dropin.hpp"
-extern "C" long ref_dropin_render(void* h, int W, int Hh, const float* light4, float* points2, float* colors3, long cap,
-                                  char* err, int errlen) {
-    RefScene* s = (RefScene*)h;
-    try {
-        static srt::Renderer* gpu = nullptr;       // one context for the test process
-        if (!gpu) gpu = new srt::Renderer(0);
-        ImageData d = gpu->sendRaysAndIntersectPointsColors<ImageData>(glm::vec2((float)W, (float)Hh),
-                                                                      glm::vec4(light4[0], light4[1], light4[2], light4[3]), &s->om);
-        const long n = (long)d.imagePoints.size();
-        for (long i = 0; i < n && i < cap; ++i) {
-            points2[2 * i] = d.imagePoints[i].x; points2[2 * i + 1] = d.imagePoints[i].y;
-            colors3[3 * i] = d.imageColors[i].x; colors3[3 * i + 1] = d.imageColors[i].y; colors3[3 * i + 2] = d.imageColors[i].z;
-        }
-        return n;
-    } catch (const std::exception& e) {
-        if (err && errlen > 0) std::snprintf(err, (size_t)errlen, "%s", e.what());
-        return -1;
-    }
-}
-// ---- the device scene prep (include/srt_prep.hpp) compiled against the REFERENCE's own types ----------------
-// Test only.  `h` holds the meshes as LOADED (no transforms).  The recipe is applied twice: to a copy of the
-// reference's ObjectManager by the reference's own transformTriangles / createBoundingHierarchy (-> flatten: the
-// expected arrays, in `h`), and through srt::DevicePrep on the GPU (-> the arrays written to the out pointers).
-#include "srt_prep.hpp"
-extern "C" long ref_device_prep(void* h, int n_calls, const char* const* names, const float* m16s, int W, int Hh,
-                                const float* light4, float* points2, float* colors3, long cap, srt_node* nodes,
-                                srt_tri_geom* geom, srt_tri_attr* attr, srt_object* objects, char* err, int errlen) {
-    RefScene* s = (RefScene*)h;
-    try {
-        static srt::Renderer* gpu = nullptr;
-        if (!gpu) gpu = new srt::Renderer(0);
-        srt::DevicePrep prep(gpu->context());
-        prep.loadMeshes(s->om);
-        for (int i = 0; i < n_calls; ++i) prep.transformTriangles(names[i], load(m16s + 16 * i));
-        srt_scene* sc = prep.commit(s->om);
-        prep.status();
-        if (srt_scene_download(gpu->context(), sc, nodes, geom, attr, nullptr, nullptr, objects) != SRT_OK)
-            throw std::runtime_error(srt_last_error());
-        ImageData d = gpu->renderPrepared<ImageData>(glm::vec2((float)W, (float)Hh), glm::vec4(light4[0], light4[1], light4[2], light4[3]), sc);
-        const long n = (long)d.imagePoints.size();
-        for (long i = 0; i < n && i < cap; ++i) {
-            points2[2 * i] = d.imagePoints[i].x; points2[2 * i + 1] = d.imagePoints[i].y;
-            colors3[3 * i] = d.imageColors[i].x; colors3[3 * i + 1] = d.imageColors[i].y; colors3[3 * i + 2] = d.imageColors[i].z;
-        }
-        return n;
-    } catch (const std::exception& e) {
-        if (err && errlen > 0) std::snprintf(err, (size_t)errlen, "%s", e.what());
-        return -1;
-    }
-}
 // The reference's drawImage(..., saveImage = true, displayImage = false) (:461-498) on caller-supplied lists: writes
 // images/generation/output<angle>.bmp under the CWD (the directory must exist, like for the reference's main()).
 extern "C" int ref_draw_image(int W, int Hh, const float* points2, const float* colors3, long n, int angle) {

@@ -3,7 +3,7 @@
  * Plain-C restatement of the reference's per-pixel render loop (leonlang/simple_raytracer,
  * simple_raytracer.cpp:32-457, 505-525) on the flattened scene of include/srt.h.  It exists to
  * check the CUDA kernel and to serve as the timed CPU baseline where oracle/_ref is absent.
- * Parity status: PINNED — tests/test_oracle_vs_reference.py compares every function here with
+ * Parity status: PINNED — tests/test_oracle_golden.py compares every function here with
  * the reference's own compiled functions (oracle/_ref/libsrt_ref.so) bit for bit, and
  * tests/golden/ holds reference-generated vectors for boxes without /root/reference.
  *

@@ -236,7 +236,8 @@ int srt_sync(srt_context* c) {
 namespace {
 
 // Rejects what would make the kernel (or the reference) read out of bounds.
-int validate_scene(const srt_scene_desc* d, uint32_t* max_depth_out, uint32_t* max_leaf_out = nullptr) {
+// `resident`: the scene being updated — desc->textures == NULL then means "keep its textures".
+int validate_scene(const srt_scene_desc* d, uint32_t* max_depth_out, uint32_t* max_leaf_out = nullptr, const srt_scene* resident = nullptr) {
     if (max_leaf_out) *max_leaf_out = 0;
     if (!d) return fail(SRT_ERR_INVALID_ARG, "scene desc is NULL");
     if (d->n_objects == 0) { *max_depth_out = 0; return SRT_OK; }
@@ -244,10 +245,10 @@ int validate_scene(const srt_scene_desc* d, uint32_t* max_depth_out, uint32_t* m
     if (d->n_nodes && !d->nodes) return fail(SRT_ERR_INVALID_ARG, "nodes is NULL");
     if (d->n_tris && (!d->geom || !d->attr)) return fail(SRT_ERR_INVALID_ARG, "geom/attr is NULL");
     if (d->n_flat && (!d->flat_geom || !d->flat_attr)) return fail(SRT_ERR_INVALID_ARG, "flat_geom/flat_attr is NULL");
-    if (d->n_textures && !d->textures) return fail(SRT_ERR_INVALID_ARG, "textures is NULL");
+    if (d->n_textures && !d->textures && !(resident && resident->n_textures == d->n_textures)) return fail(SRT_ERR_INVALID_ARG, "textures is NULL");
     if (d->n_nodes >= 0x7fffffffull || d->n_tris >= 0x7fffffffull || d->n_flat >= 0x7fffffffull)
         return fail(SRT_ERR_UNSUPPORTED, "scene too large for 31-bit indices");
-    for (uint32_t t = 0; t < d->n_textures; ++t)
+    for (uint32_t t = 0; t < d->n_textures && d->textures; ++t)
         if (!d->textures[t].rgb || d->textures[t].width <= 0 || d->textures[t].height <= 0)
             return fail(SRT_ERR_SCENE, "texture %u has no data (the reference dereferences textureData[...] at simple_raytracer.cpp:354-358)", t);
     uint32_t max_depth = 0;
@@ -307,9 +308,24 @@ int copy_in(srt_context* c, DevBuf& dst, const void* src, size_t bytes) {
     return SRT_OK;
 }
 
-int fill_scene(srt_context* c, srt_scene* s, const srt_scene_desc* d, bool textures_too) {
+// 64-bit fingerprint of a texture: its size and 96 eight-byte samples spread over the texels (both ends included).
+// Cheap enough for every frame of a series; identity of a slot = host pointer + dimensions + this.
+uint64_t texture_fingerprint(const uint8_t* rgb, size_t bytes) {
+    uint64_t h = 0x9E3779B97F4A7C15ull ^ (uint64_t)bytes;
+    auto mix = [&](uint64_t v) { h ^= v; h *= 0xff51afd7ed558ccdull; h ^= h >> 29; };
+    if (bytes < 8) { for (size_t i = 0; i < bytes; ++i) mix(rgb[i]); return h; }
+    const size_t last = bytes - 8, n = 96;
+    for (size_t k = 0; k < n; ++k) {
+        uint64_t v;
+        std::memcpy(&v, rgb + (size_t)((unsigned __int128)last * k / (n - 1)), 8);
+        mix(v);
+    }
+    return h;
+}
+
+int fill_scene(srt_context* c, srt_scene* s, const srt_scene_desc* d, bool fresh) {
     uint32_t depth = 0, max_leaf = 0;
-    int rc = validate_scene(d, &depth, &max_leaf);
+    int rc = validate_scene(d, &depth, &max_leaf, fresh ? nullptr : s);
     if (rc) return rc;
     CU(cudaSetDevice(c->device));
     if ((rc = copy_in(c, s->nodes, d->nodes, d->n_nodes * sizeof(srt_node)))) return rc;
@@ -343,22 +359,39 @@ int fill_scene(srt_context* c, srt_scene* s, const srt_scene_desc* d, bool textu
                                                 d->n_objects, (float4*)s->wide.p, (uint32_t*)s->root_ref.p, c->stream);
         if (e != cudaSuccess) return fail(SRT_ERR_CUDA, "build_wide launch: %s", cudaGetErrorString(e));
     }
-    if (textures_too) {
-        for (auto& t : s->tex) t.release();
-        s->tex.assign(d->n_textures, DevBuf());
-        s->tex_host.assign(d->n_textures, srtk::TexDev());
-        for (uint32_t t = 0; t < d->n_textures; ++t) {
-            const size_t bytes = (size_t)d->textures[t].width * d->textures[t].height * 3;
-            if ((rc = copy_in(c, s->tex[t], d->textures[t].rgb, bytes))) return rc;
-            s->tex_host[t].rgb = (const uint8_t*)s->tex[t].p;
-            s->tex_host[t].width = d->textures[t].width;
-            s->tex_host[t].height = d->textures[t].height;
-        }
-        s->n_textures = d->n_textures;
-        if ((rc = copy_in(c, s->texdesc, s->tex_host.data(), s->tex_host.size() * sizeof(srtk::TexDev)))) return rc;
-    } else if (d->n_textures != s->n_textures) {
-        return fail(SRT_ERR_INVALID_ARG, "srt_scene_update: texture count changed (%u -> %u); upload a new scene", s->n_textures, d->n_textures);
+    // Textures.  desc->textures == NULL on an update keeps the resident table (the count must match).  Otherwise every
+    // slot is compared with what the scene holds — host pointer, size and a sampled fingerprint of the texels — and only
+    // the slots that differ are uploaded again.  (The table used to be kept whenever the COUNT matched, while the
+    // flattener numbered textures in first-encounter order of a walk that moves with the camera: from the second frame
+    // of an in-place series a multi-material mesh sampled its neighbours' textures.  srt_flatten.hpp now numbers them by
+    // name, and this comparison catches whatever still changes.)
+    if (!d->textures && !fresh) {
+        if (d->n_textures != s->n_textures)
+            return fail(SRT_ERR_INVALID_ARG, "srt_scene_update: textures is NULL (keep the resident ones) but the count changed (%u -> %u)", s->n_textures, d->n_textures);
+        return SRT_OK;
     }
+    bool table_changed = fresh || d->n_textures != s->n_textures;
+    for (size_t t = d->n_textures; t < s->tex.size(); ++t) s->tex[t].release();
+    s->tex.resize(d->n_textures);
+    s->tex_host.resize(d->n_textures);
+    s->tex_key.resize(d->n_textures);
+    for (uint32_t t = 0; t < d->n_textures; ++t) {
+        const srt_texture_desc& td = d->textures[t];
+        const size_t bytes = (size_t)td.width * td.height * 3;
+        srt_scene::TexKey key = {td.rgb, td.width, td.height, texture_fingerprint(td.rgb, bytes)};
+        const srt_scene::TexKey have = s->tex_key[t];
+        if (s->tex[t].p && have.host == key.host && have.width == key.width && have.height == key.height && have.fingerprint == key.fingerprint)
+            continue;
+        const void* before = s->tex[t].p;
+        if ((rc = copy_in(c, s->tex[t], td.rgb, bytes))) return rc;
+        s->tex_key[t] = key;
+        if (s->tex[t].p != before || have.width != key.width || have.height != key.height) table_changed = true;
+        s->tex_host[t].rgb = (const uint8_t*)s->tex[t].p;
+        s->tex_host[t].width = td.width;
+        s->tex_host[t].height = td.height;
+    }
+    s->n_textures = d->n_textures;
+    if (table_changed && (rc = copy_in(c, s->texdesc, s->tex_host.data(), s->tex_host.size() * sizeof(srtk::TexDev)))) return rc;
     return SRT_OK;
 }
 
@@ -383,9 +416,7 @@ int srt_scene_upload(srt_context* c, const srt_scene_desc* d, srt_scene** out) {
 
 int srt_scene_update(srt_context* c, srt_scene* s, const srt_scene_desc* d) {
     if (!c || !s || s->ctx != c) return fail(SRT_ERR_INVALID_ARG, "scene does not belong to this context");
-    // Textures are immutable across updates unless the caller passes new ones explicitly.
-    const bool tex = d && d->textures != nullptr && d->n_textures > 0 && d->n_textures != s->n_textures;
-    return fill_scene(c, s, d, tex);
+    return fill_scene(c, s, d, false);
 }
 
 void srt_scene_destroy(srt_scene* s) {

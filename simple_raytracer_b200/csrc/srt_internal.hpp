@@ -86,6 +86,8 @@ struct srt_scene {
     float coord_bound = 0.f;                      // max |coordinate| over the root boxes
     std::vector<srti::DevBuf> tex;
     std::vector<srtk::TexDev> tex_host;
+    struct TexKey { const void* host; int32_t width, height; uint64_t fingerprint; };
+    std::vector<TexKey> tex_key;                  // what each resident slot was uploaded from (srt_scene_update compares)
     uint64_t n_nodes = 0, n_tris = 0, n_flat = 0;
     uint32_t n_objects = 0, n_textures = 0;
     uint32_t max_depth = 0;

@@ -454,3 +454,59 @@ def test_two_row_bands_equal_one_piece(gpu_ctx, key, W, H):
     assert two["stats"]["kernel_launches"] == 2 * one["stats"]["kernel_launches"] or one["stats"]["kernel_launches"] < 4
     assert np.array_equal(part["tri_id"][8:H - 3], one["tri_id"][8:H - 3]) and np.array_equal(part["rgb"][8:H - 3], one["rgb"][8:H - 3])
     sc.destroy()
+
+
+def test_scene_update_keeps_the_texture_table_valid(gpu_ctx):
+    """srt_scene_update with a texture table whose slots moved (what a flattener numbering textures in walk order produced
+    from the second frame of a series on): the scene renders with ITS table, not the resident one.  The permuted scene is
+    the same scene, so the frame must not change; an update that passes textures = NULL keeps the resident ones."""
+    cfg, arrays, light = _host_scene("C4", 0.0)
+    assert len(arrays.textures) >= 4
+    assert arrays.texture_names == sorted(arrays.texture_names), "the flattener numbers textures by name"
+    W, H, focal = scenes.scaled(cfg, 160)
+    p = _abi.default_params(W, H, focal, light, 2, True)
+    sc = gpu_ctx.upload(arrays)
+    want = gpu_ctx.render(sc, p)
+    n = len(arrays.textures)
+    perm = np.roll(np.arange(n), 1)                          # new slot k holds old texture perm[k]
+    slot_of = np.empty(n, np.int32); slot_of[perm] = np.arange(n, dtype=np.int32)
+    geom = arrays.geom.copy()
+    textured = geom["tex"] >= 0
+    geom["tex"][textured] = slot_of[geom["tex"][textured]]
+    moved = _abi.FlatSceneArrays(arrays.nodes, geom, arrays.attr, arrays.objects, [arrays.textures[k] for k in perm],
+                                 vnormal=arrays.vnormal)
+    sc.update(moved)
+    got = gpu_ctx.render(sc, p)
+    assert np.array_equal(got["rgb"], want["rgb"]) and np.array_equal(got["tri_id"], want["tri_id"])
+    sc.update(arrays)                                        # and back
+    assert np.array_equal(gpu_ctx.render(sc, p)["rgb"], want["rgb"])
+    keep = _abi.FlatSceneArrays(arrays.nodes, arrays.geom, arrays.attr, arrays.objects, (), vnormal=arrays.vnormal)
+    d = keep.desc(); d.n_textures = n                        # textures = NULL: keep the resident table
+    sc.update(d)
+    assert np.array_equal(gpu_ctx.render(sc, p)["rgb"], want["rgb"])
+    d.n_textures = n - 1
+    with pytest.raises(capi.SrtError):
+        sc.update(d)
+    sc.destroy()
+
+
+def test_textured_series_updated_in_place_matches_the_oracle(gpu_ctx):
+    """The reference's shipped main loop (:533: textured scene, rotating camera) through the series driver, which updates
+    one device scene per lane in place: every frame equals the frame of a from-scratch upload and the oracle's."""
+    from simple_raytracer_b200 import host, series
+    cfg = scenes.CONFIGS["C4"]
+    W, H, focal = scenes.scaled(cfg, 120)
+    angles = [0.0, 30.0, 270.0, 95.0, 180.0]
+    sr = series.SeriesRenderer(gpu_ctx, cfg, W, H, focal, 2, workers=2, lanes=1)
+    got = {i: rgb.copy() for i, rgb, _tm in sr.frames(angles)}
+    sr.close()
+    for i, ang in enumerate(angles):
+        _cfg, arrays, light = _host_scene("C4", ang)
+        p = _abi.default_params(W, H, focal, light, 2, True)
+        sc = gpu_ctx.upload(arrays)
+        fresh = gpu_ctx.render(sc, p, ids=False, want_t=False)["rgb"]
+        sc.destroy()
+        assert np.array_equal(got[i], fresh), f"frame {i} at {ang} deg differs from a from-scratch upload"
+        if i in (1, 2):
+            want = pyoracle.oracle_render(arrays, p)["rgb"]
+            assert np.abs(got[i].astype(np.int32) - want.astype(np.int32)).max() <= 1
