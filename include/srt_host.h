@@ -24,6 +24,10 @@ void srt_host_scene_destroy(srt_host_scene* s);
 const char* srt_host_last_error(srt_host_scene* s);
 const char* srt_host_last_warning(srt_host_scene* s);   /* what the reference prints to std::cerr */
 
+/* Directory that relative OBJ / MTL / texture paths are resolved against (NULL or "": the process CWD, like the
+ * reference, Object.cpp:35, :57).  Per scene, so host threads can load assets concurrently without chdir. */
+void srt_host_scene_set_base(srt_host_scene* s, const char* dir);
+
 /* ObjectManager (Object.h:59-89) */
 int  srt_host_load_obj(srt_host_scene* s, const char* path);                          /* loadObjFile; returns #triangles */
 void srt_host_set_color(srt_host_scene* s, const char* name, float r, float g, float b);   /* setColor */

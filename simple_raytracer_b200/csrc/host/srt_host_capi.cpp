@@ -36,6 +36,12 @@ void srt_host_scene_destroy(srt_host_scene* s) { delete s; }
 const char* srt_host_last_error(srt_host_scene* s) { return s ? s->error.c_str() : "null scene"; }
 const char* srt_host_last_warning(srt_host_scene* s) { return s ? s->om.lastWarning.c_str() : ""; }
 
+void srt_host_scene_set_base(srt_host_scene* s, const char* dir) {
+    if (!s) return;
+    s->om.baseDir = dir ? dir : "";
+    while (s->om.baseDir.size() > 1 && s->om.baseDir.back() == '/') s->om.baseDir.pop_back();
+}
+
 int srt_host_load_obj(srt_host_scene* s, const char* path) {
     s->flat_valid = false;
     s->om.loadObjFile(path);

@@ -282,7 +282,7 @@ void ObjectManager::loadObjFile(const std::string& objFilename) {
     objColors[objFilename] = vec3(1.f, 0.f, 0.f);                 // :29
     objProperties[objFilename] = vec3(0.2f, 0.5f, 15.0f);         // :31-34
     lastWarning.clear();
-    const std::shared_ptr<const CachedMesh> parsed = cached_read_obj(objFilename);
+    const std::shared_ptr<const CachedMesh> parsed = cached_read_obj(resolvePath(objFilename));
     const ObjMesh& mesh = parsed->mesh;
     if (!parsed->ok) lastWarning = "ObjReader: " + mesh.error;    // the reference prints and continues (:35-39)
     TextureDecoder decode = textureDecoder ? textureDecoder : &decode_image_rgb8;
@@ -291,7 +291,7 @@ void ObjectManager::loadObjFile(const std::string& objFilename) {
         const std::string& texturePath = material.diffuse_texname;   // as written in the MTL, relative to the CWD
         if (textureData.find(texturePath) != textureData.end()) continue;
         int width = 0, height = 0;
-        unsigned char* data = cached_decode(decode, texturePath, &width, &height);
+        unsigned char* data = cached_decode(decode, resolvePath(texturePath), &width, &height);
         if (data) {
             textureData[texturePath] = data;
             textureDimensions[texturePath] = ivec2(width, height);

@@ -71,6 +71,14 @@ public:
 
     // Not in the reference: where texture files are decoded.  Default: srt::decode_image_rgb8.
     TextureDecoder textureDecoder = nullptr;
+    // Not in the reference (which resolves every OBJ / MTL / texture path against the process CWD, Object.cpp:35, :57):
+    // a directory that relative paths are resolved against instead.  Map keys stay the names as written.  Lets a
+    // multi-threaded host (the series driver's prep pool) load assets without touching the process-wide CWD.
+    std::string baseDir;
+    std::string resolvePath(const std::string& path) const {
+        if (baseDir.empty() || path.empty() || path[0] == '/') return path;
+        return baseDir + "/" + path;
+    }
     // Not in the reference: last loader diagnostics (the reference prints them to std::cerr and continues).
     std::string lastWarning;
 };

@@ -47,6 +47,8 @@ def _lib():
         L.srt_host_last_error.argtypes = [vp]
         L.srt_host_last_warning.restype = cp
         L.srt_host_last_warning.argtypes = [vp]
+        L.srt_host_scene_set_base.argtypes = [vp, cp]
+        L.srt_host_scene_set_base.restype = None
         L.srt_host_load_obj.argtypes = [vp, cp]
         L.srt_host_set_color.argtypes = [vp, cp, fl, fl, fl]
         L.srt_host_set_color.restype = None
@@ -108,16 +110,6 @@ def _m16(m):
     return np.ascontiguousarray(np.asarray(m, dtype=np.float32).reshape(16))
 
 
-@contextlib.contextmanager
-def _cwd(path):
-    old = os.getcwd()
-    os.chdir(path)
-    try:
-        yield
-    finally:
-        os.chdir(old)
-
-
 class HostScene:
     """One srt::ObjectManager.  OBJ and texture paths resolve against `assets` (the reference resolves
     them against the process CWD, Object.cpp:55-57; scene scripts use the reference's relative names)."""
@@ -126,6 +118,7 @@ class HostScene:
         self.lib = _lib()
         self.h = self.lib.srt_host_scene_create()
         self.assets = Path(assets) if assets is not None else None
+        self.strict = True       # False: loader diagnostics only go to warning(), like the reference's std::cerr
 
     def close(self):
         if getattr(self, "h", None):
@@ -140,9 +133,17 @@ class HostScene:
 
     # -- ObjectManager
     def load_obj(self, path: str) -> int:
+        # Paths resolve against the asset directory inside the C++ scene.  (This used to chdir() around the call: the CWD is
+        # process-wide and the call releases the GIL, so two prep threads of the series driver could swap it under each
+        # other — an OBJ then failed to open, the loader "printed and continued" like the reference (Object.cpp:35-39), and
+        # the frame silently lacked that object.  DESIGN.md §4, "the intermittent series mismatch".)
         base = self.assets if self.assets is not None else assets_dir()
-        with _cwd(base):
-            n = self.lib.srt_host_load_obj(self.h, path.encode())
+        self.lib.srt_host_scene_set_base(self.h, str(Path(base).resolve()).encode())
+        n = self.lib.srt_host_load_obj(self.h, path.encode())
+        w = self.warning()
+        if w and self.strict:
+            # the reference prints this to std::cerr and renders on without the object (Object.cpp:35-39, :63-65)
+            raise FileNotFoundError(f"loadObjFile({path!r}) under {base}: {w.strip()}")
         return n
 
     def warning(self) -> str:

@@ -47,7 +47,34 @@ def test_load_defaults_and_errors():
     assert len(a.geom) == 12 and len(a.flat_geom) == 12 and len(a.nodes) == 3 and a.max_depth == 1
     # missing file: the reference prints and continues with an empty object (Object.cpp:35-39)
     s2 = host.HostScene()
-    assert s2.load_obj("does_not_exist.obj") <= 0
+    with pytest.raises(FileNotFoundError):              # ... which this mirror reports loudly unless asked not to
+        s2.load_obj("does_not_exist.obj")
+    s2.strict = False
+    assert s2.load_obj("does_not_exist.obj") <= 0 and "does_not_exist" in s2.warning()
+
+
+def test_concurrent_loads_do_not_depend_on_the_process_cwd(tmp_path):
+    """Regression for the intermittent series mismatch of round 1: load_obj used to chdir() around a call that releases
+    the GIL, so prep threads swapped the CWD under each other and a frame silently lost an object.  Eight threads load
+    the bunny at once, with the cache cold, from a CWD that holds no assets; every load must see all its triangles."""
+    import os
+    from concurrent.futures import ThreadPoolExecutor
+    need_assets()
+    host.set_asset_cache(False)
+    old = os.getcwd()
+    os.chdir(tmp_path)
+    try:
+        def load(_i):
+            hs = host.HostScene()
+            n = (hs.load_obj("./obj/stanford-bunny.obj"), hs.load_obj("./obj/cube.obj"))
+            hs.close()
+            return n, os.getcwd()
+        with ThreadPoolExecutor(8) as pool:
+            out = list(pool.map(load, range(24)))
+    finally:
+        os.chdir(old)
+    assert all(n == (69451, 12) for n, _cwd in out)
+    assert all(os.path.samefile(cwd, tmp_path) for _n, cwd in out)
 
 
 def test_flat_layout_invariants():
