@@ -309,6 +309,22 @@ int  srt_fetch_sparse(srt_context* ctx, float* points_xy, float* colors_rgb, uin
 
 /* ---- helpers ---- */
 void srt_default_params(srt_render_params* p);             /* fills the reference's literals */
+/* ---- the same compaction for callers that must not allocate ----
+ * NO COUNTERPART IN THE REFERENCE: added for callers that cannot call cudaMalloc
+ * (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  Builds the ImageData lists of
+ * srt_render_sparse from a dense frame the caller already holds: `rgb` = [height][width][3] as srt_render wrote it with
+ * no_sky_fill = 1 ((0,0,0) = not drawn, :518); rows [row_begin, row_end) (0, 0 = all) are scanned; `points_xy`
+ * (2 floats per entry), `colors_rgb` (3 floats per entry) need room for width * rows entries; `*count` receives the number
+ * of entries.  All four pointers must be addresses the DEVICE can reach — device memory, or pinned host memory from
+ * srt_host_alloc — because this call makes no copies and allocates nothing: no cudaMalloc / cudaFree, no staging buffer.
+ * Its scratch (one word per column and 32-row segment) is a static device array inside the library, 1 MiB per GPU held
+ * until exit, which bounds the frame: width * ceil(rows / 32) <= SRT_SPARSE_STATIC_MAX_SEGMENTS (a 3840x2160 frame uses
+ * 261,120), else SRT_ERR_UNSUPPORTED.  All calls on one GPU share that array: calls that overlap on the GPU (two contexts
+ * / streams of one device) race — serialise them.  Asynchronous on the context stream; srt_sync before reading. */
+#define SRT_SPARSE_STATIC_MAX_SEGMENTS 262144
+int  srt_sparse_from_frame_static(srt_context* ctx, const uint8_t* rgb, int32_t width, int32_t height, int32_t row_begin,
+                                  int32_t row_end, float* points_xy, float* colors_rgb, uint64_t* count);
+
 /* Light sample positions, out[3*i..] for i < count: the staircase of softShadow :363-383 (sequential fp32 adds) or
  * the jittered samples of light_mode. */
 int  srt_light_positions(const srt_render_params* p, float* out_xyz);

@@ -25,6 +25,7 @@ EXPORTS = [
     "srt_last_error", "srt_eval_leaf", "srt_render_sparse", "srt_fetch_sparse",
     "srt_mesh_upload", "srt_mesh_destroy", "srt_mesh_info", "srt_scene_prep", "srt_scene_prep_status",
     "srt_scene_counts", "srt_scene_download", "srt_scene_download_vnormals", "srt_measure_read_bandwidth",
+    "srt_sparse_from_frame_static",
 ]
 
 
@@ -67,6 +68,7 @@ def lib():
         L.srt_light_positions.argtypes = [C.POINTER(_abi.RenderParams), C.POINTER(C.c_float)]
         L.srt_render_sparse.argtypes = [vp, vp, C.POINTER(_abi.RenderParams), C.POINTER(C.c_uint64)]
         L.srt_fetch_sparse.argtypes = [vp, C.POINTER(C.c_float), C.POINTER(C.c_float), C.c_uint64]
+        L.srt_sparse_from_frame_static.argtypes = [vp, vp, C.c_int32, C.c_int32, C.c_int32, C.c_int32, vp, vp, vp]
         L.srt_measure_read_bandwidth.argtypes = [C.c_void_p, C.c_size_t, C.c_int, C.POINTER(C.c_double)]
         L.srt_eval_leaf.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_float), C.POINTER(C.c_float), C.c_size_t]
         L.srt_host_alloc.argtypes = [C.c_size_t]

@@ -674,6 +674,37 @@ int srt_last_stats(srt_context* c, srt_stats* out) {
     if (!c->have_last) return fail(SRT_ERR_INVALID_ARG, "no render has been issued on this context");
     CU(cudaSetDevice(c->device));
     CU(cudaStreamSynchronize(c->stream));
+// No cudaMalloc / cudaFree / DevBuf on this path: the scratch is the static device array of srt_kernels.cu.
+int srt_sparse_from_frame_static(srt_context* c, const uint8_t* rgb, int32_t width, int32_t height, int32_t row_begin,
+                                 int32_t row_end, float* points_xy, float* colors_rgb, uint64_t* count) {
+    if (!c || !rgb || !points_xy || !colors_rgb || !count) return fail(SRT_ERR_INVALID_ARG, "srt_sparse_from_frame_static: NULL argument");
+    if (width <= 0 || height <= 0) return fail(SRT_ERR_INVALID_ARG, "bad image size %dx%d", width, height);
+    int rb = row_begin, re = row_end;
+    if (rb == 0 && re == 0) re = height;
+    if (rb < 0 || re > height || rb > re) return fail(SRT_ERR_INVALID_ARG, "bad row range [%d,%d)", rb, re);
+    const size_t need = srtk::sparse_segments(width, re - rb);
+    if (need > (size_t)SRT_SPARSE_STATIC_MAX_SEGMENTS)
+        return fail(SRT_ERR_UNSUPPORTED, "srt_sparse_from_frame_static: %d columns x %d rows need %zu scratch words, the static array holds %d "
+                    "(width * ceil(rows / 32) <= SRT_SPARSE_STATIC_MAX_SEGMENTS); use srt_render_sparse", width, re - rb, need,
+                    SRT_SPARSE_STATIC_MAX_SEGMENTS);
+    CU(cudaSetDevice(c->device));
+    const void* ptrs[4] = {rgb, points_xy, colors_rgb, count};
+    const char* names[4] = {"rgb", "points_xy", "colors_rgb", "count"};
+    for (int i = 0; i < 4; ++i) {
+        cudaPointerAttributes at;
+        if (cudaPointerGetAttributes(&at, ptrs[i]) != cudaSuccess) { cudaGetLastError(); at.type = cudaMemoryTypeUnregistered; }
+        if (at.type == cudaMemoryTypeUnregistered)
+            return fail(SRT_ERR_INVALID_ARG, "srt_sparse_from_frame_static: %s is pageable host memory; pass device memory or pinned memory "
+                        "(srt_host_alloc) — this entry point makes no copies", names[i]);
+        if (at.type == cudaMemoryTypeDevice && at.device != c->device)
+            return fail(SRT_ERR_INVALID_ARG, "srt_sparse_from_frame_static: %s lives on device %d, the context on %d", names[i], at.device, c->device);
+    }
+    cudaError_t e = srtk::launch_sparse_compact_static(c->device, rgb, width, rb, re, points_xy, colors_rgb,
+                                                       (unsigned long long*)count, c->stream);
+    if (e != cudaSuccess) { cudaGetLastError(); return fail(SRT_ERR_CUDA, "srt_sparse_from_frame_static: %s", cudaGetErrorString(e)); }
+    return SRT_OK;
+}
+
     std::memset(out, 0, sizeof *out);
     const srt_context* b = c->last_banded ? c->band : nullptr;
     auto counter = [&](int slot) { return c->counters_host[slot] + (b ? b->counters_host[slot] : 0ull); };

@@ -7,6 +7,7 @@
 // through the OTHER objects -> Phong -> tone map / gamma -> 8-bit quantise -> sky fill.
 // Replaces simple_raytracer.cpp:505-525 (pixel loop), :405-457, :296-317, :321-401, and the
 // 8-bit / sky rules of drawImage :461-498.
+#include <mutex>
 #include "srt_kernels.cuh"
 #include "srt_device.cuh"
 #include "srt_shade.cuh"
@@ -245,6 +246,58 @@ cudaError_t launch_sparse_compact(const uint8_t* rgb, int width, int row_begin, 
     sparse_count_kernel<<<grid, 128, 0, stream>>>(rgb, width, row_begin, row_end, n_seg, seg_counts);
     sparse_scan_kernel<<<1, 1024, 0, stream>>>(seg_counts, (uint32_t)((size_t)width * n_seg), total);
     sparse_write_kernel<<<grid, 128, 0, stream>>>(rgb, width, row_begin, row_end, n_seg, seg_counts, points, colors);
+    return cudaGetLastError();
+}
+
+// ---- srt_sparse_from_frame_static: the ImageData compaction with its scratch in a file-scope device array --------
+// No counterpart in the reference; added for callers that cannot call cudaMalloc
+// (code under CUDA graph capture, tight serving loops).  The three compaction launches above, with the per-(column,
+// 32-row segment) count / offset words in g_sparse_static_scratch instead of a context buffer.  Every GPU that loads
+// the library holds the array (1 MiB) until exit; every call on a device shares it, so calls that overlap on the GPU race.
+// Nothing has to start at zero: the count pass writes every word [0, width * segments) the scan and write passes read,
+// and the scan pass writes the total — whatever an earlier call left behind is never read.
+constexpr size_t kSparseStaticWords = SRT_SPARSE_STATIC_MAX_SEGMENTS;
+static __device__ __align__(256) uint32_t g_sparse_static_scratch[kSparseStaticWords];
+
+namespace {
+constexpr int kMaxDevices = 64;
+std::mutex g_sparse_static_mutex;
+uint32_t* g_sparse_static_ptr[kMaxDevices] = {};      // per device: the array's DEVICE address (the symbol itself is a host stand-in)
+
+__global__ void store_u64_kernel(unsigned long long* p, unsigned long long v) { *p = v; }
+}  // namespace
+
+// Device address of the scratch array on `device`, which must be current.  Looked up once per device.
+cudaError_t sparse_static_scratch(int device, uint32_t** out) {
+    if (device < 0 || device >= kMaxDevices) return cudaErrorInvalidDevice;
+    std::lock_guard<std::mutex> lock(g_sparse_static_mutex);
+    if (!g_sparse_static_ptr[device]) {
+        void* ptr = nullptr;
+        const cudaError_t e = cudaGetSymbolAddress(&ptr, g_sparse_static_scratch);
+        if (e != cudaSuccess) return e;
+        if (!ptr) return cudaErrorInvalidSymbol;
+        g_sparse_static_ptr[device] = (uint32_t*)ptr;
+    }
+    *out = g_sparse_static_ptr[device];
+    return cudaSuccess;
+}
+
+cudaError_t launch_sparse_compact_static(int device, const uint8_t* rgb, int width, int row_begin, int row_end, float* points,
+                                         float* colors, unsigned long long* total, cudaStream_t stream) {
+    const int rows = row_end - row_begin;
+    if (width <= 0 || rows <= 0) {                    // (no cudaMemset: `total` may be pinned host memory)
+        store_u64_kernel<<<1, 1, 0, stream>>>(total, 0ull);
+        return cudaGetLastError();
+    }
+    if (sparse_segments(width, rows) > kSparseStaticWords) return cudaErrorInvalidValue;   // the entry point reports this first
+    uint32_t* scratch = nullptr;
+    const cudaError_t e = sparse_static_scratch(device, &scratch);
+    if (e != cudaSuccess) return e;
+    const int n_seg = (rows + kSegRows - 1) / kSegRows;
+    const dim3 grid((unsigned)((width + 127) / 128), (unsigned)n_seg);
+    sparse_count_kernel<<<grid, 128, 0, stream>>>(rgb, width, row_begin, row_end, n_seg, scratch);
+    sparse_scan_kernel<<<1, 1024, 0, stream>>>(scratch, (uint32_t)((size_t)width * n_seg), total);
+    sparse_write_kernel<<<grid, 128, 0, stream>>>(rgb, width, row_begin, row_end, n_seg, scratch, points, colors);
     return cudaGetLastError();
 }
 

@@ -96,6 +96,11 @@ size_t sparse_segments(int width, int rows);
 cudaError_t launch_sparse_compact(const uint8_t* rgb, int width, int row_begin, int row_end, uint32_t* seg_counts, float* points,
                                   float* colors, unsigned long long* total, cudaStream_t stream);
 
+// srt_sparse_from_frame_static: the same compaction with its scratch in a file-scope __device__ array (srt_kernels.cu);
+// `device` must be current.  Allocates nothing.
+cudaError_t launch_sparse_compact_static(int device, const uint8_t* rgb, int width, int row_begin, int row_end, float* points,
+                                         float* colors, unsigned long long* total, cudaStream_t stream);
+
 // Leaf evaluation hook (srt_eval_leaf): `in` / `out` are device arrays.
 int leaf_in_width(int op);
 int leaf_out_width(int op);
