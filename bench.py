@@ -56,6 +56,7 @@ def parse_args():
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--cpu-seconds", type=float, default=20.0, help="CPU work (core-seconds) of the cpu_baseline sample")
     ap.add_argument("--still", action="store_true", help="render frame 0 on every step (profiling)")
+    ap.add_argument("--e2e-bands", type=int, default=0, help="row bands of the two e2e lanes (0: the library default)")
     ap.add_argument("--gather", action="store_true", help="e2e: gather every rank's frame to rank 0 over NCCL before the download")
     ap.add_argument("--series-lanes", type=int, default=6, help="frames in flight (contexts / streams) of the device-prep series leg")
     ap.add_argument("--series-frames", type=int, default=-1,
@@ -335,10 +336,10 @@ def run_b200_arm(args):
         rays0 = ray_count(W, H, N, hits_of(k0), n_obj)
         c3_still = {"ms_per_frame": ms0, "value": rays0 / (ms0 * 1e-3) / 1e6, "unit": UNIT, "rays_per_frame": rays0,
                     "what": "frame 0 of the orbit = BASELINE configs[2] (C3) itself, same timing method"}
-    # the same K frames with two row bands per frame (srt_context_set_bands: opt-in, one frame at a time)
-    two_bands = None
+    # the same K frames rendered in one piece (srt_context_set_bands(ctx, 1); the default is two row bands per frame)
+    one_piece = None
     if rank == 0 and not args.still and args.variant == 0:
-        ctx.set_bands(2)
+        bands_before = ctx.set_bands(1)
         try:
             for s in range(3):
                 flush.zero_(); render_step(Wm + s)
@@ -348,11 +349,11 @@ def run_b200_arm(args):
                 evb[s][0].record(); render_step(Wm + s); evb[s][1].record()
             torch.cuda.synchronize()
             msb = float(sum(a.elapsed_time(b) for a, b in evb))
-            two_bands = {"value": rays_local / (msb * 1e-3) / 1e6, "unit": UNIT, "ms_per_step": msb / K,
-                         "what": "rank 0, the same K frames and timing as `value`, after srt_context_set_bands(ctx, 2): the upper and "
-                                 "lower half of every frame render on two streams and overlap each other's stages (same bytes)"}
+            one_piece = {"value": rays_local / (msb * 1e-3) / 1e6, "unit": UNIT, "ms_per_step": msb / K,
+                         "what": "rank 0, the same K frames and timing as `value`, after srt_context_set_bands(ctx, 1): every frame in "
+                                 "one piece on one stream (the default renders the upper and lower half on two streams; same bytes)"}
         finally:
-            ctx.set_bands(1)
+            ctx.set_bands(bands_before)
     # algorithmic work of frame Wm (the first timed one) under the REFERENCE's traversal rules, counted by the
     # instrumented CUDA kernel (SRT_VARIANT_COUNT; tests check its counters against the oracle's)
     work = None
@@ -397,6 +398,9 @@ def run_b200_arm(args):
         # --gather the frames go through NCCL on one stream instead.
         stream_b = torch.cuda.Stream(device=dev)
         ctx_b = capi.Context(local, stream=stream_b.cuda_stream)
+        e2e_bands_before = ctx.set_bands(args.e2e_bands) if args.e2e_bands else None
+        if args.e2e_bands:
+            ctx_b.set_bands(args.e2e_bands)
         lanes = [dict(ctx=ctx, stream=stream, scene=ctx.upload(pinned[0][0]), rgb=rgb, host=host_rgb)]
         if not do_gather:
             lanes.append(dict(ctx=ctx_b, stream=stream_b, scene=ctx_b.upload(pinned[0][0]), rgb=torch.empty_like(rgb),
@@ -435,6 +439,8 @@ def run_b200_arm(args):
         for ln in lanes:
             ln["scene"].destroy()
         ctx_b.destroy()
+        if e2e_bands_before:
+            ctx.set_bands(e2e_bands_before)
 
     # ---- the reference's own result format (ImageData: sparse float lists, column-major) through the C ABI ----
     imagedata = None
@@ -575,8 +581,8 @@ def run_b200_arm(args):
                                    + (" (all frames gathered to rank 0 over NCCL first)" if args.gather else "")}
         if c3_still:
             line["c3_frame0"] = c3_still
-        if two_bands:
-            line["value_two_bands"] = two_bands
+        if one_piece:
+            line["value_one_piece"] = one_piece
         if series:
             line["series_with_host_prep"] = {
                 "frames_per_s": world * series[1] / series_s, "frames": world * series[1], "host_threads_per_rank": series[2],

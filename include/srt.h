@@ -222,10 +222,12 @@ int  srt_context_create(int device, srt_context** out);
 void srt_context_destroy(srt_context* ctx);
 /* Use an existing cudaStream_t (e.g. torch's current stream) instead of the context's own. */
 int  srt_context_set_stream(srt_context* ctx, void* cuda_stream);
-/* Row bands per frame of the default pipeline: 1 (default) renders a frame in one piece; 2 renders the upper and the
- * lower half of the rows on two streams so that their stages overlap — for callers that render ONE frame at a time
- * (-11 % time per frame; the same bytes).  Callers that already keep several frames in flight on several contexts (an
- * image series) gain nothing from it.  Returns the previous value, or a negative srt_status. */
+/* Row bands per frame of the default pipeline: 2 (default) renders the upper and the lower half of the rows on two
+ * streams so that their stages overlap (-11 % time per frame; the same bytes, pixels are independent :511-523) — what a
+ * caller that renders ONE frame at a time wants; 1 renders a frame in one piece, for callers that already keep several
+ * frames in flight on several contexts (an image series gains nothing from a second band; the series driver sets 1 on
+ * its lanes).  Frames of fewer than 128 rows, sharded frames and the other kernel variants are always one piece.
+ * Returns the previous value, or a negative srt_status. */
 int  srt_context_set_bands(srt_context* ctx, int bands);
 int  srt_context_get_info(srt_context* ctx, int* sm_count, int* cc_major, int* cc_minor,
                           size_t* l2_bytes);
@@ -307,8 +309,6 @@ int  srt_last_stats(srt_context* ctx, srt_stats* out);
 int  srt_render_sparse(srt_context* ctx, const srt_scene* scene, const srt_render_params* params, uint64_t* count);
 int  srt_fetch_sparse(srt_context* ctx, float* points_xy, float* colors_rgb, uint64_t capacity);
 
-/* ---- helpers ---- */
-void srt_default_params(srt_render_params* p);             /* fills the reference's literals */
 /* ---- the same compaction for callers that must not allocate ----
  * NO COUNTERPART IN THE REFERENCE: added for callers that cannot call cudaMalloc
  * (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  Builds the ImageData lists of
@@ -325,6 +325,8 @@ void srt_default_params(srt_render_params* p);             /* fills the referenc
 int  srt_sparse_from_frame_static(srt_context* ctx, const uint8_t* rgb, int32_t width, int32_t height, int32_t row_begin,
                                   int32_t row_end, float* points_xy, float* colors_rgb, uint64_t* count);
 
+/* ---- helpers ---- */
+void srt_default_params(srt_render_params* p);             /* fills the reference's literals */
 /* Light sample positions, out[3*i..] for i < count: the staircase of softShadow :363-383 (sequential fp32 adds) or
  * the jittered samples of light_mode. */
 int  srt_light_positions(const srt_render_params* p, float* out_xyz);

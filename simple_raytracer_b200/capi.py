@@ -236,8 +236,8 @@ class Context:
             _check(lib().srt_context_set_stream(self.h, C.c_void_p(stream)))
 
     def set_bands(self, bands: int) -> int:
-        """Row bands per frame of the default pipeline (1, the default: in one piece; 2: one frame's halves overlap on two
-        streams, for callers that render one frame at a time).  Returns the previous value."""
+        """Row bands per frame of the default pipeline (2, the default: one frame's halves overlap on two streams, for
+        callers that render one frame at a time; 1: in one piece).  Returns the previous value."""
         before = lib().srt_context_set_bands(self.h, int(bands))
         if before < 0:
             _check(before)

@@ -592,7 +592,7 @@ static int render_impl(srt_context* c, const srt_scene* s, const srt_render_para
 // shadow -> shade on its own counters and scratch, and the device interleaves them — one band's shadow pass fills the
 // SMs the other band's primary pass leaves idle in its tail, and stages with different instruction mixes share the
 // issue slots.  Pixels are independent (:511-523), so the frame is the same bytes; measured -11 % time per frame
-// over the C3 orbit.  Opt-in per context: srt_context_set_bands(ctx, 2).
+// over the C3 orbit.  The default; srt_context_set_bands(ctx, 1) renders in one piece.
 int srt_render(srt_context* c, const srt_scene* s, const srt_render_params* p, const srt_frame* out) {
     if (!c || !s || !p || !out) return fail(SRT_ERR_INVALID_ARG, "NULL argument");
     int rb = p->row_begin, re = p->row_end;
@@ -616,11 +616,16 @@ int srt_render(srt_context* c, const srt_scene* s, const srt_render_params* p, c
     CU(cudaEventRecord(c->ev_fork, c->stream));                       // the band starts after everything queued so far (scene upload / prep)
     CU(cudaStreamWaitEvent(c->band->stream, c->ev_fork, 0));
     int rc = render_impl(c, s, &p0, out);
-    if (rc) return rc;
-    rc = render_impl(c->band, s, &p1, out);
-    if (rc) return rc;
-    CU(cudaEventRecord(c->ev_join, c->band->stream));
-    CU(cudaStreamWaitEvent(c->stream, c->ev_join, 0));                // whatever follows on this stream sees the whole frame
+    std::string first_error;
+    if (rc) first_error = g_err;
+    const int rc1 = rc ? SRT_OK : render_impl(c->band, s, &p1, out);
+    // Join on every path: whatever a failed band did enqueue on the second stream still writes into the caller's planes,
+    // and everything that follows on this stream (the caller's next call, a scene update or destroy) must be ordered after it.
+    const cudaError_t ej = cudaEventRecord(c->ev_join, c->band->stream);
+    const cudaError_t ew = ej == cudaSuccess ? cudaStreamWaitEvent(c->stream, c->ev_join, 0) : ej;
+    if (rc) { g_err = first_error; return rc; }
+    if (rc1) return rc1;
+    if (ew != cudaSuccess) return fail(SRT_ERR_CUDA, "joining the two row bands: %s", cudaGetErrorString(ew));
     c->last_banded = true;
     return SRT_OK;
 }
@@ -669,11 +674,6 @@ int srt_fetch_sparse(srt_context* c, float* points_xy, float* colors_rgb, uint64
     return SRT_OK;
 }
 
-int srt_last_stats(srt_context* c, srt_stats* out) {
-    if (!c || !out) return fail(SRT_ERR_INVALID_ARG, "NULL argument");
-    if (!c->have_last) return fail(SRT_ERR_INVALID_ARG, "no render has been issued on this context");
-    CU(cudaSetDevice(c->device));
-    CU(cudaStreamSynchronize(c->stream));
 // No cudaMalloc / cudaFree / DevBuf on this path: the scratch is the static device array of srt_kernels.cu.
 int srt_sparse_from_frame_static(srt_context* c, const uint8_t* rgb, int32_t width, int32_t height, int32_t row_begin,
                                  int32_t row_end, float* points_xy, float* colors_rgb, uint64_t* count) {
@@ -705,6 +705,11 @@ int srt_sparse_from_frame_static(srt_context* c, const uint8_t* rgb, int32_t wid
     return SRT_OK;
 }
 
+int srt_last_stats(srt_context* c, srt_stats* out) {
+    if (!c || !out) return fail(SRT_ERR_INVALID_ARG, "NULL argument");
+    if (!c->have_last) return fail(SRT_ERR_INVALID_ARG, "no render has been issued on this context");
+    CU(cudaSetDevice(c->device));
+    CU(cudaStreamSynchronize(c->stream));
     std::memset(out, 0, sizeof *out);
     const srt_context* b = c->last_banded ? c->band : nullptr;
     auto counter = [&](int slot) { return c->counters_host[slot] + (b ? b->counters_host[slot] : 0ull); };

@@ -70,7 +70,7 @@ struct srt_context {
     srt_context* parent = nullptr;
     cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
     bool last_banded = false;
-    int bands = 1;                    // srt_context_set_bands
+    int bands = 2;                    // srt_context_set_bands (SRT_DEFAULT_BANDS overrides the default)
     uint64_t last_primary = 0;
     int last_lights = 0;
     uint32_t last_objects = 0;

@@ -147,7 +147,8 @@ class SeriesRenderer:
 
     def frames(self, angles: Iterable[float], out: Optional[np.ndarray] = None) -> Iterator[Tuple[int, np.ndarray, dict]]:
         """Yields (index, rgb[H][W][3] host array, timing) per frame, in order.  The yielded array is the lane's
-        pinned frame (valid until as many further frames as there are lanes have been taken), or `out` if given (valid until the next iteration)."""
+        pinned frame, or `out` if given — either way valid only until the next iteration: the next frame is issued onto the
+        lane that was just retired and starts overwriting its buffer at once.  Copy what you keep."""
         angles = list(angles)
         # several lanes already keep frames in flight concurrently: a second row band per frame (a caller may have asked for
         # it on the shared context) would only add launches

@@ -130,7 +130,8 @@ def test_full_size_c3_variants_agree_and_sample_matches_oracle(gpu_ctx, ref_scen
     for o in outs[1:]:
         for k in ("rgb", "obj_id", "tri_id", "t"):
             assert np.array_equal(outs[0][k], o[k]), k
-    assert [o["stats"]["kernel_launches"] for o in outs] == [4, 2, 4, 1]
+    bands = gpu_ctx.set_bands(2); gpu_ctx.set_bands(bands)                     # the context's setting (default 2)
+    assert [o["stats"]["kernel_launches"] for o in outs] == [4 * bands, 2, 4, 1]   # row bands x four passes
     p = _abi.default_params(W, H, focal, light, N, True)
     want = pyoracle.oracle_render(arrays, p, col_begin=7, col_step=48)
     cols = np.arange(7, W, 48)
@@ -510,3 +511,54 @@ def test_textured_series_updated_in_place_matches_the_oracle(gpu_ctx):
         if i in (1, 2):
             want = pyoracle.oracle_render(arrays, p)["rgb"]
             assert np.abs(got[i].astype(np.int32) - want.astype(np.int32)).max() <= 1
+
+
+def test_series_and_single_frames_alternate_under_both_band_settings(gpu_ctx):
+    """Stress for the multi-stream paths: 200+ alternations between the series driver (two lanes, host
+    prep pool, scene updates in place) and single frames on the SHARED context, with one and with two row bands, host
+    (pageable) outputs — every frame byte-identical to the frame a fresh one-piece context renders of the same scene."""
+    from simple_raytracer_b200 import host, series
+    cfg = scenes.CONFIGS["C3"]
+    W, H, focal = scenes.scaled(cfg, 144)
+    angles = [0.0, 47.0, 123.5, 181.5, 200.0, 299.0]
+    truth_ctx = capi.Context(0)
+    truth_ctx.set_bands(1)
+    truth, uploaded = {}, {}
+    for a in angles:
+        _cfg, arrays, light = _host_scene("C3", a)
+        sc = truth_ctx.upload(arrays)
+        p = _abi.default_params(W, H, focal, light, 4, True)
+        truth[a] = truth_ctx.render(sc, p, ids=False, want_t=False)["rgb"]
+        sc.destroy()
+        uploaded[a] = (gpu_ctx.upload(arrays), p)
+    truth_ctx.destroy()
+    solo = capi.Context(0)                                        # single frames between the series' frames: its own streams
+    solo_scenes = {a: solo.upload(_host_scene("C3", a)[1]) for a in angles}
+    before = gpu_ctx.set_bands(2)
+    rounds = 0
+    try:
+        for rep in range(36):
+            bands = 1 + (rep % 2)
+            gpu_ctx.set_bands(bands)
+            solo.set_bands(bands)
+            sr = series.SeriesRenderer(gpu_ctx, cfg, W, H, focal, 4, workers=3)
+            order = angles[rep % len(angles):] + angles[:rep % len(angles)]
+            for i, rgb, _tm in sr.frames(order):
+                assert np.array_equal(rgb, truth[order[i]]), (rep, "series", i)
+                a = order[(i + 2) % len(order)]                   # a single frame of ANOTHER view while the series is in flight
+                got = solo.render(solo_scenes[a], uploaded[a][1], ids=False, want_t=False)["rgb"]
+                assert np.array_equal(got, truth[a]), (rep, "single", bands, a)
+                rounds += 1
+            sr.close()
+            a = order[0]                                          # and on the context the series just used, with its bands restored
+            got = gpu_ctx.render(uploaded[a][0], uploaded[a][1], ids=False, want_t=False)["rgb"]
+            assert np.array_equal(got, truth[a]), (rep, "after", bands, a)
+    finally:
+        gpu_ctx.set_bands(before)
+        for scn, _p in uploaded.values():
+            scn.destroy()
+        for scn in solo_scenes.values():
+            scn.destroy()
+        solo.destroy()
+        host.set_asset_cache(False)
+    assert rounds >= 200
