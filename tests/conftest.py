@@ -92,18 +92,20 @@ def scene_for_fixture(key, fx):
     included: tests/test_host_scene.py)."""
     from oracle import pyoracle
     from simple_raytracer_b200 import host, scenes
+    angle = float(fx["angle"]) if "angle" in fx.files else 0.0
+    key, cfg_key = (key, angle), key
     if key in _fixture_scene_cache:
         return _fixture_scene_cache[key]
     if "nodes" in fx.files:
         out = (flat_from_fixture(fx), np.asarray(fx["light"], np.float32))
     else:
-        cfg = scenes.CONFIGS[key]
+        cfg = scenes.CONFIGS[cfg_key]
         try:
             host.assets_dir()
         except FileNotFoundError:
             pytest.skip("staged assets not present")
         b = host.HostScene()
-        view = cfg.build(b, 0.0)
+        view = cfg.build(b, angle)
         light = scenes.light_view_space(b, view) if view is not None else np.array(scenes.LIGHT_WORLD, np.float32)
         out = (b.flatten(with_flat_lists=not cfg.use_bvh), np.asarray(light, np.float32))
     _fixture_scene_cache[key] = out

@@ -11,7 +11,8 @@ outputs of the reference's own functions executed here through oracle/_ref/libsr
                    triangle, box behind the origin, 0/0) and seeded random cases;
   frame_<key>.npz  whole small frames rendered by the reference (faithful mode: re-shading on every closer
                    hit like :429-449): rgb, obj_id, tri_id, t, the parameters, and — for the scenes small
-                   enough to commit — the flattened scene itself, so the oracle can be checked without assets.
+                   enough to commit — the flattened scene itself, so the oracle can be checked without assets;
+  frame_C3_a<angle>.npz  the same for views of the C3 / C5 scene around the camera orbit (the frames bench.py times).
 """
 import ctypes as C
 import sys
@@ -173,11 +174,39 @@ def make_frames():
         b.close()
 
 
+# Camera-orbit views of the C3 / C5 scene (the views bench.py times; the image series of configs[4] is this orbit at
+# 1.5 degrees per frame, simple_raytracer.cpp:534 with SURVEY.md C5's step): series frames 24, 120 and 239, the quarter
+# turns, and the two heaviest views of the orbit (most shadow rays cross the bunny, profiles/r01_orbit_cost.txt).
+ORBIT_ANGLES = [36.0, 90.0, 135.0, 180.0, 200.0, 270.0, 358.5]
+
+
+def angle_tag(angle):
+    return ("%g" % angle).replace(".", "p")
+
+
+def make_orbit_frames():
+    W, H, focal, N = 320, 180, 180.0, 16
+    cfg = scenes.CONFIGS["C3"]
+    for angle in ORBIT_ANGLES:
+        b = pyoracle.RefBackend()
+        view = cfg.build(b, angle)
+        light = np.asarray(scenes.light_view_space(b, view), f32)
+        r = b.render(W, H, focal, light, N, cfg.use_bvh, faithful=True, threads=0)
+        np.savez_compressed(HERE / f"frame_C3_a{angle_tag(angle)}.npz", rgb=r["rgb"], obj_id=r["obj_id"], tri_id=r["tri_id"], t=r["t"],
+                            params=np.array([W, H, focal, N, 1], np.float64), light=light[:3], angle=np.float64(angle))
+        print(f"frame_C3_a{angle_tag(angle)}.npz: {W}x{H} N={N} angle {angle}: hit pixels {int((r['obj_id'] >= 0).sum())}, "
+              f"bunny pixels {int((r['obj_id'] == 0).sum())}")
+        b.close()
+
+
 if __name__ == "__main__":
     import sys
     if "--smooth-normal-only" in sys.argv:
         make_smooth_normal_kat()
+    elif "--orbit-only" in sys.argv:
+        make_orbit_frames()
     else:
+        make_orbit_frames()
         make_leaf_kat()
         make_smooth_normal_kat()
         make_frames()

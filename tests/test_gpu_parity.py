@@ -144,6 +144,52 @@ def test_full_size_c3_variants_agree_and_sample_matches_oracle(gpu_ctx, ref_scen
           f"{outs[0]['stats']['exact_slab_tests']}")
 
 
+@pytest.mark.parametrize("angle,col0", [(180.0, 5), (135.0, 29)])
+def test_full_size_c3_heavy_orbit_views_match_the_oracle(gpu_ctx, ref_scene, angle, col0):
+    """The frames the bench times: 1920x1080, 16 lights, at the orbit's expensive views (most shadow rays cross the bunny;
+    t ~ 0 shadow hits where it touches the ground, no epsilon, :321-342).  Every 48th pixel column against the oracle."""
+    _b, arrays, light = ref_scene("C3", angle)
+    W, H, focal, N = 1920, 1080, 1080.0, 16
+    p = _abi.default_params(W, H, focal, light, N, True)
+    sc = gpu_ctx.upload(arrays)
+    got = gpu_ctx.render(sc, p)
+    sc.destroy()
+    want = pyoracle.oracle_render(arrays, p, col_begin=col0, col_step=48)
+    cols = np.arange(col0, W, 48)
+    assert np.array_equal(got["tri_id"][:, cols], want["tri_id"][:, cols])
+    assert np.array_equal(got["obj_id"][:, cols], want["obj_id"][:, cols])
+    assert np.array_equal(got["t"][:, cols], want["t"][:, cols])
+    mx, psnr = compare_images(got["rgb"][:, cols], want["rgb"][:, cols])
+    differing = int(np.count_nonzero((got["rgb"][:, cols] != want["rgb"][:, cols]).any(axis=2)))
+    assert mx <= 1 and psnr >= 50.0 and differing <= 4, (mx, psnr, differing)
+    shadowed = int(np.count_nonzero(want["obj_id"][:, cols] >= 0))
+    assert shadowed > 20000
+
+
+def test_full_size_c2_matches_the_oracle(gpu_ctx, ref_scene):
+    """BASELINE configs[1] at its own size: bunny alone, 1920x1080, one light (no other object: no shadow rays).  Every 12th
+    pixel column against the oracle, all kernel variants byte-identical."""
+    _b, arrays, light = ref_scene("C2")
+    W, H, focal, N = 1920, 1080, 1080.0, 1
+    sc = gpu_ctx.upload(arrays)
+    outs = []
+    for variant in (0, 2, 1):
+        p = _abi.default_params(W, H, focal, light, N, True)
+        p.variant = variant
+        outs.append(gpu_ctx.render(sc, p))
+    sc.destroy()
+    for o in outs[1:]:
+        for k in ("rgb", "obj_id", "tri_id", "t"):
+            assert np.array_equal(outs[0][k], o[k]), k
+    p = _abi.default_params(W, H, focal, light, N, True)
+    want = pyoracle.oracle_render(arrays, p, col_begin=3, col_step=12)
+    cols = np.arange(3, W, 12)
+    assert np.array_equal(outs[0]["tri_id"][:, cols], want["tri_id"][:, cols])
+    assert np.array_equal(outs[0]["t"][:, cols], want["t"][:, cols])
+    assert compare_images(outs[0]["rgb"][:, cols], want["rgb"][:, cols])[0] <= 1
+    assert outs[0]["stats"]["shadow_rays"] == 0 and outs[0]["stats"]["hit_pixels"] > 200000
+
+
 def test_full_size_c4_textured_4k(gpu_ctx, ref_scene):
     """BASELINE configs[3] at 3840x2160: variants agree byte for byte, a column sample equals the oracle,
     and rendering twice gives the same bytes (idempotence)."""

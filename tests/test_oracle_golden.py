@@ -14,6 +14,9 @@ from simple_raytracer_b200 import _abi
 f32 = np.float32
 _f32p = C.POINTER(C.c_float)
 FRAME_KEYS = ["C1", "C1b", "cubes4", "spheres", "shipped", "C2", "C3", "C4"]
+# views of the C3 / C5 scene around the camera orbit (tests/golden/make_golden.py ORBIT_ANGLES): series frames 24, 120, 239,
+# the quarter turns and the two heaviest views — the frames bench.py times
+ORBIT_KEYS = ["C3_a36", "C3_a90", "C3_a135", "C3_a180", "C3_a200", "C3_a270", "C3_a358p5"]
 
 
 def fp(a):
@@ -103,11 +106,11 @@ def test_light_staircase_matches_reference_sequence():
     assert same_bits(out, want)
 
 
-@pytest.mark.parametrize("key", FRAME_KEYS)
+@pytest.mark.parametrize("key", FRAME_KEYS + ORBIT_KEYS)
 def test_oracle_reproduces_reference_frames(key):
     """Whole frames rendered by the reference (committed) == the oracle on the same scene, every plane."""
     fx = np.load(GOLDEN / f"frame_{key}.npz")
-    arrays, light = scene_for_fixture(key, fx)
+    arrays, light = scene_for_fixture(key.split("_a")[0], fx)
     W, H, focal, N, use_bvh = [float(x) for x in fx["params"]]
     assert np.allclose(light[:3], fx["light"], rtol=0, atol=0)
     p = _abi.default_params(int(W), int(H), focal, fx["light"], int(N), bool(use_bvh))
