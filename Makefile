@@ -10,7 +10,7 @@ NVFLAGS  := $(ARCH) -O3 -std=c++17 -lineinfo -fmad=false --prec-div=true --prec-
             -Xcompiler -fPIC,-O2,-ffp-contract=off -Iinclude -Isimple_raytracer_b200/csrc -Isimple_raytracer_b200/csrc/host
 CSRC     := simple_raytracer_b200/csrc
 LIB      := simple_raytracer_b200/lib/libsrt_b200.so
-SRCS     := $(CSRC)/srt_capi.cu $(CSRC)/srt_kernels.cu $(CSRC)/srt_phased.cu $(CSRC)/srt_prep.cu $(CSRC)/srt_prep_capi.cu $(wildcard $(CSRC)/host/*.cpp)
+SRCS     := $(CSRC)/srt_capi.cu $(CSRC)/srt_kernels.cu $(CSRC)/srt_phased.cu $(CSRC)/srt_prep.cu $(CSRC)/srt_prep_capi.cu $(CSRC)/srt_mgpu.cu $(wildcard $(CSRC)/host/*.cpp)
 HDRS     := include/srt.h include/srt_host.h $(wildcard $(CSRC)/*.cuh) $(wildcard $(CSRC)/*.hpp) $(wildcard $(CSRC)/host/*.hpp)
 
 .PHONY: all lib oracle ref clean

@@ -325,6 +325,37 @@ int  srt_fetch_sparse(srt_context* ctx, float* points_xy, float* colors_rgb, uin
 int  srt_sparse_from_frame_static(srt_context* ctx, const uint8_t* rgb, int32_t width, int32_t height, int32_t row_begin,
                                   int32_t row_end, float* points_xy, float* colors_rgb, uint64_t* count);
 
+/* ---- several GPUs from one host thread (SURVEY.md §8b export list, §8e) ----
+ * The reference's pixel loop is a pure function of the pixel (:511-523) and its frames are independent (:534), so both
+ * shardings are exact: the output of R GPUs is byte-identical to one GPU's.
+ *   one frame     interleaved blocks of `row_block` rows, block b -> GPU b mod R (srt_render_params.row_block /
+ *                 shard_index / shard_count).  The frame lives on the first GPU; every other GPU's kernels write their
+ *                 row blocks STRAIGHT into it through peer-mapped memory (NVLink / NVSwitch stores, no staging copy, no
+ *                 collective call); where peer access is unavailable the blocks are rendered locally and moved with
+ *                 cudaMemcpyPeerAsync.  One join (events) on the first GPU's stream, then — for host planes — one D2H copy.
+ *   image series  frame f -> GPU f mod R, two frames in flight per GPU (upload / render / download overlap), each frame
+ *                 downloaded by the GPU that rendered it.
+ * devices: CUDA ordinals (NULL: 0 .. n_devices-1); an ordinal may repeat (several shards on one GPU: how the single-GPU
+ * tests exercise this path).  All calls are asynchronous; srt_mgpu_sync waits for every GPU.  One host thread at a time. */
+typedef struct srt_mgpu srt_mgpu;
+int  srt_mgpu_create(const int* devices, int n_devices, srt_mgpu** out);
+void srt_mgpu_destroy(srt_mgpu* m);
+/* peer_writes: number of GPUs whose kernels write into the first GPU's frame directly (the first GPU included). */
+int  srt_mgpu_info(srt_mgpu* m, int* n_devices, int* peer_writes);
+/* Replicates the scene on every GPU (first call uploads, later calls update in place like srt_scene_update). */
+int  srt_mgpu_scene_upload(srt_mgpu* m, const srt_scene_desc* desc);
+/* One frame of the replicated scene over all GPUs.  `out` planes: host pointers, or device pointers on the first GPU.
+ * row_block: rows per block, a multiple of 4 (0: 16).  params->row_block / shard_* are ignored (set per GPU here). */
+int  srt_mgpu_render_frame(srt_mgpu* m, const srt_render_params* params, const srt_frame* out, int row_block);
+/* n_frames frames: scenes[f] (host arrays, pinned for asynchronous uploads) rendered with params[f] into rgb_out[f]
+ * (host, width*height*3 bytes each; pinned for asynchronous downloads). */
+int  srt_mgpu_render_series(srt_mgpu* m, const srt_scene_desc* const* scenes, const srt_render_params* params,
+                            uint32_t n_frames, uint8_t* const* rgb_out);
+int  srt_mgpu_sync(srt_mgpu* m);
+/* Sums of the per-GPU statistics of the last srt_mgpu_render_frame; kernel_ms = the frame's span on the first GPU's
+ * stream, from the fork to the join of all GPUs (before the download).  Synchronises. */
+int  srt_mgpu_last_stats(srt_mgpu* m, srt_stats* out);
+
 /* ---- helpers ---- */
 void srt_default_params(srt_render_params* p);             /* fills the reference's literals */
 /* Light sample positions, out[3*i..] for i < count: the staircase of softShadow :363-383 (sequential fp32 adds) or

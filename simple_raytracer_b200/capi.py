@@ -26,6 +26,8 @@ EXPORTS = [
     "srt_mesh_upload", "srt_mesh_destroy", "srt_mesh_info", "srt_scene_prep", "srt_scene_prep_status",
     "srt_scene_counts", "srt_scene_download", "srt_scene_download_vnormals", "srt_measure_read_bandwidth",
     "srt_sparse_from_frame_static",
+    "srt_mgpu_create", "srt_mgpu_destroy", "srt_mgpu_info", "srt_mgpu_scene_upload", "srt_mgpu_render_frame",
+    "srt_mgpu_render_series", "srt_mgpu_sync", "srt_mgpu_last_stats",
 ]
 
 
@@ -69,6 +71,16 @@ def lib():
         L.srt_render_sparse.argtypes = [vp, vp, C.POINTER(_abi.RenderParams), C.POINTER(C.c_uint64)]
         L.srt_fetch_sparse.argtypes = [vp, C.POINTER(C.c_float), C.POINTER(C.c_float), C.c_uint64]
         L.srt_sparse_from_frame_static.argtypes = [vp, vp, C.c_int32, C.c_int32, C.c_int32, C.c_int32, vp, vp, vp]
+        L.srt_mgpu_create.argtypes = [C.POINTER(C.c_int), C.c_int, C.POINTER(vp)]
+        L.srt_mgpu_destroy.argtypes = [vp]
+        L.srt_mgpu_destroy.restype = None
+        L.srt_mgpu_info.argtypes = [vp, C.POINTER(C.c_int), C.POINTER(C.c_int)]
+        L.srt_mgpu_scene_upload.argtypes = [vp, C.POINTER(_abi.SceneDesc)]
+        L.srt_mgpu_render_frame.argtypes = [vp, C.POINTER(_abi.RenderParams), C.POINTER(_abi.Frame), C.c_int]
+        L.srt_mgpu_render_series.argtypes = [vp, C.POINTER(C.POINTER(_abi.SceneDesc)), C.POINTER(_abi.RenderParams), C.c_uint32,
+                                             C.POINTER(vp)]
+        L.srt_mgpu_sync.argtypes = [vp]
+        L.srt_mgpu_last_stats.argtypes = [vp, C.POINTER(_abi.Stats)]
         L.srt_measure_read_bandwidth.argtypes = [C.c_void_p, C.c_size_t, C.c_int, C.POINTER(C.c_double)]
         L.srt_eval_leaf.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_float), C.POINTER(C.c_float), C.c_size_t]
         L.srt_host_alloc.argtypes = [C.c_size_t]
@@ -331,6 +343,74 @@ class Context:
     def destroy(self):
         if self.h:
             lib().srt_context_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.destroy()
+        except Exception:
+            pass
+
+
+class MultiGpu:
+    """srt_mgpu: several GPUs of one box from one host thread (include/srt.h).  devices: CUDA ordinals, may repeat."""
+
+    def __init__(self, devices):
+        devices = [int(d) for d in devices]
+        arr = (C.c_int * len(devices))(*devices)
+        h = C.c_void_p()
+        _check(lib().srt_mgpu_create(arr, len(devices), C.byref(h)))
+        self.h, self.devices = h, devices
+        self._keep = None
+
+    def info(self) -> dict:
+        n, pw = C.c_int(), C.c_int()
+        _check(lib().srt_mgpu_info(self.h, C.byref(n), C.byref(pw)))
+        return dict(n_devices=n.value, peer_writes=pw.value)
+
+    def upload(self, arrays_or_desc):
+        d = arrays_or_desc.desc() if hasattr(arrays_or_desc, "desc") else arrays_or_desc
+        self._keep = (arrays_or_desc, d)
+        _check(lib().srt_mgpu_scene_upload(self.h, C.byref(d)))
+
+    def render_frame_raw(self, params: _abi.RenderParams, rgb=None, obj_id=None, tri_id=None, t=None, row_block: int = 0):
+        fr = _abi.Frame()
+        fr.rgb, fr.obj_id, fr.tri_id, fr.t = rgb, obj_id, tri_id, t
+        _check(lib().srt_mgpu_render_frame(self.h, C.byref(params), C.byref(fr), int(row_block)))
+
+    def render_frame(self, params: _abi.RenderParams, row_block: int = 0, ids: bool = True, want_t: bool = True):
+        H, W = params.height, params.width
+        rgb = np.zeros((H, W, 3), np.uint8)
+        obj = np.full((H, W), -1, np.int32) if ids else None
+        tri = np.full((H, W), -1, np.int32) if ids else None
+        tt = np.full((H, W), np.inf, np.float32) if want_t else None
+        self.render_frame_raw(params, rgb.ctypes.data, obj.ctypes.data if ids else None, tri.ctypes.data if ids else None,
+                              tt.ctypes.data if want_t else None, row_block)
+        self.sync()
+        return dict(rgb=rgb, obj_id=obj, tri_id=tri, t=tt, stats=self.last_stats())
+
+    def render_series(self, scenes, params, out_frames):
+        """scenes: FlatSceneArrays (or descs) per frame; params: RenderParams per frame; out_frames: host arrays [H][W][3] uint8."""
+        n = len(scenes)
+        descs = [s.desc() if hasattr(s, "desc") else s for s in scenes]
+        dp = (C.POINTER(_abi.SceneDesc) * max(n, 1))(*[C.pointer(d) for d in descs])
+        pa = (_abi.RenderParams * max(n, 1))(*params)
+        op = (C.c_void_p * max(n, 1))(*[int(o.ctypes.data) if hasattr(o, "ctypes") else int(o) for o in out_frames])
+        self._series_keep = (scenes, descs, dp, pa, op, out_frames)
+        _check(lib().srt_mgpu_render_series(self.h, dp, pa, n, op))
+
+    def sync(self):
+        _check(lib().srt_mgpu_sync(self.h))
+
+    def last_stats(self) -> dict:
+        s = _abi.Stats()
+        _check(lib().srt_mgpu_last_stats(self.h, C.byref(s)))
+        return dict(primary_rays=int(s.primary_rays), hit_pixels=int(s.hit_pixels), shadow_rays=int(s.shadow_rays),
+                    exact_slab_tests=int(s.exact_slab_tests), kernel_ms=float(s.kernel_ms), kernel_launches=int(s.kernel_launches))
+
+    def destroy(self):
+        if self.h:
+            lib().srt_mgpu_destroy(self.h)
             self.h = None
 
     def __del__(self):

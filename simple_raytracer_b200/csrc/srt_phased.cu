@@ -433,12 +433,52 @@ __device__ __forceinline__ void shadow_item(const KArgs& a, Stack& st, unsigned 
     if (lane == 0) a.shadow_mask[(size_t)tile * a.light_count + light] = ballot;
 }
 
-// Shading of one pixel (:350-401, :437-449, :476-487).  `mine`: this lane has shadow masks to read.
+// The 8-bit pixel of a shaded colour: tone map, gamma, truncating quantisation (:391-398, :447-449, :470-472) and the sky
+// rule (:518, :476-487), packed as r | g << 8 | b << 16.
+__device__ __forceinline__ uint32_t quantise_pixel(const KArgs& a, bool hit, V3 color) {
+    int r = 0, g = 0, b = 0;
+    if (hit) {
+        r = tone_quantise(color.x, a.tone_k, a.gamma) & 0xff;
+        g = tone_quantise(color.y, a.tone_k, a.gamma) & 0xff;
+        b = tone_quantise(color.z, a.tone_k, a.gamma) & 0xff;
+    }
+    if ((r | g | b) == 0 && !a.no_sky_fill) { r = a.sky[0]; g = a.sky[1]; b = a.sky[2]; }
+    return (uint32_t)r | ((uint32_t)g << 8) | ((uint32_t)b << 16);
+}
+
+// RGB8 store of a whole 8x4 tile (all 32 lanes call it; lane = pixel, c = its packed colour).  A tile row is 24
+// contiguous bytes = six 32-bit words; word w of a row takes its bytes from pixels (w/3)*4 + w%3 and the next one, so two
+// shuffles and a funnel shift build it and lanes 0..5 of every row store one word each: 24 STG.32 per tile instead of 96
+// STG.U8 — a quarter of the store instructions, and whole 32-byte sectors per row for frames that live in a peer GPU's
+// memory (srt_mgpu_render_frame writes them over NVLink).  Needs 4-byte aligned rows (width % 4 == 0, aligned base) and a
+// tile that lies inside the frame; anything else takes the byte path.
+__device__ __forceinline__ void store_tile_rgb(const KArgs& a, const Pixel& p, uint32_t c, unsigned lane) {
+    if (!a.rgb) return;
+    const bool aligned = ((a.width & 3) == 0) && ((reinterpret_cast<uintptr_t>(a.rgb) & 3u) == 0);
+    const bool full = __all_sync(kFull, p.valid);
+    if (aligned && full) {
+        const unsigned col = lane & 7u, wl = col % 3u, base = (col / 3u) * 4u + (lane & ~7u);
+        const uint32_t ca = __shfl_sync(kFull, c, (int)(base + wl));
+        const uint32_t cb = __shfl_sync(kFull, c, (int)((base + wl + 1u) & 31u));
+        if (col < 6u) {
+            const uint32_t word = __funnelshift_r(ca | (cb << 24), cb >> 8, 8u * wl);   // bytes wl..2 of ca, then the low bytes of cb
+            uint8_t* row = a.rgb + ((size_t)p.py * a.width + (size_t)(p.px - (int)col)) * 3;
+            reinterpret_cast<uint32_t*>(row)[col] = word;
+        }
+        return;
+    }
+    if (p.valid) {
+        uint8_t* q = a.rgb + ((size_t)p.py * a.width + p.px) * 3;
+        q[0] = (uint8_t)c; q[1] = (uint8_t)(c >> 8); q[2] = (uint8_t)(c >> 16);
+    }
+}
+
+// Shading of one pixel (:350-401, :437-449, :476-487).  `mine`: this lane has shadow masks to read.  Called by all 32
+// lanes of the tile's warp (the store is a warp-wide operation).
 __device__ __forceinline__ void shade_pixel(const KArgs& a, const Pixel& p, const Hit& h, V3 d, bool mine, unsigned tile,
                                             unsigned lane) {
-    if (!p.valid) return;
     V3 color = v3(0.f, 0.f, 0.f);
-    const bool hit = h.tri >= 0;
+    const bool hit = p.valid && h.tri >= 0;
     if (hit) {
         const V3 lc = v3(a.light_color[0], a.light_color[1], a.light_color[2]);
         const PhongPixel pp = prepare_pixel(a, h, d, false);
@@ -452,7 +492,7 @@ __device__ __forceinline__ void shade_pixel(const KArgs& a, const Pixel& p, cons
         }
         if (a.normalise_lights) color = average_lights(color, a.light_count);
     }
-    store_pixel(a, p.px, p.py, hit, color, h, false);   // ids / t planes were written with the hit record
+    store_tile_rgb(a, p, quantise_pixel(a, hit, color), lane);   // ids / t planes were written with the hit record
 }
 
 // Shading of a tile from its stored hit records (after its shadow items).
