@@ -58,6 +58,8 @@ def parse_args():
     ap.add_argument("--still", action="store_true", help="render frame 0 on every step (profiling)")
     ap.add_argument("--e2e-bands", type=int, default=0, help="row bands of the two e2e lanes (0: the library default)")
     ap.add_argument("--gather", action="store_true", help="e2e: gather every rank's frame to rank 0 over NCCL before the download")
+    ap.add_argument("--no-single-frame", action="store_true", help="skip the single-frame strong-scaling leg")
+    ap.add_argument("--row-block", type=int, default=16, help="rows per block of the single-frame sharding")
     ap.add_argument("--series-lanes", type=int, default=6, help="frames in flight (contexts / streams) of the device-prep series leg")
     ap.add_argument("--series-frames", type=int, default=-1,
                     help="frames of the pipelined image-series leg incl. host prep (-1: 3 x host threads, max 96; 0: skip)")
@@ -228,6 +230,123 @@ def run_reference_arm(args):
     }
     print(json.dumps(line))
     return 0
+
+
+# ------------------------------------------------------------------------------------------------
+def single_frame_leg(args, ctx, rank, world, local, dev, barrier):
+    """ONE frame over all N GPUs (strong scaling): interleaved blocks of --row-block rows, block b ->
+    rank b % N, every rank renders its blocks in place into a full-size device frame, and the blocks travel from there
+    into the same rows of rank 0's frame over NCCL (one batched send/recv group, no packing).  Rank 0 then renders the
+    whole frame alone and compares the bytes.  At N = 1 it is the plain one-GPU frame (two row bands).  Times are CUDA
+    events on each rank's stream around render + gather, max over ranks, mean over frames; L2 flushed between frames."""
+    import torch
+    import torch.distributed as dist
+    from simple_raytracer_b200 import _abi, capi, host, multigpu, scenes
+    out = {}
+    flush = torch.empty(L2_FLUSH_BYTES, dtype=torch.uint8, device=dev)
+    for key, angle in (("C3", 0.0), ("C3", 180.0), ("C4", 0.0)):
+        cfg = scenes.CONFIGS[key]
+        W, H, focal, N = cfg.width, cfg.height, cfg.focal, cfg.light_count
+        hs = host.HostScene()
+        view = cfg.build(hs, angle)
+        light = np.asarray(scenes.light_view_space(hs, view), np.float32)
+        arrays = hs.flatten()
+        hs.close()
+        sc = ctx.upload(arrays)
+        sharded = multigpu.ShardedFrameRenderer(ctx, W, H, row_block=args.row_block) if world > 1 else None
+        frame1 = torch.empty((H, W, 3), dtype=torch.uint8, device=dev)
+
+        def one_frame():
+            p = _abi.default_params(W, H, focal, light, N, True)
+            if sharded is None:
+                ctx.render_raw(sc, p, rgb=frame1.data_ptr())
+                return frame1
+            return sharded.render(sc, p)
+
+        iters, warm = 12, 3
+        evs, render_ms = [], []
+        res = None
+        for it in range(warm + iters):
+            flush.zero_()
+            barrier()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            res = one_frame()
+            e1.record()
+            torch.cuda.synchronize()
+            if it >= warm:
+                evs.append(e0.elapsed_time(e1))
+                render_ms.append(ctx.last_stats()["kernel_ms"])
+        t = torch.tensor([float(np.mean(evs)), float(np.mean(render_ms)), float(np.min(render_ms))], dtype=torch.float64, device=dev)
+        tmin = t.clone()
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            dist.all_reduce(tmin, op=dist.ReduceOp.MIN)
+        identical = None
+        hits = ctx.last_stats()["hit_pixels"]
+        if rank == 0:
+            p = _abi.default_params(W, H, focal, light, N, True)
+            ctx.render_raw(sc, p, rgb=frame1.data_ptr())
+            hits = ctx.last_stats()["hit_pixels"]
+            identical = bool(torch.equal(res, frame1)) if world > 1 else True
+            name = f"{key}_{W}x{H}_{N}lights_{angle:g}deg"
+            rays = ray_count(W, H, N, hits, len(arrays.objects))
+            out[name] = {"ms_per_frame": float(t[0]), "render_ms_slowest_rank": float(t[1]), "render_ms_fastest_rank": float(tmin[1]),
+                         "gather_and_sync_ms": float(t[0] - t[1]), "frames_per_s": 1e3 / float(t[0]), "Mrays_per_s": rays / float(t[0]) / 1e3,
+                         "identical": identical, "bytes_gathered": int(W * H * 3 * (world - 1) / world)}
+        sc.destroy()
+        barrier()
+    if rank == 0:
+        out["what"] = (f"one frame over {world} GPU(s): interleaved {args.row_block}-row blocks, rendered in place, row blocks sent from the "
+                       "owner's frame into rank 0's frame over NCCL (batched isend/irecv, no staging copy); `identical` = bytes equal to "
+                       "rank 0's own full render; ms = CUDA events around render + gather, max over ranks, mean of 12 frames after 3 warm-up, "
+                       "L2 flushed and ranks barriered before every frame") if world > 1 else \
+                      "one frame on one GPU (default pipeline, two row bands), same timing method as the N-GPU lines"
+    return out if rank == 0 else None
+
+
+def single_frame_c_abi_leg(args, world, local):
+    """The same single frame through the C entry points (srt_mgpu_*, one host thread, no Python / torch on the data path):
+    rank 0 drives all N GPUs of the box; GPUs 1.. write their row blocks straight into GPU 0's frame through peer-mapped
+    memory (NVLink stores from the shade kernel), joined by events.  Run while the other ranks wait at a barrier."""
+    from simple_raytracer_b200 import _abi, capi, host, scenes
+    out = {}
+    m = capi.MultiGpu(list(range(world)))
+    single = capi.Context(0)
+    try:
+        info = m.info()
+        for key, angle in (("C3", 0.0), ("C3", 180.0), ("C4", 0.0)):
+            cfg = scenes.CONFIGS[key]
+            W, H, focal, N = cfg.width, cfg.height, cfg.focal, cfg.light_count
+            hs = host.HostScene()
+            view = cfg.build(hs, angle)
+            light = np.asarray(scenes.light_view_space(hs, view), np.float32)
+            arrays = hs.flatten()
+            hs.close()
+            m.upload(arrays)
+            p = _abi.default_params(W, H, focal, light, N, True)
+            dev_rgb = capi.lib().srt_device_alloc(single.h, W * H * 3)
+            ms = []
+            for it in range(15):
+                m.render_frame_raw(p, rgb=dev_rgb, row_block=args.row_block)
+                m.sync()
+                if it >= 3:
+                    ms.append(m.last_stats()["kernel_ms"])
+            got = m.render_frame(p, row_block=args.row_block, ids=False, want_t=False)["rgb"]
+            sc = single.upload(arrays)
+            want = single.render(sc, p, ids=False, want_t=False)["rgb"]
+            sc.destroy()
+            capi.lib().srt_device_free(single.h, dev_rgb)
+            out[f"{key}_{W}x{H}_{N}lights_{angle:g}deg"] = {"ms_per_frame": float(np.mean(ms)), "ms_best": float(np.min(ms)),
+                                                            "frames_per_s": 1e3 / float(np.mean(ms)), "identical": bool(np.array_equal(got, want))}
+        out["peer_writes"] = info["peer_writes"]
+        out["what"] = (f"srt_mgpu_render_frame over {world} GPU(s) from one host thread: fork on GPU 0's stream, every GPU renders its "
+                       f"interleaved {args.row_block}-row blocks into GPU 0's device frame ({info['peer_writes']} of {world} through direct / peer-mapped stores), "
+                       "join by events; ms = CUDA events on GPU 0's stream from fork to join, mean of 12 frames after 3 warm-up (L2 not flushed)")
+    finally:
+        m.destroy()
+        single.destroy()
+    return out
 
 
 # ------------------------------------------------------------------------------------------------
@@ -504,6 +623,18 @@ def run_b200_arm(args):
         series_dev = (t_d1 - t_d0, n_fd, float(np.mean([tm["issue_ms"] for tm in tmd])), sd.host_fallbacks)
         sd.close()
 
+    # ---- one frame over all GPUs (strong scaling) ----
+    single_frame = single_frame_c = None
+    if not args.no_single_frame and not args.still and args.config == "C3":
+        single_frame = single_frame_leg(args, ctx, rank, world, local, dev, barrier)
+        barrier()
+        if rank == 0:
+            try:
+                single_frame_c = single_frame_c_abi_leg(args, world, local)
+            except Exception as e:               # reporting leg: never takes the bench line down
+                single_frame_c = {"failed": str(e)}
+        barrier()
+
     # ---- max over ranks, totals ----
     agg = torch.tensor([total_ms, e2e[0] if e2e else 0.0, kern_ms, prep_ms, series[0] if series else 0.0,
                         series_dev[0] if series else 0.0], dtype=torch.float64, device=dev)
@@ -579,6 +710,10 @@ def run_b200_arm(args):
                            "frames_per_s": world * K / (e2e_ms * 1e-3),
                            "what": "per rank: srt_scene_update from pinned host arrays + srt_render + D2H of the RGB8 frame to pinned host memory, frames alternating between two contexts / streams so that copies overlap renders; the L2 flushes between frames are inside this time"
                                    + (" (all frames gathered to rank 0 over NCCL first)" if args.gather else "")}
+        if single_frame:
+            line["single_frame"] = single_frame
+        if single_frame_c:
+            line["single_frame_c_abi"] = single_frame_c
         if c3_still:
             line["c3_frame0"] = c3_still
         if one_piece:

@@ -61,6 +61,32 @@ def gather_row_blocks(frame: torch.Tensor, height: int, row_block: int, group=No
     return frame[:height]
 
 
+def gather_row_blocks_in_place(frame: torch.Tensor, height: int, row_block: int, group=None, dst: int = 0) -> Optional[torch.Tensor]:
+    """`frame` is [>= height, W, C] and contiguous on every rank, with this rank's own row blocks rendered in place.  Every
+    block travels straight from the owner's frame into the same rows of rank `dst`'s frame: one send / receive per block,
+    all of them in one batch (one NCCL group: a single launch per rank), no packing on the sender, no unpacking on the
+    receiver — the render kernels wrote the bytes the collective sends.  Returns frame[:height] on `dst`, None elsewhere."""
+    world = dist.get_world_size(group)
+    rank = dist.get_rank(group)
+    if world == 1:
+        return frame[:height]
+    if not frame.is_contiguous():
+        raise ValueError("frame must be contiguous (row blocks are sent as views)")
+    n_blocks = (height + row_block - 1) // row_block
+    ops = []
+    for b in range(n_blocks):
+        owner = b % world
+        if owner == dst or rank not in (owner, dst):
+            continue
+        rows = frame[b * row_block:min((b + 1) * row_block, height)]
+        peer = dist.get_global_rank(group, dst if rank == owner else owner) if group is not None else (dst if rank == owner else owner)
+        ops.append(dist.P2POp(dist.isend if rank == owner else dist.irecv, rows, peer, group))
+    if ops:
+        for req in dist.batch_isend_irecv(ops):
+            req.wait()
+    return frame[:height] if rank == dst else None
+
+
 def gather_frames(frame: torch.Tensor, group=None, dst: int = 0) -> Optional[List[torch.Tensor]]:
     """Image series: every rank contributes one finished frame; rank `dst` receives all of them in rank order."""
     world = dist.get_world_size(group)
@@ -92,4 +118,4 @@ class ShardedFrameRenderer:
             self.ctx.sync()               # context on its own stream: order the gather after the render
         if self.world == 1:
             return self.frame[: self.height]
-        return gather_row_blocks(self.frame, self.height, self.row_block, self.group)
+        return gather_row_blocks_in_place(self.frame, self.height, self.row_block, self.group)

@@ -43,6 +43,15 @@ def _worker(rank, world, port, q):
                 results[(H, W, rb)] = bool(torch.equal(out, full))
             else:
                 assert out is None
+            # the zero-copy form: blocks travel from the owner's frame into the same rows of rank 0's frame (no padding)
+            frame2 = torch.zeros((H, W, 3), dtype=torch.uint8)
+            for r0, r1 in multigpu.owned_blocks(H, rb, rank, world):
+                frame2[r0:r1] = full[r0:r1]
+            out2 = multigpu.gather_row_blocks_in_place(frame2, H, rb)
+            if rank == 0:
+                results[(H, W, rb, "in place")] = bool(torch.equal(out2, full)) and out2.data_ptr() == frame2.data_ptr()
+            else:
+                assert out2 is None
         # image series: frame f -> rank f % world, gathered in rank order each step
         n_frames = 6
         mine = multigpu.frames_of_rank(n_frames, rank, world)
