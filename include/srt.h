@@ -300,6 +300,13 @@ int  srt_sync(srt_context* ctx);
 /* Statistics of the most recent srt_render on this context (synchronises the context). */
 int  srt_last_stats(srt_context* ctx, srt_stats* out);
 
+/* Per-pass device times of the default pipeline (measurement aid).  With stage timing on, srt_render records events
+ * around its four launches; srt_last_stage_ms returns {classify, primary, shadow, shade} in ms for the last render, which
+ * must have been a one-piece frame (srt_context_set_bands(ctx, 1): with two bands the passes of the halves interleave on
+ * two streams and a per-pass time has no meaning).  Synchronises. */
+int  srt_context_set_stage_timing(srt_context* ctx, int enabled);
+int  srt_last_stage_ms(srt_context* ctx, float* ms4);
+
 /* ---- render with the reference's own result format (struct ImageData :28, filled by :505-525) ----
  * Renders like srt_render, then compacts on the device: only the pixels whose quantised colour is not (0,0,0)
  * (:518), in the reference's column-major scan order (x outer :511, y inner :513); positions (x, y) and colours

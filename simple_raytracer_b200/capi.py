@@ -26,6 +26,7 @@ EXPORTS = [
     "srt_mesh_upload", "srt_mesh_destroy", "srt_mesh_info", "srt_scene_prep", "srt_scene_prep_status",
     "srt_scene_counts", "srt_scene_download", "srt_scene_download_vnormals", "srt_measure_read_bandwidth",
     "srt_sparse_from_frame_static",
+    "srt_context_set_stage_timing", "srt_last_stage_ms",
     "srt_mgpu_create", "srt_mgpu_destroy", "srt_mgpu_info", "srt_mgpu_scene_upload", "srt_mgpu_render_frame",
     "srt_mgpu_render_series", "srt_mgpu_sync", "srt_mgpu_last_stats",
 ]
@@ -71,6 +72,8 @@ def lib():
         L.srt_render_sparse.argtypes = [vp, vp, C.POINTER(_abi.RenderParams), C.POINTER(C.c_uint64)]
         L.srt_fetch_sparse.argtypes = [vp, C.POINTER(C.c_float), C.POINTER(C.c_float), C.c_uint64]
         L.srt_sparse_from_frame_static.argtypes = [vp, vp, C.c_int32, C.c_int32, C.c_int32, C.c_int32, vp, vp, vp]
+        L.srt_context_set_stage_timing.argtypes = [vp, C.c_int]
+        L.srt_last_stage_ms.argtypes = [vp, C.POINTER(C.c_float)]
         L.srt_mgpu_create.argtypes = [C.POINTER(C.c_int), C.c_int, C.POINTER(vp)]
         L.srt_mgpu_destroy.argtypes = [vp]
         L.srt_mgpu_destroy.restype = None
@@ -254,6 +257,15 @@ class Context:
         if before < 0:
             _check(before)
         return before
+
+    def set_stage_timing(self, enabled: bool):
+        _check(lib().srt_context_set_stage_timing(self.h, 1 if enabled else 0))
+
+    def last_stage_ms(self) -> dict:
+        """{classify, primary, shadow, shade} device ms of the last one-piece default-pipeline render (stage timing on)."""
+        ms = (C.c_float * 4)()
+        _check(lib().srt_last_stage_ms(self.h, ms))
+        return dict(classify=ms[0], primary=ms[1], shadow=ms[2], shade=ms[3])
 
     def info(self):
         sm, ma, mi, l2 = C.c_int(), C.c_int(), C.c_int(), C.c_size_t()

@@ -109,6 +109,7 @@ void srt_context_destroy(srt_context* c) {
     if (c->ev0) cudaEventDestroy(c->ev0);
     if (c->ev1) cudaEventDestroy(c->ev1);
     if (c->ev_copy) cudaEventDestroy(c->ev_copy);
+    for (auto& ev : c->stage_ev) if (ev) cudaEventDestroy(ev);
     if (c->own_stream && c->stream) cudaStreamDestroy(c->stream);
     delete c;
 }
@@ -119,6 +120,23 @@ int srt_context_set_bands(srt_context* c, int bands) {
     const int before = c->bands;
     c->bands = bands;
     return before;
+}
+
+int srt_context_set_stage_timing(srt_context* c, int enabled) {
+    if (!c) return fail(SRT_ERR_INVALID_ARG, "ctx is NULL");
+    c->stage_timing = enabled != 0;
+    c->have_stage = false;
+    return SRT_OK;
+}
+
+int srt_last_stage_ms(srt_context* c, float* ms4) {
+    if (!c || !ms4) return fail(SRT_ERR_INVALID_ARG, "NULL argument");
+    if (!c->have_stage || c->last_banded)
+        return fail(SRT_ERR_INVALID_ARG, "srt_last_stage_ms: the last render was not a one-piece frame of the default pipeline with stage timing on");
+    CU(cudaSetDevice(c->device));
+    CU(cudaStreamSynchronize(c->stream));
+    for (int k = 0; k < 4; ++k) CU(cudaEventElapsedTime(&ms4[k], c->stage_ev[k], c->stage_ev[k + 1]));
+    return SRT_OK;
 }
 
 int srt_context_set_stream(srt_context* c, void* cuda_stream) {
@@ -558,7 +576,11 @@ static int render_impl(srt_context* c, const srt_scene* s, const srt_render_para
         a.shadow_mask = (uint32_t*)c->shadow_mask.p;
         a.coord_bound = s->coord_bound;
         a.coord_bound_dev = s->coord_bound_dev;
-        e = srtk::launch_render_phased(a, p->variant, c->sm_count, c->stream, &c->last_launches);
+        const bool timed = c->stage_timing && !c->parent;
+        if (timed && !c->stage_ev[0])
+            for (auto& ev : c->stage_ev) CU(cudaEventCreate(&ev));
+        e = srtk::launch_render_phased(a, p->variant, c->sm_count, c->stream, &c->last_launches, timed ? c->stage_ev : nullptr);
+        c->have_stage = timed && (p->variant == SRT_VARIANT_DEFAULT) && a.tiles_x * a.tiles_y > 0;
     } else {
         e = srtk::launch_render(a, p->variant, c->sm_count, c->stream);
         c->last_launches = 1;

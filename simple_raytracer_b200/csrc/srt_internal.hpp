@@ -71,6 +71,8 @@ struct srt_context {
     cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
     bool last_banded = false;
     int bands = 2;                    // srt_context_set_bands (SRT_DEFAULT_BANDS overrides the default)
+    cudaEvent_t stage_ev[5] = {};     // srt_context_set_stage_timing: around classify / primary / shadow / shade
+    bool stage_timing = false, have_stage = false;
     uint64_t last_primary = 0;
     int last_lights = 0;
     uint32_t last_objects = 0;

@@ -106,6 +106,6 @@ int leaf_in_width(int op);
 int leaf_out_width(int op);
 cudaError_t launch_eval_leaf(int op, const float* in, float* out, size_t n, cudaStream_t stream);
 
-cudaError_t launch_render_phased(const KArgs& a, int variant, int sm_count, cudaStream_t stream, int* launches);
+cudaError_t launch_render_phased(const KArgs& a, int variant, int sm_count, cudaStream_t stream, int* launches, cudaEvent_t* stage_ev = nullptr);
 
 }  // namespace srtk

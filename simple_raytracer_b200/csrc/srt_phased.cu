@@ -894,7 +894,7 @@ cudaError_t persistent_blocks(K kernel, size_t smem, int sm_count, int n_tiles, 
 }
 }  // namespace
 
-cudaError_t launch_render_phased(const KArgs& a, int variant, int sm_count, cudaStream_t stream, int* launches) {
+cudaError_t launch_render_phased(const KArgs& a, int variant, int sm_count, cudaStream_t stream, int* launches, cudaEvent_t* stage_ev) {
     const int n_tiles = a.tiles_x * a.tiles_y;
     if (launches) *launches = 0;
     if (n_tiles <= 0) return cudaSuccess;
@@ -913,7 +913,11 @@ cudaError_t launch_render_phased(const KArgs& a, int variant, int sm_count, cuda
     }
     int cblocks = (n_tiles + kThreads - 1) / kThreads;
     if (cblocks > sm_count * 8) cblocks = sm_count * 8;
+    // stage_ev (srt_context_set_stage_timing): five events around the four passes of the default pipeline
+    const bool timed = stage_ev && (variant == SRT_VARIANT_DEFAULT || variant == SRT_VARIANT_SPLIT);
+    if (timed) cudaEventRecord(stage_ev[0], stream);
     classify_kernel<<<cblocks, kThreads, 0, stream>>>(a);
+    if (timed) cudaEventRecord(stage_ev[1], stream);
     cudaError_t e;
     const bool shadows = a.n_objects >= 2 && a.light_count > 0;
     if (variant == SRT_VARIANT_DEFAULT || variant == SRT_VARIANT_SPLIT || variant == SRT_VARIANT_OVERLAP) {
@@ -936,9 +940,12 @@ cudaError_t launch_render_phased(const KArgs& a, int variant, int sm_count, cuda
         } else {
             render_phase<0, false><<<bp, kThreads, smem, stream>>>(a);
             ++n;
+            if (timed) cudaEventRecord(stage_ev[2], stream);
             if (shadows) { render_phase<1, false><<<bs, kThreads, smem_s, stream>>>(a); ++n; }
+            if (timed) cudaEventRecord(stage_ev[3], stream);
         }
         render_phase<2, false><<<bc, kThreads, 0, stream>>>(a);
+        if (timed) cudaEventRecord(stage_ev[4], stream);
         ++n;
         if (launches) *launches = n;
         return cudaGetLastError();

@@ -1,5 +1,7 @@
-"""Print the metrics we track from an .ncu-rep (read here, no GPU):  python tools/ncu_summary.py file.ncu-rep"""
-import csv, io, subprocess, sys
+"""Print the metrics we track from an .ncu-rep (read here, no GPU):  python tools/ncu_summary.py file.ncu-rep [--json out.json]
+--json also writes them as a list of {kernel, grid, block, metrics{name: value}, units{name: unit}}: what bench.py reads for the
+measured-traffic fields of its roofline objects (profiles/r02_stage_metrics.json)."""
+import csv, io, json, subprocess, sys
 KEEP = ['gpu__time_duration.sum', 'launch__registers_per_thread', 'launch__grid_size', 'launch__occupancy_limit_registers',
         'sm__warps_active.avg.per_cycle_active', 'smsp__issue_active.avg.pct_of_peak_sustained_active', 'smsp__inst_executed.sum',
         'sm__inst_executed.sum.per_cycle_active', 'sm__inst_executed.sum.per_cycle_elapsed', 'sm__cycles_active.avg', 'sm__cycles_active.max',
@@ -19,8 +21,22 @@ out = subprocess.run(['ncu', '-i', sys.argv[1], '--page', 'raw', '--csv'], captu
 rows = list(csv.reader(io.StringIO(out)))
 hdr, units = rows[0], rows[1]
 ix = {h: i for i, h in enumerate(hdr)}
+KEEP += ['l1tex__m_xbar2l1tex_read_bytes.sum', 'l1tex__m_l1tex2xbar_write_bytes.sum', 'lts__t_sectors_op_read.sum', 'lts__t_sectors_op_write.sum',
+         'lts__t_sectors_srcunit_tex.sum', 'sm__throughput.avg.pct_of_peak_sustained_elapsed', 'smsp__inst_executed.avg.per_cycle_active',
+         'smsp__cycles_active.avg', 'launch__shared_mem_per_block_dynamic', 'sm__maximum_warps_per_active_cycle_pct', 'sm__warps_active.avg.pct_of_peak_sustained_active']
+kernels = []
 for r in rows[2:]:
     print('==', r[ix['Kernel Name']][:90], 'grid', r[ix['Grid Size']], 'block', r[ix['Block Size']])
+    k_out = {'kernel': r[ix['Kernel Name']], 'grid': r[ix['Grid Size']], 'block': r[ix['Block Size']], 'metrics': {}, 'units': {}}
     for k in KEEP:
         if k in ix:
             print(f'  {k} [{units[ix[k]]}] = {r[ix[k]]}')
+            try:
+                k_out['metrics'][k] = float(r[ix[k]].replace(',', ''))
+                k_out['units'][k] = units[ix[k]]
+            except ValueError:
+                pass
+    kernels.append(k_out)
+if '--json' in sys.argv:
+    with open(sys.argv[sys.argv.index('--json') + 1], 'w') as f:
+        json.dump({'source': sys.argv[1], 'kernels': kernels}, f, indent=1)
