@@ -755,12 +755,13 @@ def run_b200_arm(args):
             line["roofline_fp32"] = {"bound": "fp32 issue (non-FMA)", "achieved": flops / (kern_ms * 1e-3) / 1e12, "peak": fp32_peak,
                                      "unit": "TFLOP/s", "frac": flops / (kern_ms * 1e-3) / 1e12 / fp32_peak,
                                      "peak_source": "148 SMs x 128 lanes x SM clock under load"}
-            l2_measured = (sum(m.get("lts__t_bytes.sum", 0.0) for m in ncu_stage.values()) if len(ncu_stage) == 3 else None)
+            l2_measured = (sum(m.get("l1tex__m_xbar2l1tex_read_bytes.sum", 0.0) + m.get("l1tex__m_l1tex2xbar_write_bytes.sum", 0.0) for m in ncu_stage.values())
+                           if len(ncu_stage) == 3 else None)
             line["roofline_l2"] = {"bound": "l2", "achieved": l2b / (kern_ms * 1e-3) / 1e9, "peak": l2_peak, "unit": "GB/s",
                                    "frac": l2b / (kern_ms * 1e-3) / 1e9 / l2_peak, "algorithmic_bytes": l2b,
                                    "measured_l2_bytes": l2_measured,
                                    "measured_frac": (l2_measured / (kern_ms * 1e-3) / 1e9 / l2_peak) if l2_measured else None,
-                                   "measured_source": f"lts__t_bytes.sum of the three render kernels of ONE frame (the capture's frame, not the K-frame mean): profiles/{ncu_path.name}" if l2_measured else None,
+                                   "measured_source": f"l1tex__m_xbar2l1tex_read_bytes + l1tex__m_l1tex2xbar_write_bytes (what crosses the crossbar between L2 and the SMs' L1) of the three render kernels of ONE frame (the capture's frame, not the K-frame mean): profiles/{ncu_path.name}" if l2_measured else None,
                                    "note": "`achieved` is the ALGORITHMIC byte rate (every box / triangle fetched from L2 once per test); L1 absorbs most of "
                                            "those fetches, so the bytes that really cross L2 -> SM are `measured_l2_bytes`",
                                    "peak_source": l2_src}
@@ -778,7 +779,7 @@ def run_b200_arm(args):
                     per[tag] = {"time_share": m.get("gpu__time_duration.sum", 0.0) / tot_t if tot_t else None, "issue_slots_busy": iss,
                                 "sm_active_share": busy, "active_threads_of_32": act * 32.0, "thread_slots_used": iss * act * busy,
                                 "l1_hit_pct": m.get("l1tex__t_sector_hit_rate.pct"), "l2_hit_pct": m.get("lts__t_sector_hit_rate.pct"),
-                                "l2_bytes": m.get("lts__t_bytes.sum"), "registers": m.get("launch__registers_per_thread")}
+                                "l2_to_sm_bytes": m.get("l1tex__m_xbar2l1tex_read_bytes.sum"), "registers": m.get("launch__registers_per_thread")}
                     acc += iss * act * busy * (m.get("gpu__time_duration.sum", 0.0) / tot_t if tot_t else 0.0)
                 line["roofline"] = {"bound": "issue (thread-instruction slots)", "achieved": acc, "peak": 1.0, "unit": "fraction of thread-instruction issue slots",
                                     "frac": acc, "traffic": line["roofline_hbm"]["traffic"], "per_kernel": per,

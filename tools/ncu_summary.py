@@ -31,9 +31,14 @@ for r in rows[2:]:
     for k in KEEP:
         if k in ix:
             print(f'  {k} [{units[ix[k]]}] = {r[ix[k]]}')
-            try:
-                k_out['metrics'][k] = float(r[ix[k]].replace(',', ''))
-                k_out['units'][k] = units[ix[k]]
+            try:                                # JSON values are normalised: bytes, milliseconds
+                v, u = float(r[ix[k]].replace(',', '')), units[ix[k]]
+                scale = {'Kbyte': 1e3, 'Mbyte': 1e6, 'Gbyte': 1e9, 'Tbyte': 1e12}.get(u)
+                if scale: v, u = v * scale, 'byte'
+                tscale = {'s': 1e3, 'us': 1e-3, 'ns': 1e-6, 'msecond': 1.0, 'usecond': 1e-3, 'nsecond': 1e-6, 'second': 1e3}.get(u)
+                if tscale: v, u = v * tscale, 'ms'
+                k_out['metrics'][k] = v
+                k_out['units'][k] = u
             except ValueError:
                 pass
     kernels.append(k_out)
