@@ -388,6 +388,10 @@ int  srt_measure_read_bandwidth(srt_context* ctx, size_t bytes, int repeats, dou
  *                      (intersectRayAabbNoOrigin :252-293; `filtered` is the decision of the kernels' filtered
  *                      slab test, which must equal `exact`; used_exact = 1 when the filter deferred to the exact test)
  *   SRT_LEAF_TRIANGLE  in  o[3], d[3], p0[3], e1[3], e2[3]                                 out t or -inf           (:42-75)
+ *   SRT_LEAF_TRIANGLE_FILTERED  same input                                                  out filtered, exact, took_tail
+ *                      (the shadow pass's moller_trumbore_filtered, which decides clear misses without the division,
+ *                      and the plain function: the two must be the same bits; took_tail = 1 when the reference's own
+ *                      operation sequence was run)
  *   SRT_LEAF_PHONG     in  n[3], d[3], light[3], light_color[3], obj_color[3],
  *                          ambient, specular, shininess, t                                 out rgb[3]              (:144-200)
  *   SRT_LEAF_TONE      in  c, tone_k, gamma                                                out q (0..255)          (:391-398, :447-449)
@@ -395,7 +399,7 @@ int  srt_measure_read_bandwidth(srt_context* ctx, size_t bytes, int repeats, dou
  *                      (interpolateNormal :132-140 at the barycentric coordinates :79-117 of P)
  */
 enum { SRT_LEAF_POWF = 0, SRT_LEAF_SLAB = 1, SRT_LEAF_TRIANGLE = 2, SRT_LEAF_PHONG = 3, SRT_LEAF_TONE = 4,
-       SRT_LEAF_SMOOTH_NORMAL = 5 };
+       SRT_LEAF_SMOOTH_NORMAL = 5, SRT_LEAF_TRIANGLE_FILTERED = 6 };
 int  srt_eval_leaf(srt_context* ctx, int op, const float* in, float* out, size_t n);
 
 #ifdef __cplusplus

@@ -432,9 +432,9 @@ class MultiGpu:
             pass
 
 
-LEAF_POWF, LEAF_SLAB, LEAF_TRIANGLE, LEAF_PHONG, LEAF_TONE, LEAF_SMOOTH_NORMAL = range(6)
+LEAF_POWF, LEAF_SLAB, LEAF_TRIANGLE, LEAF_PHONG, LEAF_TONE, LEAF_SMOOTH_NORMAL, LEAF_TRIANGLE_FILTERED = range(7)
 _LEAF_WIDTHS = {LEAF_POWF: (2, 1), LEAF_SLAB: (12, 3), LEAF_TRIANGLE: (15, 1), LEAF_PHONG: (19, 3), LEAF_TONE: (3, 1),
-                LEAF_SMOOTH_NORMAL: (21, 3)}
+                LEAF_SMOOTH_NORMAL: (21, 3), LEAF_TRIANGLE_FILTERED: (15, 3)}
 
 
 def eval_leaf(ctx: "Context", op: int, cases) -> np.ndarray:

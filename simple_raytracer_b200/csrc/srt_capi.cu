@@ -377,6 +377,7 @@ int fill_scene(srt_context* c, srt_scene* s, const srt_scene_desc* d, bool fresh
                                                 d->n_objects, (float4*)s->wide.p, (uint32_t*)s->root_ref.p, c->stream);
         if (e != cudaSuccess) return fail(SRT_ERR_CUDA, "build_wide launch: %s", cudaGetErrorString(e));
     }
+    s->swide_octant = -1;                          // derived from `wide`: rebuilt by the next render that wants it
     // Textures.  desc->textures == NULL on an update keeps the resident table (the count must match).  Otherwise every
     // slot is compared with what the scene holds — host pointer, size and a sampled fingerprint of the texels — and only
     // the slots that differ are uploaded again.  (The table used to be kept whenever the COUNT matched, while the
@@ -441,7 +442,7 @@ void srt_scene_destroy(srt_scene* s) {
     if (!s) return;
     if (s->ctx) { cudaSetDevice(s->ctx->device); cudaStreamSynchronize(s->ctx->stream); }
     s->nodes.release(); s->geom.release(); s->attr.release(); s->flat_geom.release(); s->flat_attr.release();
-    s->objects.release(); s->texdesc.release(); s->wide.release(); s->root_ref.release();
+    s->objects.release(); s->texdesc.release(); s->wide.release(); s->root_ref.release(); s->swide.release();
     s->vnormal.release(); s->flat_vnormal.release();
     for (auto& t : s->tex) t.release();
     srti_prep_state_destroy(s->prep);
@@ -568,6 +569,8 @@ static int render_impl(srt_context* c, const srt_scene* s, const srt_render_para
         if ((rc = c->tile_order.reserve(n_tiles * 4))) return rc;
         if ((rc = c->shadow_mask.reserve(n_tiles * 4 * (size_t)(p->light_count > 0 ? p->light_count : 1)))) return rc;
         a.wide = (const float4*)s->wide.p;
+        a.swide = s->swide_octant >= 0 ? (const float4*)s->swide.p : nullptr;      // ensure_shadow_wide (srt_render)
+        a.shadow_octant = s->swide_octant >= 0 ? (uint32_t)s->swide_octant : 0u;
         a.root_ref = (const uint32_t*)s->root_ref.p;
         a.hit_t = (float*)c->hit_t.p; a.hit_tri = (int32_t*)c->hit_tri.p;
         a.tile_interest = (uint32_t*)c->tile_interest.p; a.tile_list = (unsigned long long*)c->tile_list.p; a.tile_done = (uint32_t*)c->tile_done.p;
@@ -610,6 +613,28 @@ static int render_impl(srt_context* c, const srt_scene* s, const srt_render_para
     return SRT_OK;
 }
 
+// The shadow pass's fast path wants the scene's nodes with their planes sorted for the octant the shadow rays point into
+// (srt_phased.cu, slab_sorted_pair).  All lights lie far outside the scene (500 units away against an extent of tens), so
+// the octant is that of the first light's position; a warp whose rays disagree takes the general path, so a wrong guess
+// costs time, never a result.  Built on the context's stream before any band forks off; kept until the scene or the
+// octant changes.
+static int ensure_shadow_wide(srt_context* c, const srt_scene* s, const srt_render_params* p) {
+    if (!s->phased_ok || !p->use_bvh || s->n_objects < 2 || p->light_count <= 0 || p->shadow_segment || s->n_nodes == 0) return SRT_OK;
+    if (p->variant != SRT_VARIANT_DEFAULT && p->variant != SRT_VARIANT_FUSED && p->variant != SRT_VARIANT_OVERLAP) return SRT_OK;
+    float L[3 * SRT_MAX_LIGHTS];
+    int rc = srt_light_positions(p, L);
+    if (rc) return rc;
+    const int oct = (L[0] < 0.f ? 1 : 0) | (L[1] < 0.f ? 2 : 0) | (L[2] < 0.f ? 4 : 0);
+    if (s->swide_octant == oct) return SRT_OK;
+    CU(cudaSetDevice(c->device));
+    s->swide_octant = -1;
+    if ((rc = s->swide.reserve(s->n_nodes * 64))) return rc;
+    const cudaError_t e = srtk::launch_build_shadow_wide((const float4*)s->wide.p, (uint32_t)s->n_nodes, (uint32_t)oct, (float4*)s->swide.p, c->stream);
+    if (e != cudaSuccess) return fail(SRT_ERR_CUDA, "build_shadow_wide launch: %s", cudaGetErrorString(e));
+    s->swide_octant = oct;
+    return SRT_OK;
+}
+
 // Frames of the staged pipeline are rendered as TWO row bands on two streams: each band runs classify -> primary ->
 // shadow -> shade on its own counters and scratch, and the device interleaves them — one band's shadow pass fills the
 // SMs the other band's primary pass leaves idle in its tail, and stages with different instruction mixes share the
@@ -622,6 +647,10 @@ int srt_render(srt_context* c, const srt_scene* s, const srt_render_params* p, c
     const bool banded = c->bands == 2 && !c->parent && (p->variant == SRT_VARIANT_DEFAULT || p->variant == SRT_VARIANT_SPLIT) && p->use_bvh &&
                         p->row_block == 0 && p->shard_count <= 1 && s->n_objects > 0 && rb >= 0 && re <= p->height && re - rb >= 128;
     c->last_banded = false;
+    if (s->ctx == c) {                                    // (a scene of another context is rejected by render_impl)
+        const int rcw = ensure_shadow_wide(c, s, p);
+        if (rcw) return rcw;
+    }
     if (!banded) return render_impl(c, s, p, out);
     CU(cudaSetDevice(c->device));
     if (!c->band) {

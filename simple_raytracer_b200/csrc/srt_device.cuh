@@ -119,6 +119,55 @@ SRT_DEV float moller_trumbore(V3 o, V3 d, float4 g0, float4 g1, float4 g2) {
     return t;
 }
 
+// The same function with the three early returns decided WITHOUT the division wherever that is certain: the value
+// returned is moller_trumbore's, bit for bit, but a triangle the ray clearly misses — nearly every candidate — costs no
+// 1/det and no products with it.  det, A = dot(tvec, pvec), B = dot(d, qvec), C = dot(e2, qvec) are the reference's own
+// values.  With s = sign(det), a = s*A, D = |det| the reference computes u = RN(A * RN(1/det)), within (1 +- 2^-23) of a/D:
+//   u < 0   is certain when a < 0 and |a| > D * 2^-80   (the product cannot round to -0);
+//   u > 1   is certain when a > RN(D * (1 + 2^-20))     (u >= (a/D)(1 - 2^-23) > 1);
+//   v < 0   likewise with b = s*B;
+//   RN(u + v) > 1 is certain when a, b >= 0 and RN(a + b) > RN(D * (1 + 2^-19));
+//   t < 0   is certain when c = s*C < 0 and |c| > D * 2^-80.
+// A comparison with NaN / inf is false, i.e. "not certain", and everything not certain takes the reference's own
+// operations (the tail below).  Rays through an edge within ~1e-6 of the triangle's width and real hits reach the tail.
+SRT_DEV float moller_trumbore_filtered(V3 o, V3 d, float4 g0, float4 g1, float4 g2, bool* took_tail = nullptr) {
+    if (took_tail) *took_tail = false;
+    const V3 p0 = v3(g0.x, g0.y, g0.z), e1 = v3(g1.x, g1.y, g1.z), e2 = v3(g2.x, g2.y, g2.z);
+    const V3 pvec = cross3(d, e2);                                    // :54
+    const float det = dot3(e1, pvec);                                 // :55
+    const float D = fabsf(det);
+    if (D < 1e-12f) return -INFINITY;                                 // :57
+    const uint32_t sgn = __float_as_uint(det) & 0x80000000u;
+    const float tiny = D * 8.2718061e-25f;                            // D * 2^-80 (normal: D >= 1e-12)
+    const V3 tvec = v3(sub(o.x, p0.x), sub(o.y, p0.y), sub(o.z, p0.z));   // :62
+    const float A = dot3(tvec, pvec);
+    const float a = __uint_as_float(__float_as_uint(A) ^ sgn);
+    if ((a < 0.0f && -a > tiny) || a > D * 1.00000095367431640625f) return -INFINITY;      // :65, certain
+    const V3 qvec = cross3(tvec, e1);                                 // :66
+    const float B = dot3(d, qvec);
+    const float b = __uint_as_float(__float_as_uint(B) ^ sgn);
+    if ((b < 0.0f && -b > tiny) || (a >= 0.0f && b >= 0.0f && a + b > D * 1.0000019073486328125f)) return -INFINITY;   // :68, certain
+    const float C = dot3(e2, qvec);
+    const float c = __uint_as_float(__float_as_uint(C) ^ sgn);
+    if (c < 0.0f && -c > tiny) return -INFINITY;                      // :73, certain
+    // not certain: the reference's own sequence
+    if (took_tail) *took_tail = true;
+    const float invDet = dvd(1.0f, det);                              // :60
+    const float u = mul(A, invDet);                                   // :64
+    if (u < 0.0f || u > 1.0f) return -INFINITY;                       // :65
+    const float v = mul(B, invDet);                                   // :67
+    if (v < 0.0f || add(u, v) > 1.0f) return -INFINITY;               // :68
+    const float t = mul(C, invDet);                                   // :70
+    if (t < 0.0f) return -INFINITY;                                   // :73
+    return t;
+}
+
+SRT_DEV bool moller_trumbore_took_tail(V3 o, V3 d, float4 g0, float4 g1, float4 g2) {      // test hook (srt_eval_leaf)
+    bool tail;
+    moller_trumbore_filtered(o, d, g0, g1, g2, &tail);
+    return tail;
+}
+
 // calculateBarycentricCoords :79-117 (v0 = e1, v1 = e2); returns (u, v, w).
 SRT_DEV V3 barycentric(V3 p0, V3 e1, V3 e2, V3 P) {
     const V3 v2 = v3(sub(P.x, p0.x), sub(P.y, p0.y), sub(P.z, p0.z));

@@ -84,6 +84,10 @@ struct srt_scene {
     srti::DevBuf vnormal, flat_vnormal;           // optional vertex normals (smooth_normals)
     bool has_vnormal = false, has_flat_vnormal = false;
     srti::DevBuf wide, root_ref;                        // device-internal traversal layout (srt_phased.cu)
+    // `wide` with plane pairs sorted near-first for one direction octant (the shadow pass's fast path).  Derived data: built on
+    // the owning context's stream by srt_render when the scene's contents or the light's octant changed (-1: stale).
+    mutable srti::DevBuf swide;
+    mutable int swide_octant = -1;
     bool phased_ok = false;                       // leaf sizes / index ranges fit the packed traversal refs
     float coord_bound = 0.f;                      // max |coordinate| over the root boxes
     std::vector<srti::DevBuf> tex;

@@ -52,6 +52,8 @@ struct KArgs {
     // ---- phased kernel only (device-internal data built at upload, scratch owned by the context) ----
     const float4* wide;         // per interior node i: the two child boxes + child refs, 4 x float4 at wide[4*i]
     const uint32_t* root_ref;   // per object: traversal ref of its root
+    const float4* swide;        // `wide` with every box's planes sorted near / far for rays of octant `shadow_octant` (or null)
+    uint32_t shadow_octant;     // bit k: the shadow rays' direction component k is negative (all lights lie far outside the scene)
     float* hit_t;               // [height][width] scratch: closest-hit parameter
     int32_t* hit_tri;           // [height][width] scratch: closest-hit triangle (leaf order) or -1
     uint32_t* tile_interest;    // [tiles] lanes whose shadow rays can reach another object's root box
@@ -87,6 +89,8 @@ constexpr uint32_t kLeafMaxCount = 15, kLeafFirstBits = 27;
 // Builds wide[] / root_ref[] from nodes[] / objects[] on the device (after every scene upload).
 cudaError_t launch_build_wide(const float4* nodes, const srt_object* objects, uint32_t n_nodes, uint32_t n_objects,
                               float4* wide, uint32_t* root_ref, cudaStream_t stream);
+// swide[] from wide[] for one ray-direction octant (the shadow pass's fast path; rebuilt when the scene or the octant changes).
+cudaError_t launch_build_shadow_wide(const float4* wide, uint32_t n_nodes, uint32_t octant, float4* swide, cudaStream_t stream);
 // Shared memory the phased kernel needs per CTA for `stack_cap`, and whether it fits.
 int phased_stack_cap(int max_depth, int n_objects);   // stack of interior nodes + room for the leaf list
 size_t phased_smem_bytes(int stack_cap);

@@ -453,6 +453,7 @@ int srt_scene_prep(srt_context* c, const srt_prep_object* objs, uint32_t n_objec
     s->n_nodes = n_nodes; s->n_tris = n_tris; s->n_flat = n_flat; s->n_objects = n_objects;
     s->max_depth = max_depth;
     s->phased_ok = n_objects > 0;                                  // leaves hold at most 8 triangles by construction
+    s->swide_octant = -1;                                          // derived from `wide`: the next render rebuilds it
     s->has_vnormal = N > 0; s->has_flat_vnormal = n_flat > 0;      // (zeros for a mesh uploaded without normals)
     s->coord_bound = 0.f;
     s->coord_bound_dev = a.coord_bound;

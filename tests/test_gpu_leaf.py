@@ -67,6 +67,47 @@ def test_moller_trumbore_equals_reference(gpu_ctx, kat):
     assert same_bits(got, kat["t"]).all()
 
 
+def test_filtered_moller_trumbore_is_the_plain_function(gpu_ctx, kat):
+    """moller_trumbore_filtered (the shadow pass: clear misses decided without 1/det) returns the bits of the plain
+    function: on the reference's known-answer vectors, and on 600 k rays aimed AT the edges and vertices of their triangle
+    (exactly, and displaced by a few ulp to 1e-3 of its size), at primary-ray and shadow-ray scales, both windings,
+    including degenerate and tiny triangles.  Both outcomes of the filter must have been exercised."""
+    p0, e1, e2 = tri_edges(kat["tri"])
+    got = capi.eval_leaf(gpu_ctx, capi.LEAF_TRIANGLE_FILTERED, np.hstack([kat["o"], kat["d"], p0, e1, e2]))
+    assert same_bits(got[:, 0], kat["t"]).all() and same_bits(got[:, 1], kat["t"]).all()
+    rng = np.random.default_rng(77)
+    n = 600_000
+    scale = 10.0 ** rng.uniform(-3, 2.5, (n, 1))
+    c = rng.normal(0, 60, (n, 3)) + np.array([0, 0, 200.0])
+    P = c[:, None, :] + rng.normal(0, 1, (n, 3, 3)) * scale[:, None, :]
+    flat = rng.random(n) < 0.03
+    P[flat, 2] = P[flat, 0] + (P[flat, 1] - P[flat, 0]) * rng.random((int(flat.sum()), 1))        # collinear: det ~ 0
+    swap = rng.random(n) < 0.5
+    P[swap, 1], P[swap, 2] = P[swap, 2].copy(), P[swap, 1].copy()
+    w = rng.random((n, 3))
+    kind = rng.integers(0, 4, n)
+    w[kind == 0, 2] = 0.0                                                # on the edge p0-p1
+    w[kind == 1, 0] = 0.0                                                # on the edge p1-p2 (u + v = 1)
+    w[kind == 2] = np.eye(3)[rng.integers(0, 3, int((kind == 2).sum()))]   # a vertex
+    w /= w.sum(axis=1, keepdims=True)                                    # kind 3: interior
+    target = (w[:, :, None] * P).sum(axis=1)
+    o = np.where(rng.random((n, 1)) < 0.5, 0.0, rng.normal(0, 80, (n, 3)))
+    d = target - o
+    eps = 10.0 ** rng.uniform(-8, -3, (n, 1)) * (rng.random((n, 1)) < 0.7)
+    d = d + rng.normal(0, 1, (n, 3)) * eps * np.linalg.norm(d, axis=1, keepdims=True)
+    behind = rng.random(n) < 0.1
+    d[behind] = -d[behind]                                               # t < 0
+    P32 = P.astype(f32)
+    x = np.hstack([o.astype(f32), d.astype(f32), P32[:, 0], P32[:, 1] - P32[:, 0], P32[:, 2] - P32[:, 0]])
+    got = capi.eval_leaf(gpu_ctx, capi.LEAF_TRIANGLE_FILTERED, x)
+    assert same_bits(got[:, 0], got[:, 1]).all()
+    hit = np.isfinite(got[:, 1])
+    tail = got[:, 2] != 0
+    assert hit.mean() > 0.15 and (~hit).mean() > 0.3
+    assert (tail | ~hit).all()                                           # every hit went through the reference's operations
+    assert (~tail & ~hit).mean() > 0.25 and (tail & ~hit).sum() > 1000   # clear misses skipped them, close calls did not
+
+
 def test_phong_equals_reference(gpu_ctx, kat):
     """phongIllumination :144-200: every operation is IEEE-defined except powf (glibc's is not correctly rounded:
     about 1e-3 of its results are one ulp off), so: bit-identical on >= 99 % of the vectors, one float ulp elsewhere."""
