@@ -184,7 +184,6 @@ enum { SRT_VARIANT_DEFAULT = 0,   /* staged pipeline: classify, primary, shadow,
                                      SIMPLE for the legacy one-box path */
        SRT_VARIANT_SIMPLE = 1,    /* one thread = one pixel, whole pixel per work item */
        SRT_VARIANT_FUSED = 2,     /* the stages fused into one persistent dataflow kernel */
-       SRT_VARIANT_SPLIT = 3,     /* = DEFAULT (kept for callers that ask for per-stage launches explicitly) */
        SRT_VARIANT_OVERLAP = 4,   /* DEFAULT with the shadow pass overlapping the primary pass's tail (programmatic
                                      dependent launch, passes ordered by published tile entries) */
        SRT_VARIANT_COUNT = 100,   /* SIMPLE + node / triangle counters */

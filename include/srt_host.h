@@ -50,8 +50,8 @@ int  srt_host_set_texture(srt_host_scene* s, const char* name, const uint8_t* rg
 int  srt_host_triangle_textures(srt_host_scene* s, const char* name, int32_t* slot_out, char* names_buf, int buflen);
 int  srt_host_texture_data(srt_host_scene* s, const char* texture_name, const uint8_t** rgb, int* width, int* height);
 /* A texture file to the RGB8 pixels stbi_load(path, &w, &h, &ch, 3) (Object.cpp:57) returns: PNG / JPEG through this
- * library's own decoders, other formats through a `.rgb8` sidecar; use_sidecar = 0 turns that fallback off (own
- * decoders or failure).  out == NULL: sizes only.  0, -1 (cannot decode) or -2 (cap too small). */
+ * library's own decoders; other formats are not decoded (use_sidecar is ignored — the pre-decoded sidecar fallback of
+ * round 1 is gone, the product opens nothing the reference's code produced).  out == NULL: sizes only.  0, -1 (cannot decode) or -2 (cap too small). */
 int  srt_host_decode_image(const char* path, int use_sidecar, uint8_t* out, size_t cap, int* width, int* height);
 /* Iteration order of ObjectManager::objTriangles for keys inserted in the given sequence (the object order of
  * simple_raytracer.cpp:409 / :322): order_out[k] = index into names of the k-th key visited; duplicates count once. */

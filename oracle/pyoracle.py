@@ -24,7 +24,7 @@ from simple_raytracer_b200 import _abi  # noqa: E402
 
 ORACLE_SO = HERE / "liboracle.so"
 REF_SO = HERE / "_ref" / "libsrt_ref.so"
-ASSETS = HERE / "_ref" / "assets"
+ASSETS = HERE.parent / "assets"        # staged reference DATA (tools/stage_assets.py); shared with the product's host mirror
 
 _f32p = C.POINTER(C.c_float)
 

@@ -499,7 +499,7 @@ int ref_chdir(const char* dir) { return chdir(dir); }
 }  // extern "C"
 
 // Decode an image file with the reference's own stb_image (compiled into Object.o): used by
-// oracle/stage_assets.py to write the `.rgb8` sidecars the product's host mirror reads.
+// the decoder tests (tests/test_host_scene.py) as the expected pixels.
 extern "C" unsigned char* stbi_load(char const* filename, int* x, int* y, int* channels_in_file, int desired_channels);
 extern "C" void stbi_image_free(void* p);
 extern "C" int ref_decode_texture(const char* path, unsigned char* out, int cap, int* w, int* h) {

@@ -28,7 +28,6 @@ TEX_TRUNCATE, TEX_NEAREST, TEX_BILINEAR = 0, 1, 2     # srt_render_params::textu
 VARIANT_DEFAULT = 0
 VARIANT_SIMPLE = 1
 VARIANT_FUSED = 2
-VARIANT_SPLIT = 3
 VARIANT_OVERLAP = 4
 VARIANT_COUNT = 100
 VARIANT_TIMELINE = 101

@@ -4,12 +4,8 @@
 // PNG and JPEG files — the two formats the reference's assets use — are decoded by this repository's own decoders
 // (srt_png.cpp, srt_jpeg.cpp), which restate the format rules and stb_image's conversions so that the pixels are
 // the ones the reference renders with (JPEG decoders differ in their IDCT / upsampling / colour conversion, so "some
-// other decoder" would not do).  Any other format, or a file variant those decoders do not cover, falls back to a
-// pre-decoded sidecar `<texture path>.rgb8` (oracle/stage_assets.py writes one next to every texture when it stages
-// the reference's data, decoded with the reference's own stb_image through oracle/_ref).
-// Sidecar layout: 4 bytes "SRT8", int32 width, int32 height (little endian), then
-// height*width*3 bytes RGB, rows top-down — exactly the buffer stbi_load(..., 3) returns.
-// When neither works the function returns nullptr, which loadObjFile reports the way the reference
+// other decoder" would not do).  Any other format, or a file variant those decoders do not cover, is not decoded: the
+// function returns nullptr, which loadObjFile reports the way the reference
 // reports a failed stbi_load (Object.cpp:63-65: message, continue); a scene that then references
 // the texture is rejected by the flattener (SRT_ERR_SCENE) instead of crashing.
 // Callers that already hold decoded RGB8 pixels can install ObjectManager::textureDecoder.
@@ -50,32 +46,11 @@ unsigned char* decode_known_format(const char* path, int* width, int* height) {
 
 unsigned char* decode_image_rgb8(const char* path, int* width, int* height) { return decode_image_file(path, width, height, true); }
 
-unsigned char* decode_image_file(const char* path, int* width, int* height, bool use_sidecar) {
+unsigned char* decode_image_file(const char* path, int* width, int* height, bool /*unused: no sidecar fallback any more*/) {
     if (width) *width = 0;
     if (height) *height = 0;
     if (!path) return nullptr;
-    if (unsigned char* own = decode_known_format(path, width, height)) return own;
-    if (!use_sidecar) return nullptr;
-    const std::string side = std::string(path) + ".rgb8";
-    FILE* f = std::fopen(side.c_str(), "rb");
-    if (!f) return nullptr;
-    unsigned char hdr[12];
-    int32_t w = 0, h = 0;
-    unsigned char* data = nullptr;
-    if (std::fread(hdr, 1, 12, f) == 12 && std::memcmp(hdr, "SRT8", 4) == 0) {
-        std::memcpy(&w, hdr + 4, 4);
-        std::memcpy(&h, hdr + 8, 4);
-        if (w > 0 && h > 0 && (int64_t)w * h <= (int64_t)1 << 28) {
-            const size_t n = (size_t)w * h * 3;
-            data = (unsigned char*)std::malloc(n);
-            if (data && std::fread(data, 1, n, f) != n) { std::free(data); data = nullptr; }
-        }
-    }
-    std::fclose(f);
-    if (!data) return nullptr;
-    if (width) *width = w;
-    if (height) *height = h;
-    return data;
+    return decode_known_format(path, width, height);
 }
 
 // drawImage(..., saveImage = true) (simple_raytracer.cpp:461-498) writes the frame with CImg<unsigned char>::save_bmp.

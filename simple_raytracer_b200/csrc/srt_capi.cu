@@ -552,7 +552,7 @@ static int render_impl(srt_context* c, const srt_scene* s, const srt_render_para
     a.stack_cap = srtk::phased_stack_cap((int)s->max_depth, (int)s->n_objects);
     const bool tl = p->variant == 102 || p->variant == 103 || p->variant == 104;   // debug: per-tile cost map of the primary stage / per-warp timestamps
     a.debug_timeline = p->variant == 102 ? 1 : (p->variant == 103 ? 2 : (p->variant == 104 ? 3 : 0));
-    const bool want_phased = (p->variant == SRT_VARIANT_DEFAULT || p->variant == SRT_VARIANT_FUSED || p->variant == SRT_VARIANT_SPLIT || p->variant == SRT_VARIANT_OVERLAP || tl) && p->use_bvh &&
+    const bool want_phased = (p->variant == SRT_VARIANT_DEFAULT || p->variant == SRT_VARIANT_FUSED || p->variant == SRT_VARIANT_OVERLAP || tl) && p->use_bvh &&
                              s->phased_ok && srtk::phased_smem_bytes(a.stack_cap) <= 96 * 1024;
     cudaError_t e;
     if (want_phased) {
@@ -644,7 +644,7 @@ int srt_render(srt_context* c, const srt_scene* s, const srt_render_params* p, c
     if (!c || !s || !p || !out) return fail(SRT_ERR_INVALID_ARG, "NULL argument");
     int rb = p->row_begin, re = p->row_end;
     if (rb == 0 && re == 0) re = p->height;
-    const bool banded = c->bands == 2 && !c->parent && (p->variant == SRT_VARIANT_DEFAULT || p->variant == SRT_VARIANT_SPLIT) && p->use_bvh &&
+    const bool banded = c->bands == 2 && !c->parent && p->variant == SRT_VARIANT_DEFAULT && p->use_bvh &&
                         p->row_block == 0 && p->shard_count <= 1 && s->n_objects > 0 && rb >= 0 && re <= p->height && re - rb >= 128;
     c->last_banded = false;
     if (s->ctx == c) {                                    // (a scene of another context is rejected by render_impl)

@@ -94,7 +94,7 @@ cudaError_t launch_build_shadow_wide(const float4* wide, uint32_t n_nodes, uint3
 // Shared memory the phased kernel needs per CTA for `stack_cap`, and whether it fits.
 int phased_stack_cap(int max_depth, int n_objects);   // stack of interior nodes + room for the leaf list
 size_t phased_smem_bytes(int stack_cap);
-// Single cooperative launch (variant SRT_VARIANT_DEFAULT) or three launches (SRT_VARIANT_SPLIT).
+// (launch_render_phased: the staged pipeline, its overlap variant, or the fused dataflow kernel.)
 // Sparse (ImageData-style) output of a rendered RGB8 frame: srt_render_sparse.  seg_counts: sparse_segments() words.
 size_t sparse_segments(int width, int rows);
 cudaError_t launch_sparse_compact(const uint8_t* rgb, int width, int row_begin, int row_end, uint32_t* seg_counts, float* points,

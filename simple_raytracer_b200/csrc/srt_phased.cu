@@ -27,6 +27,8 @@
 // and for every ray with a zero / denormal / non-finite direction component — the exact test is run.
 // The set of leaves visited is therefore exactly the reference's (S3/S5), only cheaper.
 // Closest hit uses the order-independent rule min over (t, visit index) (S6), so traversal order is free.
+#include <mutex>
+
 #include "srt_kernels.cuh"
 #include "srt_device.cuh"
 #include "srt_shade.cuh"
@@ -969,27 +971,33 @@ cudaError_t launch_render_phased(const KArgs& a, int variant, int sm_count, cuda
     if (n_tiles <= 0) return cudaSuccess;
     const size_t smem = phased_smem_bytes(a.stack_cap);
     const size_t smem_s = phased_smem_bytes(a.stack_cap - kLeafRoom);   // the shadow pass keeps its leaves in registers
-    static bool attr_set = false;
-    if (!attr_set) {
-        cudaFuncSetAttribute(render_dataflow<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024);
-        cudaFuncSetAttribute(render_dataflow<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024);
-        cudaFuncSetAttribute(render_dataflow<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024);
-        cudaFuncSetAttribute(render_phase<0, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024);
-        cudaFuncSetAttribute(render_phase<1, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024);
-        cudaFuncSetAttribute(render_phase<0, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024);
-        cudaFuncSetAttribute(render_phase<1, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024);
-        attr_set = true;
+    // The opt-in to more than 48 KB of dynamic shared memory is a per-DEVICE attribute of each kernel: once per device.
+    {
+        static std::mutex attr_mutex;
+        static bool attr_set[64] = {};
+        int dev = 0;
+        cudaError_t ea = cudaGetDevice(&dev);
+        if (ea != cudaSuccess) return ea;
+        std::lock_guard<std::mutex> lock(attr_mutex);
+        if (dev < 0 || dev >= 64 || !attr_set[dev]) {
+            const void* kernels[] = {(const void*)render_dataflow<false, false>, (const void*)render_dataflow<true, false>,
+                                     (const void*)render_dataflow<false, true>, (const void*)render_phase<0, false>,
+                                     (const void*)render_phase<1, false>, (const void*)render_phase<0, true>, (const void*)render_phase<1, true>};
+            for (const void* k : kernels)
+                if ((ea = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024)) != cudaSuccess) return ea;
+            if (dev >= 0 && dev < 64) attr_set[dev] = true;
+        }
     }
     int cblocks = (n_tiles + kThreads - 1) / kThreads;
     if (cblocks > sm_count * 8) cblocks = sm_count * 8;
     // stage_ev (srt_context_set_stage_timing): five events around the four passes of the default pipeline
-    const bool timed = stage_ev && (variant == SRT_VARIANT_DEFAULT || variant == SRT_VARIANT_SPLIT);
+    const bool timed = stage_ev && (variant == SRT_VARIANT_DEFAULT);
     if (timed) cudaEventRecord(stage_ev[0], stream);
     classify_kernel<<<cblocks, kThreads, 0, stream>>>(a);
     if (timed) cudaEventRecord(stage_ev[1], stream);
     cudaError_t e;
     const bool shadows = a.n_objects >= 2 && a.light_count > 0;
-    if (variant == SRT_VARIANT_DEFAULT || variant == SRT_VARIANT_SPLIT || variant == SRT_VARIANT_OVERLAP) {
+    if (variant == SRT_VARIANT_DEFAULT || variant == SRT_VARIANT_OVERLAP) {
         const bool overlap = variant == SRT_VARIANT_OVERLAP;
         int bp = 0, bs = 0, bc = 0;
         if ((e = persistent_blocks(render_phase<0, false>, smem, sm_count, n_tiles, &bp)) != cudaSuccess) return e;

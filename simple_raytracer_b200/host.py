@@ -20,7 +20,7 @@ _f32p = C.POINTER(C.c_float)
 
 # Mesh / texture data staged by __graft_entry__.build() from the reference checkout (data, not
 # source; git-ignored).  Override with SRT_ASSETS.
-DEFAULT_ASSETS = Path(__file__).resolve().parent.parent / "oracle" / "_ref" / "assets"
+DEFAULT_ASSETS = Path(__file__).resolve().parent.parent / "assets"
 
 
 def assets_dir() -> Path:
@@ -316,9 +316,9 @@ def write_image(path, rgb: np.ndarray):
     (write_png if str(path).lower().endswith(".png") else write_bmp)(path, rgb)
 
 
-def decode_image(path, use_sidecar: bool = True) -> np.ndarray:
+def decode_image(path, use_sidecar: bool = False) -> np.ndarray:
     """A texture file as the [H, W, 3] uint8 pixels stbi_load(path, ..., 3) returns (Object.cpp:57): PNG / JPEG through the
-    library's own decoders; other formats through a `.rgb8` sidecar unless use_sidecar is False."""
+    library's own decoders; other formats fail (use_sidecar is ignored: the sidecar fallback of round 1 is gone)."""
     w, h = C.c_int32(0), C.c_int32(0)
     if _lib().srt_host_decode_image(str(path).encode(), int(use_sidecar), None, 0, C.byref(w), C.byref(h)) != 0:
         raise ValueError(f"cannot decode {path}")
