@@ -617,11 +617,50 @@ def run_b200_arm(args):
         entries = sum(imagedata_step(Wm + s) for s in range(K))
         torch.cuda.synchronize()
         ms = 1e3 * (time.perf_counter() - t_a) / K
-        imagedata = {"ms_per_frame": ms, "frames_per_s": 1e3 / ms, "entries_per_frame": entries / K,
-                     "d2h_bytes_per_frame": 20 * entries / K,
-                     "what": "rank 0: srt_scene_update + srt_render_sparse (render, device-side compaction into the reference's "
-                             "ImageData layout, simple_raytracer.cpp:505-525) + srt_fetch_sparse into pinned host memory; synchronous "
-                             "calls, host wall clock"}
+        # the same lists with two frames in flight: two contexts take frames in turn; while the host waits for one lane's
+        # lists (27 MB per frame over PCIe), the other lane renders (srt_render_sparse_begin / _count / srt_fetch_sparse)
+        ctx_c = capi.Context(local)
+        il = [dict(ctx=ctx, scene=sc2, pts=pts, col=col, busy=False),
+              dict(ctx=ctx_c, scene=ctx_c.upload(pinned[0][0]), pts=capi.PinnedArray((W * H, 2), np.float32),
+                   col=capi.PinnedArray((W * H, 3), np.float32), busy=False)]
+
+        def retire(ln):
+            if not ln["busy"]:
+                return 0
+            capi._check(capi.lib().srt_render_sparse_count(ln["ctx"].h, capi.C.byref(n_out)))
+            capi._check(capi.lib().srt_fetch_sparse(ln["ctx"].h, ln["pts"].array.ctypes.data_as(fp), ln["col"].array.ctypes.data_as(fp), n_out.value))
+            ln["busy"] = False
+            return n_out.value
+
+        def piped_step(s):
+            k = s % n_unique
+            ln = il[s % 2]
+            got = retire(ln)
+            ln["scene"].update(pinned[k][0])
+            capi._check(capi.lib().srt_render_sparse_begin(ln["ctx"].h, ln["scene"].h, capi.C.byref(params[k])))
+            ln["busy"] = True
+            return got
+
+        for s in range(Wm):
+            piped_step(s)
+        for ln in il:
+            retire(ln)
+        torch.cuda.synchronize()
+        t_b = time.perf_counter()
+        entries_p = sum(piped_step(Wm + s) for s in range(K)) + sum(retire(ln) for ln in il)
+        torch.cuda.synchronize()
+        ms_p = 1e3 * (time.perf_counter() - t_b) / K
+        imagedata = {"ms_per_frame": ms_p, "frames_per_s": 1e3 / ms_p, "Mrays_per_s": rays_local / K / ms_p / 1e3,
+                     "entries_per_frame": entries_p / K, "d2h_bytes_per_frame": 20 * entries_p / K,
+                     "h2d_bytes_per_frame": int(sum(getattr(pinned[0][0], n).nbytes for n in ("nodes", "geom", "attr", "objects"))),
+                     "synchronous": {"ms_per_frame": ms, "frames_per_s": 1e3 / ms, "entries_per_frame": entries / K},
+                     "what": "rank 0, the reference's own return type end to end: per frame srt_scene_update from pinned host arrays + render + "
+                             "device-side compaction into the ImageData layout (simple_raytracer.cpp:505-525: non-black pixels, column-major, "
+                             "floats) + download of both lists into pinned host memory; two contexts take frames in turn "
+                             "(srt_render_sparse_begin / _count / srt_fetch_sparse), host wall clock over the K frames; `synchronous` = one "
+                             "context, one blocking srt_render_sparse + srt_fetch_sparse per frame (what srt_dropin.hpp's single call does)"}
+        il[1]["scene"].destroy(); il[1]["pts"].free(); il[1]["col"].free()
+        ctx_c.destroy()
         sc2.destroy()
         pts.free(); col.free()
 

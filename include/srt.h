@@ -313,6 +313,12 @@ int  srt_last_stage_ms(srt_context* ctx, float* ms4);
  * srt_render_sparse synchronises and returns the number of entries; srt_fetch_sparse copies up to `capacity`
  * entries to host or device arrays (points_xy[2*i], colors_rgb[3*i]; either may be NULL). */
 int  srt_render_sparse(srt_context* ctx, const srt_scene* scene, const srt_render_params* params, uint64_t* count);
+/* The same in two steps, for callers that keep several frames in flight (two contexts alternating: one renders while the
+ * other's lists travel to the host): _begin enqueues render + compaction + the count's download and returns at once;
+ * _count waits for that count alone.  srt_render_sparse = _begin + _count.  srt_fetch_sparse (which waits for a
+ * pending count itself) then copies the lists. */
+int  srt_render_sparse_begin(srt_context* ctx, const srt_scene* scene, const srt_render_params* params);
+int  srt_render_sparse_count(srt_context* ctx, uint64_t* count);
 int  srt_fetch_sparse(srt_context* ctx, float* points_xy, float* colors_rgb, uint64_t capacity);
 
 /* ---- the same compaction for callers that must not allocate ----

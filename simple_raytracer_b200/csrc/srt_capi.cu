@@ -681,12 +681,14 @@ int srt_render(srt_context* c, const srt_scene* s, const srt_render_params* p, c
     return SRT_OK;
 }
 
-int srt_render_sparse(srt_context* c, const srt_scene* s, const srt_render_params* p, uint64_t* count) {
-    if (!c || !s || !p || !count) return fail(SRT_ERR_INVALID_ARG, "NULL argument");
+// Render + device-side compaction + the count on its way to pinned host memory, all asynchronous on the context stream.
+int srt_render_sparse_begin(srt_context* c, const srt_scene* s, const srt_render_params* p) {
+    if (!c || !s || !p) return fail(SRT_ERR_INVALID_ARG, "NULL argument");
     if (p->row_block != 0 || p->shard_count > 1)
         return fail(SRT_ERR_INVALID_ARG, "srt_render_sparse: interleaved row sharding is not supported (use row_begin / row_end)");
     if (p->width <= 0 || p->height <= 0) return fail(SRT_ERR_INVALID_ARG, "bad image size %dx%d", p->width, p->height);
     CU(cudaSetDevice(c->device));
+    c->have_sparse = false;
     const size_t npix = (size_t)p->width * p->height;
     int rc;
     if ((rc = c->sparse_rgb.reserve(npix * 3))) return rc;
@@ -707,15 +709,35 @@ int srt_render_sparse(srt_context* c, const srt_scene* s, const srt_render_param
                                                 (unsigned long long*)c->sparse_total.p, c->stream);
     if (e != cudaSuccess) return fail(SRT_ERR_CUDA, "sparse compaction launch: %s", cudaGetErrorString(e));
     CU(cudaMemcpyAsync(c->sparse_total_host, c->sparse_total.p, sizeof(unsigned long long), cudaMemcpyDeviceToHost, c->stream));
-    CU(cudaStreamSynchronize(c->stream));
-    c->sparse_count = *c->sparse_total_host;
-    c->have_sparse = true;
+    CU(cudaEventRecord(c->ev_copy, c->stream));
+    c->sparse_pending = true;
+    return SRT_OK;
+}
+
+// Waits for the count of the pending srt_render_sparse_begin (its event — later work on the stream is not waited for).
+int srt_render_sparse_count(srt_context* c, uint64_t* count) {
+    if (!c || !count) return fail(SRT_ERR_INVALID_ARG, "NULL argument");
+    if (!c->sparse_pending && !c->have_sparse) return fail(SRT_ERR_INVALID_ARG, "srt_render_sparse_count: no srt_render_sparse_begin has been issued on this context");
+    CU(cudaSetDevice(c->device));
+    if (c->sparse_pending) {
+        CU(cudaEventSynchronize(c->ev_copy));
+        c->sparse_count = *c->sparse_total_host;
+        c->sparse_pending = false;
+        c->have_sparse = true;
+    }
     *count = c->sparse_count;
     return SRT_OK;
 }
 
+int srt_render_sparse(srt_context* c, const srt_scene* s, const srt_render_params* p, uint64_t* count) {
+    if (!count) return fail(SRT_ERR_INVALID_ARG, "NULL argument");
+    const int rc = srt_render_sparse_begin(c, s, p);
+    return rc ? rc : srt_render_sparse_count(c, count);
+}
+
 int srt_fetch_sparse(srt_context* c, float* points_xy, float* colors_rgb, uint64_t capacity) {
     if (!c) return fail(SRT_ERR_INVALID_ARG, "NULL context");
+    if (c->sparse_pending) { uint64_t n_ = 0; const int rc_ = srt_render_sparse_count(c, &n_); if (rc_) return rc_; }
     if (!c->have_sparse) return fail(SRT_ERR_INVALID_ARG, "srt_fetch_sparse: no srt_render_sparse has been issued on this context");
     CU(cudaSetDevice(c->device));
     const uint64_t n = c->sparse_count < capacity ? c->sparse_count : capacity;

@@ -60,7 +60,7 @@ struct srt_context {
     srti::DevBuf sparse_rgb, sparse_seg, sparse_points, sparse_colors, sparse_total;   // srt_render_sparse
     unsigned long long* sparse_total_host = nullptr;   // pinned
     uint64_t sparse_count = 0;
-    bool have_sparse = false;
+    bool have_sparse = false, sparse_pending = false;
     int last_launches = 0;
     // last render
     bool have_last = false;

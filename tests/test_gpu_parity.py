@@ -608,3 +608,42 @@ def test_series_and_single_frames_alternate_under_both_band_settings(gpu_ctx):
         solo.destroy()
         host.set_asset_cache(False)
     assert rounds >= 200
+
+
+def test_sparse_begin_count_fetch_pipeline_equals_the_blocking_call(gpu_ctx, ref_scene):
+    """srt_render_sparse_begin / _count / srt_fetch_sparse on two contexts that take frames in turn (how a caller keeps the
+    download of one frame's ImageData lists under the next frame's render): the lists of the blocking srt_render_sparse."""
+    import ctypes as C
+    _b, arrays, light = ref_scene("C3")
+    L = capi.lib()
+    other = capi.Context(0)
+    lanes = [(gpu_ctx, gpu_ctx.upload(arrays)), (other, other.upload(arrays))]
+    sizes = [(160, 90), (97, 33), (320, 180), (64, 70), (200, 120)]
+    want = []
+    for W, H in sizes:
+        want.append(gpu_ctx.render_sparse(lanes[0][1], _abi.default_params(W, H, float(H), light, 3, True)))
+    fp = C.POINTER(C.c_float)
+    got, pending = {}, {}
+    def retire(k):
+        ctx, _sc = lanes[k % 2]
+        n = C.c_uint64(0)
+        capi._check(L.srt_render_sparse_count(ctx.h, C.byref(n)))
+        pts = np.zeros((n.value, 2), np.float32); col = np.zeros((n.value, 3), np.float32)
+        capi._check(L.srt_fetch_sparse(ctx.h, pts.ctypes.data_as(fp), col.ctypes.data_as(fp), n.value))
+        got[k] = (pts, col)
+    for k, (W, H) in enumerate(sizes):
+        ctx, sc = lanes[k % 2]
+        if k >= 2:
+            retire(k - 2)
+        p = _abi.default_params(W, H, float(H), light, 3, True)
+        capi._check(L.srt_render_sparse_begin(ctx.h, sc.h, C.byref(p)))
+    retire(len(sizes) - 2); retire(len(sizes) - 1)
+    for k in range(len(sizes)):
+        assert np.array_equal(got[k][0], want[k][0]) and np.array_equal(got[k][1], want[k][1]), k
+    with pytest.raises(capi.SrtError):
+        fresh = capi.Context(0)
+        try:
+            capi._check(L.srt_render_sparse_count(fresh.h, C.byref(C.c_uint64(0))))
+        finally:
+            fresh.destroy()
+    lanes[0][1].destroy(); lanes[1][1].destroy(); other.destroy()
