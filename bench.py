@@ -628,7 +628,8 @@ def run_b200_arm(args):
             if not ln["busy"]:
                 return 0
             capi._check(capi.lib().srt_render_sparse_count(ln["ctx"].h, capi.C.byref(n_out)))
-            capi._check(capi.lib().srt_fetch_sparse(ln["ctx"].h, ln["pts"].array.ctypes.data_as(fp), ln["col"].array.ctypes.data_as(fp), n_out.value))
+            # (a consumer reads the lane's previous lists HERE: the count's return means the copies enqueued before this frame are done)
+            capi._check(capi.lib().srt_fetch_sparse_async(ln["ctx"].h, ln["pts"].array.ctypes.data_as(fp), ln["col"].array.ctypes.data_as(fp), n_out.value))
             ln["busy"] = False
             return n_out.value
 
@@ -657,7 +658,7 @@ def run_b200_arm(args):
                      "what": "rank 0, the reference's own return type end to end: per frame srt_scene_update from pinned host arrays + render + "
                              "device-side compaction into the ImageData layout (simple_raytracer.cpp:505-525: non-black pixels, column-major, "
                              "floats) + download of both lists into pinned host memory; two contexts take frames in turn "
-                             "(srt_render_sparse_begin / _count / srt_fetch_sparse), host wall clock over the K frames; `synchronous` = one "
+                             "(srt_render_sparse_begin / _count / srt_fetch_sparse_async: nothing blocks the host but the wait for a frame's count), host wall clock over the K frames incl. the final sync; `synchronous` = one "
                              "context, one blocking srt_render_sparse + srt_fetch_sparse per frame (what srt_dropin.hpp's single call does)"}
         il[1]["scene"].destroy(); il[1]["pts"].free(); il[1]["col"].free()
         ctx_c.destroy()

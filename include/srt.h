@@ -225,7 +225,8 @@ int  srt_context_set_stream(srt_context* ctx, void* cuda_stream);
  * streams so that their stages overlap (-11 % time per frame; the same bytes, pixels are independent :511-523) — what a
  * caller that renders ONE frame at a time wants; 1 renders a frame in one piece, for callers that already keep several
  * frames in flight on several contexts (an image series gains nothing from a second band; the series driver sets 1 on
- * its lanes).  Frames of fewer than 128 rows, sharded frames and the other kernel variants are always one piece.
+ * its lanes).  3 and 4 are accepted (bands of at least 64 rows) and measured no better than 2 (profiles/).  Frames of
+ * fewer than 128 rows, sharded frames and the other kernel variants are always one piece.
  * Returns the previous value, or a negative srt_status. */
 int  srt_context_set_bands(srt_context* ctx, int bands);
 int  srt_context_get_info(srt_context* ctx, int* sm_count, int* cc_major, int* cc_minor,
@@ -319,6 +320,9 @@ int  srt_render_sparse(srt_context* ctx, const srt_scene* scene, const srt_rende
  * pending count itself) then copies the lists. */
 int  srt_render_sparse_begin(srt_context* ctx, const srt_scene* scene, const srt_render_params* params);
 int  srt_render_sparse_count(srt_context* ctx, uint64_t* count);
+/* srt_fetch_sparse without the wait: the copies are enqueued on the context stream (pinned destinations for real
+ * asynchrony) and are complete after srt_sync, or once a LATER srt_render_sparse_count on this context has returned. */
+int  srt_fetch_sparse_async(srt_context* ctx, float* points_xy, float* colors_rgb, uint64_t capacity);
 int  srt_fetch_sparse(srt_context* ctx, float* points_xy, float* colors_rgb, uint64_t capacity);
 
 /* ---- the same compaction for callers that must not allocate ----

@@ -26,7 +26,7 @@ EXPORTS = [
     "srt_mesh_upload", "srt_mesh_destroy", "srt_mesh_info", "srt_scene_prep", "srt_scene_prep_status",
     "srt_scene_counts", "srt_scene_download", "srt_scene_download_vnormals", "srt_measure_read_bandwidth",
     "srt_sparse_from_frame_static",
-    "srt_render_sparse_begin", "srt_render_sparse_count",
+    "srt_render_sparse_begin", "srt_render_sparse_count", "srt_fetch_sparse_async",
     "srt_context_set_stage_timing", "srt_last_stage_ms",
     "srt_mgpu_create", "srt_mgpu_destroy", "srt_mgpu_info", "srt_mgpu_scene_upload", "srt_mgpu_render_frame",
     "srt_mgpu_render_series", "srt_mgpu_sync", "srt_mgpu_last_stats",
@@ -73,6 +73,7 @@ def lib():
         L.srt_render_sparse.argtypes = [vp, vp, C.POINTER(_abi.RenderParams), C.POINTER(C.c_uint64)]
         L.srt_render_sparse_begin.argtypes = [vp, vp, C.POINTER(_abi.RenderParams)]
         L.srt_render_sparse_count.argtypes = [vp, C.POINTER(C.c_uint64)]
+        L.srt_fetch_sparse_async.argtypes = [vp, C.POINTER(C.c_float), C.POINTER(C.c_float), C.c_uint64]
         L.srt_fetch_sparse.argtypes = [vp, C.POINTER(C.c_float), C.POINTER(C.c_float), C.c_uint64]
         L.srt_sparse_from_frame_static.argtypes = [vp, vp, C.c_int32, C.c_int32, C.c_int32, C.c_int32, vp, vp, vp]
         L.srt_context_set_stage_timing.argtypes = [vp, C.c_int]

@@ -78,7 +78,7 @@ int srt_context_create(int device, srt_context** out) {
     srt_context* c = new srt_context();
     // SRT_DEFAULT_BANDS=1|2: A/B switch for the row-band default (srt_context_set_bands overrides it per context)
     static const int env_bands = [] { const char* e = std::getenv("SRT_DEFAULT_BANDS"); return e ? std::atoi(e) : 0; }();
-    if (env_bands == 1 || env_bands == 2) c->bands = env_bands;
+    if (env_bands >= 1 && env_bands <= srt_context::kMaxBands) c->bands = env_bands;
     c->device = device;
     c->sm_count = prop.multiProcessorCount;
     c->cc_major = prop.major; c->cc_minor = prop.minor;
@@ -97,9 +97,9 @@ void srt_context_destroy(srt_context* c) {
     if (!c) return;
     cudaSetDevice(c->device);
     cudaStreamSynchronize(c->stream);
-    if (c->band) { srt_context_destroy(c->band); c->band = nullptr; }
+    for (auto& b : c->band) if (b) { srt_context_destroy(b); b = nullptr; }
     if (c->ev_fork) cudaEventDestroy(c->ev_fork);
-    if (c->ev_join) cudaEventDestroy(c->ev_join);
+    for (auto& e : c->ev_join) if (e) cudaEventDestroy(e);
     c->out_rgb.release(); c->out_obj.release(); c->out_tri.release(); c->out_t.release();
     c->hit_t.release(); c->hit_tri.release(); c->tile_interest.release(); c->tile_list.release(); c->tile_order.release(); c->tile_done.release(); c->shadow_mask.release();
     if (c->counters) cudaFree(c->counters);
@@ -116,7 +116,7 @@ void srt_context_destroy(srt_context* c) {
 
 int srt_context_set_bands(srt_context* c, int bands) {
     if (!c) return fail(SRT_ERR_INVALID_ARG, "ctx is NULL");
-    if (bands != 1 && bands != 2) return fail(SRT_ERR_INVALID_ARG, "bands must be 1 or 2");
+    if (bands < 1 || bands > srt_context::kMaxBands) return fail(SRT_ERR_INVALID_ARG, "bands must be 1 .. %d", srt_context::kMaxBands);
     const int before = c->bands;
     c->bands = bands;
     return before;
@@ -644,44 +644,58 @@ int srt_render(srt_context* c, const srt_scene* s, const srt_render_params* p, c
     if (!c || !s || !p || !out) return fail(SRT_ERR_INVALID_ARG, "NULL argument");
     int rb = p->row_begin, re = p->row_end;
     if (rb == 0 && re == 0) re = p->height;
-    const bool banded = c->bands == 2 && !c->parent && p->variant == SRT_VARIANT_DEFAULT && p->use_bvh &&
+    const bool banded = c->bands >= 2 && !c->parent && p->variant == SRT_VARIANT_DEFAULT && p->use_bvh &&
                         p->row_block == 0 && p->shard_count <= 1 && s->n_objects > 0 && rb >= 0 && re <= p->height && re - rb >= 128;
     c->last_banded = false;
+    c->last_bands = 1;
     if (s->ctx == c) {                                    // (a scene of another context is rejected by render_impl)
         const int rcw = ensure_shadow_wide(c, s, p);
         if (rcw) return rcw;
     }
     if (!banded) return render_impl(c, s, p, out);
     CU(cudaSetDevice(c->device));
-    if (!c->band) {
-        int rc = srt_context_create(c->device, &c->band);
-        if (rc) return rc;
-        c->band->parent = c;
-        CU(cudaEventCreateWithFlags(&c->ev_fork, cudaEventDisableTiming));
-        CU(cudaEventCreateWithFlags(&c->ev_join, cudaEventDisableTiming));
-    }
-    const int cut = rb + ((re - rb) / 2 / 4) * 4;
-    srt_render_params p0 = *p, p1 = *p;
-    p0.row_begin = rb; p0.row_end = cut;
-    p1.row_begin = cut; p1.row_end = re;
-    CU(cudaEventRecord(c->ev_fork, c->stream));                       // the band starts after everything queued so far (scene upload / prep)
-    CU(cudaStreamWaitEvent(c->band->stream, c->ev_fork, 0));
-    int rc = render_impl(c, s, &p0, out);
+    int nb = c->bands;
+    while (nb > 2 && (re - rb) / nb < 64) --nb;           // bands of at least 64 rows
+    for (int k = 0; k + 1 < nb; ++k)
+        if (!c->band[k]) {
+            int rc = srt_context_create(c->device, &c->band[k]);
+            if (rc) return rc;
+            c->band[k]->parent = c;
+            c->band[k]->bands = 1;
+            CU(cudaEventCreateWithFlags(&c->ev_join[k], cudaEventDisableTiming));
+        }
+    if (!c->ev_fork) CU(cudaEventCreateWithFlags(&c->ev_fork, cudaEventDisableTiming));
+    int cut[srt_context::kMaxBands + 1];
+    for (int k = 0; k <= nb; ++k) cut[k] = rb + (int)(((long long)(re - rb) * k / nb) / 4 * 4);
+    cut[nb] = re;
+    CU(cudaEventRecord(c->ev_fork, c->stream));           // the bands start after everything queued so far (scene upload / prep)
+    int rc = SRT_OK;
     std::string first_error;
-    if (rc) first_error = g_err;
-    const int rc1 = rc ? SRT_OK : render_impl(c->band, s, &p1, out);
-    // Join on every path: whatever a failed band did enqueue on the second stream still writes into the caller's planes,
-    // and everything that follows on this stream (the caller's next call, a scene update or destroy) must be ordered after it.
-    const cudaError_t ej = cudaEventRecord(c->ev_join, c->band->stream);
-    const cudaError_t ew = ej == cudaSuccess ? cudaStreamWaitEvent(c->stream, c->ev_join, 0) : ej;
+    int issued = 0;
+    for (int k = 0; k < nb; ++k) {
+        srt_context* bc = k == 0 ? c : c->band[k - 1];
+        if (k > 0) CU(cudaStreamWaitEvent(bc->stream, c->ev_fork, 0));
+        srt_render_params pk = *p;
+        pk.row_begin = cut[k]; pk.row_end = cut[k + 1];
+        if (pk.row_end > pk.row_begin || k == 0) rc = render_impl(bc, s, &pk, out);
+        issued = k + 1;
+        if (rc) { first_error = g_err; break; }
+    }
+    // Join on every path: whatever a band did enqueue on its stream still writes into the caller's planes, and everything
+    // that follows on this stream (the caller's next call, a scene update or destroy) must be ordered after it.
+    cudaError_t ew = cudaSuccess;
+    for (int k = 1; k < issued; ++k) {
+        const cudaError_t ej = cudaEventRecord(c->ev_join[k - 1], c->band[k - 1]->stream);
+        const cudaError_t e2 = ej == cudaSuccess ? cudaStreamWaitEvent(c->stream, c->ev_join[k - 1], 0) : ej;
+        if (e2 != cudaSuccess) ew = e2;
+    }
     if (rc) { g_err = first_error; return rc; }
-    if (rc1) return rc1;
-    if (ew != cudaSuccess) return fail(SRT_ERR_CUDA, "joining the two row bands: %s", cudaGetErrorString(ew));
+    if (ew != cudaSuccess) return fail(SRT_ERR_CUDA, "joining the row bands: %s", cudaGetErrorString(ew));
     c->last_banded = true;
+    c->last_bands = nb;
     return SRT_OK;
 }
 
-// Render + device-side compaction + the count on its way to pinned host memory, all asynchronous on the context stream.
 int srt_render_sparse_begin(srt_context* c, const srt_scene* s, const srt_render_params* p) {
     if (!c || !s || !p) return fail(SRT_ERR_INVALID_ARG, "NULL argument");
     if (p->row_block != 0 || p->shard_count > 1)
@@ -735,7 +749,14 @@ int srt_render_sparse(srt_context* c, const srt_scene* s, const srt_render_param
     return rc ? rc : srt_render_sparse_count(c, count);
 }
 
+static int fetch_sparse_impl(srt_context* c, float* points_xy, float* colors_rgb, uint64_t capacity, bool wait);
 int srt_fetch_sparse(srt_context* c, float* points_xy, float* colors_rgb, uint64_t capacity) {
+    return fetch_sparse_impl(c, points_xy, colors_rgb, capacity, true);
+}
+int srt_fetch_sparse_async(srt_context* c, float* points_xy, float* colors_rgb, uint64_t capacity) {
+    return fetch_sparse_impl(c, points_xy, colors_rgb, capacity, false);
+}
+static int fetch_sparse_impl(srt_context* c, float* points_xy, float* colors_rgb, uint64_t capacity, bool wait) {
     if (!c) return fail(SRT_ERR_INVALID_ARG, "NULL context");
     if (c->sparse_pending) { uint64_t n_ = 0; const int rc_ = srt_render_sparse_count(c, &n_); if (rc_) return rc_; }
     if (!c->have_sparse) return fail(SRT_ERR_INVALID_ARG, "srt_fetch_sparse: no srt_render_sparse has been issued on this context");
@@ -743,7 +764,7 @@ int srt_fetch_sparse(srt_context* c, float* points_xy, float* colors_rgb, uint64
     const uint64_t n = c->sparse_count < capacity ? c->sparse_count : capacity;
     if (n && points_xy) CU(cudaMemcpyAsync(points_xy, c->sparse_points.p, n * 2 * sizeof(float), cudaMemcpyDefault, c->stream));
     if (n && colors_rgb) CU(cudaMemcpyAsync(colors_rgb, c->sparse_colors.p, n * 3 * sizeof(float), cudaMemcpyDefault, c->stream));
-    CU(cudaStreamSynchronize(c->stream));
+    if (wait) CU(cudaStreamSynchronize(c->stream));
     return SRT_OK;
 }
 
@@ -784,29 +805,37 @@ int srt_last_stats(srt_context* c, srt_stats* out) {
     CU(cudaSetDevice(c->device));
     CU(cudaStreamSynchronize(c->stream));
     std::memset(out, 0, sizeof *out);
-    const srt_context* b = c->last_banded ? c->band : nullptr;
-    auto counter = [&](int slot) { return c->counters_host[slot] + (b ? b->counters_host[slot] : 0ull); };
-    out->primary_rays = c->last_primary + (b ? b->last_primary : 0);
+    const int nbands = c->last_banded ? c->last_bands : 1;
+    auto counter = [&](int slot) {
+        unsigned long long v = c->counters_host[slot];
+        for (int k = 1; k < nbands; ++k) v += c->band[k - 1]->counters_host[slot];
+        return v;
+    };
+    out->primary_rays = c->last_primary;
+    out->kernel_launches = c->last_launches;
+    for (int k = 1; k < nbands; ++k) { out->primary_rays += c->band[k - 1]->last_primary; out->kernel_launches += c->band[k - 1]->last_launches; }
     out->hit_pixels = counter(srtk::CNT_HIT);
     // ray-count rule of SURVEY.md §8d: the shadow rays the final image depends on
     out->shadow_rays = c->last_objects >= 2 ? (uint64_t)c->last_lights * out->hit_pixels : 0;
     out->node_visits = counter(srtk::CNT_NODE);
     out->tri_tests = counter(srtk::CNT_TRI);
     out->exact_slab_tests = counter(srtk::CNT_EXACT);
-    out->kernel_launches = c->last_launches + (b ? b->last_launches : 0);
     if (counter(srtk::CNT_TIMEOUT))
         return fail(SRT_ERR_CUDA, "render kernel: %llu warps gave up waiting for a published tile (internal error; frame incomplete)",
                     (unsigned long long)counter(srtk::CNT_TIMEOUT));
     float ms = 0.f;
     CU(cudaEventElapsedTime(&ms, c->ev0, c->ev1));
-    if (b) {                                                          // both bands: from the first launch to the later end
+    float lead_max = 0.f;
+    for (int k = 1; k < nbands; ++k) {                                // all bands: from the first launch to the last end
+        const srt_context* b = c->band[k - 1];
         float ms_b = 0.f;
         CU(cudaEventElapsedTime(&ms_b, c->ev0, b->ev1));
         if (ms_b > ms) ms = ms_b;
-        float lead = 0.f;                                             // the band may have started first
+        float lead = 0.f;                                             // a band may have started first
         CU(cudaEventElapsedTime(&lead, b->ev0, c->ev0));
-        if (lead > 0.f) ms += lead;
+        if (lead > lead_max) lead_max = lead;
     }
+    ms += lead_max;
     out->kernel_ms = ms;
     return SRT_OK;
 }

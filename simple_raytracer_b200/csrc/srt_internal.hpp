@@ -66,9 +66,11 @@ struct srt_context {
     bool have_last = false;
     // Two-band rendering (srt_render): the lower half of the rows is rendered by a child context on its own stream, so
     // that the stages of the two halves overlap (one half's shadow pass runs in the other half's primary-pass tail).
-    srt_context* band = nullptr;      // child (owned); its `parent` points back
+    static constexpr int kMaxBands = 4;
+    srt_context* band[kMaxBands - 1] = {};   // children (owned) for bands 1..; their `parent` points back
     srt_context* parent = nullptr;
-    cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
+    cudaEvent_t ev_fork = nullptr, ev_join[kMaxBands - 1] = {};
+    int last_bands = 1;               // bands of the last render (1 = one piece)
     bool last_banded = false;
     int bands = 2;                    // srt_context_set_bands (SRT_DEFAULT_BANDS overrides the default)
     cudaEvent_t stage_ev[5] = {};     // srt_context_set_stage_timing: around classify / primary / shadow / shade

@@ -489,14 +489,18 @@ def test_two_row_bands_equal_one_piece(gpu_ctx, key, W, H):
     try:
         two = gpu_ctx.render(sc, p)
         again = gpu_ctx.render(sc, p)
+        gpu_ctx.set_bands(4)                               # up to four bands (of at least 64 rows each)
+        four = gpu_ctx.render(sc, p)
+        assert gpu_ctx.set_bands(2) == 4
         p.row_begin, p.row_end = 8, H - 3                  # a row range is split the same way
         part = gpu_ctx.render(sc, p)
         with pytest.raises(capi.SrtError):
-            gpu_ctx.set_bands(3)
+            gpu_ctx.set_bands(5)
     finally:
         assert gpu_ctx.set_bands(default) == 2
     for k in ("rgb", "obj_id", "tri_id", "t"):
-        assert np.array_equal(one[k], two[k]) and np.array_equal(two[k], again[k]), k
+        assert np.array_equal(one[k], two[k]) and np.array_equal(two[k], again[k]) and np.array_equal(one[k], four[k]), k
+    assert four["stats"]["hit_pixels"] == one["stats"]["hit_pixels"] and four["stats"]["primary_rays"] == W * H
     assert one["stats"]["hit_pixels"] == two["stats"]["hit_pixels"] and one["stats"]["primary_rays"] == two["stats"]["primary_rays"] == W * H
     assert two["stats"]["kernel_launches"] == 2 * one["stats"]["kernel_launches"] or one["stats"]["kernel_launches"] < 4
     assert np.array_equal(part["tri_id"][8:H - 3], one["tri_id"][8:H - 3]) and np.array_equal(part["rgb"][8:H - 3], one["rgb"][8:H - 3])
@@ -629,7 +633,11 @@ def test_sparse_begin_count_fetch_pipeline_equals_the_blocking_call(gpu_ctx, ref
         n = C.c_uint64(0)
         capi._check(L.srt_render_sparse_count(ctx.h, C.byref(n)))
         pts = np.zeros((n.value, 2), np.float32); col = np.zeros((n.value, 3), np.float32)
-        capi._check(L.srt_fetch_sparse(ctx.h, pts.ctypes.data_as(fp), col.ctypes.data_as(fp), n.value))
+        if k % 3 == 0:
+            capi._check(L.srt_fetch_sparse_async(ctx.h, pts.ctypes.data_as(fp), col.ctypes.data_as(fp), n.value))
+            ctx.sync()
+        else:
+            capi._check(L.srt_fetch_sparse(ctx.h, pts.ctypes.data_as(fp), col.ctypes.data_as(fp), n.value))
         got[k] = (pts, col)
     for k, (W, H) in enumerate(sizes):
         ctx, sc = lanes[k % 2]
