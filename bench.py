@@ -260,7 +260,8 @@ def single_frame_leg(args, ctx, rank, world, local, dev, barrier):
     from simple_raytracer_b200 import _abi, capi, host, multigpu, scenes
     out = {}
     flush = torch.empty(L2_FLUSH_BYTES, dtype=torch.uint8, device=dev)
-    for key, angle in (("C3", 0.0), ("C3", 180.0), ("C4", 0.0)):
+    cases = [(k_, a_, m_) for (k_, a_) in (("C3", 0.0), ("C3", 180.0), ("C4", 0.0)) for m_ in (("peer", "gather") if world > 1 else ("peer",))]
+    for key, angle, mode in cases:
         cfg = scenes.CONFIGS[key]
         W, H, focal, N = cfg.width, cfg.height, cfg.focal, cfg.light_count
         hs = host.HostScene()
@@ -269,7 +270,7 @@ def single_frame_leg(args, ctx, rank, world, local, dev, barrier):
         arrays = hs.flatten()
         hs.close()
         sc = ctx.upload(arrays)
-        sharded = multigpu.ShardedFrameRenderer(ctx, W, H, row_block=args.row_block) if world > 1 else None
+        sharded = multigpu.ShardedFrameRenderer(ctx, W, H, row_block=args.row_block, mode=mode) if world > 1 else None
         frame1 = torch.empty((H, W, 3), dtype=torch.uint8, device=dev)
 
         def one_frame():
@@ -307,16 +308,24 @@ def single_frame_leg(args, ctx, rank, world, local, dev, barrier):
             identical = bool(torch.equal(res, frame1)) if world > 1 else True
             name = f"{key}_{W}x{H}_{N}lights_{angle:g}deg"
             rays = ray_count(W, H, N, hits, len(arrays.objects))
-            out[name] = {"ms_per_frame": float(t[0]), "render_ms_slowest_rank": float(t[1]), "render_ms_fastest_rank": float(tmin[1]),
-                         "gather_and_sync_ms": float(t[0] - t[1]), "frames_per_s": 1e3 / float(t[0]), "Mrays_per_s": rays / float(t[0]) / 1e3,
-                         "identical": identical, "bytes_gathered": int(W * H * 3 * (world - 1) / world)}
+            entry = {"ms_per_frame": float(t[0]), "render_ms_slowest_rank": float(t[1]), "render_ms_fastest_rank": float(tmin[1]),
+                     "join_ms": float(t[0] - t[1]), "frames_per_s": 1e3 / float(t[0]), "Mrays_per_s": rays / float(t[0]) / 1e3,
+                     "identical": identical, "bytes_from_other_ranks": int(W * H * 3 * (world - 1) / world)}
+            if mode == "peer":
+                out[name] = entry
+            else:
+                out[name]["nccl_gather"] = entry
+        if sharded is not None:
+            sharded.close()
         sc.destroy()
         barrier()
     if rank == 0:
-        out["what"] = (f"one frame over {world} GPU(s): interleaved {args.row_block}-row blocks, rendered in place, row blocks sent from the "
-                       "owner's frame into rank 0's frame over NCCL (batched isend/irecv, no staging copy); `identical` = bytes equal to "
-                       "rank 0's own full render; ms = CUDA events around render + gather, max over ranks, mean of 12 frames after 3 warm-up, "
-                       "L2 flushed and ranks barriered before every frame") if world > 1 else \
+        out["what"] = (f"one frame over {world} GPU(s), one process per GPU: interleaved {args.row_block}-row blocks, block b -> rank b mod {world}; every rank's "
+                       "kernels store their blocks straight into rank 0's frame (CUDA IPC mapping, NVLink stores, no gather, no staging copy), "
+                       "joined by one 4-byte NCCL all-reduce on the render streams; `nccl_gather` = the same frame with every rank rendering into "
+                       "its own frame and the blocks sent into rank 0's frame by batched NCCL send/recv; `identical` = bytes equal to rank 0's own "
+                       "full render; ms = CUDA events around render + join, max over ranks, mean of 12 frames after 3 warm-up, L2 flushed and "
+                       "ranks barriered before every frame") if world > 1 else \
                       "one frame on one GPU (default pipeline, two row bands), same timing method as the N-GPU lines"
     return out if rank == 0 else None
 

@@ -372,6 +372,16 @@ int  srt_mgpu_sync(srt_mgpu* m);
  * stream, from the fork to the join of all GPUs (before the download).  Synchronises. */
 int  srt_mgpu_last_stats(srt_mgpu* m, srt_stats* out);
 
+/* ---- one process per GPU: a frame shared between the processes of one box ----
+ * srt_ipc_export writes the 64-byte CUDA IPC handle of a buffer from srt_device_alloc (rank 0's frame); srt_ipc_open maps
+ * it in another process for the kernels of that process's context (peer access to the owner's GPU is opened on the way) —
+ * the returned address is a valid output plane for srt_render, whose stores then go straight into rank 0's memory over
+ * NVLink / NVSwitch (simple_raytracer_b200/multigpu.py: interleaved row blocks per rank, no gather, one small all-reduce
+ * as the join).  srt_ipc_close unmaps (synchronises the context first).  The owner must keep the buffer alive. */
+int  srt_ipc_export(srt_context* ctx, void* device_ptr, void* handle64);
+int  srt_ipc_open(srt_context* ctx, const void* handle64, void** device_ptr);
+int  srt_ipc_close(srt_context* ctx, void* device_ptr);
+
 /* ---- helpers ---- */
 void srt_default_params(srt_render_params* p);             /* fills the reference's literals */
 /* Light sample positions, out[3*i..] for i < count: the staircase of softShadow :363-383 (sequential fp32 adds) or

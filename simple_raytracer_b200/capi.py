@@ -28,6 +28,7 @@ EXPORTS = [
     "srt_sparse_from_frame_static",
     "srt_render_sparse_begin", "srt_render_sparse_count", "srt_fetch_sparse_async",
     "srt_context_set_stage_timing", "srt_last_stage_ms",
+    "srt_ipc_export", "srt_ipc_open", "srt_ipc_close",
     "srt_mgpu_create", "srt_mgpu_destroy", "srt_mgpu_info", "srt_mgpu_scene_upload", "srt_mgpu_render_frame",
     "srt_mgpu_render_series", "srt_mgpu_sync", "srt_mgpu_last_stats",
 ]
@@ -78,6 +79,9 @@ def lib():
         L.srt_sparse_from_frame_static.argtypes = [vp, vp, C.c_int32, C.c_int32, C.c_int32, C.c_int32, vp, vp, vp]
         L.srt_context_set_stage_timing.argtypes = [vp, C.c_int]
         L.srt_last_stage_ms.argtypes = [vp, C.POINTER(C.c_float)]
+        L.srt_ipc_export.argtypes = [vp, vp, vp]
+        L.srt_ipc_open.argtypes = [vp, vp, C.POINTER(vp)]
+        L.srt_ipc_close.argtypes = [vp, vp]
         L.srt_mgpu_create.argtypes = [C.POINTER(C.c_int), C.c_int, C.POINTER(vp)]
         L.srt_mgpu_destroy.argtypes = [vp]
         L.srt_mgpu_destroy.restype = None
@@ -348,6 +352,28 @@ class Context:
 
     def sync(self):
         _check(lib().srt_sync(self.h))
+
+    def device_alloc(self, nbytes: int) -> int:
+        p = lib().srt_device_alloc(self.h, int(nbytes))
+        if not p:
+            raise SrtError(_abi.SRT_ERR_OOM, "srt_device_alloc failed")
+        return int(p)
+
+    def device_free(self, ptr: int):
+        lib().srt_device_free(self.h, C.c_void_p(ptr))
+
+    def ipc_export(self, ptr: int) -> bytes:
+        buf = C.create_string_buffer(64)
+        _check(lib().srt_ipc_export(self.h, C.c_void_p(ptr), buf))
+        return buf.raw
+
+    def ipc_open(self, handle: bytes) -> int:
+        out = C.c_void_p()
+        _check(lib().srt_ipc_open(self.h, C.create_string_buffer(handle, 64), C.byref(out)))
+        return int(out.value)
+
+    def ipc_close(self, ptr: int):
+        _check(lib().srt_ipc_close(self.h, C.c_void_p(ptr)))
 
     def last_stats(self) -> dict:
         s = _abi.Stats()

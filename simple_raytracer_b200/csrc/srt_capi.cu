@@ -240,6 +240,35 @@ void srt_device_free(srt_context* c, void* p) {
     cudaFree(p);
 }
 
+// ---- a device buffer shared between the processes of one box (one process per GPU) --------------------------------
+// The multi-process form of srt_mgpu's peer writes: rank 0 exports its frame, the other ranks map it and hand the mapped
+// address to srt_render as an output plane — their kernels then store straight into rank 0's memory over NVLink.
+int srt_ipc_export(srt_context* c, void* device_ptr, void* handle64) {
+    if (!c || !device_ptr || !handle64) return fail(SRT_ERR_INVALID_ARG, "NULL argument");
+    static_assert(sizeof(cudaIpcMemHandle_t) == 64, "handle size");
+    CU(cudaSetDevice(c->device));
+    cudaIpcMemHandle_t h;
+    CU(cudaIpcGetMemHandle(&h, device_ptr));
+    std::memcpy(handle64, &h, 64);
+    return SRT_OK;
+}
+int srt_ipc_open(srt_context* c, const void* handle64, void** device_ptr) {
+    if (!c || !handle64 || !device_ptr) return fail(SRT_ERR_INVALID_ARG, "NULL argument");
+    CU(cudaSetDevice(c->device));                       // the mapping is for kernels of THIS context's device:
+    cudaIpcMemHandle_t h;                               // LazyEnablePeerAccess opens the path to the owner's device
+    std::memcpy(&h, handle64, 64);
+    *device_ptr = nullptr;
+    CU(cudaIpcOpenMemHandle(device_ptr, h, cudaIpcMemLazyEnablePeerAccess));
+    return SRT_OK;
+}
+int srt_ipc_close(srt_context* c, void* device_ptr) {
+    if (!c || !device_ptr) return fail(SRT_ERR_INVALID_ARG, "NULL argument");
+    CU(cudaSetDevice(c->device));
+    CU(cudaStreamSynchronize(c->stream));
+    CU(cudaIpcCloseMemHandle(device_ptr));
+    return SRT_OK;
+}
+
 int srt_sync(srt_context* c) {
     if (!c) return fail(SRT_ERR_INVALID_ARG, "ctx is NULL");
     CU(cudaSetDevice(c->device));

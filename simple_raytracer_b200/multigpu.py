@@ -98,24 +98,75 @@ def gather_frames(frame: torch.Tensor, group=None, dst: int = 0) -> Optional[Lis
     return parts
 
 
-class ShardedFrameRenderer:
-    """One frame over all ranks of the process group.  Every rank holds the (replicated) scene."""
+class _DeviceBuffer:
+    """A raw device allocation seen by torch through __cuda_array_interface__ (uint8, 1-D)."""
 
-    def __init__(self, ctx, width: int, height: int, row_block: int = DEFAULT_ROW_BLOCK, group=None):
+    def __init__(self, ptr: int, nbytes: int):
+        self.__cuda_array_interface__ = {"shape": (int(nbytes),), "typestr": "|u1", "data": (int(ptr), False), "version": 3, "strides": None}
+
+
+class ShardedFrameRenderer:
+    """One frame over all ranks of the process group.  Every rank holds the (replicated) scene.
+
+    mode "peer" (default on GPUs): rank 0 owns the frame (a cudaMalloc buffer exported over CUDA IPC); every other rank maps
+    it and renders its interleaved row blocks STRAIGHT into rank 0's memory — the shade kernel's stores travel over NVLink /
+    NVSwitch, there is no gather and no staging copy; the join is one 4-byte all-reduce on each rank's render stream.
+    mode "gather": every rank renders into its own full-size frame and the row blocks are sent from there into the same
+    rows of rank 0's frame (NCCL batched send / receive, gather_row_blocks_in_place) — also what the gloo CPU tests use."""
+
+    def __init__(self, ctx, width: int, height: int, row_block: int = DEFAULT_ROW_BLOCK, group=None, mode: Optional[str] = None):
         self.ctx, self.group = ctx, group
         self.width, self.height, self.row_block = width, height, row_block
         self.world = dist.get_world_size(group) if dist.is_initialized() else 1
         self.rank = dist.get_rank(group) if dist.is_initialized() else 0
-        hp = padded_height(height, row_block, self.world)
-        self.frame = torch.zeros((hp, width, 3), dtype=torch.uint8, device=torch.device("cuda", ctx.device))
+        self.mode = mode or ("peer" if self.world > 1 else "gather")
+        self._own_ptr = self._peer_ptr = None
+        dev = torch.device("cuda", ctx.device)
+        nbytes = height * width * 3
+        if self.mode == "peer" and self.world > 1:
+            info = [None]
+            if self.rank == 0:
+                self._own_ptr = ctx.device_alloc(nbytes)
+                info[0] = ctx.ipc_export(self._own_ptr)
+            dist.broadcast_object_list(info, src=dist.get_global_rank(group, 0) if group is not None else 0, group=group)
+            if self.rank == 0:
+                self.target = self._own_ptr
+                self.frame = torch.as_tensor(_DeviceBuffer(self._own_ptr, nbytes), device=dev).view(height, width, 3)
+            else:
+                self._peer_ptr = ctx.ipc_open(info[0])
+                self.target = self._peer_ptr
+                self.frame = None
+            self._token = torch.zeros(1, dtype=torch.int32, device=dev)
+        else:
+            self.mode = "gather"
+            self.frame = torch.zeros((height, width, 3), dtype=torch.uint8, device=dev)
+            self.target = self.frame.data_ptr()
 
     def render(self, scene, params) -> Optional[torch.Tensor]:
-        """Renders this rank's row blocks in place and gathers; returns the [H, W, 3] frame on rank 0."""
+        """Renders this rank's row blocks and joins; returns the [H, W, 3] frame on rank 0 (valid in stream order)."""
         params.row_begin, params.row_end = 0, self.height
-        params.row_block, params.shard_index, params.shard_count = self.row_block, self.rank, self.world
-        self.ctx.render_raw(scene, params, rgb=self.frame.data_ptr())
+        if self.world > 1:
+            params.row_block, params.shard_index, params.shard_count = self.row_block, self.rank, self.world
+        self.ctx.render_raw(scene, params, rgb=self.target)
         if getattr(self.ctx, "stream", None) is None:
-            self.ctx.sync()               # context on its own stream: order the gather after the render
+            self.ctx.sync()               # context on its own stream: order the join after the render
         if self.world == 1:
             return self.frame[: self.height]
+        if self.mode == "peer":
+            # every rank's all-reduce kernel runs after its render kernels (stream order) and none completes before all have
+            # started: when it is done on rank 0, every rank's stores into the frame have been performed
+            dist.all_reduce(self._token, group=self.group)
+            return self.frame if self.rank == 0 else None
         return gather_row_blocks_in_place(self.frame, self.height, self.row_block, self.group)
+
+    def close(self):
+        if self._peer_ptr is not None:
+            self.ctx.ipc_close(self._peer_ptr)
+            self._peer_ptr = None
+        if dist.is_initialized() and self.world > 1 and self.mode == "peer":
+            dist.barrier(group=self.group)        # nobody still maps the frame when its owner frees it
+        if self._own_ptr is not None:
+            self.frame = None
+            self.ctx.sync()
+            self.ctx.device_free(self._own_ptr)
+            self._own_ptr = None

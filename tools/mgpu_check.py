@@ -23,17 +23,21 @@ W, H, focal = scenes.scaled(cfg, 540)
 hs = host.HostScene(); view = cfg.build(hs, 0.0); light = scenes.light_view_space(hs, view); arrays = hs.flatten()
 sc = ctx.upload(arrays)
 ok = True
-for block in (16, 32):
-    r = multigpu.ShardedFrameRenderer(ctx, W, H, row_block=block)
-    p = _abi.default_params(W, H, focal, light, cfg.light_count, True)
-    out = r.render(sc, p)
-    torch.cuda.synchronize()
-    if rank == 0:
-        p2 = _abi.default_params(W, H, focal, light, cfg.light_count, True)
-        want = ctx.render(sc, p2, ids=False, want_t=False)["rgb"]
-        same = np.array_equal(out.cpu().numpy(), want)
-        print(f"row_block {block}: {world}-rank sharded frame == single-GPU frame: {same}")
-        ok &= same
+for mode in ("peer", "gather"):
+    for block in (16, 32):
+        r = multigpu.ShardedFrameRenderer(ctx, W, H, row_block=block, mode=mode)
+        p = _abi.default_params(W, H, focal, light, cfg.light_count, True)
+        for rep in range(3):
+            out = r.render(sc, p)
+            torch.cuda.synchronize()
+            dist.barrier()
+        if rank == 0:
+            p2 = _abi.default_params(W, H, focal, light, cfg.light_count, True)
+            want = ctx.render(sc, p2, ids=False, want_t=False)["rgb"]
+            same = np.array_equal(out.cpu().numpy(), want)
+            print(f"{mode}, row_block {block}: {world}-rank sharded frame == single-GPU frame: {same}")
+            ok &= same
+        r.close()
 # series: frame f -> rank f % world
 frames = multigpu.frames_of_rank(2 * world, rank, world)
 rgb = torch.empty((H, W, 3), dtype=torch.uint8, device="cuda")
