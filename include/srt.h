@@ -225,8 +225,9 @@ int  srt_context_set_stream(srt_context* ctx, void* cuda_stream);
  * streams so that their stages overlap (-11 % time per frame; the same bytes, pixels are independent :511-523) — what a
  * caller that renders ONE frame at a time wants; 1 renders a frame in one piece, for callers that already keep several
  * frames in flight on several contexts (an image series gains nothing from a second band; the series driver sets 1 on
- * its lanes).  3 and 4 are accepted (bands of at least 64 rows) and measured no better than 2 (profiles/).  Frames of
- * fewer than 128 rows, sharded frames and the other kernel variants are always one piece.
+ * its lanes).  3 and 4 are accepted (bands of at least 64 rows) and measured no better than 2 (profiles/).  A context's
+ * share of fewer than 128 rows and the other kernel variants are always one piece; a sharded frame (row_block /
+ * shard_count) is cut at a multiple of row_block * shard_count, so both bands keep the frame's block ownership.
  * Returns the previous value, or a negative srt_status. */
 int  srt_context_set_bands(srt_context* ctx, int bands);
 int  srt_context_get_info(srt_context* ctx, int* sm_count, int* cc_major, int* cc_minor,

@@ -673,8 +673,15 @@ int srt_render(srt_context* c, const srt_scene* s, const srt_render_params* p, c
     if (!c || !s || !p || !out) return fail(SRT_ERR_INVALID_ARG, "NULL argument");
     int rb = p->row_begin, re = p->row_end;
     if (rb == 0 && re == 0) re = p->height;
-    const bool banded = c->bands >= 2 && !c->parent && p->variant == SRT_VARIANT_DEFAULT && p->use_bvh &&
-                        p->row_block == 0 && p->shard_count <= 1 && s->n_objects > 0 && rb >= 0 && re <= p->height && re - rb >= 128;
+    // A sharded frame (interleaved row blocks, several GPUs) is split at a multiple of row_block * shard_count, so that block b
+    // of either band is still block b of the frame and belongs to the same shard.
+    const bool sharded = p->row_block != 0 || p->shard_count > 1;
+    const bool shard_ok = !sharded || (p->row_block > 0 && p->row_block % srtk::kTileH == 0 && p->shard_count >= 1 && p->shard_index >= 0 &&
+                                       p->shard_index < p->shard_count);
+    const int unit = sharded && shard_ok ? p->row_block * p->shard_count : 4;      // cut granularity, rows
+    const int share = sharded && shard_ok ? p->shard_count : 1;                    // this context renders 1 / share of the rows
+    const bool banded = c->bands >= 2 && !c->parent && p->variant == SRT_VARIANT_DEFAULT && p->use_bvh && shard_ok &&
+                        s->n_objects > 0 && rb >= 0 && re <= p->height && (re - rb) / share >= 128 && (re - rb) >= 2 * unit;
     c->last_banded = false;
     c->last_bands = 1;
     if (s->ctx == c) {                                    // (a scene of another context is rejected by render_impl)
@@ -684,7 +691,7 @@ int srt_render(srt_context* c, const srt_scene* s, const srt_render_params* p, c
     if (!banded) return render_impl(c, s, p, out);
     CU(cudaSetDevice(c->device));
     int nb = c->bands;
-    while (nb > 2 && (re - rb) / nb < 64) --nb;           // bands of at least 64 rows
+    while (nb > 2 && ((re - rb) / share / nb < 64 || (re - rb) / unit < nb)) --nb;   // bands of at least 64 own rows
     for (int k = 0; k + 1 < nb; ++k)
         if (!c->band[k]) {
             int rc = srt_context_create(c->device, &c->band[k]);
@@ -695,7 +702,7 @@ int srt_render(srt_context* c, const srt_scene* s, const srt_render_params* p, c
         }
     if (!c->ev_fork) CU(cudaEventCreateWithFlags(&c->ev_fork, cudaEventDisableTiming));
     int cut[srt_context::kMaxBands + 1];
-    for (int k = 0; k <= nb; ++k) cut[k] = rb + (int)(((long long)(re - rb) * k / nb) / 4 * 4);
+    for (int k = 0; k <= nb; ++k) cut[k] = rb + (int)(((long long)(re - rb) * k / nb) / unit * unit);
     cut[nb] = re;
     CU(cudaEventRecord(c->ev_fork, c->stream));           // the bands start after everything queued so far (scene upload / prep)
     int rc = SRT_OK;

@@ -79,7 +79,6 @@ int srt_mgpu_create(const int* devices, int n_devices, srt_mgpu** out) {
         g.device = devices ? devices[r] : r;
         rc = srt_context_create(g.device, &g.ctx);
         if (rc) break;
-        g.ctx->bands = 1;                                   // a shard is one piece (sharded frames never split into bands)
         if (cudaEventCreateWithFlags(&g.done, cudaEventDisableTiming) != cudaSuccess) { rc = fail(SRT_ERR_CUDA, "cudaEventCreate failed"); break; }
         const int first = m->gpus[0].device;
         if (g.device == first) {

@@ -235,6 +235,23 @@ def test_interleaved_row_block_shards_equal_full_frame(gpu_ctx, ref_scene, varia
             hits += gpu_ctx.last_stats()["hit_pixels"]
         assert np.array_equal(rgb, full["rgb"]) and np.array_equal(tri, full["tri_id"]) and np.array_equal(t, full["t"])
         assert hits == full["stats"]["hit_pixels"]
+    # large enough for every shard to be split into row bands as well (cuts at multiples of row_block * shard_count)
+    W2, H2 = 480, 540
+    p2 = _abi.default_params(W2, H2, float(H2), light, 4, True)
+    p2.variant = variant
+    full2 = gpu_ctx.render(sc, p2)
+    for world, block in ((2, 16), (3, 8)):
+        rgb = np.zeros((H2, W2, 3), np.uint8)
+        tri = np.full((H2, W2), -7, np.int32)
+        launches = 0
+        for r in range(world):
+            p2.row_block, p2.shard_index, p2.shard_count = block, r, world
+            gpu_ctx.render_raw(sc, p2, rgb.ctypes.data, None, tri.ctypes.data, None)
+            gpu_ctx.sync()
+            launches += gpu_ctx.last_stats()["kernel_launches"]
+        assert np.array_equal(rgb, full2["rgb"]) and np.array_equal(tri, full2["tri_id"])
+        if variant == 0:
+            assert launches == world * full2["stats"]["kernel_launches"]          # every shard in as many bands as the full frame
     p.row_block, p.shard_index, p.shard_count = 6, 0, 2       # not a multiple of the tile height
     with pytest.raises(Exception):
         gpu_ctx.render_raw(sc, p, None, None, None, None)
