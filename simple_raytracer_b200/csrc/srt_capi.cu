@@ -405,6 +405,10 @@ int fill_scene(srt_context* c, srt_scene* s, const srt_scene_desc* d, bool fresh
         cudaError_t e = srtk::launch_build_wide((const float4*)s->nodes.p, (const srt_object*)s->objects.p, (uint32_t)d->n_nodes,
                                                 d->n_objects, (float4*)s->wide.p, (uint32_t*)s->root_ref.p, c->stream);
         if (e != cudaSuccess) return fail(SRT_ERR_CUDA, "build_wide launch: %s", cudaGetErrorString(e));
+        if ((rc = s->pwide.reserve(d->n_nodes * 64 * 4))) return rc;
+        for (uint32_t q = 0; q < 4 && e == cudaSuccess; ++q)
+            e = srtk::launch_build_shadow_wide((const float4*)s->wide.p, (uint32_t)d->n_nodes, q, (float4*)s->pwide.p + (size_t)q * d->n_nodes * 4, c->stream);
+        if (e != cudaSuccess) return fail(SRT_ERR_CUDA, "build of the quadrant-sorted nodes: %s", cudaGetErrorString(e));
     }
     s->swide_octant = -1;                          // derived from `wide`: rebuilt by the next render that wants it
     // Textures.  desc->textures == NULL on an update keeps the resident table (the count must match).  Otherwise every
@@ -471,7 +475,7 @@ void srt_scene_destroy(srt_scene* s) {
     if (!s) return;
     if (s->ctx) { cudaSetDevice(s->ctx->device); cudaStreamSynchronize(s->ctx->stream); }
     s->nodes.release(); s->geom.release(); s->attr.release(); s->flat_geom.release(); s->flat_attr.release();
-    s->objects.release(); s->texdesc.release(); s->wide.release(); s->root_ref.release(); s->swide.release();
+    s->objects.release(); s->texdesc.release(); s->wide.release(); s->root_ref.release(); s->swide.release(); s->pwide.release();
     s->vnormal.release(); s->flat_vnormal.release();
     for (auto& t : s->tex) t.release();
     srti_prep_state_destroy(s->prep);
@@ -598,6 +602,8 @@ static int render_impl(srt_context* c, const srt_scene* s, const srt_render_para
         if ((rc = c->tile_order.reserve(n_tiles * 4))) return rc;
         if ((rc = c->shadow_mask.reserve(n_tiles * 4 * (size_t)(p->light_count > 0 ? p->light_count : 1)))) return rc;
         a.wide = (const float4*)s->wide.p;
+        a.pwide = s->pwide.p && s->pwide.cap >= s->n_nodes * 64 * 4 && !s->prep ? (const float4*)s->pwide.p : nullptr;
+        a.pwide_stride = (size_t)s->n_nodes * 4;
         a.swide = s->swide_octant >= 0 ? (const float4*)s->swide.p : nullptr;      // ensure_shadow_wide (srt_render)
         a.shadow_octant = s->swide_octant >= 0 ? (uint32_t)s->swide_octant : 0u;
         a.root_ref = (const uint32_t*)s->root_ref.p;

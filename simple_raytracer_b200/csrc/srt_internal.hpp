@@ -88,6 +88,7 @@ struct srt_scene {
     srti::DevBuf wide, root_ref;                        // device-internal traversal layout (srt_phased.cu)
     // `wide` with plane pairs sorted near-first for one direction octant (the shadow pass's fast path).  Derived data: built on
     // the owning context's stream by srt_render when the scene's contents or the light's octant changed (-1: stale).
+    srti::DevBuf pwide;                                 // four quadrant-sorted copies of `wide` for the primary pass (built with it)
     mutable srti::DevBuf swide;
     mutable int swide_octant = -1;
     bool phased_ok = false;                       // leaf sizes / index ranges fit the packed traversal refs

@@ -52,6 +52,8 @@ struct KArgs {
     // ---- phased kernel only (device-internal data built at upload, scratch owned by the context) ----
     const float4* wide;         // per interior node i: the two child boxes + child refs, 4 x float4 at wide[4*i]
     const uint32_t* root_ref;   // per object: traversal ref of its root
+    const float4* pwide;        // four copies of `wide`, planes sorted near / far for the primary rays' quadrants 0..3 (or null)
+    size_t pwide_stride;        // float4s per copy
     const float4* swide;        // `wide` with every box's planes sorted near / far for rays of octant `shadow_octant` (or null)
     uint32_t shadow_octant;     // bit k: the shadow rays' direction component k is negative (all lights lie far outside the scene)
     float* hit_t;               // [height][width] scratch: closest-hit parameter

@@ -214,7 +214,11 @@ __device__ __forceinline__ uint32_t leaf_count(uint32_t ref) { return (ref >> kL
 // Closest hit over everything on the stack (refs of nodes whose own box already passed).  The reference visits
 // EVERY reachable leaf (no pruning by distance, S5) and the closest hit is the order-independent min over
 // (t, visit index) (S6), so collecting leaves first changes nothing but the schedule.
-__device__ __forceinline__ void trace_closest(const KArgs& a, const FRay& r, Stack& st, Hit& h, unsigned& exact_count) {
+// SORTED: every ray of the warp points into the quadrant (sign of d.x, sign of d.y, d.z > 0) whose pre-sorted copy of the nodes
+// `nodes` is (a.pwide): the pair test needs no min / max to sort the plane values (slab_sorted_pair).
+template <bool SORTED>
+__device__ __forceinline__ void trace_closest(const KArgs& a, const FRay& r, Stack& st, Hit& h, unsigned& exact_count,
+                                              const float4* nodes, uint32_t oct) {
     const int cap = a.stack_cap;
     int nl = 0;
     uint32_t ref = st.pop();
@@ -224,11 +228,12 @@ __device__ __forceinline__ void trace_closest(const KArgs& a, const FRay& r, Sta
                 st.put_leaf(cap, nl, ref);
                 ref = st.pop();
             } else {
-                const float4* w = a.wide + 4 * (size_t)ref;
+                const float4* w = nodes + 4 * (size_t)ref;
                 const float4 w0 = ldg4(w), w1 = ldg4(w + 1), w2 = ldg4(w + 2), w3 = ldg4(w + 3);
                 float tnl, tfl, tnr, tfr;
                 bool hl, hr;
-                slab_filtered_pair(r, w0, w1, w2, hl, hr, tnl, tfl, tnr, tfr, exact_count);
+                if (SORTED) slab_sorted_pair(r, oct, w0, w1, w2, hl, hr, tnl, tfl, tnr, tfr, exact_count);
+                else slab_filtered_pair(r, w0, w1, w2, hl, hr, tnl, tfl, tnr, tfr, exact_count);
                 const uint32_t rl = __float_as_uint(w3.x), rr = __float_as_uint(w3.y);
                 if (hl && is_leaf(rl)) { st.put_leaf(cap, nl, rl); hl = false; }
                 if (hr && is_leaf(rr)) { st.put_leaf(cap, nl, rr); hr = false; }
@@ -408,7 +413,14 @@ __device__ __forceinline__ unsigned primary_tile(const KArgs& a, Stack& st, unsi
     h.t = INFINITY; h.tri = -1; h.obj = -1;
     st.sp = 0;
     if (p.valid) push_roots(a, r, st, -1, exact_count);                       // :409 (S2 order via the S6 rule)
-    trace_closest(a, r, st, h, exact_count);
+    // primary rays of a tile share the signs of d.x and d.y unless the tile straddles the centre column / row (d.z = focal)
+    const uint32_t quad = (d.x < 0.f ? 1u : 0u) | (d.y < 0.f ? 2u : 0u);
+    const uint32_t quad0 = __shfl_sync(kFull, quad, 0);
+    const bool fits = !p.valid || (quad == quad0 && d.x != 0.f && d.y != 0.f);
+    if (a.pwide != nullptr && a.focal > 0.f && __all_sync(kFull, fits) && __shfl_sync(kFull, p.valid ? 1 : 0, 0))
+        trace_closest<true>(a, r, st, h, exact_count, a.pwide + (size_t)quad0 * a.pwide_stride, quad0);
+    else
+        trace_closest<false>(a, r, st, h, exact_count, a.wide, 0u);
     bool interested = false;
     if (p.valid) {
         const size_t at = (size_t)p.py * a.width + p.px;
