@@ -14,4 +14,4 @@ $C4 > gpurun_out/${T}_c4_plain.log 2>&1 && \
 ncu --metrics gpu__time_duration.sum --clock-control none -s 0 -c 60 --csv --log-file gpurun_out/${T}_c4_launches.csv $C4 > gpurun_out/${T}_c4_launches.log 2>&1
 $C4 > /dev/null 2>&1 && \
 ncu --set full --clock-control none --import-source on -k regex:render_phase -s 6 -c 3 -f -o gpurun_out/${T}_c4_stages $C4 > gpurun_out/${T}_c4_full.log 2>&1
-tail -3 gpurun_out/${T}_c3_plain.log gpurun_out/${T}_c4_plain.log
+tail -n 1 gpurun_out/${T}_c3_plain.log; tail -n 1 gpurun_out/${T}_c4_plain.log
