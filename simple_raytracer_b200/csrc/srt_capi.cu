@@ -653,6 +653,32 @@ static int render_impl(srt_context* c, const srt_scene* s, const srt_render_para
 // the octant is that of the first light's position; a warp whose rays disagree takes the general path, so a wrong guess
 // costs time, never a result.  Built on the context's stream before any band forks off; kept until the scene or the
 // octant changes.
+// A/B switch (SRT_L2_PERSIST=1): mark the traversal data of the scene as persisting in L2 for the context's stream(s).
+// The scene is L2-resident anyway (7-50 MB against 126 MB); what a persisting window can add is surviving whatever else
+// streams through L2 between two frames (the bench's flush, another tenant).  Measured: DESIGN.md §4.
+static void apply_l2_window(srt_context* c, const srt_scene* s) {
+    static const bool on = [] { const char* e = std::getenv("SRT_L2_PERSIST"); return e && std::atoi(e) != 0; }();
+    if (!on || !s->wide.p) return;
+    static bool limit_set = false;
+    if (!limit_set) { cudaDeviceSetLimit(cudaLimitPersistingL2CacheSize, 64u << 20); limit_set = true; cudaGetLastError(); }
+    const srti::DevBuf* bufs[3] = {&s->wide, &s->geom, s->swide.p ? &s->swide : &s->wide};
+    srt_context* ctxs[2] = {c, c->band[0]};
+    for (srt_context* cc : ctxs) {
+        if (!cc) continue;
+        // one window per stream: cover the largest of the buffers that a pass streams through most (the nodes)
+        cudaStreamAttrValue v;
+        std::memset(&v, 0, sizeof v);
+        v.accessPolicyWindow.base_ptr = bufs[2]->p;
+        v.accessPolicyWindow.num_bytes = bufs[2]->cap < (32u << 20) ? bufs[2]->cap : (32u << 20);
+        v.accessPolicyWindow.hitRatio = 1.0f;
+        v.accessPolicyWindow.hitProp = cudaAccessPropertyPersisting;
+        v.accessPolicyWindow.missProp = cudaAccessPropertyStreaming;
+        cudaStreamSetAttribute(cc->stream, cudaStreamAttributeAccessPolicyWindow, &v);
+        cudaGetLastError();
+    }
+    (void)bufs;
+}
+
 static int ensure_shadow_wide(srt_context* c, const srt_scene* s, const srt_render_params* p) {
     if (!s->phased_ok || !p->use_bvh || s->n_objects < 2 || p->light_count <= 0 || p->shadow_segment || s->n_nodes == 0) return SRT_OK;
     if (p->variant != SRT_VARIANT_DEFAULT && p->variant != SRT_VARIANT_FUSED && p->variant != SRT_VARIANT_OVERLAP) return SRT_OK;
@@ -693,6 +719,7 @@ int srt_render(srt_context* c, const srt_scene* s, const srt_render_params* p, c
     if (s->ctx == c) {                                    // (a scene of another context is rejected by render_impl)
         const int rcw = ensure_shadow_wide(c, s, p);
         if (rcw) return rcw;
+        apply_l2_window(c, s);
     }
     if (!banded) return render_impl(c, s, p, out);
     CU(cudaSetDevice(c->device));
