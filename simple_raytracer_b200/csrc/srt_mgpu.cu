@@ -10,6 +10,8 @@
 #include <cuda_runtime.h>
 
 #include <cstring>
+#include <string>
+#include <thread>
 #include <vector>
 
 #include "srt.h"
@@ -163,7 +165,8 @@ int srt_mgpu_render_frame(srt_mgpu* m, const srt_render_params* params, const sr
     }
     CU(cudaEventRecord(m->t0, g0.ctx->stream));
     CU(cudaEventRecord(m->fork, g0.ctx->stream));           // every GPU starts after what is queued on the first one's stream
-    for (int r = 0; r < R; ++r) {
+    // One GPU's share: wait for the fork, render its blocks into the frame (or locally + peer copies), record `done`.
+    auto issue = [&](int r) -> int {
         srt_mgpu::Gpu& g = m->gpus[(size_t)r];
         CU(cudaSetDevice(g.device));
         if (r > 0) CU(cudaStreamWaitEvent(g.ctx->stream, m->fork, 0));
@@ -194,7 +197,21 @@ int srt_mgpu_render_frame(srt_mgpu* m, const srt_render_params* params, const sr
             }
         }
         if (r > 0) CU(cudaEventRecord(g.done, g.ctx->stream));
-    }
+        return SRT_OK;
+    };
+    // A frame is a dozen launches per GPU: issued from one thread, eight GPUs start one after the other and the last one
+    // starts ~0.4 ms late.  Every GPU but the first gets its own short-lived issuing thread (distinct contexts, distinct
+    // devices: no shared state but the read-only frame description).
+    std::vector<int> rcs((size_t)R, SRT_OK);
+    std::vector<std::string> errs((size_t)R);
+    std::vector<std::thread> workers;
+    for (int r = 1; r < R; ++r)
+        workers.emplace_back([&, r] { rcs[(size_t)r] = issue(r); if (rcs[(size_t)r]) errs[(size_t)r] = srti::g_err; });
+    rcs[0] = issue(0);
+    if (rcs[0]) errs[0] = srti::g_err;
+    for (auto& w : workers) w.join();
+    for (int r = 0; r < R; ++r)
+        if (rcs[(size_t)r]) { srti::g_err = errs[(size_t)r]; return rcs[(size_t)r]; }
     CU(cudaSetDevice(g0.device));
     for (int r = 1; r < R; ++r) CU(cudaStreamWaitEvent(g0.ctx->stream, m->gpus[(size_t)r].done, 0));   // the join
     CU(cudaEventRecord(m->t1, g0.ctx->stream));
