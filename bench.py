@@ -56,6 +56,7 @@ def parse_args():
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--cpu-seconds", type=float, default=20.0, help="CPU work (core-seconds) of the cpu_baseline sample")
     ap.add_argument("--still", action="store_true", help="render frame 0 on every step (profiling)")
+    ap.add_argument("--e2e-lanes", type=int, default=2, help="contexts / streams that take the e2e leg's frames in turn")
     ap.add_argument("--e2e-bands", type=int, default=0, help="row bands of the two e2e lanes (0: the library default)")
     ap.add_argument("--gather", action="store_true", help="e2e: gather every rank's frame to rank 0 over NCCL before the download")
     ap.add_argument("--no-single-frame", action="store_true", help="skip the single-frame strong-scaling leg")
@@ -563,14 +564,17 @@ def run_b200_arm(args):
         # Two contexts on two streams, frames alternating between them: the upload of frame k+1 and the download of
         # frame k-1 run on the copy engines while frame k renders (frames of a series are independent).  With
         # --gather the frames go through NCCL on one stream instead.
-        stream_b = torch.cuda.Stream(device=dev)
-        ctx_b = capi.Context(local, stream=stream_b.cuda_stream)
+        n_lanes = 1 if do_gather else max(1, args.e2e_lanes)
+        extra = []
+        for _i in range(n_lanes - 1):
+            st_ = torch.cuda.Stream(device=dev)
+            extra.append((capi.Context(local, stream=st_.cuda_stream), st_))
         e2e_bands_before = ctx.set_bands(args.e2e_bands) if args.e2e_bands else None
-        if args.e2e_bands:
-            ctx_b.set_bands(args.e2e_bands)
         lanes = [dict(ctx=ctx, stream=stream, scene=ctx.upload(pinned[0][0]), rgb=rgb, host=host_rgb)]
-        if not do_gather:
-            lanes.append(dict(ctx=ctx_b, stream=stream_b, scene=ctx_b.upload(pinned[0][0]), rgb=torch.empty_like(rgb),
+        for cx, st_ in extra:
+            if args.e2e_bands:
+                cx.set_bands(args.e2e_bands)
+            lanes.append(dict(ctx=cx, stream=st_, scene=cx.upload(pinned[0][0]), rgb=torch.empty_like(rgb),
                               host=torch.empty((1, H, W, 3), dtype=torch.uint8).pin_memory()))
 
         def e2e_step(s):
@@ -594,18 +598,22 @@ def run_b200_arm(args):
         e_start, e_end = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e_join = torch.cuda.Event()
         e_start.record(stream)
-        stream_b.wait_event(e_start)
+        for _cx, st_ in extra:
+            st_.wait_event(e_start)
         for s in range(K):
             e2e_step(Wm + s)
-        e_join.record(stream_b)
-        stream.wait_event(e_join)
+        for _cx, st_ in extra:
+            ej = torch.cuda.Event()
+            ej.record(st_)
+            stream.wait_event(ej)
         e_end.record(stream)
         barrier()
         e2e_ms = float(e_start.elapsed_time(e_end))                      # includes the K L2 flushes
         e2e = (e2e_ms, h2d, d2h)
         for ln in lanes:
             ln["scene"].destroy()
-        ctx_b.destroy()
+        for cx, _st in extra:
+            cx.destroy()
         if e2e_bands_before:
             ctx.set_bands(e2e_bands_before)
 
@@ -718,8 +726,15 @@ def run_b200_arm(args):
         barrier()
         # rank 0 drives all GPUs alone; the other ranks wait on the HOST (a key of the rendezvous store) — an NCCL barrier
         # would spin in a kernel on their GPUs and time-slice against rank 0's render kernels there
-        store = dist.distributed_c10d._get_default_store() if world > 1 else None
-        if rank == 0:
+        store = None
+        if world > 1:
+            try:
+                store = dist.distributed_c10d._get_default_store()
+            except Exception:
+                store = None                     # no store to wait on: the leg is skipped on every rank alike
+        if world > 1 and store is None:
+            single_frame_c = {"skipped": "no rendezvous store to park the other ranks on"} if rank == 0 else None
+        elif rank == 0:
             try:
                 single_frame_c = single_frame_c_abi_leg(args, world, local)
             except Exception as e:               # reporting leg: never takes the bench line down
@@ -849,7 +864,7 @@ def run_b200_arm(args):
             line["e2e"] = {"value": rays_total / (e2e_ms * 1e-3) / 1e6, "unit": UNIT, "h2d_bytes_per_step": int(e2e[1]) * world,
                            "d2h_bytes_per_step": int(e2e[2]) * (1 if args.gather else world), "ms_per_step": e2e_ms / K,
                            "frames_per_s": world * K / (e2e_ms * 1e-3),
-                           "what": "per rank: srt_scene_update from pinned host arrays + srt_render + D2H of the RGB8 frame to pinned host memory, frames alternating between two contexts / streams so that copies overlap renders; the L2 flushes between frames are inside this time"
+                           "what": f"per rank: srt_scene_update from pinned host arrays + srt_render + D2H of the RGB8 frame to pinned host memory, frames taken in turn by {max(1, args.e2e_lanes)} contexts / streams so that copies overlap renders; the L2 flushes between frames are inside this time"
                                    + (" (all frames gathered to rank 0 over NCCL first)" if args.gather else "")}
         if single_frame:
             line["single_frame"] = single_frame

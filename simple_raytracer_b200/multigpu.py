@@ -129,18 +129,39 @@ class ShardedFrameRenderer:
                 self._own_ptr = ctx.device_alloc(nbytes)
                 info[0] = ctx.ipc_export(self._own_ptr)
             dist.broadcast_object_list(info, src=dist.get_global_rank(group, 0) if group is not None else 0, group=group)
-            if self.rank == 0:
-                self.target = self._own_ptr
-                self.frame = torch.as_tensor(_DeviceBuffer(self._own_ptr, nbytes), device=dev).view(height, width, 3)
-            else:
-                self._peer_ptr = ctx.ipc_open(info[0])
-                self.target = self._peer_ptr
-                self.frame = None
-            self._token = torch.zeros(1, dtype=torch.int32, device=dev)
-        else:
-            self.mode = "gather"
-            self.frame = torch.zeros((height, width, 3), dtype=torch.uint8, device=dev)
-            self.target = self.frame.data_ptr()
+            ok = 1
+            if self.rank != 0:
+                try:
+                    self._peer_ptr = ctx.ipc_open(info[0])
+                except Exception:
+                    ok = 0                                  # no peer access to rank 0's GPU from here
+            flag = torch.tensor([ok], dtype=torch.int32, device=dev)
+            dist.all_reduce(flag, op=dist.ReduceOp.MIN, group=group)   # every rank takes the same path
+            if int(flag.item()) == 1:
+                if self.rank == 0:
+                    self.target = self._own_ptr
+                    self.frame = torch.as_tensor(_DeviceBuffer(self._own_ptr, nbytes), device=dev).view(height, width, 3)
+                else:
+                    self.target = self._peer_ptr
+                    self.frame = None
+                self._token = torch.zeros(1, dtype=torch.int32, device=dev)
+                return
+            self._release_shared()
+        self.mode = "gather"
+        self.frame = torch.zeros((height, width, 3), dtype=torch.uint8, device=dev)
+        self.target = self.frame.data_ptr()
+
+    def _release_shared(self):
+        if self._peer_ptr is not None:
+            self.ctx.ipc_close(self._peer_ptr)
+            self._peer_ptr = None
+        if dist.is_initialized() and self.world > 1:
+            dist.barrier(group=self.group)        # nobody still maps the frame when its owner frees it
+        if self._own_ptr is not None:
+            self.frame = None
+            self.ctx.sync()
+            self.ctx.device_free(self._own_ptr)
+            self._own_ptr = None
 
     def render(self, scene, params) -> Optional[torch.Tensor]:
         """Renders this rank's row blocks and joins; returns the [H, W, 3] frame on rank 0 (valid in stream order)."""
@@ -160,13 +181,5 @@ class ShardedFrameRenderer:
         return gather_row_blocks_in_place(self.frame, self.height, self.row_block, self.group)
 
     def close(self):
-        if self._peer_ptr is not None:
-            self.ctx.ipc_close(self._peer_ptr)
-            self._peer_ptr = None
-        if dist.is_initialized() and self.world > 1 and self.mode == "peer":
-            dist.barrier(group=self.group)        # nobody still maps the frame when its owner frees it
-        if self._own_ptr is not None:
-            self.frame = None
-            self.ctx.sync()
-            self.ctx.device_free(self._own_ptr)
-            self._own_ptr = None
+        if self.mode == "peer" and self.world > 1:
+            self._release_shared()
