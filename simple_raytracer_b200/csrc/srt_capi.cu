@@ -602,7 +602,7 @@ static int render_impl(srt_context* c, const srt_scene* s, const srt_render_para
         if ((rc = c->tile_order.reserve(n_tiles * 4))) return rc;
         if ((rc = c->shadow_mask.reserve(n_tiles * 4 * (size_t)(p->light_count > 0 ? p->light_count : 1)))) return rc;
         a.wide = (const float4*)s->wide.p;
-        a.pwide = s->pwide.p && s->pwide.cap >= s->n_nodes * 64 * 4 && !s->prep ? (const float4*)s->pwide.p : nullptr;
+        a.pwide = s->pwide.p && s->pwide.cap >= s->n_nodes * 64 * 4 ? (const float4*)s->pwide.p : nullptr;
         a.pwide_stride = (size_t)s->n_nodes * 4;
         a.swide = s->swide_octant >= 0 ? (const float4*)s->swide.p : nullptr;      // ensure_shadow_wide (srt_render)
         a.shadow_octant = s->swide_octant >= 0 ? (uint32_t)s->swide_octant : 0u;

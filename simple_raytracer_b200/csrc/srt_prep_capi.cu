@@ -215,6 +215,7 @@ int srt_scene_prep(srt_context* c, const srt_prep_object* objs, uint32_t n_objec
     if ((rc = s->flat_vnormal.reserve(n_flat * sizeof(srt_tri_vnormal)))) return bail(rc);
     if ((rc = s->objects.reserve((size_t)n_objects * sizeof(srt_object)))) return bail(rc);
     if ((rc = s->wide.reserve(n_nodes * 64))) return bail(rc);
+    if ((rc = s->pwide.reserve(n_nodes * 64 * 4))) return bail(rc);            // quadrant-sorted copies for the primary pass
     if ((rc = s->root_ref.reserve((size_t)n_objects * sizeof(uint32_t)))) return bail(rc);
     const size_t segq_stride = N / 8 + 8;
     if ((rc = ps.xpts.reserve(N * 48))) return bail(rc);
@@ -370,7 +371,9 @@ int srt_scene_prep(srt_context* c, const srt_prep_object* objs, uint32_t n_objec
         if (e == cudaSuccess && n_objects > 0)
             e = srtk::launch_build_wide((const float4*)s->nodes.p, (const srt_object*)s->objects.p, (uint32_t)n_nodes, n_objects,
                                         (float4*)s->wide.p, (uint32_t*)s->root_ref.p, c->stream);
-        launches += 3;
+        for (uint32_t q = 0; q < 4 && e == cudaSuccess && n_objects > 0; ++q)
+            e = srtk::launch_build_shadow_wide((const float4*)s->wide.p, (uint32_t)n_nodes, q, (float4*)s->pwide.p + (size_t)q * n_nodes * 4, c->stream);
+        launches += 7;
         if (e == cudaSuccess) e = cudaMemcpyAsync(ps.status_host, a.status, sizeof(uint32_t), cudaMemcpyDeviceToHost, c->stream);
         return e;
     };
@@ -400,7 +403,7 @@ int srt_scene_prep(srt_context* c, const srt_prep_object* objs, uint32_t n_objec
         std::vector<uint64_t> sig;
         auto put = [&](const void* ptr) { sig.push_back((uint64_t)(uintptr_t)ptr); };
         put(s->nodes.p); put(s->geom.p); put(s->attr.p); put(s->flat_geom.p); put(s->flat_attr.p); put(s->objects.p);
-        put(s->wide.p); put(s->root_ref.p); put(s->vnormal.p); put(s->flat_vnormal.p); put(ps.xpts.p); put(ps.lite.p); put(ps.order.p); put(ps.key.p); put(ps.idx.p);
+        put(s->wide.p); put(s->pwide.p); put(s->root_ref.p); put(s->vnormal.p); put(s->flat_vnormal.p); put(ps.xpts.p); put(ps.lite.p); put(ps.order.p); put(ps.key.p); put(ps.idx.p);
         put(ps.posl.p); put(ps.posr.p); put(ps.segq.p); put(ps.blob.p); put(ps.wide.p); put(ps.misc.p); put(c->stream);
         sig.push_back(blob.size()); sig.push_back(n_objects); sig.push_back((uint64_t)(with_flat_lists != 0));
         sig.push_back((uint64_t)single_cta_big);
