@@ -121,3 +121,59 @@ def test_mgpu_argument_errors():
     with pytest.raises(capi.SrtError):          # no scene yet
         m.render_frame(p)
     m.destroy()
+
+
+_CHILD = r"""
+import sys
+import numpy as np
+sys.path.insert(0, sys.argv[1])
+from simple_raytracer_b200 import _abi, capi, host, scenes
+handle = bytes.fromhex(sys.argv[2]); W, H, shard, world = (int(x) for x in sys.argv[3:7])
+cfg = scenes.CONFIGS["C3"]
+hs = host.HostScene(); view = cfg.build(hs, 200.0); light = np.asarray(scenes.light_view_space(hs, view), np.float32); arrays = hs.flatten(); hs.close()
+ctx = capi.Context(0)
+ptr = ctx.ipc_open(handle)                       # the parent's frame, mapped into this process
+sc = ctx.upload(arrays)
+p = _abi.default_params(W, H, float(H), light, 4, True)
+p.row_block, p.shard_index, p.shard_count = 16, shard, world
+ctx.render_raw(sc, p, rgb=ptr)                   # this process's kernels store straight into the parent's memory
+ctx.sync()
+ctx.ipc_close(ptr); sc.destroy(); ctx.destroy()
+print("CHILD OK")
+"""
+
+
+def test_ipc_shared_frame_between_two_processes(gpu_ctx, tmp_path):
+    """srt_ipc_export / srt_ipc_open / srt_ipc_close: another PROCESS maps this process's frame and renders its shard of the
+    rows straight into it (the one-process-per-GPU form of the peer stores; here both processes share GPU 0).  The union of
+    the parent's shard and the child's equals the one-piece frame byte for byte."""
+    import subprocess
+    import sys
+    from pathlib import Path
+    torch = pytest.importorskip("torch")
+    from simple_raytracer_b200 import multigpu
+    repo = Path(__file__).resolve().parent.parent
+    cfg, arrays, light = _scene("C3", 200.0)
+    W, H = 480, 272
+    p = _abi.default_params(W, H, float(H), light, 4, True)
+    sc = gpu_ctx.upload(arrays)
+    want = gpu_ctx.render(sc, p, ids=False, want_t=False)["rgb"]
+    ptr = gpu_ctx.device_alloc(W * H * 3)
+    try:
+        frame = torch.as_tensor(multigpu._DeviceBuffer(ptr, W * H * 3), device=torch.device("cuda", 0))
+        frame.zero_()
+        torch.cuda.synchronize()
+        handle = gpu_ctx.ipc_export(ptr)
+        assert len(handle) == 64
+        script = tmp_path / "child.py"
+        script.write_text(_CHILD)
+        r = subprocess.run([sys.executable, str(script), str(repo), handle.hex(), str(W), str(H), "1", "2"], capture_output=True, text=True, timeout=300)
+        assert r.returncode == 0 and "CHILD OK" in r.stdout, r.stderr[-2000:]
+        p.row_block, p.shard_index, p.shard_count = 16, 0, 2
+        gpu_ctx.render_raw(sc, p, rgb=ptr)
+        gpu_ctx.sync()
+        got = frame.view(H, W, 3).cpu().numpy()
+        assert np.array_equal(got, want)
+    finally:
+        gpu_ctx.device_free(ptr)
+        sc.destroy()
