@@ -139,7 +139,7 @@ def test_powf_is_correctly_rounded_and_agrees_with_libm(gpu_ctx):
     x = np.concatenate([rng.random(n, dtype=f32),                              # specular base / tone-mapped colour
                         (rng.random(n, dtype=f32) ** 8).astype(f32),
                         np.exp(rng.normal(0, 8, n)).astype(f32)])
-    y = np.concatenate([rng.choice(np.array([1.1, 5, 32, 50, 100, 0.5, 2], f32), n),
+    y = np.concatenate([rng.choice(np.array([1.1, 5, 15, 32, 50, 100, 0.5, 2, 3, 1], f32), n),
                         (rng.random(n, dtype=f32) * 300).astype(f32),
                         rng.normal(0, 4, n).astype(f32)])
     got = capi.eval_leaf(gpu_ctx, capi.LEAF_POWF, np.stack([x, y], axis=1))[:, 0]
