@@ -280,9 +280,9 @@ __device__ __forceinline__ bool trace_any(const KArgs& a, const FRay& r, Stack& 
             if (COUNT) *boxes += 2;
             const uint32_t rl = __float_as_uint(w3.x), rr = __float_as_uint(w3.y);
             if (hl && hr) {
-                const float kl = tfl < 0.f ? 3.0e38f : fmaxf(tnl, 0.f);
-                const float kr = tfr < 0.f ? 3.0e38f : fmaxf(tnr, 0.f);
-                if (kr < kl) { st.push(rl); ref = rr; } else { st.push(rr); ref = rl; }
+                // the child the ray enters first (raw entry parameter; measured against "clamped to the origin, boxes behind it last",
+                // nearer exit first and always-left: -1.7 % / +1.5 % / +9.5 % shadow time at 180 degrees)
+                if (tnr < tnl) { st.push(rl); ref = rr; } else { st.push(rr); ref = rl; }
             } else if (hl) ref = rl;
             else if (hr) ref = rr;
             else ref = st.pop();
