@@ -558,6 +558,13 @@ static int render_impl(srt_context* c, const srt_scene* s, const srt_render_para
     a.counters = c->counters;
     int rc = srt_light_positions(p, a.lights);
     if (rc) return rc;
+    for (int k = 0; k < 3; ++k) {
+        a.light_lo[k] = INFINITY; a.light_hi[k] = -INFINITY;
+        for (int i = 0; i < p->light_count; ++i) {
+            a.light_lo[k] = std::fmin(a.light_lo[k], a.lights[3 * i + k]);
+            a.light_hi[k] = std::fmax(a.light_hi[k], a.lights[3 * i + k]);
+        }
+    }
 
     // Output planes: device pointers are written in place, host pointers through staging buffers.
     const size_t npix = (size_t)p->width * p->height;

@@ -49,6 +49,7 @@ struct KArgs {
     float* t;
     unsigned long long* counters;   // CNT_* slots, zeroed before launch
     float lights[3 * SRT_MAX_LIGHTS];   // staircase positions, softShadow :363-383
+    float light_lo[3], light_hi[3];     // bounding box of the light positions (bundle test of the primary pass)
     // ---- phased kernel only (device-internal data built at upload, scratch owned by the context) ----
     const float4* wide;         // per interior node i: the two child boxes + child refs, 4 x float4 at wide[4*i]
     const uint32_t* root_ref;   // per object: traversal ref of its root

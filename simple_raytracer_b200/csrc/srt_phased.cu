@@ -349,6 +349,29 @@ __device__ __forceinline__ void shadow_ray(const KArgs& a, V3 d, float t, int i,
     sd = v3(sub(a.lights[3 * i], so.x), sub(a.lights[3 * i + 1], so.y), sub(a.lights[3 * i + 2], so.z));
 }
 
+// Can ANY of the shadow rays of one hit point — origin `so`, directions RN(L - so) for the light positions L inside the box
+// [llo, lhi] — pass the reference's slab test (:252-293) for this box?  Returns true only when NONE can, decided once for the
+// whole bundle: per axis the rays' plane parameters RN(RN(b - so) / d) share their numerators (one origin) and are monotone
+// in d (rounding is monotone; d = RN(L - so) is monotone in L and must not reach zero), so they lie between the values at
+// the two ends of the direction interval — computed here with the very same operations.  If the hull intervals of two axes
+// are disjoint, every ray has maxA < minB for that pair, which the reference's compare sequence turns into a miss whichever
+// pair it is.  Anything else (a direction interval that touches zero, a NaN) answers "don't know".
+__device__ __forceinline__ bool bundle_misses_box(V3 so, const float* llo, const float* lhi, float4 bmin, float4 bmax) {
+    const float o[3] = {so.x, so.y, so.z}, lo[3] = {bmin.x, bmin.y, bmin.z}, hi[3] = {bmax.x, bmax.y, bmax.z};
+    float tmin[3], tmax[3];
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+        const float d0 = sub(llo[k], o[k]), d1 = sub(lhi[k], o[k]);
+        if (!(d0 > 0.f || d1 < 0.f)) return false;                          // the interval touches zero (or NaN): don't know
+        const float n0 = sub(lo[k], o[k]), n1 = sub(hi[k], o[k]);
+        const float q00 = dvd(n0, d0), q01 = dvd(n0, d1), q10 = dvd(n1, d0), q11 = dvd(n1, d1);
+        tmin[k] = fminf(fminf(q00, q01), fminf(q10, q11));
+        tmax[k] = fmaxf(fmaxf(q00, q01), fmaxf(q10, q11));
+        if (!(tmin[k] <= tmax[k])) return false;                           // NaN somewhere: don't know
+    }
+    return tmax[0] < tmin[1] || tmax[1] < tmin[0] || tmax[0] < tmin[2] || tmax[2] < tmin[0] || tmax[1] < tmin[2] || tmax[2] < tmin[1];
+}
+
 // ---- phase 0: queue order -------------------------------------------------------------------------
 // Tiles whose rays enter the root box of a large object cost 10-50x more than ground / sky tiles
 // (profiles/r01_*: 100-400 k cycles against 6-20 k).  To keep them out of the tail they are queued
@@ -431,7 +454,18 @@ __device__ __forceinline__ unsigned primary_tile(const KArgs& a, Stack& st, unsi
         if (a.tri_id) a.tri_id[at] = h.tri;
         if (a.t && a.debug_timeline != 2) a.t[at] = h.t;
         if (h.tri >= 0 && a.n_objects >= 2) {
-            for (int i = 0; i < a.light_count && !interested; ++i) {
+            // all light samples at once first: most pixels of most views cannot reach another object's box with ANY of their
+            // shadow rays, and saying so per light costs a ray set-up and a root test each (16 x ~90 instructions per pixel)
+            bool maybe = a.light_count <= 2;
+            if (!maybe) {
+                const V3 so = v3(mul(d.x, h.t), mul(d.y, h.t), mul(d.z, h.t));                 // shadow_ray's origin (:326)
+                for (int ob = 0; ob < (int)a.n_objects && !maybe; ++ob) {
+                    if (ob == h.obj) continue;
+                    const float4* n = a.nodes + 2 * (size_t)a.objects[ob].root;
+                    maybe = !bundle_misses_box(so, a.light_lo, a.light_hi, ldg4(n), ldg4(n + 1));
+                }
+            }
+            for (int i = 0; i < a.light_count && maybe && !interested; ++i) {
                 V3 so, sd;
                 shadow_ray(a, d, h.t, i, so, sd);
                 const FRay s = make_fray(so, sd, coord_bound_of(a));
