@@ -39,7 +39,7 @@ METRIC = "Mrays/s (bunny + ground, 16-light soft shadows, 1920x1080)"
 UNIT = "Mrays/s"
 WORKLOAD = ("C3/C5: stanford-bunny.obj (x150) + ground cube, 16 staircase lights, 1920x1080, focal 1080, BVH; "
             "image series over one camera orbit, frame step*N+rank of N*(steps+warmup), frame 0 = C3")
-L2_FLUSH_BYTES = 512 << 20
+L2_FLUSH_BYTES = 256 << 20          # twice the 126 MB L2
 
 
 def parse_args():
@@ -56,7 +56,7 @@ def parse_args():
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--cpu-seconds", type=float, default=20.0, help="CPU work (core-seconds) of the cpu_baseline sample")
     ap.add_argument("--still", action="store_true", help="render frame 0 on every step (profiling)")
-    ap.add_argument("--e2e-lanes", type=int, default=2, help="contexts / streams that take the e2e leg's frames in turn")
+    ap.add_argument("--e2e-lanes", type=int, default=3, help="contexts / streams that take the e2e leg's frames in turn")
     ap.add_argument("--e2e-bands", type=int, default=0, help="row bands of the two e2e lanes (0: the library default)")
     ap.add_argument("--gather", action="store_true", help="e2e: gather every rank's frame to rank 0 over NCCL before the download")
     ap.add_argument("--no-single-frame", action="store_true", help="skip the single-frame strong-scaling leg")
@@ -449,7 +449,7 @@ def run_b200_arm(args):
     sampler = ClockSampler(local) if rank == 0 else None
     t0 = time.time()
     for s in range(K):
-        flush.zero_()                               # L2 flush between timed iterations (512 MiB > 126 MB L2)
+        flush.zero_()                               # L2 flush between timed iterations (256 MiB = 2 x the 126 MB L2)
         ev[s][0].record()
         render_step(Wm + s)
         ev[s][1].record()
@@ -642,10 +642,11 @@ def run_b200_arm(args):
         ms = 1e3 * (time.perf_counter() - t_a) / K
         # the same lists with two frames in flight: two contexts take frames in turn; while the host waits for one lane's
         # lists (27 MB per frame over PCIe), the other lane renders (srt_render_sparse_begin / _count / srt_fetch_sparse)
-        ctx_c = capi.Context(local)
-        il = [dict(ctx=ctx, scene=sc2, pts=pts, col=col, busy=False),
-              dict(ctx=ctx_c, scene=ctx_c.upload(pinned[0][0]), pts=capi.PinnedArray((W * H, 2), np.float32),
-                   col=capi.PinnedArray((W * H, 3), np.float32), busy=False)]
+        il = [dict(ctx=ctx, scene=sc2, pts=pts, col=col, busy=False)]
+        for _i in range(1):                              # two lanes: a third measured slower here (1.53 vs 1.48 ms; the lists' 27 MB per frame bound the lane)
+            ctx_c = capi.Context(local)
+            il.append(dict(ctx=ctx_c, scene=ctx_c.upload(pinned[0][0]), pts=capi.PinnedArray((W * H, 2), np.float32),
+                           col=capi.PinnedArray((W * H, 3), np.float32), busy=False))
 
         def retire(ln):
             if not ln["busy"]:
@@ -658,7 +659,7 @@ def run_b200_arm(args):
 
         def piped_step(s):
             k = s % n_unique
-            ln = il[s % 2]
+            ln = il[s % len(il)]
             got = retire(ln)
             ln["scene"].update(pinned[k][0])
             capi._check(capi.lib().srt_render_sparse_begin(ln["ctx"].h, ln["scene"].h, capi.C.byref(params[k])))
@@ -680,11 +681,12 @@ def run_b200_arm(args):
                      "synchronous": {"ms_per_frame": ms, "frames_per_s": 1e3 / ms, "entries_per_frame": entries / K},
                      "what": "rank 0, the reference's own return type end to end: per frame srt_scene_update from pinned host arrays + render + "
                              "device-side compaction into the ImageData layout (simple_raytracer.cpp:505-525: non-black pixels, column-major, "
-                             "floats) + download of both lists into pinned host memory; two contexts take frames in turn "
+                             f"floats) + download of both lists into pinned host memory; {len(il)} contexts take frames in turn "
                              "(srt_render_sparse_begin / _count / srt_fetch_sparse_async: nothing blocks the host but the wait for a frame's count), host wall clock over the K frames incl. the final sync; `synchronous` = one "
                              "context, one blocking srt_render_sparse + srt_fetch_sparse per frame (what srt_dropin.hpp's single call does)"}
-        il[1]["scene"].destroy(); il[1]["pts"].free(); il[1]["col"].free()
-        ctx_c.destroy()
+        for ln in il[1:]:
+            ln["scene"].destroy(); ln["pts"].free(); ln["col"].free()
+            ln["ctx"].destroy()
         sc2.destroy()
         pts.free(); col.free()
 
@@ -786,7 +788,7 @@ def run_b200_arm(args):
             "ms_per_step": total_ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "f32", "data": "synthetic",
             "config": make_config(args, cfg, W, H, focal, N, world, len(frames[0][0].geom), len(frames[0][0].nodes)),
-            "timing": {"l2": "flushed between timed iterations (512 MiB device memset)", "variant": args.variant,
+            "timing": {"l2": f"flushed between timed iterations ({L2_FLUSH_BYTES >> 20} MiB device memset, 2 x the 126 MB L2)", "variant": args.variant,
                        "sm_count": info["sm_count"], "row_bands": 2 if args.variant == 0 else 1,
                        "events": "CUDA events on the launching stream around every srt_render, max over ranks"},
             "frames_per_s": world * K / (total_ms * 1e-3),
