@@ -23,7 +23,12 @@ hdr, units = rows[0], rows[1]
 ix = {h: i for i, h in enumerate(hdr)}
 KEEP += ['l1tex__m_xbar2l1tex_read_bytes.sum', 'l1tex__m_l1tex2xbar_write_bytes.sum', 'lts__t_sectors_op_read.sum', 'lts__t_sectors_op_write.sum',
          'lts__t_sectors_srcunit_tex.sum', 'sm__throughput.avg.pct_of_peak_sustained_elapsed', 'smsp__inst_executed.avg.per_cycle_active',
-         'smsp__cycles_active.avg', 'launch__shared_mem_per_block_dynamic', 'sm__maximum_warps_per_active_cycle_pct', 'sm__warps_active.avg.pct_of_peak_sustained_active']
+         'smsp__cycles_active.avg', 'launch__shared_mem_per_block_dynamic', 'sm__maximum_warps_per_active_cycle_pct', 'sm__warps_active.avg.pct_of_peak_sustained_active',
+         # the L1 / LSU side (round 2, late): data-pipe wavefronts are the second-busiest unit of the shadow pass
+         'l1tex__throughput.avg.pct_of_peak_sustained_active', 'l1tex__throughput.avg.pct_of_peak_sustained_elapsed',
+         'l1tex__data_pipe_lsu_wavefronts.avg.pct_of_peak_sustained_elapsed', 'l1tex__lsu_writeback_active.avg.pct_of_peak_sustained_elapsed',
+         'l1tex__t_requests_pipe_lsu_mem_global_op_ld.sum', 'l1tex__t_output_wavefronts_pipe_lsu_mem_global_op_ld.sum',
+         'l1tex__t_sectors_pipe_lsu_mem_global_op_ld.sum', 'sm__inst_executed_pipe_lsu.avg.pct_of_peak_sustained_active']
 kernels = []
 for r in rows[2:]:
     print('==', r[ix['Kernel Name']][:90], 'grid', r[ix['Grid Size']], 'block', r[ix['Block Size']])
