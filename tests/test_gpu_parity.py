@@ -117,7 +117,7 @@ def test_oracle_matches_reference_on_gpu_box(ref_scene):
 def test_full_size_c3_variants_agree_and_sample_matches_oracle(gpu_ctx, ref_scene):
     """BASELINE configs[2] at its full size (1920x1080, 16 lights): the four kernel variants give identical
     bytes (the simple kernel evaluates every slab test with the exact divisions, the phased ones with the
-    filter), and every 16th pixel column equals the oracle."""
+    filter), and EVERY pixel of the frame equals the oracle (the C restatement renders the 25 M rays in about a second)."""
     _b, arrays, light = ref_scene("C3")
     W, H, focal, N = 1920, 1080, 1080.0, 16
     sc = gpu_ctx.upload(arrays)
@@ -133,8 +133,8 @@ def test_full_size_c3_variants_agree_and_sample_matches_oracle(gpu_ctx, ref_scen
     bands = gpu_ctx.set_bands(2); gpu_ctx.set_bands(bands)                     # the context's setting (default 2)
     assert [o["stats"]["kernel_launches"] for o in outs] == [4 * bands, 2, 4, 1]   # row bands x four passes
     p = _abi.default_params(W, H, focal, light, N, True)
-    want = pyoracle.oracle_render(arrays, p, col_begin=7, col_step=16)
-    cols = np.arange(7, W, 16)
+    want = pyoracle.oracle_render(arrays, p)
+    cols = np.arange(W)
     assert np.array_equal(outs[0]["tri_id"][:, cols], want["tri_id"][:, cols])
     assert np.array_equal(outs[0]["t"][:, cols], want["t"][:, cols])
     assert compare_images(outs[0]["rgb"][:, cols], want["rgb"][:, cols])[0] <= 1
@@ -144,31 +144,66 @@ def test_full_size_c3_variants_agree_and_sample_matches_oracle(gpu_ctx, ref_scen
           f"{outs[0]['stats']['exact_slab_tests']}")
 
 
-@pytest.mark.parametrize("angle,col0", [(180.0, 5), (135.0, 29)])
-def test_full_size_c3_heavy_orbit_views_match_the_oracle(gpu_ctx, ref_scene, angle, col0):
+@pytest.mark.parametrize("angle,col0,step", [(180.0, 0, 1), (135.0, 0, 1), (270.0, 7, 16)])
+def test_full_size_c3_heavy_orbit_views_match_the_oracle(gpu_ctx, ref_scene, angle, col0, step):
     """The frames the bench times: 1920x1080, 16 lights, at the orbit's expensive views (most shadow rays cross the bunny;
-    t ~ 0 shadow hits where it touches the ground, no epsilon, :321-342).  Every 48th pixel column against the oracle."""
+    t ~ 0 shadow hits where it touches the ground, no epsilon, :321-342).  EVERY pixel of the two heaviest views against the
+    oracle (2 M pixels, 25 M rays each on the host cores), every 16th column of a third."""
     _b, arrays, light = ref_scene("C3", angle)
     W, H, focal, N = 1920, 1080, 1080.0, 16
     p = _abi.default_params(W, H, focal, light, N, True)
     sc = gpu_ctx.upload(arrays)
     got = gpu_ctx.render(sc, p)
     sc.destroy()
-    want = pyoracle.oracle_render(arrays, p, col_begin=col0, col_step=48)
-    cols = np.arange(col0, W, 48)
+    want = pyoracle.oracle_render(arrays, p, col_begin=col0, col_step=step)
+    cols = np.arange(col0, W, step)
     assert np.array_equal(got["tri_id"][:, cols], want["tri_id"][:, cols])
     assert np.array_equal(got["obj_id"][:, cols], want["obj_id"][:, cols])
     assert np.array_equal(got["t"][:, cols], want["t"][:, cols])
     mx, psnr = compare_images(got["rgb"][:, cols], want["rgb"][:, cols])
     differing = int(np.count_nonzero((got["rgb"][:, cols] != want["rgb"][:, cols]).any(axis=2)))
-    assert mx <= 1 and psnr >= 50.0 and differing <= 4, (mx, psnr, differing)
+    assert mx <= 1 and psnr >= 50.0 and differing <= (12 if step > 1 else 200), (mx, psnr, differing)   # powf ties: a handful of 1-LSB pixels
     shadowed = int(np.count_nonzero(want["obj_id"][:, cols] >= 0))
     assert shadowed > 20000
+    if step == 1:
+        print(f"C3 at {angle:g} deg, every pixel: {differing} of {W * H} pixels differ by 1 LSB, PSNR {psnr:.1f} dB, oracle {want['seconds']:.1f} s")
+
+
+def test_every_view_of_the_default_bench_run_matches_the_oracle_in_every_pixel(gpu_ctx):
+    """`python bench.py` (N = 1, 20 steps + 5 warm-up) times the 25 views 360 * g / 25 degrees of the C3 / C5 orbit at
+    1920x1080 with 16 lights.  Each of them, built with the bench's own frame builder, rendered through the C ABI with the
+    library's defaults (two row bands) and compared with the oracle in EVERY pixel: ids, t bit-identical, rgb within 1 LSB."""
+    import bench
+    from simple_raytracer_b200 import host
+    try:
+        host.assets_dir()
+    except FileNotFoundError:
+        pytest.skip("staged assets not present")
+    cfg = scenes.CONFIGS["C3"]
+    W, H, focal, N = cfg.width, cfg.height, cfg.focal, cfg.light_count
+    assert (W, H, N) == (1920, 1080, 16)
+    total, worst, secs = 25, 0, 0.0
+    for g in range(total):
+        b, arrays, light = bench.build_frame(host.HostScene, cfg, bench.frame_angle(g, total))
+        p = _abi.default_params(W, H, focal, light, N, True)
+        sc = gpu_ctx.upload(arrays)
+        got = gpu_ctx.render(sc, p)
+        sc.destroy()
+        want = pyoracle.oracle_render(arrays, p)
+        b.close()
+        secs += want["seconds"]
+        for k in ("tri_id", "obj_id", "t"):
+            assert np.array_equal(got[k], want[k]), (g, k)
+        mx, psnr = compare_images(got["rgb"], want["rgb"])
+        differing = int(np.count_nonzero((got["rgb"] != want["rgb"]).any(axis=2)))
+        assert mx <= 1 and psnr >= 50.0 and differing <= 200, (g, mx, psnr, differing)
+        worst = max(worst, differing)
+    print(f"25 orbit views, every pixel: at most {worst} of {W * H} pixels differ by 1 LSB; oracle {secs:.1f} s in all")
 
 
 def test_full_size_c2_matches_the_oracle(gpu_ctx, ref_scene):
-    """BASELINE configs[1] at its own size: bunny alone, 1920x1080, one light (no other object: no shadow rays).  Every 12th
-    pixel column against the oracle, all kernel variants byte-identical."""
+    """BASELINE configs[1] at its own size: bunny alone, 1920x1080, one light (no other object: no shadow rays).  Every
+    pixel against the oracle, all kernel variants byte-identical."""
     _b, arrays, light = ref_scene("C2")
     W, H, focal, N = 1920, 1080, 1080.0, 1
     sc = gpu_ctx.upload(arrays)
@@ -182,8 +217,8 @@ def test_full_size_c2_matches_the_oracle(gpu_ctx, ref_scene):
         for k in ("rgb", "obj_id", "tri_id", "t"):
             assert np.array_equal(outs[0][k], o[k]), k
     p = _abi.default_params(W, H, focal, light, N, True)
-    want = pyoracle.oracle_render(arrays, p, col_begin=3, col_step=12)
-    cols = np.arange(3, W, 12)
+    want = pyoracle.oracle_render(arrays, p)
+    cols = np.arange(W)
     assert np.array_equal(outs[0]["tri_id"][:, cols], want["tri_id"][:, cols])
     assert np.array_equal(outs[0]["t"][:, cols], want["t"][:, cols])
     assert compare_images(outs[0]["rgb"][:, cols], want["rgb"][:, cols])[0] <= 1
@@ -191,8 +226,8 @@ def test_full_size_c2_matches_the_oracle(gpu_ctx, ref_scene):
 
 
 def test_full_size_c4_textured_4k(gpu_ctx, ref_scene):
-    """BASELINE configs[3] at 3840x2160: variants agree byte for byte, a column sample equals the oracle,
-    and rendering twice gives the same bytes (idempotence)."""
+    """BASELINE configs[3] at 3840x2160: variants agree byte for byte, every one of the 8.3 M pixels equals the
+    oracle, and rendering twice gives the same bytes (idempotence)."""
     _b, arrays, light = ref_scene("C4")
     W, H, focal, N = 3840, 2160, 2160.0, 1
     sc = gpu_ctx.upload(arrays)
@@ -205,8 +240,8 @@ def test_full_size_c4_textured_4k(gpu_ctx, ref_scene):
     for k in ("rgb", "obj_id", "tri_id", "t"):
         assert np.array_equal(a[k], b[k]) and np.array_equal(a[k], c[k]), k
     p.variant = 0
-    want = pyoracle.oracle_render(arrays, p, col_begin=11, col_step=32)
-    cols = np.arange(11, W, 32)
+    want = pyoracle.oracle_render(arrays, p)
+    cols = np.arange(W)
     assert np.array_equal(a["tri_id"][:, cols], want["tri_id"][:, cols])
     assert np.array_equal(a["t"][:, cols], want["t"][:, cols])
     assert compare_images(a["rgb"][:, cols], want["rgb"][:, cols])[0] <= 1
