@@ -858,6 +858,25 @@ def run_b200_arm(args):
                                     "source": f"profiles/{ncu_path.name} (ncu --set full, one heavy mid-orbit frame, one piece)",
                                     "note": "issue-slot utilisation x SM-active share x active threads per instruction / 32, time-weighted over primary / shadow / shade; "
                                             "the contract's hbm object is `roofline_hbm`, the L2 and FP32 figures `roofline_l2` / `roofline_fp32`"}
+        # the second bound of the dominant (shadow) kernel: L1 data-pipe wavefronts, from the end-of-round capture that holds the LSU metrics
+        try:
+            if args.config == "C3" and args.variant == 0:
+                l1_path = REPO / "profiles" / "r02f_c3_stage_metrics.json"
+                for kr in json.loads(l1_path.read_text())["kernels"]:
+                    m = kr["metrics"]
+                    if "render_phase<1" in kr["kernel"] and "l1tex__data_pipe_lsu_wavefronts.avg.pct_of_peak_sustained_elapsed" in m:
+                        f = m["l1tex__data_pipe_lsu_wavefronts.avg.pct_of_peak_sustained_elapsed"] / 100.0
+                        rq = m.get("l1tex__t_requests_pipe_lsu_mem_global_op_ld.sum")
+                        line["roofline_l1"] = {"bound": "l1 data pipe (LSU wavefronts) of the shadow pass", "achieved": f, "peak": 1.0,
+                                               "unit": "wavefronts per clock per SM", "frac": f,
+                                               "frac_of_active_cycles": m.get("l1tex__throughput.avg.pct_of_peak_sustained_active", 0.0) / 100.0,
+                                               "issue_slots_busy_same_capture": m.get("smsp__issue_active.avg.pct_of_peak_sustained_active", 0.0) / 100.0,
+                                               "global_load_requests": rq, "source": f"profiles/{l1_path.name} (ncu --set full, the 180-degree frame, one piece)",
+                                               "note": "a 16-byte load is four data-pipe wavefronts whatever the number of active lanes: the pass is within 15 % of "
+                                                       "this bound and of the issue bound at once"}
+                        break
+        except Exception:
+            pass
         if "roofline" not in line:
             line["roofline"] = dict(line["roofline_hbm"], note="no ncu capture for this configuration: the hbm object stands in; see roofline_l2 / roofline_fp32")
         if imagedata:
